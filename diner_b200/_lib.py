@@ -1,0 +1,86 @@
+"""ctypes loader for the C-ABI CUDA library (include/diner_b200.h).
+
+There is no CPU fallback: if the library is missing it is built in-tree with nvcc; if that fails, or a
+kernel returns a CUDA error, a RuntimeError is raised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+from . import _build
+
+_lib = None
+
+c_p = C.c_void_p
+c_i = C.c_int
+c_ll = C.c_longlong
+c_f = C.c_float
+c_ull = C.c_ulonglong
+
+_SIGNATURES = {
+    "dnr_abi_version": (c_i, []),
+    "dnr_last_error": (C.c_char_p, []),
+    "dnr_composite_fwd": (c_i, [c_p, c_p, c_p, c_i, c_i, c_i, c_p, c_p, c_p, c_p]),
+    "dnr_composite_bwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_p, c_p]),
+    "dnr_pad_depth_std": (c_i, [c_p, c_p, c_i, c_i, c_i, c_i, c_p, c_p]),
+    "dnr_sampler_fwd": (c_i, [c_p] * 13 + [c_ull] + [c_i] * 9 + [c_f] * 5 + [c_i] + [c_p] * 5),
+    "dnr_view_row_tiles": (c_i, [c_ll, c_i]),
+    "dnr_encode_fwd": (c_i, [c_p] * 9 + [c_i] * 10 + [c_ll, c_ll] + [c_f] * 4 + [c_p, c_p, c_p]),
+    "dnr_encode_bwd": (c_i, [c_p] * 8 + [c_i] * 10 + [c_ll, c_ll] + [c_f] * 4 + [c_p, c_p, c_p]),
+    "dnr_pack_latent_nhwc": (c_i, [c_p, c_i, c_i, c_i, c_i, c_p, c_p]),
+    "dnr_unpack_dlatent_nchw": (c_i, [c_p, c_i, c_i, c_i, c_i, c_p, c_p]),
+    "dnr_mlp_gemm": (c_i, [c_p, c_p, c_i, c_p, c_p, c_i, c_p, c_p, c_i, c_i, c_i, c_p, c_p, c_p, c_p, c_p, c_i, c_i,
+                           c_ll, c_i, c_p]),
+    "dnr_mlp_wgrad": (c_i, [c_p, c_i, c_p, c_i, c_i, c_p, c_i, c_i, c_i, c_p, c_p]),
+    "dnr_pack_weight": (c_i, [c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_p, c_p]),
+    "dnr_head_fwd": (c_i, [c_p, c_p, c_p, c_ll, c_p, c_p]),
+    "dnr_head_bwd": (c_i, [c_p, c_p, c_p, c_p, c_ll, c_p, c_p, c_p, c_p]),
+    "dnr_mean_bwd": (c_i, [c_p, c_i, c_ll, c_i, c_p, c_p, c_p]),
+    "dnr_pack_rows": (c_i, [c_p, c_ll, c_i, c_ll, c_p, c_p]),
+    "dnr_unpack_rows": (c_i, [c_p, c_ll, c_i, c_p, c_p]),
+    "dnr_xr_to_rows": (c_i, [c_p, c_ll, c_i, c_p, c_p]),
+    "dnr_rows_to_xr": (c_i, [c_p, c_ll, c_i, c_ll, c_p, c_p]),
+}
+
+EXPORTED_SYMBOLS = tuple(_SIGNATURES)
+
+
+def lib_path() -> str:
+    return _build.LIB_PATH
+
+
+def load(build_if_missing: bool = True):
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.LIB_PATH
+    if not os.path.exists(path):
+        if not build_if_missing:
+            raise RuntimeError(f"{path} is missing and building was disabled; diner_b200 has no CPU fallback")
+        _build.build()
+    lib = C.CDLL(path)
+    for name, (res, args) in _SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def ptr(t):
+    """Device pointer of a tensor (None -> NULL)."""
+    return None if t is None else t.data_ptr()
+
+
+def call(name: str, *args):
+    lib = load()
+    rc = getattr(lib, name)(*args)
+    if rc != 0:
+        msg = lib.dnr_last_error()
+        raise RuntimeError(f"{name} failed (code {rc}): {msg.decode() if msg else '?'}")
+
+
+def stream_ptr():
+    import torch
+    return torch.cuda.current_stream().cuda_stream

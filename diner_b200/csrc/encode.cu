@@ -1,0 +1,332 @@
+// Field input encoding: every sample point is projected into the NV source views; per (sample, view)
+// row the kernel gathers the 512-channel encoder feature (bilinear, border) from the NHWC bf16 latent,
+// taps the predicted depth (nearest, border) and builds the 55-wide geometric code
+// [x_cam 3 | posenc 36 | dir_cam 3 | depth-dist 1 | posenc 12].  Restates reference
+// pixelnerf.py:91-128, image_encoder.py:97-151, positional_encoding.py:33-53.
+//
+// Rows are written straight into the MLP's packed A-operand layouts (PK<128>, see common.cuh), staged
+// through shared memory so that every global store is a full 128-byte line.  The backward kernel
+// scatters d(feature) back into the NHWC fp32 latent gradient with vector reductions.
+//
+// Algorithmic bytes per (sample, view) row, fwd: 4 taps * 512 ch * 2 B + 4 B depth read,
+// 512*2 + 64*2 B written.
+#include "common.cuh"
+
+namespace dnr {
+
+struct EncodeParams {
+  const float* rays;     // [SB*NR, 8]
+  const float* z;        // [SB*NR, K]
+  const float* poses;    // [SB,NV,4,4]
+  const float* focal;    // [SB,NV,2]
+  const float* cxy;      // [SB,NV,2]
+  const float* depth;    // [SB,NV,H,W]
+  const __nv_bfloat16* latent;  // [SB,NV,Hl,Wl,L] channels-last
+  const float* freqs;    // [2*NF] (f0,f0,f1,f1,...)
+  const float* phases;   // [2*NF] (0,pi/2,...)
+  int SB, NV, NR, K, H, W, Hl, Wl, NF;
+  float img_w, img_h, lat_sx, lat_sy;
+  long long n_samples;   // rays_in_chunk*K
+  long long ray_offset;  // index of the chunk's first ray in the (SB*NR) batch
+  long long n_rays;      // rays in this chunk
+  unsigned char* lat_pk; // PK<128> [rows_pad x 512] bf16
+  unsigned char* in_pk;  // PK<128> [rows_pad x 64] bf16
+  float* d_latent;       // bwd: [SB,NV,Hl,Wl,L] fp32 (accumulated into)
+  const float* d_lat_xr; // bwd: XR [rows_pad x 512] fp32
+};
+
+struct RowGeom {
+  float xc, yc, zc, dx, dy, dz, dd;
+  int x0, y0, x1, y1;
+  float wx, wy;
+  size_t map;   // (sb*NV+v)
+};
+
+// projection chain shared by fwd and bwd (pixelnerf.py:91-93,99-101,105-116)
+__device__ __forceinline__ void row_geometry(const EncodeParams& P, long long sample, int view, RowGeom& g) {
+  const long long ray = sample / P.K;
+  const int sb = (int)((ray + P.ray_offset) / P.NR);
+  const float* rp = P.rays + ray * 8;
+  const float zs = P.z[sample];
+  const float x0 = __fadd_rn(rp[0], __fmul_rn(zs, rp[3]));
+  const float x1 = __fadd_rn(rp[1], __fmul_rn(zs, rp[4]));
+  const float x2 = __fadd_rn(rp[2], __fmul_rn(zs, rp[5]));
+  g.map = (size_t)sb * P.NV + view;
+  const float* E = P.poses + g.map * 16;
+  g.xc = __fadd_rn(fmaf(E[2], x2, fmaf(E[1], x1, __fmul_rn(E[0], x0))), E[3]);
+  g.yc = __fadd_rn(fmaf(E[6], x2, fmaf(E[5], x1, __fmul_rn(E[4], x0))), E[7]);
+  g.zc = __fadd_rn(fmaf(E[10], x2, fmaf(E[9], x1, __fmul_rn(E[8], x0))), E[11]);
+  g.dx = fmaf(E[2], rp[5], fmaf(E[1], rp[4], __fmul_rn(E[0], rp[3])));
+  g.dy = fmaf(E[6], rp[5], fmaf(E[5], rp[4], __fmul_rn(E[4], rp[3])));
+  g.dz = fmaf(E[10], rp[5], fmaf(E[9], rp[4], __fmul_rn(E[8], rp[3])));
+  float u = __fdiv_rn(g.xc, g.zc), v = __fdiv_rn(g.yc, g.zc);
+  u = __fadd_rn(__fmul_rn(u, P.focal[g.map * 2 + 0]), P.cxy[g.map * 2 + 0]);
+  v = __fadd_rn(__fmul_rn(v, P.focal[g.map * 2 + 1]), P.cxy[g.map * 2 + 1]);
+  u = __fsub_rn(__fmul_rn(__fdiv_rn(u, P.img_w), 2.0f), 1.0f);
+  v = __fsub_rn(__fmul_rn(__fdiv_rn(v, P.img_h), 2.0f), 1.0f);
+  // nearest depth tap, border padding
+  float px = __fdiv_rn(__fsub_rn(__fmul_rn(__fadd_rn(u, 1.0f), (float)P.W), 1.0f), 2.0f);
+  float py = __fdiv_rn(__fsub_rn(__fmul_rn(__fadd_rn(v, 1.0f), (float)P.H), 1.0f), 2.0f);
+  px = fminf(fmaxf(px, 0.0f), (float)(P.W - 1));
+  py = fminf(fmaxf(py, 0.0f), (float)(P.H - 1));
+  const int ix = (int)nearbyintf(px), iy = (int)nearbyintf(py);
+  const float dref = __ldg(P.depth + g.map * (size_t)P.H * P.W + (size_t)iy * P.W + ix);
+  g.dd = __fsub_rn(dref, g.zc);
+  // bilinear latent tap, border padding; feature-padding rescale (image_encoder.py:113-123)
+  const float ul = __fmul_rn(u, P.lat_sx), vl = __fmul_rn(v, P.lat_sy);
+  float fx = fmaf(__fadd_rn(ul, 1.0f), (float)P.Wl, -1.0f) * 0.5f;   // torch's bilinear path fuses here
+  float fy = fmaf(__fadd_rn(vl, 1.0f), (float)P.Hl, -1.0f) * 0.5f;
+  fx = fminf(fmaxf(fx, 0.0f), (float)(P.Wl - 1));
+  fy = fminf(fmaxf(fy, 0.0f), (float)(P.Hl - 1));
+  const float flx = floorf(fx), fly = floorf(fy);
+  g.x0 = (int)flx; g.y0 = (int)fly;
+  g.x1 = min(g.x0 + 1, P.Wl - 1); g.y1 = min(g.y0 + 1, P.Hl - 1);
+  g.wx = fx - flx; g.wy = fy - fly;     // weight of the +1 neighbour (0 when it is out of range)
+}
+
+constexpr int kEncWarps = 4;
+constexpr int kLatChunkStride = 144;   // 8 rows * 16 B + 16 B pad -> conflict-free staging
+
+__global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams P) {
+  __shared__ __align__(16) unsigned char stage_lat[kEncWarps][64 * kLatChunkStride];
+  __shared__ __align__(16) unsigned char stage_in[kEncWarps][8 * 128];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const RowMap rm = RowMap::make(P.NV);
+  const long long group = (long long)blockIdx.x * kEncWarps + warp;   // 8-row group index
+  const long long row_base = group * 8;
+  unsigned char* sl = stage_lat[warp];
+  unsigned char* si = stage_in[warp];
+  const int L = 512;
+
+  for (int i = 0; i < 8; ++i) {
+    const long long row = row_base + i;
+    long long sample; int view;
+    const bool valid = rm.decode(row, P.n_samples, sample, view);
+    uint4 o0 = make_uint4(0, 0, 0, 0), o1 = o0;
+    float e0 = 0.f, e1 = 0.f;
+    if (valid) {
+      RowGeom g;
+      row_geometry(P, sample, view, g);
+      const __nv_bfloat16* lat = P.latent + g.map * (size_t)P.Hl * P.Wl * L;
+      const size_t p00 = ((size_t)g.y0 * P.Wl + g.x0) * L, p01 = ((size_t)g.y0 * P.Wl + g.x1) * L;
+      const size_t p10 = ((size_t)g.y1 * P.Wl + g.x0) * L, p11 = ((size_t)g.y1 * P.Wl + g.x1) * L;
+      const float w00 = (1.f - g.wx) * (1.f - g.wy), w01 = g.wx * (1.f - g.wy);
+      const float w10 = (1.f - g.wx) * g.wy, w11 = g.wx * g.wy;
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const int ch = half * 256 + lane * 8;
+        const uint4 a = __ldg(reinterpret_cast<const uint4*>(lat + p00 + ch));
+        const uint4 b = __ldg(reinterpret_cast<const uint4*>(lat + p01 + ch));
+        const uint4 c = __ldg(reinterpret_cast<const uint4*>(lat + p10 + ch));
+        const uint4 d = __ldg(reinterpret_cast<const uint4*>(lat + p11 + ch));
+        const uint32_t av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+        const uint32_t cv[4] = {c.x, c.y, c.z, c.w}, dv[4] = {d.x, d.y, d.z, d.w};
+        uint32_t r[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float lo = bf16lo(av[q]) * w00 + bf16lo(bv[q]) * w01 + bf16lo(cv[q]) * w10 + bf16lo(dv[q]) * w11;
+          const float hi = bf16hi(av[q]) * w00 + bf16hi(bv[q]) * w01 + bf16hi(cv[q]) * w10 + bf16hi(dv[q]) * w11;
+          r[q] = pack_bf16x2(lo, hi);
+        }
+        if (half == 0) o0 = make_uint4(r[0], r[1], r[2], r[3]); else o1 = make_uint4(r[0], r[1], r[2], r[3]);
+      }
+      // geometric code, two elements per lane (e = lane, lane + 32)
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+        const int e = lane + hh * 32;
+        float val = 0.f;
+        const int npos = 3 + 6 * P.NF;          // 39
+        const int ndep = 1 + 2 * P.NF;          // 13
+        if (e < 3) val = e == 0 ? g.xc : (e == 1 ? g.yc : g.zc);
+        else if (e < npos) {
+          const int q = e - 3, j = q % 3, fs = q / 3;
+          const float x = j == 0 ? g.xc : (j == 1 ? g.yc : g.zc);
+          val = sinf(__fadd_rn(P.phases[fs], __fmul_rn(x, P.freqs[fs])));
+        } else if (e < npos + 3) { const int j = e - npos; val = j == 0 ? g.dx : (j == 1 ? g.dy : g.dz); }
+        else if (e == npos + 3) val = g.dd;
+        else if (e < npos + 3 + ndep) { const int fs = e - (npos + 4); val = sinf(__fadd_rn(P.phases[fs], __fmul_rn(g.dd, P.freqs[fs]))); }
+        if (hh == 0) e0 = val; else e1 = val;
+      }
+    }
+    *reinterpret_cast<uint4*>(sl + lane * kLatChunkStride + i * 16) = o0;
+    *reinterpret_cast<uint4*>(sl + (32 + lane) * kLatChunkStride + i * 16) = o1;
+    reinterpret_cast<__nv_bfloat16*>(si + (lane >> 3) * 128 + i * 16)[lane & 7] = __float2bfloat16_rn(e0);
+    reinterpret_cast<__nv_bfloat16*>(si + (4 + (lane >> 3)) * 128 + i * 16)[lane & 7] = __float2bfloat16_rn(e1);
+  }
+  __syncwarp();
+  // write-out: every 8 lanes move one 128-byte line (8 rows x 16 B of one feature chunk)
+  const long long tile = row_base / 128;
+  const int rr = (int)(row_base % 128);
+  unsigned char* lat_tile = P.lat_pk + (size_t)tile * (512 / 8) * 2048;
+  unsigned char* in_tile = P.in_pk + (size_t)tile * (64 / 8) * 2048;
+#pragma unroll 4
+  for (int it = 0; it < 16; ++it) {
+    const int c = it * 4 + (lane >> 3), i = lane & 7;
+    const uint4 v = *reinterpret_cast<const uint4*>(sl + c * kLatChunkStride + i * 16);
+    *reinterpret_cast<uint4*>(lat_tile + (size_t)c * 2048 + (size_t)(rr + i) * 16) = v;
+  }
+#pragma unroll
+  for (int it = 0; it < 2; ++it) {
+    const int c = it * 4 + (lane >> 3), i = lane & 7;
+    const uint4 v = *reinterpret_cast<const uint4*>(si + c * 128 + i * 16);
+    *reinterpret_cast<uint4*>(in_tile + (size_t)c * 2048 + (size_t)(rr + i) * 16) = v;
+  }
+}
+
+__device__ __forceinline__ void red_add_v4(float* addr, float4 v) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
+// One lane per row (a 32-row slab per warp): d_latent[tap] += w_tap * d_feature, 4 channels per red.
+__global__ void __launch_bounds__(128) encode_bwd_kernel(EncodeParams P) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const RowMap rm = RowMap::make(P.NV);
+  const long long slab = (long long)blockIdx.x * 4 + warp;
+  const long long row = slab * 32 + lane;
+  long long sample; int view;
+  const bool valid = rm.decode(row, P.n_samples, sample, view);
+  if (!__any_sync(0xffffffffu, valid)) return;
+  const int L = 512;
+  RowGeom g;
+  float w00 = 0.f, w01 = 0.f, w10 = 0.f, w11 = 0.f;
+  float *q00 = nullptr, *q01 = nullptr, *q10 = nullptr, *q11 = nullptr;
+  if (valid) {
+    row_geometry(P, sample, view, g);
+    float* dl = P.d_latent + g.map * (size_t)P.Hl * P.Wl * L;
+    q00 = dl + ((size_t)g.y0 * P.Wl + g.x0) * L; q01 = dl + ((size_t)g.y0 * P.Wl + g.x1) * L;
+    q10 = dl + ((size_t)g.y1 * P.Wl + g.x0) * L; q11 = dl + ((size_t)g.y1 * P.Wl + g.x1) * L;
+    w00 = (1.f - g.wx) * (1.f - g.wy); w01 = g.wx * (1.f - g.wy); w10 = (1.f - g.wx) * g.wy; w11 = g.wx * g.wy;
+  }
+  const long long tile = row / 128;
+  const int rr = (int)(row % 128);
+  const float4* src = reinterpret_cast<const float4*>(P.d_lat_xr) + (size_t)tile * (L / 4) * 128 + rr;
+#pragma unroll 4
+  for (int n4 = 0; n4 < L / 4; ++n4) {
+    const float4 d = src[(size_t)n4 * 128];
+    if (valid) {
+      const int ch = n4 * 4;
+      if (w00 != 0.f) red_add_v4(q00 + ch, make_float4(d.x * w00, d.y * w00, d.z * w00, d.w * w00));
+      if (w01 != 0.f) red_add_v4(q01 + ch, make_float4(d.x * w01, d.y * w01, d.z * w01, d.w * w01));
+      if (w10 != 0.f) red_add_v4(q10 + ch, make_float4(d.x * w10, d.y * w10, d.z * w10, d.w * w10));
+      if (w11 != 0.f) red_add_v4(q11 + ch, make_float4(d.x * w11, d.y * w11, d.z * w11, d.w * w11));
+    }
+  }
+}
+
+// latent (N,C,H,W) fp32 -> (N,H,W,C) bf16, tiled transpose through shared memory
+__global__ void nchw_to_nhwc_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int C, int HW) {
+  __shared__ float tile[32][33];
+  const size_t n = blockIdx.z;
+  const int c0 = blockIdx.y * 32, p0 = blockIdx.x * 32;
+  const int tx = threadIdx.x, ty = threadIdx.y;   // 32 x 8
+  for (int j = ty; j < 32; j += 8) {
+    const int c = c0 + j, p = p0 + tx;
+    tile[j][tx] = (c < C && p < HW) ? src[(n * C + c) * (size_t)HW + p] : 0.f;
+  }
+  __syncthreads();
+  for (int j = ty; j < 32; j += 8) {
+    const int p = p0 + j, c = c0 + tx;
+    if (c < C && p < HW) dst[(n * (size_t)HW + p) * C + c] = __float2bfloat16_rn(tile[tx][j]);
+  }
+}
+// d_latent (N,H,W,C) fp32 -> (N,C,H,W) fp32
+__global__ void nhwc_to_nchw_f32_kernel(const float* __restrict__ src, float* __restrict__ dst, int C, int HW) {
+  __shared__ float tile[32][33];
+  const size_t n = blockIdx.z;
+  const int c0 = blockIdx.y * 32, p0 = blockIdx.x * 32;
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  for (int j = ty; j < 32; j += 8) {
+    const int p = p0 + j, c = c0 + tx;
+    tile[j][tx] = (c < C && p < HW) ? src[(n * (size_t)HW + p) * C + c] : 0.f;
+  }
+  __syncthreads();
+  for (int j = ty; j < 32; j += 8) {
+    const int c = c0 + j, p = p0 + tx;
+    if (c < C && p < HW) dst[(n * C + c) * (size_t)HW + p] = tile[tx][j];
+  }
+}
+
+}  // namespace dnr
+
+static int fill_encode_params(dnr::EncodeParams& P, const float* rays, const float* z, const float* poses,
+                              const float* focal, const float* cxy, const float* depth, const void* latent_nhwc,
+                              const float* freqs, const float* phases, int SB, int NV, int NR, int K, int H, int W,
+                              int Hl, int Wl, int L, int NF, long long ray_offset, long long n_rays, float img_w, float img_h,
+                              float lat_sx, float lat_sy) {
+  DNR_REQUIRE(L == 512, "encode: latent width must be 512");
+  DNR_REQUIRE(NF == 6, "encode: num_freqs must be 6 (55-wide geometric code)");
+  DNR_REQUIRE(NV >= 1 && NV <= 8, "encode: NV must be in [1,8]");
+  P.rays = rays; P.z = z; P.poses = poses; P.focal = focal; P.cxy = cxy; P.depth = depth;
+  P.latent = (const __nv_bfloat16*)latent_nhwc; P.freqs = freqs; P.phases = phases;
+  P.SB = SB; P.NV = NV; P.NR = NR; P.K = K; P.H = H; P.W = W; P.Hl = Hl; P.Wl = Wl; P.NF = NF;
+  P.img_w = img_w; P.img_h = img_h; P.lat_sx = lat_sx; P.lat_sy = lat_sy;
+  P.n_samples = n_rays * K; P.ray_offset = ray_offset; P.n_rays = n_rays;
+  DNR_REQUIRE(ray_offset >= 0 && ray_offset + n_rays <= (long long)SB * NR, "encode: ray chunk out of range");
+  P.lat_pk = nullptr; P.in_pk = nullptr; P.d_latent = nullptr; P.d_lat_xr = nullptr;
+  return 0;
+}
+
+// Number of 128-row tiles of the per-view MLP batch for n_samples points seen from NV views.
+DNR_EXPORT int dnr_view_row_tiles(long long n_samples, int NV) {
+  if (NV < 1 || NV > 8) return -1;
+  return dnr::RowMap::make(NV).tiles_for(n_samples);
+}
+
+// Replaces PixelNeRF.forward's projection / gather / encoding (pixelnerf.py:91-128).
+DNR_EXPORT int dnr_encode_fwd(const float* rays, const float* z, const float* poses, const float* focal,
+                              const float* cxy, const float* depth, const void* latent_nhwc_bf16, const float* freqs,
+                              const float* phases, int SB, int NV, int NR, int K, int H, int W, int Hl, int Wl, int L,
+                              int NF, long long ray_offset, long long n_rays, float img_w, float img_h, float lat_sx,
+                              float lat_sy, void* lat_pk, void* in_pk,
+                              cudaStream_t stream) {
+  dnr::EncodeParams P;
+  int rc = fill_encode_params(P, rays, z, poses, focal, cxy, depth, latent_nhwc_bf16, freqs, phases, SB, NV, NR, K, H,
+                              W, Hl, Wl, L, NF, ray_offset, n_rays, img_w, img_h, lat_sx, lat_sy);
+  if (rc) return rc;
+  P.lat_pk = (unsigned char*)lat_pk; P.in_pk = (unsigned char*)in_pk;
+  if (P.n_samples <= 0) return 0;
+  const int tiles = dnr::RowMap::make(NV).tiles_for(P.n_samples);
+  const int groups = tiles * 16;
+  dnr::encode_fwd_kernel<<<groups / dnr::kEncWarps, dnr::kEncWarps * 32, 0, stream>>>(P);
+  DNR_CHECK_LAUNCH("dnr_encode_fwd");
+  return 0;
+}
+
+// Backward of SpatialEncoder.index (grid_sample bilinear w.r.t. the latent map, image_encoder.py:117-123).
+DNR_EXPORT int dnr_encode_bwd(const float* rays, const float* z, const float* poses, const float* focal,
+                              const float* cxy, const float* depth, const float* freqs, const float* phases, int SB,
+                              int NV, int NR, int K, int H, int W, int Hl, int Wl, int L, int NF, long long ray_offset,
+                              long long n_rays, float img_w, float img_h, float lat_sx, float lat_sy,
+                              const float* d_lat_xr, float* d_latent_nhwc,
+                              cudaStream_t stream) {
+  dnr::EncodeParams P;
+  int rc = fill_encode_params(P, rays, z, poses, focal, cxy, depth, nullptr, freqs, phases, SB, NV, NR, K, H, W, Hl,
+                              Wl, L, NF, ray_offset, n_rays, img_w, img_h, lat_sx, lat_sy);
+  if (rc) return rc;
+  P.d_lat_xr = d_lat_xr; P.d_latent = d_latent_nhwc;
+  if (P.n_samples <= 0) return 0;
+  const int tiles = dnr::RowMap::make(NV).tiles_for(P.n_samples);
+  dnr::encode_bwd_kernel<<<tiles, 128, 0, stream>>>(P);
+  DNR_CHECK_LAUNCH("dnr_encode_bwd");
+  return 0;
+}
+
+// Per-scene repack of encoder.latent (SB*NV, C, Hl, Wl) fp32 -> channels-last bf16.
+DNR_EXPORT int dnr_pack_latent_nhwc(const float* latent_nchw, int n_maps, int C, int Hl, int Wl, void* out_bf16,
+                                    cudaStream_t stream) {
+  const int HW = Hl * Wl;
+  dim3 grid((HW + 31) / 32, (C + 31) / 32, n_maps), block(32, 8);
+  dnr::nchw_to_nhwc_bf16_kernel<<<grid, block, 0, stream>>>(latent_nchw, (__nv_bfloat16*)out_bf16, C, HW);
+  DNR_CHECK_LAUNCH("dnr_pack_latent_nhwc");
+  return 0;
+}
+
+DNR_EXPORT int dnr_unpack_dlatent_nchw(const float* d_latent_nhwc, int n_maps, int C, int Hl, int Wl, float* out_nchw,
+                                       cudaStream_t stream) {
+  const int HW = Hl * Wl;
+  dim3 grid((HW + 31) / 32, (C + 31) / 32, n_maps), block(32, 8);
+  dnr::nhwc_to_nchw_f32_kernel<<<grid, block, 0, stream>>>(d_latent_nhwc, out_nchw, C, HW);
+  DNR_CHECK_LAUNCH("dnr_unpack_dlatent_nchw");
+  return 0;
+}

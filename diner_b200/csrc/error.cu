@@ -1,0 +1,14 @@
+// Error reporting + ABI version for the diner_b200 C ABI.
+#include "common.cuh"
+#include <string.h>
+
+namespace dnr {
+static thread_local char g_last_error[512] = "";
+void set_last_error(const char* where, cudaError_t e) {
+  snprintf(g_last_error, sizeof(g_last_error), "%s: %s (%s)", where, cudaGetErrorName(e), cudaGetErrorString(e));
+}
+void set_last_error_msg(const char* msg) { snprintf(g_last_error, sizeof(g_last_error), "%s", msg); }
+}  // namespace dnr
+
+DNR_EXPORT const char* dnr_last_error() { return dnr::g_last_error; }
+DNR_EXPORT int dnr_abi_version() { return 1; }

@@ -1,0 +1,235 @@
+"""Host-side sequencing of the field evaluation (reference PixelNeRF.forward, src/models/pixelnerf.py:55-145,
+and ResnetFC.forward, src/models/resnetfc.py:129-159) on the CUDA kernels, forward and backward.
+
+    encode (project + gather + codes)            dnr_encode_fwd
+    x0   = lin_in(code) + lin_z[0](lat)          one GEMM, two K segments
+    for b in 0..2:  net = relu(fc_0(relu(x)))    GEMM, ReLU epilogue
+                    x  += fc_1(net) [+ lin_z[b+1](lat)]    GEMM, residual epilogue (b == 2: + view mean)
+    for b in 3..4:  same on the pooled rows
+    rgb, sigma = sigmoid / relu(lin_out(relu(x)))          dnr_head_fwd
+
+Activations never exist in row-major form: every GEMM epilogue writes the next GEMM's A operand directly
+in the packed tensor-core layout (csrc/common.cuh).  The backward pass runs the same kernels on the
+transposed weights (dgrad) and dnr_mlp_wgrad on the saved operands.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field as dc_field
+
+import torch
+
+from . import _lib
+from .scene import SceneBuffers
+
+HID = 512
+IN_PAD = 64
+
+
+def _mlp_signature(mlp):
+    return tuple((p.data_ptr(), p._version) for p in mlp.parameters())
+
+
+class PackedMLP:
+    """bf16 tensor-core images of the ResnetFC weights (W for forward, W^T for dgrad) + fp32 biases."""
+
+    def __init__(self, mlp, need_transposed: bool):
+        dev = mlp.lin_out.weight.device
+        self.sig = _mlp_signature(mlp)
+        self.has_t = need_transposed
+        st = _lib.stream_ptr()
+
+        def pack(w, transpose=False):
+            w = w.detach().to(torch.float32).contiguous()
+            rows, cols = w.shape
+            n, k = (cols, rows) if transpose else (rows, cols)
+            n_pad, k_pad = (n + 255) // 256 * 256, (k + 63) // 64 * 64
+            out = torch.empty(n_pad * k_pad, device=dev, dtype=torch.bfloat16)
+            _lib.call("dnr_pack_weight", _lib.ptr(w), rows, cols, cols, 1 if transpose else 0, n_pad, k_pad,
+                      _lib.ptr(out), st)
+            return out
+
+        f = lambda t: t.detach().to(torch.float32).contiguous()
+        self.w_in = pack(mlp.lin_in.weight)                      # [512 x 64]
+        self.w_z = [pack(l.weight) for l in mlp.lin_z]
+        self.w_0 = [pack(b.fc_0.weight) for b in mlp.blocks]
+        self.w_1 = [pack(b.fc_1.weight) for b in mlp.blocks]
+        self.b_first = f(mlp.lin_in.bias + mlp.lin_z[0].bias)
+        self.b_0 = [f(b.fc_0.bias) for b in mlp.blocks]
+        # fc_1 bias of block b merged with the lin_z bias that is added right after it (b = 0, 1)
+        self.b_1 = [f(mlp.blocks[b].fc_1.bias + (mlp.lin_z[b + 1].bias if b + 1 < len(mlp.lin_z) else 0))
+                    for b in range(len(mlp.blocks))]
+        self.w_out = f(mlp.lin_out.weight)
+        self.b_out = f(mlp.lin_out.bias)
+        if need_transposed:
+            self.wt_z = [pack(l.weight, True) for l in mlp.lin_z]
+            self.wt_0 = [pack(b.fc_0.weight, True) for b in mlp.blocks]
+            self.wt_1 = [pack(b.fc_1.weight, True) for b in mlp.blocks]
+
+
+_packed_cache: dict = {}
+
+
+def get_packed(mlp, need_transposed: bool) -> PackedMLP:
+    hit = _packed_cache.get(id(mlp))
+    if hit is not None and hit.sig == _mlp_signature(mlp) and (hit.has_t or not need_transposed):
+        return hit
+    pk = PackedMLP(mlp, need_transposed)
+    _packed_cache.clear()
+    _packed_cache[id(mlp)] = pk
+    return pk
+
+
+def _gemm(A0, B0, K0, m_tiles, N=HID, A1=None, B1=None, K1=0, A2=None, B2=None, K2=0, bias=None, mask=None,
+          res_in=None, res_out=None, act_out=None, relu=0, mean_nv=0, n_samples=0, max_ctas=0):
+    p = _lib.ptr
+    _lib.call("dnr_mlp_gemm", p(A0), p(B0), K0, p(A1), p(B1), K1, p(A2), p(B2), K2, m_tiles, N, p(bias), p(mask),
+              p(res_in), p(res_out), p(act_out), relu, mean_nv, n_samples, max_ctas, _lib.stream_ptr())
+
+
+@dataclass
+class FieldSaved:
+    """Operands kept for the backward pass (all in packed layouts)."""
+    n_samples: int = 0
+    mv: int = 0
+    ms: int = 0
+    lat: torch.Tensor = None
+    code: torch.Tensor = None
+    xa: list = dc_field(default_factory=list)      # relu(x_b) entering block b (b = 0..4); xa[5] = relu(x_5)
+    net: list = dc_field(default_factory=list)     # relu(fc_0(.)) of block b
+    out: torch.Tensor = None
+
+
+def _encode_args(sc: SceneBuffers, NR: int, K: int, ray0: int, n_rays: int):
+    return (sc.SB, sc.NV, NR, K, sc.H, sc.W, sc.Hl, sc.Wl, sc.L, sc.num_freqs, ray0, n_rays,
+            sc.img_w, sc.img_h, sc.lat_sx, sc.lat_sy)
+
+
+def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.Tensor, NR: int, ray0: int,
+                  save: bool):
+    """Evaluate the field on one chunk of rays.
+
+    rays (n,8) / z (n,K) are the chunk's rows of the flattened (SB*NR) batch, `ray0` the index of its first
+    ray in that batch (the scene of a ray is ray // NR).  Returns (rgbsigma (n*K,4) fp32, FieldSaved | None).
+    """
+    p, st = _lib.ptr, _lib.stream_ptr()
+    dev = rays.device
+    n, K = z.shape
+    n_samples = n * K
+    NV = sc.NV
+    mv = _lib.load().dnr_view_row_tiles(n_samples, NV)
+    ms = (n_samples + 127) // 128
+    bf = dict(device=dev, dtype=torch.bfloat16)
+    f32 = dict(device=dev, dtype=torch.float32)
+
+    lat = torch.empty(mv * 128 * HID, **bf)
+    code = torch.empty(mv * 128 * IN_PAD, **bf)
+    _lib.call("dnr_encode_fwd", p(rays), p(z), p(sc.poses), p(sc.focal), p(sc.cxy), p(sc.depth), p(sc.latent_nhwc),
+              p(sc.freqs), p(sc.phases), *_encode_args(sc, NR, K, ray0, n), p(lat), p(code), st)
+
+    sv = FieldSaved(n_samples=n_samples, mv=mv, ms=ms, lat=lat, code=code) if save else None
+    x = torch.empty(mv * 128 * HID, **f32)                      # residual stream, XR layout (updated in place)
+    new_act = lambda tiles: torch.empty(tiles * 128 * HID, **bf)
+    xa = new_act(mv)
+    net = new_act(mv)
+    # x0 = lin_in(code) + lin_z[0](lat)                           resnetfc.py:139,152-154
+    _gemm(code, pk.w_in, IN_PAD, mv, A1=lat, B1=pk.w_z[0], K1=HID, bias=pk.b_first, res_out=x, act_out=xa, relu=1)
+    xm = xam = None
+    for b in range(3):
+        if save:
+            sv.xa.append(xa)
+        # net = relu(fc_0(relu(x)))                               resnetfc.py:62
+        _gemm(xa, pk.w_0[b], HID, mv, bias=pk.b_0[b], act_out=net, relu=1)
+        if save:
+            sv.net.append(net)
+        if b < 2:
+            xa_next = new_act(mv) if save else xa
+            # x = x + fc_1(net) + lin_z[b+1](lat)                 resnetfc.py:63-69,152-154
+            _gemm(net, pk.w_1[b], HID, mv, A1=lat, B1=pk.w_z[b + 1], K1=HID, bias=pk.b_1[b], res_in=x, res_out=x,
+                  act_out=xa_next, relu=1)
+            xa = xa_next
+            if save:
+                net = new_act(mv)
+        else:
+            # last per-view block: the epilogue averages the NV rows of each sample (resnetfc.py:147-151)
+            xm = torch.zeros(ms * 128 * HID, **f32)
+            xam = torch.zeros(ms * 128 * HID, **bf)
+            _gemm(net, pk.w_1[b], HID, mv, bias=pk.b_1[b], res_in=x, res_out=xm, act_out=xam, relu=1, mean_nv=NV,
+                  n_samples=n_samples)
+    del x
+    xa, net = xam, torch.zeros(ms * 128 * HID, **bf)
+    for b in (3, 4):
+        if save:
+            sv.xa.append(xa)
+        _gemm(xa, pk.w_0[b], HID, ms, bias=pk.b_0[b], act_out=net, relu=1)
+        if save:
+            sv.net.append(net)
+        xa_next = new_act(ms) if save else xa
+        _gemm(net, pk.w_1[b], HID, ms, bias=pk.b_1[b], res_in=xm, res_out=xm, act_out=xa_next, relu=1)
+        xa = xa_next
+        if save and b == 3:
+            net = new_act(ms)
+    out = torch.empty(n_samples, 4, **f32)
+    _lib.call("dnr_head_fwd", p(xa), p(pk.w_out), p(pk.b_out), n_samples, p(out), st)
+    if save:
+        sv.xa.append(xa)
+        sv.out = out
+    return out, sv
+
+
+def _wgrad(dY, Fy, X, Fx, tiles, dW, n_valid, k_valid, db):
+    p = _lib.ptr
+    _lib.call("dnr_mlp_wgrad", p(dY), Fy, p(X), Fx, tiles, p(dW), dW.shape[1], n_valid, k_valid, p(db),
+              _lib.stream_ptr())
+
+
+def field_backward(sc: SceneBuffers, pk: PackedMLP, mlp, sv: FieldSaved, rays, z, NR: int, ray0: int,
+                   d_out: torch.Tensor, grads: dict, d_latent_nhwc):
+    """Backward of field_forward.  Accumulates parameter gradients into `grads` (name -> fp32 tensor shaped like
+    the parameter, zero-initialised by the caller) and, if not None, the feature gradient into
+    d_latent_nhwc (SB,NV,Hl,Wl,512) fp32."""
+    p, st = _lib.ptr, _lib.stream_ptr()
+    dev = d_out.device
+    n, K = z.shape
+    mv, ms, n_samples, NV = sv.mv, sv.ms, sv.n_samples, sc.NV
+    bf = dict(device=dev, dtype=torch.bfloat16)
+    f32 = dict(device=dev, dtype=torch.float32)
+    G = lambda name: grads[name]
+
+    # ---- head: lin_out + activations ----
+    dx = torch.empty(ms * 128 * HID, **f32)           # d(block output), XR
+    dx_pk = torch.empty(ms * 128 * HID, **bf)
+    draw = torch.zeros(ms * 128 * 128, **bf)
+    _lib.call("dnr_head_bwd", p(sv.xa[5]), p(pk.w_out), p(sv.out), p(d_out.contiguous()), n_samples, p(dx), p(dx_pk),
+              p(draw), st)
+    _wgrad(draw, 128, sv.xa[5], HID, ms, G("lin_out.weight"), 4, HID, G("lin_out.bias"))
+
+    def block_bwd(b, tiles, dx, dx_pk):
+        """dx = d x_{b+1} -> returns d x_b' (gradient at the block's input, after its lin_z was added)."""
+        _wgrad(dx_pk, HID, sv.net[b], HID, tiles, G(f"blocks.{b}.fc_1.weight"), HID, HID, G(f"blocks.{b}.fc_1.bias"))
+        dnet = torch.empty(tiles * 128 * HID, **bf)
+        _gemm(dx_pk, pk.wt_1[b], HID, tiles, mask=sv.net[b], act_out=dnet)
+        _wgrad(dnet, HID, sv.xa[b], HID, tiles, G(f"blocks.{b}.fc_0.weight"), HID, HID, G(f"blocks.{b}.fc_0.bias"))
+        dx_pk2 = torch.empty(tiles * 128 * HID, **bf)
+        _gemm(dnet, pk.wt_0[b], HID, tiles, mask=sv.xa[b], res_in=dx, res_out=dx, act_out=dx_pk2)
+        return dx, dx_pk2
+
+    for b in (4, 3):
+        dx, dx_pk = block_bwd(b, ms, dx, dx_pk)
+    # ---- view mean ----
+    dxv = torch.empty(mv * 128 * HID, **f32)
+    dxv_pk = torch.empty(mv * 128 * HID, **bf)
+    _lib.call("dnr_mean_bwd", p(dx), NV, n_samples, mv, p(dxv), p(dxv_pk), st)
+    del dx, dx_pk
+    dz_pk = [None, None, None]
+    for b in (2, 1, 0):
+        dxv, dxv_pk = block_bwd(b, mv, dxv, dxv_pk)
+        dz_pk[b] = dxv_pk
+        _wgrad(dxv_pk, HID, sv.lat, HID, mv, G(f"lin_z.{b}.weight"), HID, HID, G(f"lin_z.{b}.bias"))
+    _wgrad(dz_pk[0], HID, sv.code, IN_PAD, mv, G("lin_in.weight"), HID, mlp.d_in, G("lin_in.bias"))
+    # ---- feature map ----
+    if d_latent_nhwc is not None:
+        dlat = torch.empty(mv * 128 * HID, **f32)
+        _gemm(dz_pk[0], pk.wt_z[0], HID, mv, A1=dz_pk[1], B1=pk.wt_z[1], K1=HID, A2=dz_pk[2], B2=pk.wt_z[2], K2=HID,
+              res_out=dlat)
+        _lib.call("dnr_encode_bwd", p(rays), p(z), p(sc.poses), p(sc.focal), p(sc.cxy), p(sc.depth), p(sc.freqs),
+                  p(sc.phases), *_encode_args(sc, NR, K, ray0, n), p(dlat), p(d_latent_nhwc), st)
