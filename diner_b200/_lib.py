@@ -11,6 +11,12 @@ import os
 from . import _build
 
 _lib = None
+ABI_VERSION = 2
+
+# instrumentation used by bench.py: number of kernel launches issued through the ABI, and (when `profile` is a
+# list) one (name, start_event, end_event, tag) record per call for per-kernel CUDA-event timing
+launch_count = 0
+profile = None
 
 c_p = C.c_void_p
 c_i = C.c_int
@@ -24,7 +30,7 @@ _SIGNATURES = {
     "dnr_composite_fwd": (c_i, [c_p, c_p, c_p, c_i, c_i, c_i, c_p, c_p, c_p, c_p]),
     "dnr_composite_bwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_p, c_p]),
     "dnr_pad_depth_std": (c_i, [c_p, c_p, c_i, c_i, c_i, c_i, c_p, c_p]),
-    "dnr_sampler_fwd": (c_i, [c_p] * 13 + [c_ull] + [c_i] * 9 + [c_f] * 5 + [c_i] + [c_p] * 5),
+    "dnr_sampler_fwd": (c_i, [c_p] * 13 + [c_ull] + [c_i] * 9 + [c_f] * 5 + [c_i, c_i] + [c_p] * 6),
     "dnr_view_row_tiles": (c_i, [c_ll, c_i]),
     "dnr_encode_fwd": (c_i, [c_p] * 9 + [c_i] * 10 + [c_ll, c_ll] + [c_f] * 4 + [c_p, c_p, c_p]),
     "dnr_encode_bwd": (c_i, [c_p] * 8 + [c_i] * 10 + [c_ll, c_ll] + [c_f] * 4 + [c_p, c_p, c_p]),
@@ -64,6 +70,9 @@ def load(build_if_missing: bool = True):
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
+    if lib.dnr_abi_version() != ABI_VERSION:
+        raise RuntimeError(f"{path} has ABI version {lib.dnr_abi_version()}, expected {ABI_VERSION}: rebuild it "
+                           "(python -m diner_b200._build --force)")
     _lib = lib
     return lib
 
@@ -73,9 +82,19 @@ def ptr(t):
     return None if t is None else t.data_ptr()
 
 
-def call(name: str, *args):
+def call(name: str, *args, tag=None):
+    global launch_count
     lib = load()
-    rc = getattr(lib, name)(*args)
+    launch_count += 1
+    if profile is not None:
+        import torch
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        rc = getattr(lib, name)(*args)
+        e1.record()
+        profile.append((name, e0, e1, tag))
+    else:
+        rc = getattr(lib, name)(*args)
     if rc != 0:
         msg = lib.dnr_last_error()
         raise RuntimeError(f"{name} failed (code {rc}): {msg.decode() if msg else '?'}")

@@ -33,10 +33,12 @@ struct SamplerParams {
   int SB, NV, NR, H, W, C, K, G, P;
   float depth_diff_max, img_w, img_h, std_sx, std_sy, inv_c_step;
   int count_only;
+  int unpacked;           // n_gauss is [SB*NR, G] and u_fill is [SB*NR, K] (indexed by ray / sorted slot)
   float* z_out;           // [SB*NR, K]
   int* ray_mask_out;      // [SB*NR] or null
   int* n_missing_out;     // [SB*NR] or null
   int* sel_idx_out;       // [SB*NR, K-G] or null (-1 = empty slot)
+  float* p_out;           // [SB*NR, C] or null: per-candidate likelihood (debug / parity tests)
 };
 
 __device__ __forceinline__ int nearest_border(float u, int size) {
@@ -145,6 +147,7 @@ __global__ void __launch_bounds__(kSamplerWarps * 32) sampler_kernel(SamplerPara
         p = fmaxf(p, pv);                              // :129
       }
     }
+    if (P.p_out && i < C) P.p_out[ray * C + i] = p;
     const unsigned nzmask = __ballot_sync(0xffffffffu, p != 0.0f);
     if (p != 0.0f) {
       const int pos = n_nz + __popc(nzmask & ((1u << lane) - 1u));
@@ -201,7 +204,7 @@ __global__ void __launch_bounds__(kSamplerWarps * 32) sampler_kernel(SamplerPara
     const float sd = sqrtf(warp_sum(var));
     for (int g = lane; g < G; g += 32) {
       float n;
-      if (P.n_gauss) n = P.n_gauss[(size_t)P.gauss_off[ray] * G + g];
+      if (P.n_gauss) n = P.n_gauss[(size_t)(P.unpacked ? ray : (long long)P.gauss_off[ray]) * G + g];
       else {
         uint4 r = rng((uint32_t)ray, (uint32_t)(ray >> 32), (uint32_t)g, 1u);
         const float u1 = fmaxf(u01(r.x), 5.9604645e-8f), u2 = u01(r.y);
@@ -242,7 +245,7 @@ __global__ void __launch_bounds__(kSamplerWarps * 32) sampler_kernel(SamplerPara
     for (int i = lane; i < K; i += 32) {
       if (sorted[i] == 0.0f) {
         float u;
-        if (P.u_fill) u = P.u_fill[(size_t)P.fill_off[ray] + (i - n_neg)];
+        if (P.u_fill) u = P.unpacked ? P.u_fill[(size_t)ray * K + i] : P.u_fill[(size_t)P.fill_off[ray] + (i - n_neg)];
         else { uint4 r = rng((uint32_t)ray, (uint32_t)(ray >> 32), (uint32_t)i, 2u); u = u01(r.x); }
         float zm = near + (float)i * mstep;                   // :389
         zm = zm + u * mstep;                                  // :390
@@ -302,13 +305,15 @@ DNR_EXPORT int dnr_sampler_fwd(const float* rays, const float* poses, const floa
                                const float* lin_tab, const float* u_coarse, const float* n_gauss, const float* u_fill,
                                const int* gauss_off, const int* fill_off, unsigned long long seed, int SB, int NV,
                                int NR, int H, int W, int C, int K, int G, int pad, float depth_diff_max, float img_w,
-                               float img_h, float std_sx, float std_sy, int count_only, float* z_out,
-                               int* ray_mask_out, int* n_missing_out, int* sel_idx_out, cudaStream_t stream) {
+                               float img_h, float std_sx, float std_sy, int count_only, int unpacked_noise,
+                               float* z_out,
+                               int* ray_mask_out, int* n_missing_out, int* sel_idx_out, float* p_out,
+                               cudaStream_t stream) {
   DNR_REQUIRE(NV >= 1 && NV <= dnr::kMaxViews, "dnr_sampler_fwd: NV must be in [1,8]");
   DNR_REQUIRE(K >= 1 && K <= 256 && G >= 0 && G <= K, "dnr_sampler_fwd: need 1 <= K <= 256, 0 <= G <= K");
   DNR_REQUIRE(C >= 1 && C <= 4096, "dnr_sampler_fwd: C must be in [1,4096]");
-  DNR_REQUIRE((n_gauss == nullptr) || gauss_off != nullptr, "dnr_sampler_fwd: n_gauss needs gauss_off");
-  DNR_REQUIRE((u_fill == nullptr) || fill_off != nullptr, "dnr_sampler_fwd: u_fill needs fill_off");
+  DNR_REQUIRE((n_gauss == nullptr) || unpacked_noise || gauss_off != nullptr, "dnr_sampler_fwd: n_gauss needs gauss_off");
+  DNR_REQUIRE((u_fill == nullptr) || unpacked_noise || fill_off != nullptr, "dnr_sampler_fwd: u_fill needs fill_off");
   const long long n_rays = (long long)SB * NR;
   if (n_rays <= 0) return 0;
   dnr::SamplerParams P;
@@ -318,8 +323,8 @@ DNR_EXPORT int dnr_sampler_fwd(const float* rays, const float* poses, const floa
   P.SB = SB; P.NV = NV; P.NR = NR; P.H = H; P.W = W; P.C = C; P.K = K; P.G = G; P.P = pad;
   P.depth_diff_max = depth_diff_max; P.img_w = img_w; P.img_h = img_h; P.std_sx = std_sx; P.std_sy = std_sy;
   P.inv_c_step = (float)(1.0 / (double)C);
-  P.count_only = count_only; P.z_out = z_out; P.ray_mask_out = ray_mask_out; P.n_missing_out = n_missing_out;
-  P.sel_idx_out = sel_idx_out;
+  P.count_only = count_only; P.unpacked = unpacked_noise; P.z_out = z_out; P.ray_mask_out = ray_mask_out; P.n_missing_out = n_missing_out;
+  P.sel_idx_out = sel_idx_out; P.p_out = p_out;
   const size_t smem = dnr::sampler_smem_bytes(C, K);
   static size_t configured = 0;
   if (smem > configured) {

@@ -10,6 +10,7 @@
 // extra N=16 MMA per K step against a constant tile of ones.
 #include "common.cuh"
 #include "tc05.cuh"
+#include <stdlib.h>
 
 namespace dnr {
 
@@ -27,6 +28,7 @@ struct WgradParams {
   float* dW;                 // [Fy_valid x ldw] fp32 row-major (accumulated into)
   int ldw, n_valid, k_valid; // only n < n_valid, k < k_valid are written
   float* db;                 // [n_valid] or null
+  int copy_piece;            // bytes per bulk copy of the X tile
 };
 
 __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const WgradParams P) {
@@ -76,8 +78,12 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const WgradPar
         tc::mbar_arrive_expect_tx(full + stage, kWgAStage + b_stage);
         tc::bulk_g2s(sA + (size_t)stage * kWgAStage, P.dY + ((size_t)rt * (P.Fy / 8) + (size_t)n_tile * 16) * 2048,
                      kWgAStage, full + stage);
-        tc::bulk_g2s(sB + (size_t)stage * b_stage, P.X + ((size_t)rt * (P.Fx / 8) + (size_t)k_tile * (P.NB / 8)) * 2048,
-                     b_stage, full + stage);
+        {
+          const unsigned char* xsrc = P.X + ((size_t)rt * (P.Fx / 8) + (size_t)k_tile * (P.NB / 8)) * 2048;
+          const int piece = P.copy_piece;
+          for (int off = 0; off < b_stage; off += piece)
+            tc::bulk_g2s(sB + (size_t)stage * b_stage + off, xsrc + off, piece, full + stage);
+        }
         if (++stage == kWgStages) { stage = 0; phase ^= 1; }
       }
     }
@@ -151,6 +157,9 @@ DNR_EXPORT int dnr_mlp_wgrad(const void* dY_pk, int Fy, const void* X_pk, int Fx
   dnr::WgradParams P;
   P.dY = (const unsigned char*)dY_pk; P.X = (const unsigned char*)X_pk; P.Fy = Fy; P.Fx = Fx;
   P.NB = Fx < 256 ? Fx : 256;
+  { const char* e = getenv("DNR_WG_NB"); if (e && Fx >= 256) P.NB = atoi(e); }
+  P.copy_piece = P.NB * 256;
+  { const char* e = getenv("DNR_WG_PIECE"); if (e) { int v = atoi(e); if (v > 0 && v < P.copy_piece) P.copy_piece = v; } }
   P.row_tiles = row_tiles; P.dW = dW; P.ldw = ldw; P.n_valid = n_valid; P.k_valid = k_valid; P.db = db;
   const int out_tiles = (Fy / 128) * (Fx / P.NB);
   static int num_sms = 0;

@@ -40,40 +40,49 @@ def sample_rays(sc: SceneBuffers, rays: torch.Tensor, K: int, C: int, G: int, no
     n_rays = SB * NR
     z = torch.empty(n_rays, K, device=dev, dtype=torch.float32)
     dbg = {}
-    ray_mask = n_missing = sel = None
+    ray_mask = n_missing = sel = p_cand = None
     if want_debug:
+        p_cand = torch.empty(n_rays, C, device=dev, dtype=torch.float32)
         ray_mask = torch.empty(n_rays, device=dev, dtype=torch.int32)
         n_missing = torch.empty(n_rays, device=dev, dtype=torch.int32)
         sel = torch.empty(n_rays, K - G, device=dev, dtype=torch.int32)
-        dbg = dict(ray_mask=ray_mask, n_missing=n_missing, sel_idx=sel)
+        dbg = dict(ray_mask=ray_mask, n_missing=n_missing, sel_idx=sel, p=p_cand)
     lin = lin_table(C, dev)
     if seed is None:
         seed = int(torch.empty((), dtype=torch.int64).random_().item())
 
-    def launch(u_coarse, n_gauss, u_fill, goff, foff, count_only, rm, nm, sl):
+    def launch(u_coarse, n_gauss, u_fill, goff, foff, count_only, rm, nm, sl, pc=None, unpacked=False):
         _lib.call("dnr_sampler_fwd", p(rays), p(sc.poses), p(sc.focal), p(sc.cxy), p(sc.depth), p(sc.std_padded),
                   p(sc.normal), p(lin), p(u_coarse), p(n_gauss), p(u_fill), p(goff), p(foff), seed & (2 ** 64 - 1),
                   SB, sc.NV, NR, sc.H, sc.W, C, K, G, STD_PAD, DEPTH_DIFF_MAX, sc.img_w, sc.img_h, sc.std_sx, sc.std_sy,
-                  1 if count_only else 0, p(z), p(rm), p(nm), p(sl), st)
+                  1 if count_only else 0, 1 if unpacked else 0, p(z), p(rm), p(nm), p(sl), p(pc), st)
 
     if noise is None:
-        launch(None, None, None, None, None, False, ray_mask, n_missing, sel)
+        launch(None, None, None, None, None, False, ray_mask, n_missing, sel, p_cand)
     else:
         f = lambda t: None if t is None else t.to(device=dev, dtype=torch.float32).contiguous()
         u_coarse, n_gauss, u_fill = f(noise.get("u_coarse")), f(noise.get("n_gauss")), f(noise.get("u_fill"))
-        goff = foff = None
-        if n_gauss is not None or u_fill is not None:
+        if noise.get("n_gauss_full") is not None or noise.get("u_fill_full") is not None:
+            # unpacked draws: (SB*NR, G) and (SB*NR, K), indexed by ray and sorted slot (packing-independent)
+            launch(u_coarse, f(noise.get("n_gauss_full")), f(noise.get("u_fill_full")), None, None, False, ray_mask,
+                   n_missing, sel, p_cand, unpacked=True)
+            return (z, dbg) if want_debug else z
+        i32 = lambda t: None if t is None else t.to(device=dev, dtype=torch.int32).contiguous()
+        goff, foff = i32(noise.get("gauss_off")), i32(noise.get("fill_off"))   # explicit slices (tests)
+        if goff is None and foff is None and (n_gauss is not None or u_fill is not None):
             # packed draws: a counting pass tells where each ray's slice starts
             rm = torch.empty(n_rays, device=dev, dtype=torch.int32)
             nm = torch.empty(n_rays, device=dev, dtype=torch.int32)
             launch(u_coarse, None, None, None, None, True, rm, nm, None)
             goff = (torch.cumsum(rm, 0) - rm).to(torch.int32)
             foff = (torch.cumsum(nm, 0) - nm).to(torch.int32)
-            if n_gauss is not None and n_gauss.numel() == 0:
-                n_gauss = torch.zeros(1, G, device=dev)
-            if u_fill is not None and u_fill.numel() == 0:
-                u_fill = torch.zeros(1, device=dev)
-        launch(u_coarse, n_gauss, u_fill, goff, foff, False, ray_mask, n_missing, sel)
+        # the reference's packing depends on its own ray_mask / missing counts; should a ray disagree (a flipped
+        # texel), the slices shift -- pad so that no slice can run past the end of the recorded draws
+        if n_gauss is not None:
+            n_gauss = torch.cat([n_gauss.view(-1, max(G, 1)), torch.zeros(n_rays + 1, max(G, 1), device=dev)], 0)
+        if u_fill is not None:
+            u_fill = torch.cat([u_fill.view(-1), torch.zeros((n_rays + 1) * K, device=dev)], 0)
+        launch(u_coarse, n_gauss, u_fill, goff, foff, False, ray_mask, n_missing, sel, p_cand)
     return (z, dbg) if want_debug else z
 
 
@@ -183,7 +192,11 @@ class NeRFRendererDGS(torch.nn.Module):
             raise ValueError(f"rays batch {SB} does not match the encoded scenes {sc.SB}")
         rays = rays.detach().to(torch.float32).contiguous()
         K = self.n_samples
-        z = sample_rays(sc, rays, K, self.n_depth_candidates, self.n_gaussian, noise=noise)
+        if noise is not None and noise.get("z") is not None:
+            # parity hook: evaluate field + compositing on externally supplied (sorted) sample depths
+            z = noise["z"].detach().to(device=rays.device, dtype=torch.float32).reshape(SB * NR, K).contiguous()
+        else:
+            z = sample_rays(sc, rays, K, self.n_depth_candidates, self.n_gaussian, noise=noise)
 
         mlp = model.mlp_fine
         names = [n for n, _ in mlp.named_parameters()]

@@ -333,6 +333,18 @@ def make_scene(workload: Workload | str, seed: int = 0, latent_dtype=torch.float
     return scene
 
 
+def target_rays(scene, azimuth_deg: float, elevation_deg: float = 8.0) -> torch.Tensor:
+    """Rays (SB, tgt_H*tgt_W, 8) of a target camera on the sweep ring around the scene (one frame of the
+    reference's create_cam_sweep loop, diner.py:178-199)."""
+    wl = scene.workload
+    dist = 0.5 * (wl.near + wl.far)
+    tE = torch.stack([look_at_extrinsics(_cam_center(azimuth_deg + 2.0 * sb, elevation_deg, dist)).float()
+                      for sb in range(wl.SB)])
+    rays = gen_rays(tE, scene.target_intrinsics, wl.tgt_W, wl.tgt_H, torch.full((wl.SB,), wl.near),
+                    torch.full((wl.SB,), wl.far))
+    return rays.view(wl.SB, wl.tgt_H * wl.tgt_W, 8).contiguous()
+
+
 # ----------------------------------------------------------------------------------------
 # stock-torch field evaluation, used ONLY to calibrate the random-init density head
 # ----------------------------------------------------------------------------------------

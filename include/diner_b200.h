@@ -1,0 +1,147 @@
+/* diner_b200 -- C ABI of the B200 (sm_100a) implementation of DINER's per-ray rendering hot path.
+ *
+ * This header is the drop-in boundary below the Python plugin class `diner_b200.NeRFRendererDGS`
+ * (which itself replaces the reference's `src.models.nerf_renderer.NeRFRendererDGS`, selected by the
+ * `renderer.module` string of the reference's YAML configs, reference src/models/diner.py:48).
+ * The reference is pure Python/PyTorch, so there is no reference FFI to copy; every entry point
+ * below cites the reference Python function (file:line, relative to the reference repo) it replaces.
+ *
+ * Conventions
+ *   - plain C: raw DEVICE pointers, explicit sizes, a cudaStream_t passed as `void*`; no torch types
+ *   - every function returns 0 on success, otherwise a cudaError_t value (cudaErrorInvalidValue for
+ *     argument violations); `dnr_last_error()` returns a thread-local description
+ *   - all work is enqueued on `stream`; nothing synchronises, nothing allocates device memory
+ *   - there is no CPU implementation behind this ABI
+ *
+ * Packed operand layouts (see DESIGN.md "Data layout in HBM")
+ *   PK128 : bf16 matrix [rows x F] stored as [rows/128][F/8][128][8]  (tcgen05 canonical no-swizzle image)
+ *   PK256 : bf16 weights [N x K] stored as [N/256][K/8][256][8]
+ *   XR    : fp32 matrix [rows x N] stored as [rows/128][N/4][128] float4
+ *   view rows: the per-view MLP batch is ordered sample-major / view-minor in 32-row slabs holding
+ *   floor(32/NV) samples each (`dnr_view_row_tiles` gives the number of 128-row tiles).
+ */
+#ifndef DINER_B200_H
+#define DINER_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* dnr_stream_t; /* cudaStream_t */
+
+/* ---- library ------------------------------------------------------------------------------------------- */
+int dnr_abi_version(void);
+const char* dnr_last_error(void);
+
+/* ---- depth-guided sampler ------------------------------------------------------------------------------- */
+/* Exponentially padded depth-std map, built once per scene.  Replaces the per-call rebuild inside
+ * SpatialEncoder.index_depth_std (src/models/image_encoder.py:153-180) -> exponential_padding
+ * (src/util/torch_helpers.py:100-122).  gain_tab[e] = exp(e/12*ln2), e in [0,pad).
+ * depth_std [n_maps,H,W] -> out [n_maps,H+2*pad,W+2*pad]. */
+int dnr_pad_depth_std(const float* depth_std, const float* gain_tab, int n_maps, int H, int W, int pad, float* out,
+                      dnr_stream_t stream);
+
+/* Replaces NeRFRendererDGS.sample_coarse + sample_depthguided + fill_up_uniform_samples
+ * (src/models/nerf_renderer.py:39-63, 65-284, 367-397) incl. the three nearest taps
+ * (image_encoder.py:129-204) and weighted_mean_n_std (torch_helpers.py:294-302).
+ *   rays [SB*NR,8] = [o3,d3,near,far]; poses [SB,NV,4,4] world->cam; focal,cxy [SB,NV,2];
+ *   depth [SB,NV,H,W]; depth_std_padded [SB,NV,H+2pad,W+2pad]; normal [SB,NV,3,H,W];
+ *   lin_tab [C] = linspace(0,1-1/C,C).
+ *   Jitter: u_coarse [SB*NR,C] | NULL (-> Philox(seed)); n_gauss / u_fill: recorded draws of the reference,
+ *   either packed in the reference's order (gauss_off/fill_off [SB*NR] = exclusive prefix sums of ray_mask /
+ *   n_missing, obtained from a count_only=1 pass) or, with unpacked_noise=1, [SB*NR,G] / [SB*NR,K].
+ *   z_out [SB*NR,K] ascending.  Debug outputs (nullable): ray_mask_out, n_missing_out [SB*NR],
+ *   sel_idx_out [SB*NR,K-G] (candidate index per shortlist rank, -1 = empty), p_out [SB*NR,C] likelihood. */
+int dnr_sampler_fwd(const float* rays, const float* poses, const float* focal, const float* cxy, const float* depth,
+                    const float* depth_std_padded, const float* normal, const float* lin_tab, const float* u_coarse,
+                    const float* n_gauss, const float* u_fill, const int* gauss_off, const int* fill_off,
+                    unsigned long long seed, int SB, int NV, int NR, int H, int W, int C, int K, int G, int pad,
+                    float depth_diff_max, float img_w, float img_h, float std_sx, float std_sy, int count_only,
+                    int unpacked_noise, float* z_out, int* ray_mask_out, int* n_missing_out, int* sel_idx_out,
+                    float* p_out, dnr_stream_t stream);
+
+/* ---- projection + gather + encoding --------------------------------------------------------------------- */
+/* Per-scene repack of encoder.latent (SB*NV,C,Hl,Wl) fp32 NCHW -> (SB*NV,Hl,Wl,C) bf16 channels-last, and the
+ * inverse for the feature gradient. */
+int dnr_pack_latent_nhwc(const float* latent_nchw, int n_maps, int C, int Hl, int Wl, void* out_bf16,
+                         dnr_stream_t stream);
+int dnr_unpack_dlatent_nchw(const float* d_latent_nhwc, int n_maps, int C, int Hl, int Wl, float* out_nchw,
+                            dnr_stream_t stream);
+/* Number of 128-row tiles of the per-view MLP batch (-1 on bad NV). */
+int dnr_view_row_tiles(long long n_samples, int NV);
+
+/* Replaces PixelNeRF.forward's projection / gather / encoding (src/models/pixelnerf.py:91-128) with
+ * SpatialEncoder.index + index_depth (image_encoder.py:97-151) and PositionalEncoding.forward
+ * (positional_encoding.py:33-53).  For the chunk of n_rays rays starting at ray_offset of the (SB*NR) batch
+ * (rays/z point at the chunk's first row) it writes the MLP A operands lat_pk PK128[rows x 512] and
+ * in_pk PK128[rows x 64] (55 valid columns). */
+int dnr_encode_fwd(const float* rays, const float* z, const float* poses, const float* focal, const float* cxy,
+                   const float* depth, const void* latent_nhwc_bf16, const float* freqs, const float* phases, int SB,
+                   int NV, int NR, int K, int H, int W, int Hl, int Wl, int L, int NF, long long ray_offset,
+                   long long n_rays, float img_w, float img_h, float lat_sx, float lat_sy, void* lat_pk, void* in_pk,
+                   dnr_stream_t stream);
+/* Backward of SpatialEncoder.index w.r.t. the latent map (grid_sample bilinear backward,
+ * image_encoder.py:117-123): d_latent_nhwc [SB,NV,Hl,Wl,512] fp32 += scatter(d_lat_xr XR[rows x 512]). */
+int dnr_encode_bwd(const float* rays, const float* z, const float* poses, const float* focal, const float* cxy,
+                   const float* depth, const float* freqs, const float* phases, int SB, int NV, int NR, int K, int H,
+                   int W, int Hl, int Wl, int L, int NF, long long ray_offset, long long n_rays, float img_w,
+                   float img_h, float lat_sx, float lat_sy, const float* d_lat_xr, float* d_latent_nhwc,
+                   dnr_stream_t stream);
+
+/* ---- field MLP (ResnetFC) on tcgen05 -------------------------------------------------------------------- */
+/* nn.Linear weight (fp32 row-major [rows_w x cols_w], leading dimension ld) -> PK256 bf16 [N_pad x K_pad];
+ * transpose=1 packs W^T (dgrad operand).  Zero outside the source. */
+int dnr_pack_weight(const float* W, int rows_w, int cols_w, int ld, int transpose, int N_pad, int K_pad,
+                    void* out_pk256, dnr_stream_t stream);
+
+/* One fused linear layer of ResnetFC (src/models/resnetfc.py:61-69,129-159), forward or dgrad:
+ *   D[rows x N] = sum_{seg<3} A_seg[rows x K_seg] * B_seg[N x K_seg]^T   (bf16 in, fp32 accumulate in TMEM)
+ * epilogue: + bias[N]; * [mask_pk > 0] (ReLU backward); + res_in (XR); optional mean over the NV view rows of
+ * each sample (combine(), resnetfc.py:9-14; outputs then indexed by sample); outputs res_out (XR fp32) and/or
+ * act_out (PK128 bf16, relu_act=1 applies ReLU).  A: PK128, B: PK256, K multiple of 64, N multiple of 256.
+ * max_ctas > 0 caps the persistent grid. */
+int dnr_mlp_gemm(const void* A0, const void* B0, int K0, const void* A1, const void* B1, int K1, const void* A2,
+                 const void* B2, int K2, int m_tiles, int N, const float* bias, const void* mask_pk,
+                 const float* res_in, float* res_out, void* act_out, int relu_act, int mean_nv, long long n_samples,
+                 int max_ctas, dnr_stream_t stream);
+
+/* Weight / bias gradient of one nn.Linear (autograd of F.linear in resnetfc.py):
+ *   dW[n,k] += sum_rows dY[row,n] * X[row,k],  db[n] += sum_rows dY[row,n]
+ * dY PK128[rows x Fy], X PK128[rows x Fx]; only n < n_valid, k < k_valid are written. */
+int dnr_mlp_wgrad(const void* dY_pk, int Fy, const void* X_pk, int Fx, int row_tiles, float* dW, int ldw, int n_valid,
+                  int k_valid, float* db, dnr_stream_t stream);
+
+/* lin_out + activations: rgbsigma[s] = [sigmoid(o0..2), relu(o3)], o = lin_out(xa)
+ * (resnetfc.py:158, src/models/pixelnerf.py:137-145); xa = relu(x) PK128[rows x 512]. */
+int dnr_head_fwd(const void* xa_pk, const float* Wout, const float* bout, long long n_samples, float* rgbsigma,
+                 dnr_stream_t stream);
+/* Backward of the head: dx (XR fp32 + PK128 bf16) and d_raw as PK128[rows x 128] (columns 0..3) for wgrad. */
+int dnr_head_bwd(const void* xa_pk, const float* Wout, const float* rgbsigma, const float* d_rgbsigma,
+                 long long n_samples, float* dx_xr, void* dx_pk, void* draw_pk, dnr_stream_t stream);
+/* Backward of the view mean (resnetfc.py:9-14): d_x[(sample,view)] = d_mean[sample] / NV. */
+int dnr_mean_bwd(const float* dmean_xr, int NV, long long n_samples, int view_tiles, float* dx_xr, void* dx_pk,
+                 dnr_stream_t stream);
+
+/* Layout converters (tests, small tensors). */
+int dnr_pack_rows(const float* src, long long rows, int F, long long rows_pad, void* out_pk128, dnr_stream_t stream);
+int dnr_unpack_rows(const void* pk128, long long rows, int F, float* out, dnr_stream_t stream);
+int dnr_xr_to_rows(const float* xr, long long rows, int N, float* out, dnr_stream_t stream);
+int dnr_rows_to_xr(const float* src, long long rows, int N, long long rows_pad, float* xr, dnr_stream_t stream);
+
+/* ---- alpha compositing ----------------------------------------------------------------------------------- */
+/* Replaces the blending tail of NeRFRendererDGS.composite (src/models/nerf_renderer.py:299-301,344-365).
+ * rgbsigma [n_rays,K,4] (activated), z [n_rays,K] ascending, rays [n_rays,8] -> weights [n_rays,K] (nullable),
+ * rgb [n_rays,3], depth [n_rays]. */
+int dnr_composite_fwd(const float* rgbsigma, const float* z, const float* rays, int n_rays, int K, int white_bkgd,
+                      float* weights, float* rgb, float* depth, dnr_stream_t stream);
+/* Its backward w.r.t. rgbsigma (d_depth, d_weights nullable). */
+int dnr_composite_bwd(const float* rgbsigma, const float* z, const float* rays, const float* d_rgb,
+                      const float* d_depth, const float* d_weights, int n_rays, int K, int white_bkgd,
+                      float* d_rgbsigma, dnr_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DINER_B200_H */

@@ -201,6 +201,9 @@ def sample_depthguided(model, rays, n_samples, n_cand, n_gaussian, depth_diff_ma
         ray_mask = torch.any(p_opq != 0, dim=-1)
         mean, std = weighted_moments(z_cand[ray_mask], p_opq[ray_mask])
         g = torch.zeros(SB, NR, n_gaussian, dtype=z_cand.dtype, device=z_cand.device)
+        if noise.get("n_gauss") is None and noise.get("n_gauss_full") is not None:
+            # per-ray (unpacked) draws (SB*NR,G): packing-independent form used to compare torch backends
+            noise["n_gauss"] = noise["n_gauss_full"].view(SB, NR, n_gaussian)[ray_mask]
         if noise.get("n_gauss") is None:
             noise["n_gauss"] = torch.randn_like(g[ray_mask])
         g[ray_mask] = noise["n_gauss"] * std + mean
@@ -209,9 +212,10 @@ def sample_depthguided(model, rays, n_samples, n_cand, n_gaussian, depth_diff_ma
     return z_sel, noise, dbg
 
 
-def fill_up_uniform(z, rays, u_fill=None):
+def fill_up_uniform(z, rays, u_fill=None, u_fill_full=None):
     """nerf_renderer.py:367-397: sort, fill the zero slots (now in front) with stratified uniform samples
-    using the *sorted position* as stratum index, sort again."""
+    using the *sorted position* as stratum index, sort again.  `u_fill_full` (SB*NR,K) is the unpacked,
+    per-(ray, sorted slot) form of the draws."""
     shp = rays.shape
     z = z.sort(dim=-1).values
     z = z.view(-1, z.shape[-1])
@@ -222,6 +226,8 @@ def fill_up_uniform(z, rays, u_fill=None):
     near, far = r[iray, -2], r[iray, -1]
     step = (far - near) / n_missing
     zm = near + islot * step
+    if u_fill is None and u_fill_full is not None:
+        u_fill = u_fill_full[iray, islot]
     if u_fill is None:
         u_fill = torch.rand_like(zm)
     zm += u_fill * step

@@ -12,7 +12,7 @@ import time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
-STAGES = ["composite", "gemm", "wgrad", "sampler", "encode", "render", "grads"]
+STAGES = ["composite", "gemm", "wgrad", "sampler", "encode", "render", "fieldgrad", "grads"]
 
 
 def _stats(name, got, want, tol=None):
@@ -171,7 +171,8 @@ def stage_wgrad():
         rp = (rows + 127) // 128 * 128
         dY = torch.randn(rows, 512, device="cuda"); X = torch.randn(rows, Fx, device="cuda")
         dW = torch.zeros(512, kv, device="cuda"); db = torch.zeros(512, device="cuda")
-        _lib.call("dnr_mlp_wgrad", _lib.ptr(_pack_rows(dY, rp)), 512, _lib.ptr(_pack_rows(X, rp)), Fx, rp // 128,
+        dYp, Xp = _pack_rows(dY, rp), _pack_rows(X, rp)
+        _lib.call("dnr_mlp_wgrad", _lib.ptr(dYp), 512, _lib.ptr(Xp), Fx, rp // 128,
                   _lib.ptr(dW), kv, 512, kv, _lib.ptr(db), _lib.stream_ptr())
         torch.cuda.synchronize()
         print(f" rows={rows} Fx={Fx}")
@@ -184,39 +185,81 @@ def _golden(name):
     return load_golden(name)
 
 
+def _full_noise(g, wl, n_rays, seed=5):
+    """Unpacked per-ray draws: u_coarse from the golden file, fresh gaussian / fill draws for every ray and slot."""
+    import torch
+    gen = torch.Generator().manual_seed(seed)
+    return dict(u_coarse=torch.from_numpy(g["u_coarse"]),
+                n_gauss_full=torch.randn(n_rays, wl.n_gaussian, generator=gen),
+                u_fill_full=torch.rand(n_rays, wl.n_samples, generator=gen))
+
+
+def _oracle_sampler(model, rays, wl, noise):
+    import torch
+    from oracle import dgs_oracle as O
+    with torch.no_grad():
+        z0, _, dbg = O.sample_depthguided(model, rays, wl.n_samples, wl.n_candidates, wl.n_gaussian, noise=dict(noise))
+        z, _ = O.fill_up_uniform(z0.clone(), rays, None, noise["u_fill_full"])
+    K, G = wl.n_samples, wl.n_gaussian
+    M = K - G
+    order = dbg.order.view(-1, K)[:, :M]
+    p = dbg.p.view(-1, wl.n_candidates)
+    psel = torch.gather(p, 1, order)
+    idx = torch.where(psel > 0, order, torch.full_like(order, -1))
+    rm = dbg.ray_mask.view(-1).int()
+    nm = (z0.view(-1, K) == 0).sum(-1).int()
+    return dict(z=z.view(-1, K), p=p, idx=idx, rm=rm, nm=nm)
+
+
 def stage_sampler():
     import torch
     from diner_b200 import sample_rays
     from diner_b200.scene import get_scene
-    from oracle import dgs_oracle as O
     for name in ("tiny", "tiny3", "plumbing64"):
-        g, scene, rays, noise = _golden(name)
+        g, scene, rays, _ = _golden(name)
         wl = scene.workload
-        with torch.no_grad():
-            z0, _, dbg = O.sample_depthguided(scene.model, rays, wl.n_samples, wl.n_candidates, wl.n_gaussian, noise=dict(noise))
+        noise = _full_noise(g, wl, rays.shape[0] * rays.shape[1])
+        oc = _oracle_sampler(scene.model, rays, wl, noise)                       # torch CPU ops
         scene.model.to_device("cuda")
+        noise_d = {k: v.cuda() for k, v in noise.items()}
+        og = _oracle_sampler(scene.model, rays.cuda(), wl, noise_d)             # torch CUDA ops
         sc = get_scene(scene.model)
-        z, d = sample_rays(sc, rays.cuda(), wl.n_samples, wl.n_candidates, wl.n_gaussian,
-                           noise={k: v.cuda() for k, v in noise.items()}, want_debug=True)
+        z, d = sample_rays(sc, rays.cuda(), wl.n_samples, wl.n_candidates, wl.n_gaussian, noise=noise_d, want_debug=True)
         torch.cuda.synchronize()
-        zg = torch.from_numpy(g["z"]).view(-1, wl.n_samples)
-        zc = z.cpu()
-        exact_rays = (zc == zg).all(-1)
-        close = torch.isclose(zc, zg, rtol=1e-5, atol=1e-6).all(-1)
-        M = wl.n_samples - wl.n_gaussian
-        order = dbg.order.view(-1, wl.n_samples)[:, :M]
-        psel = torch.gather(dbg.p.view(-1, wl.n_candidates), 1, order)
-        want_idx = torch.where(psel > 0, order, torch.full_like(order, -1))
-        got_idx = d["sel_idx"].cpu().long()
-        same_set = (torch.sort(want_idx, -1).values == torch.sort(got_idx, -1).values).all(-1)
-        rm = d["ray_mask"].cpu().bool()
-        print(f" [{name}] rays={zc.shape[0]} bit-exact rays={int(exact_rays.sum())} close(1e-5) rays={int(close.sum())} "
-              f"same shortlist set={int(same_set.sum())} ray_mask agree={int((rm == dbg.ray_mask.view(-1)).sum())} "
-              f"max|dz|={float((zc - zg).abs().max()):.3e}", flush=True)
-        bad = (~same_set).nonzero().flatten()[:3]
-        for r in bad.tolist():
-            print("   mismatch ray", r, "want", sorted(want_idx[r].tolist())[-6:], "got", sorted(got_idx[r].tolist())[-6:])
-        # performance-mode smoke (Philox): sorted, in range
+        print(f" [{name}] rays={oc['z'].shape[0]}")
+        for tag, o in (("cpu-oracle", oc), ("cuda-oracle", og)):
+            zc, zo = z.cpu(), o["z"].cpu()
+            po, pg = o["p"].cpu(), d["p"].cpu()
+            exact = (zc == zo).all(-1)
+            close = torch.isclose(zc, zo, rtol=1e-5, atol=1e-6).all(-1)
+            same_idx = (d["sel_idx"].cpu().long() == o["idx"].cpu()).all(-1)
+            same_set = (torch.sort(d["sel_idx"].cpu().long(), -1).values == torch.sort(o["idx"].cpu(), -1).values).all(-1)
+            pdiff = (po != pg)
+            flips = ((po == 0) != (pg == 0))
+            rel = ((po - pg).abs() / po.abs().clamp(min=1e-30))[pdiff & ~flips]
+            print(f"   vs {tag}: z bit-exact rays={int(exact.sum())} close1e-5={int(close.sum())} idx exact(order)={int(same_idx.sum())} "
+                  f"idx same set={int(same_set.sum())} ray_mask agree={int((d['ray_mask'].cpu() == o['rm'].cpu()).sum())} "
+                  f"n_missing agree={int((d['n_missing'].cpu() == o['nm'].cpu()).sum())}")
+            print(f"      p: differing candidates={int(pdiff.sum())} of {int((po != 0).sum())} nonzero; zero/nonzero flips={int(flips.sum())} "
+                  f"max rel diff={float(rel.max()) if rel.numel() else 0:.3e} rays with p diff={int(pdiff.any(-1).sum())}", flush=True)
+            bad = (~same_idx).nonzero().flatten()[:2]
+            for r in bad.tolist():
+                print("      idx mismatch ray", r, "want", o["idx"][r].tolist()[:8], "got", d["sel_idx"][r].tolist()[:8])
+                c = pdiff[r].nonzero().flatten()[:4].tolist()
+                print("         p diffs at", c, [float(po[r, i]) for i in c], [float(pg[r, i]) for i in c])
+            badz = (~close).nonzero().flatten()[:2]
+            for r in badz.tolist():
+                dz = (zc[r] - zo[r]).abs()
+                print("      z mismatch ray", r, "n bad slots", int((dz > 1e-5).sum()), "max", float(dz.max()))
+        pdiff = (oc["p"] != og["p"].cpu())
+        print(f"   cpu-oracle vs cuda-oracle: p differing={int(pdiff.sum())} flips={int(((oc['p'] == 0) != (og['p'].cpu() == 0)).sum())} "
+              f"idx equal rays={int((oc['idx'] == og['idx'].cpu()).all(-1).sum())} "
+              f"z exact rays={int((oc['z'] == og['z'].cpu()).all(-1).sum())} z close rays={int(torch.isclose(oc['z'], og['z'].cpu(), rtol=1e-5, atol=1e-6).all(-1).sum())}")
+        # packed (reference-order) noise through the counting pass must reproduce the golden file where the masks agree
+        _, _, _, pnoise = _golden(name)
+        zg = sample_rays(sc, rays.cuda(), wl.n_samples, wl.n_candidates, wl.n_gaussian, noise={k: v.cuda() for k, v in pnoise.items()})
+        gz = torch.from_numpy(g["z"]).view(-1, wl.n_samples)
+        print(f"   packed noise vs golden: z bit-exact rays={int((zg.cpu() == gz).all(-1).sum())} close={int(torch.isclose(zg.cpu(), gz, rtol=1e-5, atol=1e-6).all(-1).sum())}")
         zp = sample_rays(sc, rays.cuda(), wl.n_samples, wl.n_candidates, wl.n_gaussian, seed=1)
         ok = bool((zp[:, 1:] >= zp[:, :-1]).all())
         print(f"   philox mode: sorted={ok} min={float(zp.min()):.3f} max={float(zp.max()):.3f}")
@@ -268,11 +311,57 @@ def stage_render():
         scene.model.to_device("cuda")
         r = NeRFRendererDGS(wl.n_samples, wl.n_candidates, wl.n_gaussian, white_bkgd=wl.white_bkgd)
         with torch.no_grad():
-            out = r(scene.model, rays.cuda(), want_weights=True, noise={k: v.cuda() for k, v in noise.items()})
+            out = r(scene.model, rays.cuda(), want_weights=True, noise=dict(z=torch.from_numpy(g["z"])))
         torch.cuda.synchronize()
         print(f" [{name}]")
         _stats("rgb", out.fine.rgb, torch.from_numpy(g["rgb"])); _stats("depth", out.fine.depth, torch.from_numpy(g["depth"]))
         _stats("weights", out.fine.weights, torch.from_numpy(g["weights"]))
+
+
+def stage_fieldgrad():
+    """MLP + gather backward in isolation: unit-scale random d(rgbsigma), compared with autograd through the oracle."""
+    import torch
+    from diner_b200.renderer import _FieldFn
+    from diner_b200.scene import get_scene
+    from oracle import dgs_oracle as O
+    for name in ("tiny", "tiny3"):
+        g, scene, rays, _ = _golden(name)
+        wl = scene.workload
+        K, SB = wl.n_samples, wl.SB
+        NR = rays.shape[1]
+        z = torch.from_numpy(g["z"])
+        m = scene.model
+        gen = torch.Generator().manual_seed(3)
+        d_out = torch.randn(SB * NR * K, 4, generator=gen)
+        if os.environ.get("DIAG_RGB_ONLY") == "1":
+            d_out[:, 3] = 0      # no gradient through the (ill-conditioned) relu(sigma) channel
+        lat = m.encoder.latent.detach().clone().requires_grad_(True)
+        m.encoder.latent = lat
+        pts = (rays[..., None, :3] + z.unsqueeze(-1) * rays[..., None, 3:6]).reshape(SB, NR * K, 3)
+        dirs = rays[..., None, 3:6].expand(-1, -1, K, -1).reshape(SB, NR * K, 3)
+        want = O.field(m, pts, dirs).reshape(-1, 4)
+        (want * d_out).sum().backward()
+        ref = {k: v.grad.clone() for k, v in m.mlp_fine.named_parameters()}
+        ref_lat = lat.grad.clone()
+        for v in m.mlp_fine.parameters():
+            v.grad = None
+        m.encoder.latent = lat.detach()
+        m.to_device("cuda")
+        m.encoder.latent = m.encoder.latent.detach().requires_grad_(True)
+        sc = get_scene(m)
+        mlp = m.mlp_fine
+        names = [n for n, _ in mlp.named_parameters()]
+        params = [q for _, q in mlp.named_parameters()]
+        out = _FieldFn.apply(sc, mlp, names, rays.view(-1, 8).cuda(), z.view(-1, K).cuda(), NR, 0, m.encoder.latent, *params)
+        (out * d_out.cuda()).sum().backward()
+        torch.cuda.synchronize()
+        print(f" [{name}]")
+        _stats("out", out, want)
+        for k, v in mlp.named_parameters():
+            e = (v.grad.cpu() - ref[k]).double().norm().item() / max(ref[k].double().norm().item(), 1e-30)
+            print(f"  d {k}: rel_l2_err={e:.3e} |want|={ref[k].double().norm().item():.3e}")
+        gl = m.encoder.latent.grad.cpu()
+        print(f"  d latent: rel_l2_err={(gl - ref_lat).double().norm().item() / ref_lat.double().norm().item():.3e} |want|={ref_lat.double().norm().item():.3e}")
 
 
 def stage_grads():
@@ -285,7 +374,7 @@ def stage_grads():
         m.to_device("cuda")
         m.encoder.latent = m.encoder.latent.detach().requires_grad_(True)
         r = NeRFRendererDGS(wl.n_samples, wl.n_candidates, wl.n_gaussian, white_bkgd=wl.white_bkgd)
-        out = r(m, rays.cuda(), noise={k: v.cuda() for k, v in noise.items()})
+        out = r(m, rays.cuda(), noise=dict(z=torch.from_numpy(g["z"])))
         gen = torch.Generator().manual_seed(11)
         w_rgb = torch.randn(out.fine.rgb.shape, generator=gen).cuda()
         w_dep = torch.randn(out.fine.depth.shape, generator=gen).cuda()
