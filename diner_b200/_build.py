@@ -18,6 +18,7 @@ SOURCES = [
     ("sampler.cu", ["--fmad=false"]),
     ("encode.cu", []),
     ("gemm.cu", []),
+    ("mlp_fused.cu", []),
     ("wgrad.cu", []),
     ("mlp_misc.cu", []),
 ]

@@ -31,11 +31,15 @@ constexpr int kHid = 512;
 __global__ void __launch_bounds__(128) head_fwd_kernel(const unsigned char* __restrict__ xa_pk,
                                                        const float* __restrict__ Wout,  // [4,512]
                                                        const float* __restrict__ bout,  // [4]
-                                                       long long n_samples, float4* __restrict__ out) {
+                                                       long long n_samples, int samples_per_tile,
+                                                       float4* __restrict__ out) {
   __shared__ float sw[4 * kHid];
   for (int i = threadIdx.x; i < 4 * kHid; i += blockDim.x) sw[i] = Wout[i];
   __syncthreads();
-  const long long row = (long long)blockIdx.x * 128 + threadIdx.x;
+  // tiles hold samples_per_tile (<= 128) samples each: 128 for the per-layer path, 4*NV*floor(32/NV) for the
+  // fused kernel's pooled tiles
+  const long long row = (int)threadIdx.x < samples_per_tile ? (long long)blockIdx.x * samples_per_tile + threadIdx.x
+                                                            : n_samples;
   const unsigned char* base = xa_pk + (size_t)blockIdx.x * (kHid / 8) * 2048 + (size_t)threadIdx.x * 16;
   float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
 #pragma unroll 4
@@ -185,10 +189,12 @@ DNR_EXPORT int dnr_pack_weight(const float* W, int rows_w, int cols_w, int ld, i
 
 // lin_out + sigmoid/relu (resnetfc.py:158, pixelnerf.py:137-145).
 DNR_EXPORT int dnr_head_fwd(const void* xa_pk, const float* Wout, const float* bout, long long n_samples,
-                            float* rgbsigma, cudaStream_t stream) {
+                            int samples_per_tile, float* rgbsigma, cudaStream_t stream) {
+  DNR_REQUIRE(samples_per_tile >= 1 && samples_per_tile <= 128, "dnr_head_fwd: samples_per_tile must be in [1,128]");
   if (n_samples <= 0) return 0;
-  const int tiles = (int)((n_samples + 127) / 128);
-  dnr::head_fwd_kernel<<<tiles, 128, 0, stream>>>((const unsigned char*)xa_pk, Wout, bout, n_samples, (float4*)rgbsigma);
+  const int tiles = (int)((n_samples + samples_per_tile - 1) / samples_per_tile);
+  dnr::head_fwd_kernel<<<tiles, 128, 0, stream>>>((const unsigned char*)xa_pk, Wout, bout, n_samples, samples_per_tile,
+                                                  (float4*)rgbsigma);
   DNR_CHECK_LAUNCH("dnr_head_fwd");
   return 0;
 }

@@ -23,6 +23,7 @@ from .scene import SceneBuffers
 
 HID = 512
 IN_PAD = 64
+USE_FUSED_FORWARD = True     # tests flip this to compare the fused kernel with the per-layer path
 
 
 def _mlp_signature(mlp):
@@ -60,6 +61,12 @@ class PackedMLP:
                     for b in range(len(mlp.blocks))]
         self.w_out = f(mlp.lin_out.weight)
         self.b_out = f(mlp.lin_out.bias)
+        # host arrays of device pointers for the fused forward kernel (dnr_mlp_fused_fwd)
+        import ctypes as C
+        ws = [self.w_in, *self.w_z, *self.w_0, *self.w_1]
+        bs = [self.b_first, *self.b_0, *self.b_1]
+        self.w_ptrs = (C.c_void_p * len(ws))(*[t.data_ptr() for t in ws])
+        self.b_ptrs = (C.c_void_p * len(bs))(*[t.data_ptr() for t in bs])
         if need_transposed:
             self.wt_z = [pack(l.weight, True) for l in mlp.lin_z]
             self.wt_0 = [pack(b.fc_0.weight, True) for b in mlp.blocks]
@@ -77,6 +84,18 @@ def get_packed(mlp, need_transposed: bool) -> PackedMLP:
     _packed_cache.clear()
     _packed_cache[id(mlp)] = pk
     return pk
+
+
+_scratch: dict = {}
+
+
+def _fused_scratch(dev) -> torch.Tensor:
+    """Per-CTA activation scratch of the fused forward kernel (1 MB per SM; re-used by every tile, L2-resident)."""
+    k = str(dev)
+    if k not in _scratch:
+        n = _lib.load().dnr_mlp_fused_scratch_bytes(0)
+        _scratch[k] = torch.zeros(n, device=dev, dtype=torch.uint8)
+    return _scratch[k]
 
 
 def _gemm(A0, B0, K0, m_tiles, N=HID, A1=None, B1=None, K1=0, A2=None, B2=None, K2=0, bias=None, mask=None,
@@ -126,6 +145,16 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
     _lib.call("dnr_encode_fwd", p(rays), p(z), p(sc.poses), p(sc.focal), p(sc.cxy), p(sc.depth), p(sc.latent_nhwc),
               p(sc.freqs), p(sc.phases), *_encode_args(sc, NR, K, ray0, n), p(lat), p(code), st)
 
+    if not save and USE_FUSED_FORWARD:
+        # inference: the whole ResnetFC in one persistent kernel, activations stay in L2 (csrc/mlp_fused.cu)
+        S = 4 * NV * (32 // NV)
+        groups = (mv + NV - 1) // NV
+        xa = torch.empty(groups * 128 * HID, **bf)
+        _lib.call("dnr_mlp_fused_fwd", p(lat), p(code), pk.w_ptrs, pk.b_ptrs, NV, mv, n_samples,
+                  p(_fused_scratch(dev)), p(xa), 0, st)
+        out = torch.empty(n_samples, 4, **f32)
+        _lib.call("dnr_head_fwd", p(xa), p(pk.w_out), p(pk.b_out), n_samples, S, p(out), st)
+        return out, None
     sv = FieldSaved(n_samples=n_samples, mv=mv, ms=ms, lat=lat, code=code) if save else None
     x = torch.empty(mv * 128 * HID, **f32)                      # residual stream, XR layout (updated in place)
     new_act = lambda tiles: torch.empty(tiles * 128 * HID, **bf)
@@ -169,7 +198,7 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
         if save and b == 3:
             net = new_act(ms)
     out = torch.empty(n_samples, 4, **f32)
-    _lib.call("dnr_head_fwd", p(xa), p(pk.w_out), p(pk.b_out), n_samples, p(out), st)
+    _lib.call("dnr_head_fwd", p(xa), p(pk.w_out), p(pk.b_out), n_samples, 128, p(out), st)
     if save:
         sv.xa.append(xa)
         sv.out = out

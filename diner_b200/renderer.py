@@ -205,11 +205,15 @@ class NeRFRendererDGS(torch.nn.Module):
         flat = rays.view(SB * NR, 8)
         n_rays = SB * NR
         per_chunk = max(1, self.rows_per_chunk // (K * sc.NV))
+        track = torch.is_grad_enabled() and (latent.requires_grad or any(q.requires_grad for q in params))
         rgbs, depths, weights = [], [], []
         for r0 in range(0, n_rays, per_chunk):
             r1 = min(n_rays, r0 + per_chunk)
             rc, zc = flat[r0:r1], z[r0:r1]
-            rgbsigma = _FieldFn.apply(sc, mlp, names, rc, zc, NR, r0, latent, *params)
+            if track:
+                rgbsigma = _FieldFn.apply(sc, mlp, names, rc, zc, NR, r0, latent, *params)
+            else:       # inference: nothing is saved, the MLP runs as one persistent kernel
+                rgbsigma, _ = F_.field_forward(sc, F_.get_packed(mlp, need_transposed=False), rc, zc, NR, r0, save=False)
             rgb, depth, w = _CompositeFn.apply(rgbsigma, zc, rc, self.white_bkgd)
             rgbs.append(rgb); depths.append(depth); weights.append(w)
         cat = (lambda xs: xs[0] if len(xs) == 1 else torch.cat(xs, 0))

@@ -107,6 +107,18 @@ int dnr_mlp_gemm(const void* A0, const void* B0, int K0, const void* A1, const v
                  const float* res_in, float* res_out, void* act_out, int relu_act, int mean_nv, long long n_samples,
                  int max_ctas, dnr_stream_t stream);
 
+/* Whole ResnetFC forward in ONE persistent kernel (inference): all 13 linear layers of resnetfc.py:129-159 with
+ * the view mean (combine(), :9-14) fused, activations kept in an L2-resident per-CTA scratch instead of HBM.
+ * Inputs are the operands written by dnr_encode_fwd (mv_tiles view-row tiles).  weights = 14 PK256 pointers
+ * [lin_in, lin_z0..2, fc_0 of blocks 0..4, fc_1 of blocks 0..4]; biases = 11 fp32[512] pointers
+ * [lin_in+lin_z0, fc_0 x5, fc_1 (+lin_z[b+1]) x5] (host arrays of device pointers).  xa_out: PK128
+ * [ceil(mv_tiles/NV)*128 x 512] = relu(x) after the last block, pooled tile g holding samples
+ * [g*S, (g+1)*S), S = 4*NV*floor(32/NV) -> dnr_head_fwd(..., samples_per_tile = S). */
+long long dnr_mlp_fused_scratch_bytes(int max_ctas);
+int dnr_mlp_fused_fwd(const void* lat_pk, const void* code_pk, const void* const* weights, const float* const* biases,
+                      int NV, int mv_tiles, long long n_samples, void* scratch, void* xa_out, int max_ctas,
+                      dnr_stream_t stream);
+
 /* Weight / bias gradient of one nn.Linear (autograd of F.linear in resnetfc.py):
  *   dW[n,k] += sum_rows dY[row,n] * X[row,k],  db[n] += sum_rows dY[row,n]
  * dY PK128[rows x Fy], X PK128[rows x Fx]; only n < n_valid, k < k_valid are written. */
@@ -114,9 +126,10 @@ int dnr_mlp_wgrad(const void* dY_pk, int Fy, const void* X_pk, int Fx, int row_t
                   int k_valid, float* db, dnr_stream_t stream);
 
 /* lin_out + activations: rgbsigma[s] = [sigmoid(o0..2), relu(o3)], o = lin_out(xa)
- * (resnetfc.py:158, src/models/pixelnerf.py:137-145); xa = relu(x) PK128[rows x 512]. */
-int dnr_head_fwd(const void* xa_pk, const float* Wout, const float* bout, long long n_samples, float* rgbsigma,
-                 dnr_stream_t stream);
+ * (resnetfc.py:158, src/models/pixelnerf.py:137-145); xa = relu(x) PK128[tiles*128 x 512], tile t holding samples
+ * [t*samples_per_tile, (t+1)*samples_per_tile) in its first rows (128 for the per-layer path). */
+int dnr_head_fwd(const void* xa_pk, const float* Wout, const float* bout, long long n_samples, int samples_per_tile,
+                 float* rgbsigma, dnr_stream_t stream);
 /* Backward of the head: dx (XR fp32 + PK128 bf16) and d_raw as PK128[rows x 128] (columns 0..3) for wgrad. */
 int dnr_head_bwd(const void* xa_pk, const float* Wout, const float* rgbsigma, const float* d_rgbsigma,
                  long long n_samples, float* dx_xr, void* dx_pk, void* draw_pk, dnr_stream_t stream);
