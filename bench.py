@@ -140,7 +140,7 @@ def run_reference(args, rank, world):
     line = dict(impl="reference", metric="render_rays_per_s", value=value, unit="rays/s", n_gpus=args.gpus,
                 steps=len(rates), warmup=args.warmup, ms_per_step=1e3 * chunk / value, higher_is_better=True,
                 scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
-                config=dict(workload=args.workload, rays_per_step=chunk, samples_per_ray=wl.n_samples, n_views=wl.NV,
+                config=dict(workload=args.workload + "_eval", rays_per_step=chunk, samples_per_ray=wl.n_samples, n_views=wl.NV,
                             note="bounded sample: one 4096-ray chunk of the frame per step"),
                 msamples_per_s=value * wl.n_samples / 1e6,
                 cpu_baseline=dict(value=value, unit="rays/s", cores=threads, kind="port",

@@ -19,6 +19,7 @@ SOURCES = [
     ("encode.cu", []),
     ("gemm.cu", []),
     ("mlp_fused.cu", []),
+    ("mlp_pair.cu", []),
     ("wgrad.cu", []),
     ("mlp_misc.cu", []),
 ]

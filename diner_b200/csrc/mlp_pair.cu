@@ -1,0 +1,475 @@
+// ResnetFC field MLP, inference, fully on-chip: a CLUSTER OF TWO CTAs walks one 128-row view tile through all
+// layers (reference resnetfc.py:129-159, combine() :9-14, head pixelnerf.py:137-145).
+//
+// CTA r of the pair owns output columns [256 r, 256 r + 256) of every layer:
+//   TMEM   (512 cols)  X = fp32 residual stream of its 256 columns (fc_1 / lin_z accumulate straight into it, so the
+//                      residual add costs nothing and never leaves the SM) + T = fc_0 accumulator
+//   smem   128 KB      the full-K bf16 A operand (relu(x) or relu(net)) in the tcgen05 canonical layout: its own
+//                      256 columns are written by its epilogue warps, the peer's 256 columns arrive as ONE 64 KB
+//                      cp.async.bulk from a small L2-resident exchange buffer (DSMEM stores are ~20 B/clk - too slow)
+//          3 x 32 KB   ring for the streamed operands: weight K-blocks of its 256 output rows, and the
+//                      gathered-feature / code K-blocks for lin_in / lin_z
+// so per layer a CTA moves 256 KB of weights + 64 KB out + 64 KB in through L2 instead of ~1.1 MB, and nothing of
+// the layer chain depends on HBM.  lin_z[b](lat) K-steps are issued FIRST in their layer: they do not depend on the
+// previous epilogue and hide it.  After the view mean every row carries its sample's mean, i.e. blocks 3-4 run on
+// NV duplicates (+18 % MMA work at NV=2) - the price of keeping the tile on chip.
+//
+//   warp 0 : ring producer            warp 1 : tcgen05.mma issuer       warp 2 : peer-half loader
+//   warps 4..11 : epilogue (two per TMEM lane quadrant, 128 columns each)
+#include "common.cuh"
+#include "tc05.cuh"
+#include <stdlib.h>
+
+namespace dnr {
+
+constexpr int kPThreads = 384;
+constexpr int kPRing = 3;
+constexpr int kPSlot = 32768;
+constexpr int kPAbuf = 131072;
+constexpr int kPHeadScratch = 2048;
+constexpr size_t kPSmem = (size_t)kPAbuf + kPRing * kPSlot + kPHeadScratch + 256;
+constexpr int kPOps = 11;
+constexpr size_t kXchPerCluster = 2 * 2 * 65536;     // [slot][rank][64 KB]
+
+struct PairParams {
+  const unsigned char* lat_pk;    // PK128 [mv_tiles x 512]
+  const unsigned char* code_pk;   // PK128 [mv_tiles x 64]
+  const unsigned char* w_in;      // PK256 [512 x 64]
+  const unsigned char* w_z[3];
+  const unsigned char* w_0[5];
+  const unsigned char* w_1[5];
+  const float* cb[6];             // cumulative residual-stream biases: after lin_in+z0, block 0, 1, 2 | block 3, 4
+  const float* b_0[5];
+  const float* w_out;             // fp32 [4 x 512]
+  unsigned char* xch;             // n_clusters * kXchPerCluster
+  float4* head_partial;           // [mv_tiles][2][128]: partial lin_out sums of each CTA's 256 columns
+  int NV, SPW, mv_tiles;
+  long long* prof;                // optional [gridDim][8] cycle counters (debug)
+  int flags;                      // bit 0: every epilogue thread issues its own gpu-scope fence (default: leader only)
+};
+
+enum { EPI_X = 0, EPI_T = 1, EPI_MEAN = 2, EPI_HEAD = 3 };
+
+struct POp {
+  const unsigned char* lat_w;     // lin_z weights (A = streamed lat) or null
+  const unsigned char* abuf_w;    // weights applied to the resident A operand or null
+  const float* bias;
+  int code;                       // lin_in K-step (op 0)
+  int acc_x;                      // accumulator: X (1) or T (0)
+  int fresh;                      // first MMA overwrites
+  int epi;
+};
+
+__device__ __forceinline__ void pair_get_op(const PairParams& P, int o, POp& d) {
+  d.lat_w = nullptr; d.abuf_w = nullptr; d.code = 0; d.acc_x = 1; d.fresh = 0; d.epi = EPI_X;
+  if (o == 0) { d.code = 1; d.lat_w = P.w_z[0]; d.fresh = 1; d.bias = P.cb[0]; return; }
+  const int b = (o - 1) >> 1;
+  if (o & 1) {                      // fc_0 of block b
+    d.abuf_w = P.w_0[b]; d.acc_x = 0; d.fresh = 1; d.epi = EPI_T; d.bias = P.b_0[b];
+  } else {                          // fc_1 of block b (+ lin_z[b+1])
+    d.abuf_w = P.w_1[b];
+    if (b < 2) d.lat_w = P.w_z[b + 1];
+    d.bias = P.cb[b + 1];
+    d.epi = b == 4 ? EPI_HEAD : EPI_X;
+  }
+}
+
+// K-block order of the resident-operand GEMMs: own K-blocks first, in the order the epilogue finishes them
+// ({0,2} after its first 64-column stage, {1,3} after the second), then the peer's four.
+__device__ __forceinline__ int pair_kb_order(int rank, int i) {
+  if (i < 4) return 4 * rank + ((i & 1) << 1) + (i >> 1);      // 0, 2, 1, 3
+  return 4 * (rank ^ 1) + (((i - 4) & 1) << 1) + ((i - 4) >> 1);
+}
+
+__device__ __forceinline__ void bar_sync_epi() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+
+// mean over the NV view rows of a sample (adjacent lanes of the warp; RowMap)
+template <int NV>
+__device__ __forceinline__ float view_mean(float v, int lane) {
+  if (NV == 1) return v;
+  if (NV == 2) return (v + __shfl_xor_sync(0xffffffffu, v, 1)) * 0.5f;
+  if (NV == 4) {
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    return v * 0.25f;
+  }
+  const int l0 = lane - lane % NV;
+  float s = __shfl_sync(0xffffffffu, v, l0);
+#pragma unroll
+  for (int dd = 1; dd < NV; ++dd) s += __shfl_sync(0xffffffffu, v, min(l0 + dd, 31));
+  return s / (float)NV;
+}
+
+// one 64-column stage of an activation epilogue: (+bias, [view mean], relu, bf16) -> resident A buffer + exchange buffer
+template <int NV, bool POOLED>
+__device__ __forceinline__ void pair_act_stage(const uint32_t (&acc)[64], const float* __restrict__ bias, int lane,
+                                               unsigned char* dst_s) {
+#pragma unroll
+  for (int g = 0; g < 8; ++g) {
+    const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + g * 8));
+    const float4 b1 = __ldg(reinterpret_cast<const float4*>(bias + g * 8 + 4));
+    float v[8] = {__uint_as_float(acc[g * 8 + 0]) + b0.x, __uint_as_float(acc[g * 8 + 1]) + b0.y,
+                  __uint_as_float(acc[g * 8 + 2]) + b0.z, __uint_as_float(acc[g * 8 + 3]) + b0.w,
+                  __uint_as_float(acc[g * 8 + 4]) + b1.x, __uint_as_float(acc[g * 8 + 5]) + b1.y,
+                  __uint_as_float(acc[g * 8 + 6]) + b1.z, __uint_as_float(acc[g * 8 + 7]) + b1.w};
+    if (POOLED) {
+      // x (pooled) = mean over the view rows.  The per-view rows keep accumulating the (identical) block-3/4
+      // updates in TMEM, so the mean is re-taken whenever the stream is read (resnetfc.py:9-14,148-151).
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = view_mean<NV>(v[j], lane);
+    }
+    const uint32_t w0 = pack_bf16x2(fmaxf(v[0], 0.f), fmaxf(v[1], 0.f)), w1 = pack_bf16x2(fmaxf(v[2], 0.f), fmaxf(v[3], 0.f));
+    const uint32_t w2 = pack_bf16x2(fmaxf(v[4], 0.f), fmaxf(v[5], 0.f)), w3 = pack_bf16x2(fmaxf(v[6], 0.f), fmaxf(v[7], 0.f));
+    *reinterpret_cast<uint4*>(dst_s + (size_t)g * 2048) = make_uint4(w0, w1, w2, w3);
+  }
+}
+
+// one 64-column stage of the head: partial lin_out sums on the bf16-rounded relu(mean x) (contract of dnr_head_fwd)
+template <int NV>
+__device__ __forceinline__ void pair_head_stage(const uint32_t (&acc)[64], const float* __restrict__ bias,
+                                                const float* __restrict__ wo, int lane, float& h0, float& h1, float& h2,
+                                                float& h3) {
+#pragma unroll
+  for (int q = 0; q < 16; ++q) {
+    const float4 b = __ldg(reinterpret_cast<const float4*>(bias + q * 4));
+    float v[4] = {__uint_as_float(acc[q * 4 + 0]) + b.x, __uint_as_float(acc[q * 4 + 1]) + b.y,
+                  __uint_as_float(acc[q * 4 + 2]) + b.z, __uint_as_float(acc[q * 4 + 3]) + b.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = __bfloat162float(__float2bfloat16_rn(fmaxf(view_mean<NV>(v[j], lane), 0.f)));
+    const float4 w0 = __ldg(reinterpret_cast<const float4*>(wo + q * 4));
+    const float4 w1 = __ldg(reinterpret_cast<const float4*>(wo + 512 + q * 4));
+    const float4 w2 = __ldg(reinterpret_cast<const float4*>(wo + 1024 + q * 4));
+    const float4 w3 = __ldg(reinterpret_cast<const float4*>(wo + 1536 + q * 4));
+    h0 = fmaf(v[0], w0.x, fmaf(v[1], w0.y, fmaf(v[2], w0.z, fmaf(v[3], w0.w, h0))));
+    h1 = fmaf(v[0], w1.x, fmaf(v[1], w1.y, fmaf(v[2], w1.z, fmaf(v[3], w1.w, h1))));
+    h2 = fmaf(v[0], w2.x, fmaf(v[1], w2.y, fmaf(v[2], w2.z, fmaf(v[3], w2.w, h2))));
+    h3 = fmaf(v[0], w3.x, fmaf(v[1], w3.y, fmaf(v[2], w3.z, fmaf(v[3], w3.w, h3))));
+  }
+}
+
+template <int NV>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pair_fwd_kernel(const PairParams P) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  unsigned char* abuf = smem;                                   // 128 KB resident A operand
+  unsigned char* ring = smem + kPAbuf;                          // 3 x 32 KB
+  float* head_s = reinterpret_cast<float*>(ring + kPRing * kPSlot);      // [128][4]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ring + kPRing * kPSlot + kPHeadScratch);
+  uint64_t* full = bars;                  // [3]  ring slot landed
+  uint64_t* empty = bars + 3;             // [3]  ring slot consumed
+  uint64_t* accf = bars + 6;              // [2]  accumulator of op (parity) complete
+  uint64_t* a_own = bars + 8;             // [2]  own K-blocks {0,2} / {1,3} of the A operand written (256 epilogue threads)
+  uint64_t* a_peer = bars + 10;           // [2]  peer K-blocks {0,2} / {1,3} landed (bulk copies)
+  uint64_t* peer_rdy = bars + 12;         // [2 stages][2 slots]  peer's stage is in the exchange buffer (remote arrive)
+  uint64_t* pushed = bars + 16;           // [1]  pusher finished reading my half of the A buffer (bulk stores done)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = tc::cluster_ctarank();
+  const uint32_t peer = rank ^ 1u;
+  const int cluster = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+  unsigned char* xch = P.xch + (size_t)cluster * kXchPerCluster;
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < kPRing; ++s) { tc::mbar_init(full + s, 1); tc::mbar_init(empty + s, 1); }
+    tc::mbar_init(accf + 0, 1); tc::mbar_init(accf + 1, 1);
+    tc::mbar_init(a_own + 0, 8); tc::mbar_init(a_own + 1, 8); tc::mbar_init(a_peer + 0, 1); tc::mbar_init(a_peer + 1, 1);
+    for (int i = 0; i < 4; ++i) tc::mbar_init(peer_rdy + i, 1);
+    tc::mbar_init(pushed, 1);
+    tc::fence_barrier_init();
+  }
+  if (warp == 1) tc::tmem_alloc(tmem_slot, 512);
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::cluster_sync_all();               // the peer's barriers exist before anyone arrives on them remotely
+  tc::fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================= ring producer =================
+    if (lane == 0) {
+      const uint64_t pol_keep = tc::policy_evict_last(), pol_stream = tc::policy_evict_first();
+      const uint64_t pol_norm = tc::policy_evict_normal();
+      int slot = 0; uint32_t phase = 0;
+      auto fill = [&](const unsigned char* src, uint32_t bytes, uint64_t pol) {
+        tc::mbar_wait(empty + slot, phase ^ 1);
+        tc::mbar_arrive_expect_tx(full + slot, bytes);
+        tc::bulk_g2s_hint(ring + (size_t)slot * kPSlot, src, bytes, full + slot, pol);
+        if (++slot == kPRing) { slot = 0; phase ^= 1; }
+      };
+      POp d;
+      for (int tile = cluster; tile < P.mv_tiles; tile += n_clusters) {
+        const unsigned char* lat = P.lat_pk + (size_t)tile * 131072;
+        if (tile + n_clusters < P.mv_tiles) {     // pull the next tile's inputs from HBM into L2 while this one computes
+          tc::bulk_prefetch_l2(P.lat_pk + (size_t)(tile + n_clusters) * 131072, 131072);
+          tc::bulk_prefetch_l2(P.code_pk + (size_t)(tile + n_clusters) * 16384, 16384);
+        }
+        for (int o = 0; o < kPOps; ++o) {
+          pair_get_op(P, o, d);
+          if (d.code) {
+            fill(P.code_pk + (size_t)tile * 16384, 16384, pol_stream);
+            fill(P.w_in + (size_t)rank * 32768, 32768, pol_keep);
+          }
+          if (d.lat_w) {
+            for (int kb = 0; kb < 8; ++kb) {
+              fill(lat + (size_t)kb * 16384, 16384, o == 4 ? pol_stream : pol_norm);   // last use: evict first
+              fill(d.lat_w + (size_t)rank * 262144 + (size_t)kb * 32768, 32768, pol_keep);
+            }
+          }
+          if (d.abuf_w) {
+            for (int i = 0; i < 8; ++i) {
+              const int kb = pair_kb_order((int)rank, i);
+              fill(d.abuf_w + (size_t)rank * 262144 + (size_t)kb * 32768, 32768, pol_keep);
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    if (lane == 0) {
+      constexpr uint32_t idesc = tc::make_idesc_bf16(128, 256, 0, 0);
+      int slot = 0; uint32_t phase = 0;
+      int opc = 0;                           // ops issued (all kinds)
+      int aops = 0;                          // ops that read the resident A operand
+      int titer = 0;
+      POp d;
+      const uint32_t abuf0 = tc::smem_u32(abuf);
+      long long w_ring = 0, w_own = 0, w_peer = 0, t_start = clock64();
+#define TIMED(acc, stmt) { long long t__ = clock64(); stmt; acc += clock64() - t__; }
+      for (int tile = cluster; tile < P.mv_tiles; tile += n_clusters, ++titer) {
+        const uint32_t x_col = (titer & 1) ? 256u : 0u;           // X / T swap regions every tile
+        for (int o = 0; o < kPOps; ++o, ++opc) {
+          pair_get_op(P, o, d);
+          const uint32_t d_tmem = tmem_base + (d.acc_x ? x_col : (256u - x_col));
+          uint32_t accumulate = d.fresh ? 0u : 1u;
+          auto step_ring_ab = [&]() {        // A and B both come from consecutive ring slots
+            TIMED(w_ring, tc::mbar_wait(full + slot, phase));
+            const int sa = slot;
+            if (++slot == kPRing) { slot = 0; phase ^= 1; }
+            TIMED(w_ring, tc::mbar_wait(full + slot, phase));
+            const int sb = slot;
+            if (++slot == kPRing) { slot = 0; phase ^= 1; }
+            tc::fence_after_sync();
+            const uint32_t a0 = tc::smem_u32(ring + (size_t)sa * kPSlot), b0 = tc::smem_u32(ring + (size_t)sb * kPSlot);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              tc::mma_bf16(d_tmem, tc::make_smem_desc(a0 + j * 4096, 2048, 128), tc::make_smem_desc(b0 + j * 8192, 4096, 128),
+                           idesc, accumulate);
+              accumulate = 1;
+            }
+            tc::mma_commit(empty + sa);
+            tc::mma_commit(empty + sb);
+          };
+          if (d.code) step_ring_ab();
+          if (d.lat_w)
+            for (int kb = 0; kb < 8; ++kb) step_ring_ab();
+          if (d.abuf_w) {
+            const uint32_t par = (uint32_t)((aops) & 1);
+            for (int i = 0; i < 8; ++i) {
+              const int kb = pair_kb_order((int)rank, i);
+              if (i == 0) TIMED(w_own, tc::mbar_wait(a_own + 0, par));
+              if (i == 2) TIMED(w_own, tc::mbar_wait(a_own + 1, par));
+              if (i == 4) TIMED(w_peer, tc::mbar_wait(a_peer + 0, par));
+              if (i == 6) TIMED(w_peer, tc::mbar_wait(a_peer + 1, par));
+              TIMED(w_ring, tc::mbar_wait(full + slot, phase));
+              tc::fence_after_sync();
+              const uint32_t a0 = abuf0 + (uint32_t)kb * 16384u, b0 = tc::smem_u32(ring + (size_t)slot * kPSlot);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                tc::mma_bf16(d_tmem, tc::make_smem_desc(a0 + j * 4096, 2048, 128),
+                             tc::make_smem_desc(b0 + j * 8192, 4096, 128), idesc, accumulate);
+                accumulate = 1;
+              }
+              tc::mma_commit(empty + slot);
+              if (++slot == kPRing) { slot = 0; phase ^= 1; }
+            }
+            ++aops;
+          }
+          tc::mma_commit(accf + (opc & 1));
+        }
+      }
+      if (P.prof) {
+        long long* pr = P.prof + (size_t)blockIdx.x * 16;
+        pr[0] = clock64() - t_start; pr[1] = w_ring; pr[2] = w_own; pr[3] = w_peer;
+      }
+    }
+  } else if (warp == 2) {
+    // ================= pusher: my finished K-blocks -> exchange buffer (TMA store), then tell the peer =================
+    if (lane == 0) {
+      const uint64_t pol_keep = tc::policy_evict_last();
+      int xops = 0;
+      for (int tile = cluster; tile < P.mv_tiles; tile += n_clusters) {
+        for (int o = 0; o < kPOps - 1; ++o, ++xops) {          // every op but the head produces an A operand
+          unsigned char* mine = xch + ((size_t)(xops & 1) * 2 + rank) * 65536;
+          for (int st = 0; st < 2; ++st) {
+            tc::mbar_wait(a_own + st, (uint32_t)(xops & 1));     // all epilogue warps wrote (and proxy-fenced) this stage
+            tc::bulk_s2g_hint(mine + (size_t)st * 16384, abuf + (size_t)rank * 65536 + (size_t)st * 16384, 16384, pol_keep);
+            tc::bulk_s2g_hint(mine + (size_t)(2 + st) * 16384, abuf + (size_t)rank * 65536 + (size_t)(2 + st) * 16384, 16384,
+                              pol_keep);
+            tc::bulk_commit_group();
+            tc::bulk_wait_group0();                              // the stores are performed
+            __threadfence();
+            tc::mbar_arrive_remote(peer_rdy + st * 2 + (xops & 1), peer);
+          }
+          tc::mbar_arrive(pushed);
+        }
+      }
+    }
+  } else if (warp == 3) {
+    // ================= puller: the peer's K-blocks -> my resident A buffer =================
+    if (lane == 0) {
+      const uint64_t pol_keep = tc::policy_evict_last();
+      int opc = 0, xops = 0;
+      for (int tile = cluster; tile < P.mv_tiles; tile += n_clusters) {
+        for (int o = 0; o < kPOps; ++o, ++opc) {
+          if (o == kPOps - 1) continue;
+          tc::mbar_wait(accf + (opc & 1), (uint32_t)((opc >> 1) & 1));     // my MMAs of this op no longer read the buffer
+          const unsigned char* theirs = xch + ((size_t)(xops & 1) * 2 + peer) * 65536;
+          for (int st = 0; st < 2; ++st) {
+            tc::mbar_wait_cluster(peer_rdy + st * 2 + (xops & 1), (uint32_t)((xops >> 1) & 1));
+            tc::mbar_arrive_expect_tx(a_peer + st, 32768);
+            tc::bulk_g2s_hint(abuf + (size_t)peer * 65536 + (size_t)st * 16384, theirs + (size_t)st * 16384, 16384,
+                              a_peer + st, pol_keep);
+            tc::bulk_g2s_hint(abuf + (size_t)peer * 65536 + (size_t)(2 + st) * 16384, theirs + (size_t)(2 + st) * 16384, 16384,
+                              a_peer + st, pol_keep);
+          }
+          ++xops;
+        }
+      }
+    }
+  }
+  else if (warp >= 4) {
+    // ================= epilogue =================
+    const int quad = warp & 3;
+    const int half = (warp - 4) >> 2;
+    const int row = quad * 32 + lane;
+    const bool leader = (warp == 4 && lane == 0);
+    int opc = 0, xops = 0, titer = 0;
+    long long w_acc = 0, w_fence = 0, t_epi0 = clock64();
+    long long w_kind[4] = {0, 0, 0, 0};
+    POp d;
+    for (int tile = cluster; tile < P.mv_tiles; tile += n_clusters, ++titer) {
+      const uint32_t x_col = (titer & 1) ? 256u : 0u;
+      for (int o = 0; o < kPOps; ++o, ++opc) {
+        pair_get_op(P, o, d);
+        TIMED(w_acc, tc::mbar_wait(accf + (opc & 1), (uint32_t)((opc >> 1) & 1)));
+        tc::fence_after_sync();
+        const uint32_t t0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (d.acc_x ? x_col : (256u - x_col)) + half * 128;
+        const bool pooled = d.acc_x && o >= 6;                 // residual stream after the view mean
+        // the previous operand has left my half of the A buffer (pusher's bulk stores have read it)
+        if (d.epi != EPI_HEAD && xops > 0) tc::mbar_wait(pushed, (uint32_t)((xops - 1) & 1));
+        float hp0 = 0.f, hp1 = 0.f, hp2 = 0.f, hp3 = 0.f;
+        const long long tl0 = clock64();
+#pragma unroll 1
+        for (int st = 0; st < 2; ++st) {                       // two 64-column stages = own K-blocks (half*2 + st)
+          uint32_t acc[64];
+          tc::tmem_ld64(t0 + st * 64, acc);
+          tc::tmem_ld_wait();
+          const int nl0 = half * 128 + st * 64;                // first column inside the CTA's 256
+          const float* bias = d.bias + (int)rank * 256 + nl0;
+          if (d.epi == EPI_HEAD) {
+            const float* wo = P.w_out + (int)rank * 256 + nl0;
+            pair_head_stage<NV>(acc, bias, wo, lane, hp0, hp1, hp2, hp3);
+          } else {
+            unsigned char* dst_s = abuf + ((size_t)rank * 32 + nl0 / 8) * 2048 + (size_t)row * 16;
+            if (pooled) pair_act_stage<NV, true>(acc, bias, lane, dst_s);
+            else pair_act_stage<NV, false>(acc, bias, lane, dst_s);
+            // my part of K-block (half*2 + st) is in shared memory: order it before the MMAs (async proxy) and
+            // before the peer's bulk copy of the exchange buffer, then one arrival per warp
+            tc::fence_before_sync();
+            tc::fence_proxy_async();            // generic smem writes -> async proxy (MMA reads, pusher's bulk store)
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(a_own + st);
+          }
+        }
+        w_kind[d.epi] += clock64() - tl0;
+        if (d.epi == EPI_HEAD) {
+          tc::fence_before_sync();
+          // combine the two column halves of the CTA, then one float4 of partial sums per row
+          if (half == 1) reinterpret_cast<float4*>(head_s)[row] = make_float4(hp0, hp1, hp2, hp3);
+          bar_sync_epi();
+          if (half == 0) {
+            const float4 o4 = reinterpret_cast<const float4*>(head_s)[row];
+            P.head_partial[((size_t)tile * 2 + rank) * 128 + row] = make_float4(hp0 + o4.x, hp1 + o4.y, hp2 + o4.z, hp3 + o4.w);
+          }
+          bar_sync_epi();
+        } else {
+          ++xops;
+        }
+      }
+    }
+    if (leader && P.prof) {
+      long long* pr = P.prof + (size_t)blockIdx.x * 16;
+      pr[4] = clock64() - t_epi0; pr[5] = w_acc; pr[6] = w_fence;
+      pr[8] = w_kind[0]; pr[9] = w_kind[1]; pr[10] = w_kind[2]; pr[11] = w_kind[3];
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::cluster_sync_all();               // nobody exits while its peer may still signal it
+  if (warp == 1) { tc::fence_after_sync(); tc::tmem_dealloc(tmem_base, 512); }
+}
+
+// out[s] = [sigmoid, sigmoid, sigmoid, relu](partial_0 + partial_1 + b_out) read at the leader row of sample s
+__global__ void head_finalize_kernel(const float4* __restrict__ part, const float* __restrict__ bout, int NV, int SPW,
+                                     long long n_samples, float4* __restrict__ out) {
+  const long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n_samples) return;
+  const long long per_tile = 4LL * SPW;
+  const long long tile = s / per_tile;
+  const int j = (int)(s % per_tile);
+  const int row = (j / SPW) * 32 + (j % SPW) * NV;
+  const float4 a = part[(tile * 2 + 0) * 128 + row], b = part[(tile * 2 + 1) * 128 + row];
+  const float o0 = a.x + b.x + bout[0], o1 = a.y + b.y + bout[1], o2 = a.z + b.z + bout[2], o3 = a.w + b.w + bout[3];
+  out[s] = make_float4(1.f / (1.f + expf(-o0)), 1.f / (1.f + expf(-o1)), 1.f / (1.f + expf(-o2)), fmaxf(o3, 0.f));
+}
+
+}  // namespace dnr
+
+DNR_EXPORT long long dnr_mlp_pair_scratch_bytes(void) { return 74LL * (long long)dnr::kXchPerCluster; }
+
+// Whole ResnetFC forward + lin_out partial sums on CTA pairs (see file header).  weights: 14 PK256 pointers
+// [lin_in, lin_z0..2, fc_0 x5, fc_1 x5]; biases: 11 fp32[512] pointers [cb0..cb5 (cumulative residual biases),
+// fc_0 bias x5]; w_out fp32 [4 x 512]; xch: dnr_mlp_pair_scratch_bytes(); head_partial: [mv_tiles*2*128] float4.
+DNR_EXPORT int dnr_mlp_pair_fwd(const void* lat_pk, const void* code_pk, const void* const* weights,
+                                const float* const* biases, const float* w_out, int NV, int mv_tiles, void* xch,
+                                float* head_partial, long long* prof, cudaStream_t stream) {
+  DNR_REQUIRE(NV >= 1 && NV <= 4, "dnr_mlp_pair_fwd: NV must be in [1,4]");
+  DNR_REQUIRE(lat_pk && code_pk && weights && biases && w_out && xch && head_partial, "dnr_mlp_pair_fwd: null argument");
+  if (mv_tiles <= 0) return 0;
+  dnr::PairParams P;
+  P.lat_pk = (const unsigned char*)lat_pk; P.code_pk = (const unsigned char*)code_pk;
+  P.w_in = (const unsigned char*)weights[0];
+  for (int i = 0; i < 3; ++i) P.w_z[i] = (const unsigned char*)weights[1 + i];
+  for (int i = 0; i < 5; ++i) { P.w_0[i] = (const unsigned char*)weights[4 + i]; P.w_1[i] = (const unsigned char*)weights[9 + i]; }
+  for (int i = 0; i < 6; ++i) P.cb[i] = biases[i];
+  for (int i = 0; i < 5; ++i) P.b_0[i] = biases[6 + i];
+  P.w_out = w_out; P.xch = (unsigned char*)xch; P.head_partial = (float4*)head_partial;
+  P.NV = NV; P.SPW = 32 / NV; P.mv_tiles = mv_tiles; P.prof = prof;
+  { const char* e = getenv("DNR_PAIR_FLAGS"); P.flags = e ? atoi(e) : 0; }
+  void (*kern)(const dnr::PairParams) = NV == 1 ? dnr::mlp_pair_fwd_kernel<1>
+                                         : NV == 2 ? dnr::mlp_pair_fwd_kernel<2>
+                                         : NV == 3 ? dnr::mlp_pair_fwd_kernel<3> : dnr::mlp_pair_fwd_kernel<4>;
+  static bool configured[5] = {false, false, false, false, false};
+  if (!configured[NV]) {
+    DNR_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dnr::kPSmem),
+              "dnr_mlp_pair_fwd/attr");
+    configured[NV] = true;
+  }
+  int clusters = mv_tiles < 74 ? mv_tiles : 74;
+  kern<<<2 * clusters, dnr::kPThreads, dnr::kPSmem, stream>>>(P);
+  DNR_CHECK_LAUNCH("dnr_mlp_pair_fwd");
+  return 0;
+}
+
+DNR_EXPORT int dnr_head_finalize(const float* head_partial, const float* bout, int NV, long long n_samples,
+                                 float* rgbsigma, cudaStream_t stream) {
+  DNR_REQUIRE(NV >= 1 && NV <= 8, "dnr_head_finalize: NV must be in [1,8]");
+  if (n_samples <= 0) return 0;
+  const int blocks = (int)((n_samples + 255) / 256);
+  dnr::head_finalize_kernel<<<blocks, 256, 0, stream>>>((const float4*)head_partial, bout, NV, 32 / NV, n_samples,
+                                                       (float4*)rgbsigma);
+  DNR_CHECK_LAUNCH("dnr_head_finalize");
+  return 0;
+}

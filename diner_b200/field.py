@@ -24,6 +24,8 @@ from .scene import SceneBuffers
 HID = 512
 IN_PAD = 64
 USE_FUSED_FORWARD = True     # tests flip this to compare the fused kernel with the per-layer path
+PAIR_PROF = None             # debug: int64 tensor [148*8] receiving cycle counters of the pair kernel
+FORWARD_KERNEL = "pair"      # inference MLP: "pair" (mlp_pair.cu) | "chain" (mlp_fused.cu) | "layers" (gemm.cu)
 
 
 def _mlp_signature(mlp):
@@ -67,6 +69,15 @@ class PackedMLP:
         bs = [self.b_first, *self.b_0, *self.b_1]
         self.w_ptrs = (C.c_void_p * len(ws))(*[t.data_ptr() for t in ws])
         self.b_ptrs = (C.c_void_p * len(bs))(*[t.data_ptr() for t in bs])
+        # cumulative residual-stream biases for the CTA-pair kernel (the stream lives in TMEM without biases)
+        cb = [self.b_first]
+        for b in range(3):
+            cb.append(cb[-1] + self.b_1[b])
+        cb.append(cb[-1] + self.b_1[3])
+        cb.append(cb[-1] + self.b_1[4])
+        self.cb = [t.contiguous() for t in cb]
+        pb = [*self.cb, *self.b_0]
+        self.pair_b_ptrs = (C.c_void_p * len(pb))(*[t.data_ptr() for t in pb])
         if need_transposed:
             self.wt_z = [pack(l.weight, True) for l in mlp.lin_z]
             self.wt_0 = [pack(b.fc_0.weight, True) for b in mlp.blocks]
@@ -95,6 +106,13 @@ def _fused_scratch(dev) -> torch.Tensor:
     if k not in _scratch:
         n = _lib.load().dnr_mlp_fused_scratch_bytes(0)
         _scratch[k] = torch.zeros(n, device=dev, dtype=torch.uint8)
+    return _scratch[k]
+
+
+def _pair_scratch(dev) -> torch.Tensor:
+    k = "pair" + str(dev)
+    if k not in _scratch:
+        _scratch[k] = torch.zeros(_lib.load().dnr_mlp_pair_scratch_bytes(), device=dev, dtype=torch.uint8)
     return _scratch[k]
 
 
@@ -145,7 +163,15 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
     _lib.call("dnr_encode_fwd", p(rays), p(z), p(sc.poses), p(sc.focal), p(sc.cxy), p(sc.depth), p(sc.latent_nhwc),
               p(sc.freqs), p(sc.phases), *_encode_args(sc, NR, K, ray0, n), p(lat), p(code), st)
 
-    if not save and USE_FUSED_FORWARD:
+    if not save and FORWARD_KERNEL == "pair" and NV <= 4:
+        # inference: CTA-pair kernel, residual stream in TMEM, lin_out fused (csrc/mlp_pair.cu)
+        part = torch.empty(mv * 2 * 128, 4, **f32)
+        _lib.call("dnr_mlp_pair_fwd", p(lat), p(code), pk.w_ptrs, pk.pair_b_ptrs, p(pk.w_out), NV, mv,
+                  p(_pair_scratch(dev)), p(part), p(PAIR_PROF), st)
+        out = torch.empty(n_samples, 4, **f32)
+        _lib.call("dnr_head_finalize", p(part), p(pk.b_out), NV, n_samples, p(out), st)
+        return out, None
+    if not save and FORWARD_KERNEL != "layers":
         # inference: the whole ResnetFC in one persistent kernel, activations stay in L2 (csrc/mlp_fused.cu)
         S = 4 * NV * (32 // NV)
         groups = (mv + NV - 1) // NV

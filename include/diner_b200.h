@@ -119,6 +119,19 @@ int dnr_mlp_fused_fwd(const void* lat_pk, const void* code_pk, const void* const
                       int NV, int mv_tiles, long long n_samples, void* scratch, void* xa_out, int max_ctas,
                       dnr_stream_t stream);
 
+/* The same forward on CLUSTERS OF TWO CTAs with the fp32 residual stream resident in TMEM (csrc/mlp_pair.cu): CTA r
+ * of a pair owns output columns [256r, 256r+256) of every layer and the two exchange only the bf16 A operand
+ * (64 KB per layer) through an L2-resident buffer, so nothing of the layer chain touches HBM.  lin_out is fused as
+ * partial sums.  weights as for dnr_mlp_fused_fwd; biases = 11 fp32[512] pointers [cb0..cb5, fc_0 bias x5] where
+ * cb0 = lin_in+lin_z0, cb1..5 = cb0 plus the cumulative fc_1 (+lin_z[b+1]) biases of blocks 0..4;
+ * head_partial: [mv_tiles*2*128] float4, consumed by dnr_head_finalize (sigmoid / relu, pixelnerf.py:137-145). */
+long long dnr_mlp_pair_scratch_bytes(void);
+int dnr_mlp_pair_fwd(const void* lat_pk, const void* code_pk, const void* const* weights, const float* const* biases,
+                     const float* w_out, int NV, int mv_tiles, void* xch, float* head_partial, long long* prof /* nullable: [grid][16] cycle counters */,
+                     dnr_stream_t stream);
+int dnr_head_finalize(const float* head_partial, const float* bout, int NV, long long n_samples, float* rgbsigma,
+                      dnr_stream_t stream);
+
 /* Weight / bias gradient of one nn.Linear (autograd of F.linear in resnetfc.py):
  *   dW[n,k] += sum_rows dY[row,n] * X[row,k],  db[n] += sum_rows dY[row,n]
  * dY PK128[rows x Fy], X PK128[rows x Fx]; only n < n_valid, k < k_valid are written. */

@@ -1,0 +1,21 @@
+"""Cycle-counter breakdown of the CTA-pair MLP kernel (development tool)."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from diner_b200 import NeRFRendererDGS, field as F_
+from diner_b200.synthetic import make_scene
+
+scene = make_scene("facescape", seed=0)
+wl = scene.workload
+m = scene.model.to_device("cuda")
+r = NeRFRendererDGS(wl.n_samples, wl.n_candidates, wl.n_gaussian, white_bkgd=True)
+rays = scene.rays.cuda()
+with torch.no_grad():
+    r(m, rays)
+    F_.PAIR_PROF = torch.zeros(148 * 16, dtype=torch.int64, device="cuda")
+    r(m, rays)
+torch.cuda.synchronize()
+p = F_.PAIR_PROF.view(148, 16).double().cpu()
+names = ["mma_total", "mma_wait_ring", "mma_wait_own", "mma_wait_peer", "epi_total", "epi_wait_accf", "epi_fence_bar", "-", "loop_EPI_X(4/tile)", "loop_EPI_T(5/tile)", "loop_EPI_MEAN(1)", "loop_EPI_HEAD(1)"]
+for i, n in enumerate(names):
+    print(f"{n:16s} mean {p[:, i].mean():14.0f} cyc  ({100 * p[:, i].mean() / p[:, 0].mean():5.1f}% of mma_total)  min {p[:, i].min():.0f} max {p[:, i].max():.0f}")
