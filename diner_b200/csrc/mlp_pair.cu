@@ -161,8 +161,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
   uint64_t* a_own = bars + 8;             // [2]  own K-blocks {0,2} / {1,3} of the A operand written (256 epilogue threads)
   uint64_t* a_peer = bars + 10;           // [2]  peer K-blocks {0,2} / {1,3} landed (bulk copies)
   uint64_t* peer_rdy = bars + 12;         // [2 stages][2 slots]  peer's stage is in the exchange buffer (remote arrive)
-  uint64_t* pushed = bars + 16;           // [1]  pusher finished reading my half of the A buffer (bulk stores done)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
+  uint64_t* pushed = bars + 16;           // [1]  the peer has received my whole half (remote ack): my half may be rewritten
+  uint64_t* peer_free = bars + 17;        // [1]  the peer's A buffer may receive my next operand (remote credit)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = tc::cluster_ctarank();
@@ -175,7 +176,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
     tc::mbar_init(accf + 0, 1); tc::mbar_init(accf + 1, 1);
     tc::mbar_init(a_own + 0, 8); tc::mbar_init(a_own + 1, 8); tc::mbar_init(a_peer + 0, 1); tc::mbar_init(a_peer + 1, 1);
     for (int i = 0; i < 4; ++i) tc::mbar_init(peer_rdy + i, 1);
-    tc::mbar_init(pushed, 1);
+    tc::mbar_init(pushed, 1); tc::mbar_init(peer_free, 1);
     tc::fence_barrier_init();
   }
   if (warp == 1) tc::tmem_alloc(tmem_slot, 512);
@@ -270,8 +271,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
               const int kb = pair_kb_order((int)rank, i);
               if (i == 0) TIMED(w_own, tc::mbar_wait(a_own + 0, par));
               if (i == 2) TIMED(w_own, tc::mbar_wait(a_own + 1, par));
-              if (i == 4) TIMED(w_peer, tc::mbar_wait(a_peer + 0, par));
-              if (i == 6) TIMED(w_peer, tc::mbar_wait(a_peer + 1, par));
+              if (i == 4) TIMED(w_peer, tc::mbar_wait_cluster(a_peer + 0, par));
+              if (i == 6) TIMED(w_peer, tc::mbar_wait_cluster(a_peer + 1, par));
               TIMED(w_ring, tc::mbar_wait(full + slot, phase));
               tc::fence_after_sync();
               const uint32_t a0 = abuf0 + (uint32_t)kb * 16384u, b0 = tc::smem_u32(ring + (size_t)slot * kPSlot);
@@ -295,45 +296,35 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
       }
     }
   } else if (warp == 2) {
-    // ================= pusher: my finished K-blocks -> exchange buffer (TMA store), then tell the peer =================
+    // ================= pusher: my finished K-blocks -> the peer's resident A buffer (bulk copy over DSMEM) =============
     if (lane == 0) {
-      const uint64_t pol_keep = tc::policy_evict_last();
       int xops = 0;
       for (int tile = cluster; tile < P.mv_tiles; tile += n_clusters) {
         for (int o = 0; o < kPOps - 1; ++o, ++xops) {          // every op but the head produces an A operand
-          unsigned char* mine = xch + ((size_t)(xops & 1) * 2 + rank) * 65536;
+          unsigned char* mine = abuf + (size_t)rank * 65536;
           for (int st = 0; st < 2; ++st) {
             tc::mbar_wait(a_own + st, (uint32_t)(xops & 1));     // all epilogue warps wrote (and proxy-fenced) this stage
-            tc::bulk_s2g_hint(mine + (size_t)st * 16384, abuf + (size_t)rank * 65536 + (size_t)st * 16384, 16384, pol_keep);
-            tc::bulk_s2g_hint(mine + (size_t)(2 + st) * 16384, abuf + (size_t)rank * 65536 + (size_t)(2 + st) * 16384, 16384,
-                              pol_keep);
-            tc::bulk_commit_group();
-            tc::bulk_wait_group0();                              // the stores are performed
-            __threadfence();
-            tc::mbar_arrive_remote(peer_rdy + st * 2 + (xops & 1), peer);
+            if (st == 0) tc::mbar_wait_cluster(peer_free, (uint32_t)(xops & 1));   // peer's MMAs left its buffer, tx armed
+            tc::bulk_s2s_peer(mine + (size_t)st * 16384, 16384, a_peer + st, peer);
+            tc::bulk_s2s_peer(mine + (size_t)(2 + st) * 16384, 16384, a_peer + st, peer);
           }
-          tc::mbar_arrive(pushed);
         }
       }
     }
   } else if (warp == 3) {
-    // ================= puller: the peer's K-blocks -> my resident A buffer =================
+    // ================= receiver: arm the landing barriers, grant the credit, acknowledge =================
     if (lane == 0) {
-      const uint64_t pol_keep = tc::policy_evict_last();
       int opc = 0, xops = 0;
       for (int tile = cluster; tile < P.mv_tiles; tile += n_clusters) {
         for (int o = 0; o < kPOps; ++o, ++opc) {
           if (o == kPOps - 1) continue;
           tc::mbar_wait(accf + (opc & 1), (uint32_t)((opc >> 1) & 1));     // my MMAs of this op no longer read the buffer
-          const unsigned char* theirs = xch + ((size_t)(xops & 1) * 2 + peer) * 65536;
-          for (int st = 0; st < 2; ++st) {
-            tc::mbar_wait_cluster(peer_rdy + st * 2 + (xops & 1), (uint32_t)((xops >> 1) & 1));
-            tc::mbar_arrive_expect_tx(a_peer + st, 32768);
-            tc::bulk_g2s_hint(abuf + (size_t)peer * 65536 + (size_t)st * 16384, theirs + (size_t)st * 16384, 16384,
-                              a_peer + st, pol_keep);
-            tc::bulk_g2s_hint(abuf + (size_t)peer * 65536 + (size_t)(2 + st) * 16384, theirs + (size_t)(2 + st) * 16384, 16384,
-                              a_peer + st, pol_keep);
-          }
+          tc::mbar_arrive_expect_tx(a_peer + 0, 32768);
+          tc::mbar_arrive_expect_tx(a_peer + 1, 32768);
+          tc::mbar_arrive_remote(peer_free, peer);
+          tc::mbar_wait_cluster(a_peer + 1, (uint32_t)(xops & 1));         // everything of this operand has landed
+          tc::mbar_wait_cluster(a_peer + 0, (uint32_t)(xops & 1));
+          tc::mbar_arrive_remote(pushed, peer);
           ++xops;
         }
       }
@@ -358,7 +349,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
         const uint32_t t0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (d.acc_x ? x_col : (256u - x_col)) + half * 128;
         const bool pooled = d.acc_x && o >= 6;                 // residual stream after the view mean
         // the previous operand has left my half of the A buffer (pusher's bulk stores have read it)
-        if (d.epi != EPI_HEAD && xops > 0) tc::mbar_wait(pushed, (uint32_t)((xops - 1) & 1));
+        if (d.epi != EPI_HEAD && xops > 0) tc::mbar_wait_cluster(pushed, (uint32_t)((xops - 1) & 1));
         float hp0 = 0.f, hp1 = 0.f, hp2 = 0.f, hp3 = 0.f;
         const long long tl0 = clock64();
 #pragma unroll 1

@@ -63,6 +63,17 @@ __device__ __forceinline__ void bulk_g2s_hint(void* smem_dst, const void* gmem_s
       "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
       : "memory");
 }
+// bulk async copy from my shared memory into the SAME offset of CTA `rank`'s shared memory (DSMEM), completing
+// (complete_tx) on the mbarrier at `bar`'s offset in that CTA
+__device__ __forceinline__ void bulk_s2s_peer(void* smem_same_offset, uint32_t bytes, uint64_t* bar, uint32_t rank) {
+  asm volatile(
+      "{\n\t"
+      ".reg .b32 rd, rb;\n\t"
+      "mapa.shared::cluster.u32 rd, %0, %3;\n\t"
+      "mapa.shared::cluster.u32 rb, %2, %3;\n\t"
+      "cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [rd], [%0], %1, [rb];\n\t"
+      "}" ::"r"(smem_u32(smem_same_offset)), "r"(bytes), "r"(smem_u32(bar)), "r"(rank) : "memory");
+}
 // bulk async copy shared -> global (TMA engine), bulk-group completion
 __device__ __forceinline__ void bulk_s2g_hint(void* gmem_dst, const void* smem_src, uint32_t bytes, uint64_t policy) {
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(gmem_dst),
