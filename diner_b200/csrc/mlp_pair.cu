@@ -5,17 +5,19 @@
 //   TMEM   (512 cols)  X = fp32 residual stream of its 256 columns (fc_1 / lin_z accumulate straight into it, so the
 //                      residual add costs nothing and never leaves the SM) + T = fc_0 accumulator
 //   smem   128 KB      the full-K bf16 A operand (relu(x) or relu(net)) in the tcgen05 canonical layout: its own
-//                      256 columns are written by its epilogue warps, the peer's 256 columns arrive as ONE 64 KB
-//                      cp.async.bulk from a small L2-resident exchange buffer (DSMEM stores are ~20 B/clk - too slow)
+//                      256 columns are written by its epilogue warps and pushed, 32 KB at a time, into the peer's
+//                      buffer by cp.async.bulk shared::cta -> shared::cluster (DSMEM), which completes the peer's
+//                      landing barrier; the peer does the same, so nothing of the exchange touches L2
 //          3 x 32 KB   ring for the streamed operands: weight K-blocks of its 256 output rows, and the
 //                      gathered-feature / code K-blocks for lin_in / lin_z
-// so per layer a CTA moves 256 KB of weights + 64 KB out + 64 KB in through L2 instead of ~1.1 MB, and nothing of
+// so per layer a CTA pulls 256 KB of weights from L2 instead of ~1.1 MB of weights + activations, and nothing of
 // the layer chain depends on HBM.  lin_z[b](lat) K-steps are issued FIRST in their layer: they do not depend on the
 // previous epilogue and hide it.  After the view mean every row carries its sample's mean, i.e. blocks 3-4 run on
 // NV duplicates (+18 % MMA work at NV=2) - the price of keeping the tile on chip.
 //
-//   warp 0 : ring producer            warp 1 : tcgen05.mma issuer       warp 2 : peer-half loader
-//   warps 4..11 : epilogue (two per TMEM lane quadrant, 128 columns each)
+//   warp 0 : ring producer      warp 1 : tcgen05.mma issuer      warp 2 : pusher      warp 3 : receiver (credits / acks)
+//   warps 4..11 : epilogue (two per TMEM lane quadrant; four 32-column pieces each, the two warps of a quadrant
+//                 complete one 64-column K-block per piece so the next layer's MMAs start after a quarter epilogue)
 #include "common.cuh"
 #include "tc05.cuh"
 #include <stdlib.h>
@@ -29,7 +31,6 @@ constexpr int kPAbuf = 131072;
 constexpr int kPHeadScratch = 2048;
 constexpr size_t kPSmem = (size_t)kPAbuf + kPRing * kPSlot + kPHeadScratch + 256;
 constexpr int kPOps = 11;
-constexpr size_t kXchPerCluster = 2 * 2 * 65536;     // [slot][rank][64 KB]
 
 struct PairParams {
   const unsigned char* lat_pk;    // PK128 [mv_tiles x 512]
@@ -41,11 +42,10 @@ struct PairParams {
   const float* cb[6];             // cumulative residual-stream biases: after lin_in+z0, block 0, 1, 2 | block 3, 4
   const float* b_0[5];
   const float* w_out;             // fp32 [4 x 512]
-  unsigned char* xch;             // n_clusters * kXchPerCluster
   float4* head_partial;           // [mv_tiles][2][128]: partial lin_out sums of each CTA's 256 columns
   int NV, SPW, mv_tiles;
   long long* prof;                // optional [gridDim][8] cycle counters (debug)
-  int flags;                      // bit 0: every epilogue thread issues its own gpu-scope fence (default: leader only)
+  int flags;                      // DNR_PAIR_FLAGS (development): bit 0 = probe the latency of one bulk copy from L2
 };
 
 enum { EPI_X = 0, EPI_T = 1, EPI_MEAN = 2, EPI_HEAD = 3 };
@@ -77,8 +77,7 @@ __device__ __forceinline__ void pair_get_op(const PairParams& P, int o, POp& d) 
 // K-block order of the resident-operand GEMMs: own K-blocks first, in the order the epilogue finishes them
 // ({0,2} after its first 64-column stage, {1,3} after the second), then the peer's four.
 __device__ __forceinline__ int pair_kb_order(int rank, int i) {
-  if (i < 4) return 4 * rank + ((i & 1) << 1) + (i >> 1);      // 0, 2, 1, 3
-  return 4 * (rank ^ 1) + (((i - 4) & 1) << 1) + ((i - 4) >> 1);
+  return i < 4 ? 4 * rank + i : 4 * (rank ^ 1) + (i - 4);      // own K-blocks first, in the order the epilogue writes them
 }
 
 __device__ __forceinline__ void bar_sync_epi() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
@@ -101,12 +100,12 @@ __device__ __forceinline__ float view_mean(float v, int lane) {
   return s / (float)NV;
 }
 
-// one 64-column stage of an activation epilogue: (+bias, [view mean], relu, bf16) -> resident A buffer + exchange buffer
+// one 32-column piece of an activation epilogue: (+bias, [view mean], relu, bf16) -> resident A buffer
 template <int NV, bool POOLED>
-__device__ __forceinline__ void pair_act_stage(const uint32_t (&acc)[64], const float* __restrict__ bias, int lane,
+__device__ __forceinline__ void pair_act_stage(const uint32_t (&acc)[32], const float* __restrict__ bias, int lane,
                                                unsigned char* dst_s) {
 #pragma unroll
-  for (int g = 0; g < 8; ++g) {
+  for (int g = 0; g < 4; ++g) {
     const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + g * 8));
     const float4 b1 = __ldg(reinterpret_cast<const float4*>(bias + g * 8 + 4));
     float v[8] = {__uint_as_float(acc[g * 8 + 0]) + b0.x, __uint_as_float(acc[g * 8 + 1]) + b0.y,
@@ -125,18 +124,21 @@ __device__ __forceinline__ void pair_act_stage(const uint32_t (&acc)[64], const 
   }
 }
 
-// one 64-column stage of the head: partial lin_out sums on the bf16-rounded relu(mean x) (contract of dnr_head_fwd)
+// one 32-column piece of the head: partial lin_out sums on the bf16-rounded relu(mean x) (contract of dnr_head_fwd)
 template <int NV>
-__device__ __forceinline__ void pair_head_stage(const uint32_t (&acc)[64], const float* __restrict__ bias,
+__device__ __forceinline__ void pair_head_stage(const uint32_t (&acc)[32], const float* __restrict__ bias,
                                                 const float* __restrict__ wo, int lane, float& h0, float& h1, float& h2,
                                                 float& h3) {
 #pragma unroll
-  for (int q = 0; q < 16; ++q) {
+  for (int q = 0; q < 8; ++q) {
     const float4 b = __ldg(reinterpret_cast<const float4*>(bias + q * 4));
     float v[4] = {__uint_as_float(acc[q * 4 + 0]) + b.x, __uint_as_float(acc[q * 4 + 1]) + b.y,
                   __uint_as_float(acc[q * 4 + 2]) + b.z, __uint_as_float(acc[q * 4 + 3]) + b.w};
-#pragma unroll
-    for (int j = 0; j < 4; ++j) v[j] = __bfloat162float(__float2bfloat16_rn(fmaxf(view_mean<NV>(v[j], lane), 0.f)));
+    for (int j = 0; j < 4; ++j) v[j] = fmaxf(view_mean<NV>(v[j], lane), 0.f);
+    {   // round to bf16 two at a time (one packed convert instead of two quarter-rate scalar ones)
+      const uint32_t p01 = pack_bf16x2(v[0], v[1]), p23 = pack_bf16x2(v[2], v[3]);
+      v[0] = bf16lo(p01); v[1] = bf16hi(p01); v[2] = bf16lo(p23); v[3] = bf16hi(p23);
+    }
     const float4 w0 = __ldg(reinterpret_cast<const float4*>(wo + q * 4));
     const float4 w1 = __ldg(reinterpret_cast<const float4*>(wo + 512 + q * 4));
     const float4 w2 = __ldg(reinterpret_cast<const float4*>(wo + 1024 + q * 4));
@@ -158,9 +160,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
   uint64_t* full = bars;                  // [3]  ring slot landed
   uint64_t* empty = bars + 3;             // [3]  ring slot consumed
   uint64_t* accf = bars + 6;              // [2]  accumulator of op (parity) complete
-  uint64_t* a_own = bars + 8;             // [2]  own K-blocks {0,2} / {1,3} of the A operand written (256 epilogue threads)
-  uint64_t* a_peer = bars + 10;           // [2]  peer K-blocks {0,2} / {1,3} landed (bulk copies)
-  uint64_t* peer_rdy = bars + 12;         // [2 stages][2 slots]  peer's stage is in the exchange buffer (remote arrive)
+  uint64_t* a_own = bars + 12;            // [4]  own K-block p of the A operand written (one arrival per epilogue warp)
+  uint64_t* a_peer = bars + 10;           // [2]  peer K-blocks {0,1} / {2,3} landed (bulk copies over DSMEM)
   uint64_t* pushed = bars + 16;           // [1]  the peer has received my whole half (remote ack): my half may be rewritten
   uint64_t* peer_free = bars + 17;        // [1]  the peer's A buffer may receive my next operand (remote credit)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
@@ -169,14 +170,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
   const uint32_t rank = tc::cluster_ctarank();
   const uint32_t peer = rank ^ 1u;
   const int cluster = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
-  unsigned char* xch = P.xch + (size_t)cluster * kXchPerCluster;
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < kPRing; ++s) { tc::mbar_init(full + s, 1); tc::mbar_init(empty + s, 1); }
     tc::mbar_init(accf + 0, 1); tc::mbar_init(accf + 1, 1);
-    tc::mbar_init(a_own + 0, 8); tc::mbar_init(a_own + 1, 8); tc::mbar_init(a_peer + 0, 1); tc::mbar_init(a_peer + 1, 1);
-    for (int i = 0; i < 4; ++i) tc::mbar_init(peer_rdy + i, 1);
+    for (int i = 0; i < 4; ++i) tc::mbar_init(a_own + i, 8);
+    tc::mbar_init(a_peer + 0, 1); tc::mbar_init(a_peer + 1, 1);
     tc::mbar_init(pushed, 1); tc::mbar_init(peer_free, 1);
+    tc::mbar_init(bars + 18, 1);
     tc::fence_barrier_init();
   }
   if (warp == 1) tc::tmem_alloc(tmem_slot, 512);
@@ -199,6 +200,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
         if (++slot == kPRing) { slot = 0; phase ^= 1; }
       };
       POp d;
+      if ((P.flags & 1) && P.prof) {          // probe: latency of one bulk copy from L2 into an idle ring slot
+        long long* pr = P.prof + (size_t)blockIdx.x * 16;
+        uint32_t ph = 0;
+        for (int it = 0; it < 6; ++it) {
+          const uint32_t bytes = it < 3 ? 32768u : 16384u;
+          const long long t0 = clock64();
+          tc::mbar_arrive_expect_tx(bars + 18, bytes);
+          tc::bulk_g2s_hint(ring, P.w_0[4] + (size_t)rank * 262144 + (size_t)(it % 3) * 32768, bytes, bars + 18, pol_keep);
+          tc::mbar_wait(bars + 18, ph); ph ^= 1;
+          if (it == 1) pr[13] = clock64() - t0;     // second 32 KB load (first one may miss L2)
+          if (it == 2) pr[14] = clock64() - t0;
+          if (it == 5) pr[15] = clock64() - t0;     // 16 KB load
+        }
+      }
       for (int tile = cluster; tile < P.mv_tiles; tile += n_clusters) {
         const unsigned char* lat = P.lat_pk + (size_t)tile * 131072;
         if (tile + n_clusters < P.mv_tiles) {     // pull the next tile's inputs from HBM into L2 while this one computes
@@ -269,10 +284,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
             const uint32_t par = (uint32_t)((aops) & 1);
             for (int i = 0; i < 8; ++i) {
               const int kb = pair_kb_order((int)rank, i);
-              if (i == 0) TIMED(w_own, tc::mbar_wait(a_own + 0, par));
-              if (i == 2) TIMED(w_own, tc::mbar_wait(a_own + 1, par));
-              if (i == 4) TIMED(w_peer, tc::mbar_wait_cluster(a_peer + 0, par));
-              if (i == 6) TIMED(w_peer, tc::mbar_wait_cluster(a_peer + 1, par));
+              if (i < 4) TIMED(w_own, tc::mbar_wait(a_own + i, par));
+              if (i == 4) TIMED(w_peer, tc::mbar_wait(a_peer + 0, par));
+              if (i == 6) TIMED(w_peer, tc::mbar_wait(a_peer + 1, par));
               TIMED(w_ring, tc::mbar_wait(full + slot, phase));
               tc::fence_after_sync();
               const uint32_t a0 = abuf0 + (uint32_t)kb * 16384u, b0 = tc::smem_u32(ring + (size_t)slot * kPSlot);
@@ -303,10 +317,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
         for (int o = 0; o < kPOps - 1; ++o, ++xops) {          // every op but the head produces an A operand
           unsigned char* mine = abuf + (size_t)rank * 65536;
           for (int st = 0; st < 2; ++st) {
-            tc::mbar_wait(a_own + st, (uint32_t)(xops & 1));     // all epilogue warps wrote (and proxy-fenced) this stage
-            if (st == 0) tc::mbar_wait_cluster(peer_free, (uint32_t)(xops & 1));   // peer's MMAs left its buffer, tx armed
-            tc::bulk_s2s_peer(mine + (size_t)st * 16384, 16384, a_peer + st, peer);
-            tc::bulk_s2s_peer(mine + (size_t)(2 + st) * 16384, 16384, a_peer + st, peer);
+            // all epilogue warps wrote (and proxy-fenced) K-blocks 2st, 2st+1 (a warp reaches 2st+1 after 2st)
+            tc::mbar_wait(a_own + 2 * st + 1, (uint32_t)(xops & 1));
+            if (st == 0) tc::mbar_wait(peer_free, (uint32_t)(xops & 1));   // peer's MMAs left its buffer, tx armed
+            tc::bulk_s2s_peer(mine + (size_t)st * 32768, 32768, a_peer + st, peer);
           }
         }
       }
@@ -321,10 +335,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
           tc::mbar_wait(accf + (opc & 1), (uint32_t)((opc >> 1) & 1));     // my MMAs of this op no longer read the buffer
           tc::mbar_arrive_expect_tx(a_peer + 0, 32768);
           tc::mbar_arrive_expect_tx(a_peer + 1, 32768);
-          tc::mbar_arrive_remote(peer_free, peer);
-          tc::mbar_wait_cluster(a_peer + 1, (uint32_t)(xops & 1));         // everything of this operand has landed
-          tc::mbar_wait_cluster(a_peer + 0, (uint32_t)(xops & 1));
-          tc::mbar_arrive_remote(pushed, peer);
+          tc::mbar_arrive_remote_relaxed(peer_free, peer);
+          tc::mbar_wait(a_peer + 1, (uint32_t)(xops & 1));         // everything of this operand has landed
+          tc::mbar_wait(a_peer + 0, (uint32_t)(xops & 1));
+          tc::mbar_arrive_remote_relaxed(pushed, peer);
           ++xops;
         }
       }
@@ -337,7 +351,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
     const int row = quad * 32 + lane;
     const bool leader = (warp == 4 && lane == 0);
     int opc = 0, xops = 0, titer = 0;
-    long long w_acc = 0, w_fence = 0, t_epi0 = clock64();
+    long long w_acc = 0, w_fence = 0, w_sig = 0, w_push = 0, t_epi0 = clock64();
     long long w_kind[4] = {0, 0, 0, 0};
     POp d;
     for (int tile = cluster; tile < P.mv_tiles; tile += n_clusters, ++titer) {
@@ -346,18 +360,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
         pair_get_op(P, o, d);
         TIMED(w_acc, tc::mbar_wait(accf + (opc & 1), (uint32_t)((opc >> 1) & 1)));
         tc::fence_after_sync();
-        const uint32_t t0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (d.acc_x ? x_col : (256u - x_col)) + half * 128;
+        const uint32_t t0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (d.acc_x ? x_col : (256u - x_col));
         const bool pooled = d.acc_x && o >= 6;                 // residual stream after the view mean
         // the previous operand has left my half of the A buffer (pusher's bulk stores have read it)
-        if (d.epi != EPI_HEAD && xops > 0) tc::mbar_wait_cluster(pushed, (uint32_t)((xops - 1) & 1));
+        if (d.epi != EPI_HEAD && xops > 0) TIMED(w_push, tc::mbar_wait(pushed, (uint32_t)((xops - 1) & 1)));
         float hp0 = 0.f, hp1 = 0.f, hp2 = 0.f, hp3 = 0.f;
         const long long tl0 = clock64();
 #pragma unroll 1
-        for (int st = 0; st < 2; ++st) {                       // two 64-column stages = own K-blocks (half*2 + st)
-          uint32_t acc[64];
-          tc::tmem_ld64(t0 + st * 64, acc);
+        for (int st = 0; st < 4; ++st) {                       // four 32-column pieces; the two halves share K-block st
+          uint32_t acc[32];
+          const int nl0 = st * 64 + half * 32;                 // first column inside the CTA's 256
+          { const long long t__ = clock64();
+          tc::tmem_ld32(t0 + nl0, acc);
           tc::tmem_ld_wait();
-          const int nl0 = half * 128 + st * 64;                // first column inside the CTA's 256
+          w_fence += clock64() - t__; }
           const float* bias = d.bias + (int)rank * 256 + nl0;
           if (d.epi == EPI_HEAD) {
             const float* wo = P.w_out + (int)rank * 256 + nl0;
@@ -367,11 +383,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
             if (pooled) pair_act_stage<NV, true>(acc, bias, lane, dst_s);
             else pair_act_stage<NV, false>(acc, bias, lane, dst_s);
             // my part of K-block (half*2 + st) is in shared memory: order it before the MMAs (async proxy) and
-            // before the peer's bulk copy of the exchange buffer, then one arrival per warp
+            // before the pusher's bulk copy, then one arrival per warp
+            const long long t__ = clock64();
             tc::fence_before_sync();
             tc::fence_proxy_async();            // generic smem writes -> async proxy (MMA reads, pusher's bulk store)
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(a_own + st);
+            w_sig += clock64() - t__;
           }
         }
         w_kind[d.epi] += clock64() - tl0;
@@ -392,7 +410,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
     }
     if (leader && P.prof) {
       long long* pr = P.prof + (size_t)blockIdx.x * 16;
-      pr[4] = clock64() - t_epi0; pr[5] = w_acc; pr[6] = w_fence;
+      pr[4] = clock64() - t_epi0; pr[5] = w_acc; pr[6] = w_fence; pr[7] = w_sig; pr[12] = w_push;
       pr[8] = w_kind[0]; pr[9] = w_kind[1]; pr[10] = w_kind[2]; pr[11] = w_kind[3];
     }
   }
@@ -418,16 +436,14 @@ __global__ void head_finalize_kernel(const float4* __restrict__ part, const floa
 
 }  // namespace dnr
 
-DNR_EXPORT long long dnr_mlp_pair_scratch_bytes(void) { return 74LL * (long long)dnr::kXchPerCluster; }
-
 // Whole ResnetFC forward + lin_out partial sums on CTA pairs (see file header).  weights: 14 PK256 pointers
 // [lin_in, lin_z0..2, fc_0 x5, fc_1 x5]; biases: 11 fp32[512] pointers [cb0..cb5 (cumulative residual biases),
-// fc_0 bias x5]; w_out fp32 [4 x 512]; xch: dnr_mlp_pair_scratch_bytes(); head_partial: [mv_tiles*2*128] float4.
+// fc_0 bias x5]; w_out fp32 [4 x 512]; head_partial: [mv_tiles*2*128] float4.
 DNR_EXPORT int dnr_mlp_pair_fwd(const void* lat_pk, const void* code_pk, const void* const* weights,
-                                const float* const* biases, const float* w_out, int NV, int mv_tiles, void* xch,
+                                const float* const* biases, const float* w_out, int NV, int mv_tiles,
                                 float* head_partial, long long* prof, cudaStream_t stream) {
   DNR_REQUIRE(NV >= 1 && NV <= 4, "dnr_mlp_pair_fwd: NV must be in [1,4]");
-  DNR_REQUIRE(lat_pk && code_pk && weights && biases && w_out && xch && head_partial, "dnr_mlp_pair_fwd: null argument");
+  DNR_REQUIRE(lat_pk && code_pk && weights && biases && w_out && head_partial, "dnr_mlp_pair_fwd: null argument");
   if (mv_tiles <= 0) return 0;
   dnr::PairParams P;
   P.lat_pk = (const unsigned char*)lat_pk; P.code_pk = (const unsigned char*)code_pk;
@@ -436,7 +452,7 @@ DNR_EXPORT int dnr_mlp_pair_fwd(const void* lat_pk, const void* code_pk, const v
   for (int i = 0; i < 5; ++i) { P.w_0[i] = (const unsigned char*)weights[4 + i]; P.w_1[i] = (const unsigned char*)weights[9 + i]; }
   for (int i = 0; i < 6; ++i) P.cb[i] = biases[i];
   for (int i = 0; i < 5; ++i) P.b_0[i] = biases[6 + i];
-  P.w_out = w_out; P.xch = (unsigned char*)xch; P.head_partial = (float4*)head_partial;
+  P.w_out = w_out; P.head_partial = (float4*)head_partial;
   P.NV = NV; P.SPW = 32 / NV; P.mv_tiles = mv_tiles; P.prof = prof;
   { const char* e = getenv("DNR_PAIR_FLAGS"); P.flags = e ? atoi(e) : 0; }
   void (*kern)(const dnr::PairParams) = NV == 1 ? dnr::mlp_pair_fwd_kernel<1>

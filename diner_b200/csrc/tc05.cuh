@@ -172,7 +172,18 @@ __device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t rank)
       "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t"
       "}" ::"r"(smem_u32(bar)), "r"(rank) : "memory");
 }
-// wait with cluster-scope acquire (the barrier receives remote arrivals)
+// remote arrival that only hands over a credit (write-after-read protection of shared memory that is touched by the
+// async proxy / tensor core only): no release fence, so no MEMBAR.GPU in front of it
+__device__ __forceinline__ void mbar_arrive_remote_relaxed(uint64_t* bar, uint32_t rank) {
+  asm volatile(
+      "{\n\t"
+      ".reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [ra];\n\t"
+      "}" ::"r"(smem_u32(bar)), "r"(rank) : "memory");
+}
+// wait with cluster-scope acquire (the barrier receives remote arrivals).  NOTE: compiles to CCTL.IVALL after the
+// wait -- it invalidates the SM's whole L1, so keep it off paths that share an SM with L1-cached loads.
 __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
   asm volatile(
       "{\n\t"

@@ -109,13 +109,6 @@ def _fused_scratch(dev) -> torch.Tensor:
     return _scratch[k]
 
 
-def _pair_scratch(dev) -> torch.Tensor:
-    k = "pair" + str(dev)
-    if k not in _scratch:
-        _scratch[k] = torch.zeros(_lib.load().dnr_mlp_pair_scratch_bytes(), device=dev, dtype=torch.uint8)
-    return _scratch[k]
-
-
 def _gemm(A0, B0, K0, m_tiles, N=HID, A1=None, B1=None, K1=0, A2=None, B2=None, K2=0, bias=None, mask=None,
           res_in=None, res_out=None, act_out=None, relu=0, mean_nv=0, n_samples=0, max_ctas=0):
     p = _lib.ptr
@@ -167,7 +160,7 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
         # inference: CTA-pair kernel, residual stream in TMEM, lin_out fused (csrc/mlp_pair.cu)
         part = torch.empty(mv * 2 * 128, 4, **f32)
         _lib.call("dnr_mlp_pair_fwd", p(lat), p(code), pk.w_ptrs, pk.pair_b_ptrs, p(pk.w_out), NV, mv,
-                  p(_pair_scratch(dev)), p(part), p(PAIR_PROF), st)
+                  p(part), p(PAIR_PROF), st)
         out = torch.empty(n_samples, 4, **f32)
         _lib.call("dnr_head_finalize", p(part), p(pk.b_out), NV, n_samples, p(out), st)
         return out, None

@@ -121,13 +121,14 @@ int dnr_mlp_fused_fwd(const void* lat_pk, const void* code_pk, const void* const
 
 /* The same forward on CLUSTERS OF TWO CTAs with the fp32 residual stream resident in TMEM (csrc/mlp_pair.cu): CTA r
  * of a pair owns output columns [256r, 256r+256) of every layer and the two exchange only the bf16 A operand
- * (64 KB per layer) through an L2-resident buffer, so nothing of the layer chain touches HBM.  lin_out is fused as
+ * (64 KB per layer) by bulk copies over distributed shared memory, so nothing of the layer chain touches HBM or
+ * L2 except the weights.  lin_out is fused as
  * partial sums.  weights as for dnr_mlp_fused_fwd; biases = 11 fp32[512] pointers [cb0..cb5, fc_0 bias x5] where
  * cb0 = lin_in+lin_z0, cb1..5 = cb0 plus the cumulative fc_1 (+lin_z[b+1]) biases of blocks 0..4;
  * head_partial: [mv_tiles*2*128] float4, consumed by dnr_head_finalize (sigmoid / relu, pixelnerf.py:137-145). */
-long long dnr_mlp_pair_scratch_bytes(void);
 int dnr_mlp_pair_fwd(const void* lat_pk, const void* code_pk, const void* const* weights, const float* const* biases,
-                     const float* w_out, int NV, int mv_tiles, void* xch, float* head_partial, long long* prof /* nullable: [grid][16] cycle counters */,
+                     const float* w_out, int NV, int mv_tiles, float* head_partial,
+                     long long* prof /* nullable: [grid][16] cycle counters */,
                      dnr_stream_t stream);
 int dnr_head_finalize(const float* head_partial, const float* bout, int NV, long long n_samples, float* rgbsigma,
                       dnr_stream_t stream);

@@ -16,6 +16,6 @@ with torch.no_grad():
     r(m, rays)
 torch.cuda.synchronize()
 p = F_.PAIR_PROF.view(148, 16).double().cpu()
-names = ["mma_total", "mma_wait_ring", "mma_wait_own", "mma_wait_peer", "epi_total", "epi_wait_accf", "epi_fence_bar", "-", "loop_EPI_X(4/tile)", "loop_EPI_T(5/tile)", "loop_EPI_MEAN(1)", "loop_EPI_HEAD(1)"]
+names = ["mma_total", "mma_wait_ring", "mma_wait_own", "mma_wait_peer", "epi_total", "epi_wait_accf", "epi_tmem_ld", "epi_fence_arrive", "loop_EPI_X(4/tile)", "loop_EPI_T(5/tile)", "loop_EPI_MEAN(1)", "loop_EPI_HEAD(1)", "epi_wait_pushed", "probe32K_a", "probe32K_b", "probe16K"]
 for i, n in enumerate(names):
     print(f"{n:16s} mean {p[:, i].mean():14.0f} cyc  ({100 * p[:, i].mean() / p[:, 0].mean():5.1f}% of mma_total)  min {p[:, i].min():.0f} max {p[:, i].max():.0f}")
