@@ -420,6 +420,317 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
   if (warp == 1) { tc::fence_after_sync(); tc::tmem_dealloc(tmem_base, 512); }
 }
 
+// =====================================================================================================================
+// Quad variant: a cluster of FOUR CTAs = 2 row tiles x 2 column halves.  CTA (h, t) -- cluster rank 2h + t -- owns output
+// columns [256h, 256h+256) of tile t.  The two CTAs with the same h form a tcgen05 CTA pair: ONE thread of the even one
+// issues tcgen05.mma.cta_group::2 (M = 256: 128 rows from each CTA, N = 256) for both, and each CTA streams only HALF of
+// the weight K-block (its 128 of the 256 output rows, 16 KB) -- the L2 -> SM weight traffic per tile, which bounds the
+// pair kernel above, is halved.  The A-operand exchange runs between the CTAs with the same t (rank ^ 2) exactly as in
+// the pair kernel.  Weights are read in the PK128 layout ([N/128][K/8][128][8]): CTA rank r streams N-tile r.
+// The odd CTA of a pair has no MMA thread; its warp 1 forwards "my operands for ring step s are in place" to the even
+// CTA (one relaxed remote mbarrier arrival per ring slot).
+constexpr int kQRing = 6;
+constexpr int kQSlot = 16384;
+constexpr size_t kQSmem = (size_t)kPAbuf + kQRing * kQSlot + 512;
+
+template <int NV>
+__global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_quad_fwd_kernel(const PairParams P) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  unsigned char* abuf = smem;                                   // 128 KB resident A operand
+  unsigned char* ring = smem + kPAbuf;                          // 6 x 16 KB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ring + kQRing * kQSlot);
+  uint64_t* full = bars;                  // [6]  my ring slot landed
+  uint64_t* empty = bars + 6;             // [6]  ring slot consumed in BOTH CTAs of the MMA pair (multicast commit)
+  uint64_t* peer_full = bars + 12;        // [6]  (even CTA) the odd CTA's operands of this ring step are in place
+  uint64_t* accf = bars + 18;             // [2]  accumulator of op (parity) complete (multicast commit)
+  uint64_t* a_peer = bars + 20;           // [2]  exchange partner's K-blocks {0,1} / {2,3} landed
+  uint64_t* a_own = bars + 22;            // [4]  own K-block p written (one arrival per epilogue warp)
+  uint64_t* pushed = bars + 26;           // [1]  partner received my whole half
+  uint64_t* peer_free = bars + 27;        // [1]  partner's A buffer may receive my next operand
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 30);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t cr = tc::cluster_ctarank();
+  const int h = (int)(cr >> 1), t = (int)(cr & 1);
+  const uint32_t partner = cr ^ 2u;       // same tile, other column half
+  const uint32_t mma_peer = cr ^ 1u;      // same column half, other tile
+  const uint16_t pair_mask = (uint16_t)(3u << (2 * h));
+  const int cluster = blockIdx.x >> 2, n_clusters = gridDim.x >> 2;
+  const int n_pairs = (P.mv_tiles + 1) >> 1;
+  auto tile_of = [&](int q) { const int x = 2 * q + t; return x < P.mv_tiles ? x : P.mv_tiles - 1; };
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < kQRing; ++s) { tc::mbar_init(full + s, 1); tc::mbar_init(empty + s, 1); tc::mbar_init(peer_full + s, 1); }
+    tc::mbar_init(accf + 0, 1); tc::mbar_init(accf + 1, 1);
+    for (int i = 0; i < 4; ++i) tc::mbar_init(a_own + i, 8);
+    tc::mbar_init(a_peer + 0, 1); tc::mbar_init(a_peer + 1, 1);
+    tc::mbar_init(pushed, 1); tc::mbar_init(peer_free, 1);
+    tc::fence_barrier_init();
+  }
+  __syncthreads();
+  tc::cluster_sync_all();               // every CTA's barriers exist before anything can signal them
+  if (warp == 1) tc::tmem_alloc_2cta(tmem_slot, 512);
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::cluster_sync_all();
+  tc::fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================= ring producer (every CTA: its half of the weights, its tile's streamed operands) =============
+    if (lane == 0) {
+      const uint64_t pol_keep = tc::policy_evict_last(), pol_stream = tc::policy_evict_first();
+      const uint64_t pol_norm = tc::policy_evict_normal();
+      int slot = 0; uint32_t phase = 0;
+      auto fill = [&](const unsigned char* src, uint64_t pol) {
+        tc::mbar_wait(empty + slot, phase ^ 1);
+        tc::mbar_arrive_expect_tx(full + slot, kQSlot);
+        tc::bulk_g2s_hint(ring + (size_t)slot * kQSlot, src, kQSlot, full + slot, pol);
+        if (++slot == kQRing) { slot = 0; phase ^= 1; }
+      };
+      POp d;
+      for (int q = cluster; q < n_pairs; q += n_clusters) {
+        const int tile = tile_of(q);
+        const unsigned char* lat = P.lat_pk + (size_t)tile * 131072;
+        if (q + n_clusters < n_pairs) {           // pull the next tile's inputs from HBM into L2 while this one computes
+          const int nt = tile_of(q + n_clusters);
+          tc::bulk_prefetch_l2(P.lat_pk + (size_t)nt * 131072, 131072);
+          tc::bulk_prefetch_l2(P.code_pk + (size_t)nt * 16384, 16384);
+        }
+        for (int o = 0; o < kPOps; ++o) {
+          pair_get_op(P, o, d);
+          if (d.code) {
+            fill(P.code_pk + (size_t)tile * 16384, pol_stream);
+            fill(P.w_in + (size_t)cr * 16384, pol_keep);
+          }
+          if (d.lat_w) {
+            for (int kb = 0; kb < 8; ++kb) {
+              fill(lat + (size_t)kb * 16384, o == 4 ? pol_stream : pol_norm);       // last use: evict first
+              fill(d.lat_w + (size_t)cr * 131072 + (size_t)kb * 16384, pol_keep);
+            }
+          }
+          if (d.abuf_w) {
+            for (int i = 0; i < 8; ++i) {
+              const int kb = pair_kb_order(h, i);
+              fill(d.abuf_w + (size_t)cr * 131072 + (size_t)kb * 16384, pol_keep);
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && t == 0) {
+      // ================= MMA issuer for the CTA pair =================
+      constexpr uint32_t idesc = tc::make_idesc_bf16(256, 256, 0, 0);
+      int slot = 0; uint32_t phase = 0;
+      int opc = 0, aops = 0, titer = 0;
+      POp d;
+      const uint32_t abuf0 = tc::smem_u32(abuf);
+      long long w_ring = 0, w_own = 0, w_peer = 0, w_pfull = 0, w_ring_lat = 0, w_pfull_lat = 0, t_start = clock64();
+      for (int q = cluster; q < n_pairs; q += n_clusters, ++titer) {
+        const uint32_t x_col = (titer & 1) ? 256u : 0u;           // X / T swap regions every tile
+        for (int o = 0; o < kPOps; ++o, ++opc) {
+          pair_get_op(P, o, d);
+          const uint32_t d_tmem = tmem_base + (d.acc_x ? x_col : (256u - x_col));
+          uint32_t accumulate = d.fresh ? 0u : 1u;
+          auto step_ring_ab = [&]() {        // A and B both come from consecutive ring slots
+            const int sa = slot;
+            TIMED(w_ring_lat, tc::mbar_wait(full + sa, phase));
+            TIMED(w_pfull_lat, tc::mbar_wait(peer_full + sa, phase));
+            if (++slot == kQRing) { slot = 0; phase ^= 1; }
+            const int sb = slot;
+            TIMED(w_ring_lat, tc::mbar_wait(full + sb, phase));
+            TIMED(w_pfull_lat, tc::mbar_wait(peer_full + sb, phase));
+            if (++slot == kQRing) { slot = 0; phase ^= 1; }
+            tc::fence_after_sync();
+            const uint32_t a0 = tc::smem_u32(ring + (size_t)sa * kQSlot), b0 = tc::smem_u32(ring + (size_t)sb * kQSlot);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              tc::mma_bf16_2cta(d_tmem, tc::make_smem_desc(a0 + j * 4096, 2048, 128),
+                                tc::make_smem_desc(b0 + j * 4096, 2048, 128), idesc, accumulate);
+              accumulate = 1;
+            }
+            tc::mma_commit_2cta_mc(empty + sa, pair_mask);
+            tc::mma_commit_2cta_mc(empty + sb, pair_mask);
+          };
+          if (d.code) step_ring_ab();
+          if (d.lat_w)
+            for (int kb = 0; kb < 8; ++kb) step_ring_ab();
+          if (d.abuf_w) {
+            const uint32_t par = (uint32_t)(aops & 1);
+            for (int i = 0; i < 8; ++i) {
+              const int kb = pair_kb_order(h, i);
+              if (i < 4) TIMED(w_own, tc::mbar_wait(a_own + i, par));
+              if (i == 4) TIMED(w_peer, tc::mbar_wait(a_peer + 0, par));
+              if (i == 6) TIMED(w_peer, tc::mbar_wait(a_peer + 1, par));
+              TIMED(w_ring, tc::mbar_wait(full + slot, phase));
+              TIMED(w_pfull, tc::mbar_wait(peer_full + slot, phase));
+              tc::fence_after_sync();
+              const uint32_t a0 = abuf0 + (uint32_t)kb * 16384u, b0 = tc::smem_u32(ring + (size_t)slot * kQSlot);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                tc::mma_bf16_2cta(d_tmem, tc::make_smem_desc(a0 + j * 4096, 2048, 128),
+                                  tc::make_smem_desc(b0 + j * 4096, 2048, 128), idesc, accumulate);
+                accumulate = 1;
+              }
+              tc::mma_commit_2cta_mc(empty + slot, pair_mask);
+              if (++slot == kQRing) { slot = 0; phase ^= 1; }
+            }
+            ++aops;
+          }
+          tc::mma_commit_2cta_mc(accf + (opc & 1), pair_mask);
+        }
+      }
+      if (P.prof) {
+        long long* pr = P.prof + (size_t)blockIdx.x * 16;
+        pr[0] = clock64() - t_start; pr[1] = w_ring; pr[2] = w_own; pr[3] = w_peer; pr[13] = w_pfull;
+        pr[14] = w_ring_lat; pr[15] = w_pfull_lat;
+      }
+    } else if (lane == 0) {
+      // ================= odd CTA: forward "operands of ring step s in place" to the even CTA =================
+      int slot = 0; uint32_t phase = 0;
+      int aops = 0;
+      POp d;
+      auto forward = [&]() {
+        tc::mbar_wait(full + slot, phase);
+        tc::mbar_arrive_remote_relaxed(peer_full + slot, mma_peer);
+        if (++slot == kQRing) { slot = 0; phase ^= 1; }
+      };
+      for (int q = cluster; q < n_pairs; q += n_clusters) {
+        for (int o = 0; o < kPOps; ++o) {
+          pair_get_op(P, o, d);
+          if (d.code) { forward(); forward(); }
+          if (d.lat_w)
+            for (int kb = 0; kb < 8; ++kb) { forward(); forward(); }
+          if (d.abuf_w) {
+            const uint32_t par = (uint32_t)(aops & 1);
+            for (int i = 0; i < 8; ++i) {
+              if (i < 4) tc::mbar_wait(a_own + i, par);
+              if (i == 4) tc::mbar_wait(a_peer + 0, par);
+              if (i == 6) tc::mbar_wait(a_peer + 1, par);
+              forward();
+            }
+            ++aops;
+          }
+        }
+      }
+    }
+  }
+  else if (warp == 2) {
+    // ================= pusher: my finished K-blocks -> the partner's resident A buffer (bulk copy over DSMEM) =========
+    if (lane == 0) {
+      int xops = 0;
+      unsigned char* mine = abuf + (size_t)h * 65536;
+      for (int q = cluster; q < n_pairs; q += n_clusters) {
+        for (int o = 0; o < kPOps - 1; ++o, ++xops) {          // every op but the head produces an A operand
+          for (int st = 0; st < 2; ++st) {
+            tc::mbar_wait(a_own + 2 * st + 1, (uint32_t)(xops & 1));
+            if (st == 0) tc::mbar_wait(peer_free, (uint32_t)(xops & 1));
+            tc::bulk_s2s_peer(mine + (size_t)st * 32768, 32768, a_peer + st, partner);
+          }
+        }
+      }
+    }
+  } else if (warp == 3) {
+    // ================= receiver: arm the landing barriers, grant the credit, acknowledge =================
+    if (lane == 0) {
+      int opc = 0, xops = 0;
+      for (int q = cluster; q < n_pairs; q += n_clusters) {
+        for (int o = 0; o < kPOps; ++o, ++opc) {
+          if (o == kPOps - 1) continue;
+          tc::mbar_wait(accf + (opc & 1), (uint32_t)((opc >> 1) & 1));     // the MMAs of this op no longer read my buffer
+          tc::mbar_arrive_expect_tx(a_peer + 0, 32768);
+          tc::mbar_arrive_expect_tx(a_peer + 1, 32768);
+          tc::mbar_arrive_remote_relaxed(peer_free, partner);
+          tc::mbar_wait(a_peer + 1, (uint32_t)(xops & 1));
+          tc::mbar_wait(a_peer + 0, (uint32_t)(xops & 1));
+          tc::mbar_arrive_remote_relaxed(pushed, partner);
+          ++xops;
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ================= epilogue (identical to the pair kernel; column half = h) =================
+    const int quad = warp & 3;
+    const int half = (warp - 4) >> 2;
+    const int row = quad * 32 + lane;
+    const bool leader = (warp == 4 && lane == 0);
+    int opc = 0, xops = 0, titer = 0;
+    long long w_acc = 0, t_epi0 = clock64();
+    long long w_kind[4] = {0, 0, 0, 0};
+    POp d;
+    for (int q = cluster; q < n_pairs; q += n_clusters, ++titer) {
+      const int tile = tile_of(q);
+      const bool valid = 2 * q + t < P.mv_tiles;
+      const uint32_t x_col = (titer & 1) ? 256u : 0u;
+      for (int o = 0; o < kPOps; ++o, ++opc) {
+        pair_get_op(P, o, d);
+        TIMED(w_acc, tc::mbar_wait(accf + (opc & 1), (uint32_t)((opc >> 1) & 1)));
+        tc::fence_after_sync();
+        const uint32_t t0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (d.acc_x ? x_col : (256u - x_col));
+        const bool pooled = d.acc_x && o >= 6;
+        if (d.epi != EPI_HEAD && xops > 0) tc::mbar_wait(pushed, (uint32_t)((xops - 1) & 1));
+        float hp0 = 0.f, hp1 = 0.f, hp2 = 0.f, hp3 = 0.f;
+        const long long tl0 = clock64();
+#pragma unroll 1
+        for (int st = 0; st < 4; ++st) {
+          uint32_t acc[32];
+          const int nl0 = st * 64 + half * 32;
+          tc::tmem_ld32(t0 + nl0, acc);
+          tc::tmem_ld_wait();
+          const float* bias = d.bias + h * 256 + nl0;
+          if (d.epi == EPI_HEAD) {
+            pair_head_stage<NV>(acc, bias, P.w_out + h * 256 + nl0, lane, hp0, hp1, hp2, hp3);
+          } else {
+            unsigned char* dst_s = abuf + ((size_t)h * 32 + nl0 / 8) * 2048 + (size_t)row * 16;
+            if (pooled) pair_act_stage<NV, true>(acc, bias, lane, dst_s);
+            else pair_act_stage<NV, false>(acc, bias, lane, dst_s);
+            tc::fence_before_sync();
+            tc::fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(a_own + st);
+          }
+        }
+        w_kind[d.epi] += clock64() - tl0;
+        if (d.epi == EPI_HEAD) {
+          tc::fence_before_sync();
+          // the two column groups of a row are summed by head_finalize (4 partials per row and tile)
+          if (valid)
+            P.head_partial[(((size_t)tile * 2 + h) * 2 + half) * 128 + row] = make_float4(hp0, hp1, hp2, hp3);
+        } else {
+          ++xops;
+        }
+      }
+    }
+    if (leader && P.prof) {
+      long long* pr = P.prof + (size_t)blockIdx.x * 16;
+      pr[4] = clock64() - t_epi0; pr[5] = w_acc;
+      pr[8] = w_kind[0]; pr[9] = w_kind[1]; pr[10] = w_kind[2]; pr[11] = w_kind[3];
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::cluster_sync_all();               // nobody exits (or frees TMEM) while another CTA may still signal or read it
+  if (warp == 1) { tc::fence_after_sync(); tc::tmem_dealloc_2cta(tmem_base, 512); }
+}
+
+// quad kernel: 4 partial sums per row (2 column halves x 2 column groups)
+__global__ void head_finalize4_kernel(const float4* __restrict__ part, const float* __restrict__ bout, int NV, int SPW,
+                                      long long n_samples, float4* __restrict__ out) {
+  const long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n_samples) return;
+  const long long per_tile = 4LL * SPW;
+  const long long tile = s / per_tile;
+  const int j = (int)(s % per_tile);
+  const int row = (j / SPW) * 32 + (j % SPW) * NV;
+  const float4 a0 = part[(tile * 4 + 0) * 128 + row], a1 = part[(tile * 4 + 1) * 128 + row];
+  const float4 b0 = part[(tile * 4 + 2) * 128 + row], b1 = part[(tile * 4 + 3) * 128 + row];
+  // same association as the pair kernel: (half 0 + half 1) per column half, then the two halves, then the bias
+  const float o0 = (a0.x + a1.x) + (b0.x + b1.x) + bout[0], o1 = (a0.y + a1.y) + (b0.y + b1.y) + bout[1];
+  const float o2 = (a0.z + a1.z) + (b0.z + b1.z) + bout[2], o3 = (a0.w + a1.w) + (b0.w + b1.w) + bout[3];
+  out[s] = make_float4(1.f / (1.f + expf(-o0)), 1.f / (1.f + expf(-o1)), 1.f / (1.f + expf(-o2)), fmaxf(o3, 0.f));
+}
+
 // out[s] = [sigmoid, sigmoid, sigmoid, relu](partial_0 + partial_1 + b_out) read at the leader row of sample s
 __global__ void head_finalize_kernel(const float4* __restrict__ part, const float* __restrict__ bout, int NV, int SPW,
                                      long long n_samples, float4* __restrict__ out) {
@@ -470,13 +781,66 @@ DNR_EXPORT int dnr_mlp_pair_fwd(const void* lat_pk, const void* code_pk, const v
   return 0;
 }
 
+// The quad variant (clusters of 4 CTAs, tcgen05 cta_group::2; see above).  weights: the same 14 matrices as
+// dnr_mlp_pair_fwd but in the PK128 layout [N/128][K/8][128][8]; head_partial: [mv_tiles*4*128] float4
+// (dnr_head_finalize with n_partials = 4).
+DNR_EXPORT int dnr_mlp_quad_fwd(const void* lat_pk, const void* code_pk, const void* const* weights_pk128,
+                                const float* const* biases, const float* w_out, int NV, int mv_tiles,
+                                float* head_partial, long long* prof, cudaStream_t stream) {
+  DNR_REQUIRE(NV >= 1 && NV <= 4, "dnr_mlp_quad_fwd: NV must be in [1,4]");
+  DNR_REQUIRE(lat_pk && code_pk && weights_pk128 && biases && w_out && head_partial, "dnr_mlp_quad_fwd: null argument");
+  if (mv_tiles <= 0) return 0;
+  dnr::PairParams P;
+  P.lat_pk = (const unsigned char*)lat_pk; P.code_pk = (const unsigned char*)code_pk;
+  P.w_in = (const unsigned char*)weights_pk128[0];
+  for (int i = 0; i < 3; ++i) P.w_z[i] = (const unsigned char*)weights_pk128[1 + i];
+  for (int i = 0; i < 5; ++i) {
+    P.w_0[i] = (const unsigned char*)weights_pk128[4 + i]; P.w_1[i] = (const unsigned char*)weights_pk128[9 + i];
+  }
+  for (int i = 0; i < 6; ++i) P.cb[i] = biases[i];
+  for (int i = 0; i < 5; ++i) P.b_0[i] = biases[6 + i];
+  P.w_out = w_out; P.head_partial = (float4*)head_partial;
+  P.NV = NV; P.SPW = 32 / NV; P.mv_tiles = mv_tiles; P.prof = prof;
+  { const char* e = getenv("DNR_PAIR_FLAGS"); P.flags = e ? atoi(e) : 0; }
+  void (*kern)(const dnr::PairParams) = NV == 1 ? dnr::mlp_quad_fwd_kernel<1>
+                                         : NV == 2 ? dnr::mlp_quad_fwd_kernel<2>
+                                         : NV == 3 ? dnr::mlp_quad_fwd_kernel<3> : dnr::mlp_quad_fwd_kernel<4>;
+  static int max_clusters[5] = {0, 0, 0, 0, 0};
+  if (!max_clusters[NV]) {
+    DNR_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dnr::kQSmem),
+              "dnr_mlp_quad_fwd/attr");
+    // how many 4-CTA clusters the device can hold at once (GPCs whose SM count is not a multiple of 4 leave SMs idle)
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(4 * 37, 1, 1); cfg.blockDim = dim3(dnr::kPThreads, 1, 1); cfg.dynamicSmemBytes = dnr::kQSmem;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 4; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    int n = 0;
+    DNR_CHECK(cudaOccupancyMaxActiveClusters(&n, (const void*)kern, &cfg), "dnr_mlp_quad_fwd/occupancy");
+    DNR_REQUIRE(n >= 1, "dnr_mlp_quad_fwd: the device cannot hold a cluster of 4 CTAs with 225 KB of shared memory each");
+    max_clusters[NV] = n;
+  }
+  const int n_pairs = (mv_tiles + 1) / 2;
+  const int clusters = n_pairs < max_clusters[NV] ? n_pairs : max_clusters[NV];
+  kern<<<4 * clusters, dnr::kPThreads, dnr::kQSmem, stream>>>(P);
+  DNR_CHECK_LAUNCH("dnr_mlp_quad_fwd");
+  return 0;
+}
+
+// n_partials = 2 (dnr_mlp_pair_fwd) or 4 (dnr_mlp_quad_fwd) partial lin_out sums per row and tile.
 DNR_EXPORT int dnr_head_finalize(const float* head_partial, const float* bout, int NV, long long n_samples,
-                                 float* rgbsigma, cudaStream_t stream) {
+                                 int n_partials, float* rgbsigma, cudaStream_t stream) {
   DNR_REQUIRE(NV >= 1 && NV <= 8, "dnr_head_finalize: NV must be in [1,8]");
+  DNR_REQUIRE(n_partials == 2 || n_partials == 4, "dnr_head_finalize: n_partials must be 2 or 4");
   if (n_samples <= 0) return 0;
   const int blocks = (int)((n_samples + 255) / 256);
-  dnr::head_finalize_kernel<<<blocks, 256, 0, stream>>>((const float4*)head_partial, bout, NV, 32 / NV, n_samples,
-                                                       (float4*)rgbsigma);
+  if (n_partials == 2)
+    dnr::head_finalize_kernel<<<blocks, 256, 0, stream>>>((const float4*)head_partial, bout, NV, 32 / NV, n_samples,
+                                                         (float4*)rgbsigma);
+  else
+    dnr::head_finalize4_kernel<<<blocks, 256, 0, stream>>>((const float4*)head_partial, bout, NV, 32 / NV, n_samples,
+                                                          (float4*)rgbsigma);
   DNR_CHECK_LAUNCH("dnr_head_finalize");
   return 0;
 }

@@ -25,7 +25,8 @@ HID = 512
 IN_PAD = 64
 USE_FUSED_FORWARD = True     # tests flip this to compare the fused kernel with the per-layer path
 PAIR_PROF = None             # debug: int64 tensor [148*8] receiving cycle counters of the pair kernel
-FORWARD_KERNEL = "pair"      # inference MLP: "pair" (mlp_pair.cu) | "chain" (mlp_fused.cu) | "layers" (gemm.cu)
+# inference MLP: "quad" / "pair" (mlp_pair.cu: 4- / 2-CTA clusters) | "chain" (mlp_fused.cu) | "layers" (gemm.cu)
+FORWARD_KERNEL = "quad"
 
 
 def _mlp_signature(mlp):
@@ -78,6 +79,11 @@ class PackedMLP:
         self.cb = [t.contiguous() for t in cb]
         pb = [*self.cb, *self.b_0]
         self.pair_b_ptrs = (C.c_void_p * len(pb))(*[t.data_ptr() for t in pb])
+        # PK128 images of the forward weights for the quad kernel: [N/256][K/8][256][8] -> [N/128][K/8][128][8]
+        def to128(w, k_pad):
+            return w.view(-1, k_pad // 8, 2, 128, 8).permute(0, 2, 1, 3, 4).contiguous().view(-1)
+        self.w128 = [to128(self.w_in, IN_PAD)] + [to128(w, HID) for w in ws[1:]]
+        self.w128_ptrs = (C.c_void_p * len(self.w128))(*[t.data_ptr() for t in self.w128])
         if need_transposed:
             self.wt_z = [pack(l.weight, True) for l in mlp.lin_z]
             self.wt_0 = [pack(b.fc_0.weight, True) for b in mlp.blocks]
@@ -156,13 +162,18 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
     _lib.call("dnr_encode_fwd", p(rays), p(z), p(sc.poses), p(sc.focal), p(sc.cxy), p(sc.depth), p(sc.latent_nhwc),
               p(sc.freqs), p(sc.phases), *_encode_args(sc, NR, K, ray0, n), p(lat), p(code), st)
 
-    if not save and FORWARD_KERNEL == "pair" and NV <= 4:
-        # inference: CTA-pair kernel, residual stream in TMEM, lin_out fused (csrc/mlp_pair.cu)
-        part = torch.empty(mv * 2 * 128, 4, **f32)
-        _lib.call("dnr_mlp_pair_fwd", p(lat), p(code), pk.w_ptrs, pk.pair_b_ptrs, p(pk.w_out), NV, mv,
-                  p(part), p(PAIR_PROF), st)
+    if not save and FORWARD_KERNEL in ("quad", "pair") and NV <= 4:
+        # inference: CTA-cluster kernels, residual stream in TMEM, lin_out fused (csrc/mlp_pair.cu)
+        n_part = 4 if FORWARD_KERNEL == "quad" else 2
+        part = torch.empty(mv * n_part * 128, 4, **f32)
+        if n_part == 4:
+            _lib.call("dnr_mlp_quad_fwd", p(lat), p(code), pk.w128_ptrs, pk.pair_b_ptrs, p(pk.w_out), NV, mv,
+                      p(part), p(PAIR_PROF), st)
+        else:
+            _lib.call("dnr_mlp_pair_fwd", p(lat), p(code), pk.w_ptrs, pk.pair_b_ptrs, p(pk.w_out), NV, mv,
+                      p(part), p(PAIR_PROF), st)
         out = torch.empty(n_samples, 4, **f32)
-        _lib.call("dnr_head_finalize", p(part), p(pk.b_out), NV, n_samples, p(out), st)
+        _lib.call("dnr_head_finalize", p(part), p(pk.b_out), NV, n_samples, n_part, p(out), st)
         return out, None
     if not save and FORWARD_KERNEL != "layers":
         # inference: the whole ResnetFC in one persistent kernel, activations stay in L2 (csrc/mlp_fused.cu)

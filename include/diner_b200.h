@@ -130,8 +130,16 @@ int dnr_mlp_pair_fwd(const void* lat_pk, const void* code_pk, const void* const*
                      const float* w_out, int NV, int mv_tiles, float* head_partial,
                      long long* prof /* nullable: [grid][16] cycle counters */,
                      dnr_stream_t stream);
-int dnr_head_finalize(const float* head_partial, const float* bout, int NV, long long n_samples, float* rgbsigma,
-                      dnr_stream_t stream);
+/* The same on clusters of FOUR CTAs (2 row tiles x 2 column halves) with tcgen05.mma.cta_group::2: the two CTAs of a
+ * column half share every weight K-block, each streaming half of it, which halves the L2 -> SM traffic that bounds the
+ * pair kernel.  weights_pk128: the same 14 matrices in the PK128 layout [N/128][K/8][128][8] bf16;
+ * head_partial: [mv_tiles*4*128] float4. */
+int dnr_mlp_quad_fwd(const void* lat_pk, const void* code_pk, const void* const* weights_pk128,
+                     const float* const* biases, const float* w_out, int NV, int mv_tiles, float* head_partial,
+                     long long* prof /* nullable */, dnr_stream_t stream);
+/* n_partials = 2 after dnr_mlp_pair_fwd, 4 after dnr_mlp_quad_fwd. */
+int dnr_head_finalize(const float* head_partial, const float* bout, int NV, long long n_samples, int n_partials,
+                      float* rgbsigma, dnr_stream_t stream);
 
 /* Weight / bias gradient of one nn.Linear (autograd of F.linear in resnetfc.py):
  *   dW[n,k] += sum_rows dY[row,n] * X[row,k],  db[n] += sum_rows dY[row,n]

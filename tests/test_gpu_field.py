@@ -225,7 +225,7 @@ def test_inference_kernels_agree(golden_cache, name):
         pk = F_.get_packed(scene.model.mlp_fine, need_transposed=False)
         r, z = rays.view(-1, 8).to(dev), torch.from_numpy(g["z"]).view(-1, K).to(dev)
         outs = {}
-        for kern in ("layers", "chain", "pair"):
+        for kern in ("layers", "chain", "pair", "quad"):
             F_.FORWARD_KERNEL = kern
             outs[kern], _ = F_.field_forward(sc, pk, r, z, NR, 0, save=False)
             again, _ = F_.field_forward(sc, pk, r, z, NR, 0, save=False)     # scratch re-use: deterministic
@@ -233,6 +233,8 @@ def test_inference_kernels_agree(golden_cache, name):
             assert torch.isfinite(outs[kern]).all(), kern
             assert torch.equal(outs[kern], again), kern
         assert torch.equal(outs["chain"], outs["layers"])
+        # the quad kernel performs the pair kernel's arithmetic in the same order on twice the CTAs
+        assert torch.equal(outs["quad"], outs["pair"])
         a, b = outs["pair"], outs["layers"]
         smax = float(b[:, 3].max())
         assert float((a[:, :3] - b[:, :3]).abs().max()) < 1.5e-2 and float((a[:, :3] - b[:, :3]).abs().mean()) < 5e-4
