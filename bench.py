@@ -261,6 +261,8 @@ def main():
     torch.cuda.synchronize()
     per = {}
     for name, e0, e1, tag in _lib.profile:
+        if tag == "overlapped":              # runs on a second stream beside another kernel: not additive
+            name += " (overlapped)"
         d = per.setdefault(name, [0.0, 0])
         d[0] += e0.elapsed_time(e1); d[1] += 1
     _lib.profile = None
@@ -270,8 +272,10 @@ def main():
     n_samples = n_rays * wl.n_samples
     gemm_flops = 2.0 * (wl.NV * (55 * 512 + 9 * 512 * 512) + 4 * 512 * 512) * n_samples * (3.0 if args.train else 1.0)
     # every C-ABI call whose kernel runs the MLP's tcgen05 GEMMs (inference: one fused launch per chunk)
-    gemm_names = ("dnr_mlp_pair_fwd", "dnr_mlp_fused_fwd", "dnr_mlp_gemm", "dnr_mlp_wgrad")
-    kernel_name = ("mlp_pair_fwd_kernel (tcgen05, CTA pair, whole ResnetFC per launch)" if "dnr_mlp_pair_fwd" in breakdown
+    gemm_names = ("dnr_mlp_quad_fwd", "dnr_mlp_pair_fwd", "dnr_mlp_fused_fwd", "dnr_mlp_gemm", "dnr_mlp_wgrad")
+    kernel_name = ("mlp_quad_fwd_kernel (tcgen05 cta_group::2, 4-CTA clusters, whole ResnetFC per launch; "
+                   "mlp_pair_fwd_kernel on the spare SMs, overlapped)" if "dnr_mlp_quad_fwd" in breakdown
+                   else "mlp_pair_fwd_kernel (tcgen05, CTA pair, whole ResnetFC per launch)" if "dnr_mlp_pair_fwd" in breakdown
                    else "mlp_fused_fwd_kernel (tcgen05)" if "dnr_mlp_fused_fwd" in breakdown
                    else "mlp_gemm_kernel + mlp_wgrad_kernel (tcgen05)")
     gemm_ms = sum(breakdown[k]["ms_per_step"] for k in gemm_names if k in breakdown)

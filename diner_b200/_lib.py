@@ -42,7 +42,8 @@ _SIGNATURES = {
     "dnr_pack_weight": (c_i, [c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_p, c_p]),
     "dnr_head_fwd": (c_i, [c_p, c_p, c_p, c_ll, c_i, c_p, c_p]),
     "dnr_mlp_fused_scratch_bytes": (c_ll, [c_i]),
-    "dnr_mlp_pair_fwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_p, c_p, c_p]),
+    "dnr_mlp_pair_fwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_p, c_p, c_p]),
+    "dnr_mlp_quad_max_clusters": (c_i, [c_i]),
     "dnr_mlp_quad_fwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_p, c_p, c_p]),
     "dnr_head_finalize": (c_i, [c_p, c_p, c_i, c_ll, c_i, c_p, c_p]),
     "dnr_mlp_fused_fwd": (c_i, [c_p, c_p, c_p, c_p, c_i, c_i, c_ll, c_p, c_p, c_i, c_p]),

@@ -749,11 +749,13 @@ __global__ void head_finalize_kernel(const float4* __restrict__ part, const floa
 
 // Whole ResnetFC forward + lin_out partial sums on CTA pairs (see file header).  weights: 14 PK256 pointers
 // [lin_in, lin_z0..2, fc_0 x5, fc_1 x5]; biases: 11 fp32[512] pointers [cb0..cb5 (cumulative residual biases),
-// fc_0 bias x5]; w_out fp32 [4 x 512]; head_partial: [mv_tiles*2*128] float4.
+// fc_0 bias x5]; w_out fp32 [4 x 512]; head_partial: [mv_tiles*2*128] float4; max_clusters: 0 = all SM pairs, else
+// the number of clusters to launch (to run beside another kernel on the SMs that one leaves idle).
 DNR_EXPORT int dnr_mlp_pair_fwd(const void* lat_pk, const void* code_pk, const void* const* weights,
-                                const float* const* biases, const float* w_out, int NV, int mv_tiles,
+                                const float* const* biases, const float* w_out, int NV, int mv_tiles, int max_clusters,
                                 float* head_partial, long long* prof, cudaStream_t stream) {
   DNR_REQUIRE(NV >= 1 && NV <= 4, "dnr_mlp_pair_fwd: NV must be in [1,4]");
+  DNR_REQUIRE(max_clusters >= 0, "dnr_mlp_pair_fwd: max_clusters must be >= 0 (0 = one cluster per SM pair)");
   DNR_REQUIRE(lat_pk && code_pk && weights && biases && w_out && head_partial, "dnr_mlp_pair_fwd: null argument");
   if (mv_tiles <= 0) return 0;
   dnr::PairParams P;
@@ -775,11 +777,38 @@ DNR_EXPORT int dnr_mlp_pair_fwd(const void* lat_pk, const void* code_pk, const v
               "dnr_mlp_pair_fwd/attr");
     configured[NV] = true;
   }
-  int clusters = mv_tiles < 74 ? mv_tiles : 74;
+  const int cap = max_clusters > 0 && max_clusters < 74 ? max_clusters : 74;
+  int clusters = mv_tiles < cap ? mv_tiles : cap;
   kern<<<2 * clusters, dnr::kPThreads, dnr::kPSmem, stream>>>(P);
   DNR_CHECK_LAUNCH("dnr_mlp_pair_fwd");
   return 0;
 }
+
+namespace dnr {
+// how many 4-CTA clusters the device holds at once (GPCs whose SM count is not a multiple of 4 leave SMs idle); -1 on error
+static int quad_max_clusters(int NV) {
+  static int cached[5] = {0, 0, 0, 0, 0};
+  if (NV < 1 || NV > 4) return -1;
+  if (cached[NV]) return cached[NV];
+  void (*kern)(const PairParams) = NV == 1 ? mlp_quad_fwd_kernel<1> : NV == 2 ? mlp_quad_fwd_kernel<2>
+                                   : NV == 3 ? mlp_quad_fwd_kernel<3> : mlp_quad_fwd_kernel<4>;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kQSmem) != cudaSuccess) return -1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(4 * 37, 1, 1); cfg.blockDim = dim3(kPThreads, 1, 1); cfg.dynamicSmemBytes = kQSmem;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 4; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, (const void*)kern, &cfg) != cudaSuccess) return -1;
+  cached[NV] = n;
+  return n;
+}
+}  // namespace dnr
+
+// Number of 4-CTA clusters dnr_mlp_quad_fwd keeps resident (<= 37); the SMs beyond 4x that number stay idle and can
+// run dnr_mlp_pair_fwd clusters concurrently.  Negative on error.
+DNR_EXPORT int dnr_mlp_quad_max_clusters(int NV) { return dnr::quad_max_clusters(NV); }
 
 // The quad variant (clusters of 4 CTAs, tcgen05 cta_group::2; see above).  weights: the same 14 matrices as
 // dnr_mlp_pair_fwd but in the PK128 layout [N/128][K/8][128][8]; head_partial: [mv_tiles*4*128] float4
@@ -805,24 +834,10 @@ DNR_EXPORT int dnr_mlp_quad_fwd(const void* lat_pk, const void* code_pk, const v
   void (*kern)(const dnr::PairParams) = NV == 1 ? dnr::mlp_quad_fwd_kernel<1>
                                          : NV == 2 ? dnr::mlp_quad_fwd_kernel<2>
                                          : NV == 3 ? dnr::mlp_quad_fwd_kernel<3> : dnr::mlp_quad_fwd_kernel<4>;
-  static int max_clusters[5] = {0, 0, 0, 0, 0};
-  if (!max_clusters[NV]) {
-    DNR_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dnr::kQSmem),
-              "dnr_mlp_quad_fwd/attr");
-    // how many 4-CTA clusters the device can hold at once (GPCs whose SM count is not a multiple of 4 leave SMs idle)
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(4 * 37, 1, 1); cfg.blockDim = dim3(dnr::kPThreads, 1, 1); cfg.dynamicSmemBytes = dnr::kQSmem;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 4; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
-    int n = 0;
-    DNR_CHECK(cudaOccupancyMaxActiveClusters(&n, (const void*)kern, &cfg), "dnr_mlp_quad_fwd/occupancy");
-    DNR_REQUIRE(n >= 1, "dnr_mlp_quad_fwd: the device cannot hold a cluster of 4 CTAs with 225 KB of shared memory each");
-    max_clusters[NV] = n;
-  }
+  const int max_cl = dnr::quad_max_clusters(NV);
+  DNR_REQUIRE(max_cl >= 1, "dnr_mlp_quad_fwd: the device cannot hold a cluster of 4 CTAs with 225 KB of shared memory each");
   const int n_pairs = (mv_tiles + 1) / 2;
-  const int clusters = n_pairs < max_clusters[NV] ? n_pairs : max_clusters[NV];
+  const int clusters = n_pairs < max_cl ? n_pairs : max_cl;
   kern<<<4 * clusters, dnr::kPThreads, dnr::kQSmem, stream>>>(P);
   DNR_CHECK_LAUNCH("dnr_mlp_quad_fwd");
   return 0;

@@ -16,6 +16,8 @@ from __future__ import annotations
 
 from dataclasses import dataclass, field as dc_field
 
+import contextlib
+
 import torch
 
 from . import _lib
@@ -27,6 +29,12 @@ USE_FUSED_FORWARD = True     # tests flip this to compare the fused kernel with 
 PAIR_PROF = None             # debug: int64 tensor [148*8] receiving cycle counters of the pair kernel
 # inference MLP: "quad" / "pair" (mlp_pair.cu: 4- / 2-CTA clusters) | "chain" (mlp_fused.cu) | "layers" (gemm.cu)
 FORWARD_KERNEL = "quad"
+# With "quad": share of a chunk's tiles rendered by 2-CTA clusters on the SMs that the 4-CTA clusters cannot use
+# (the quad kernel keeps 33 clusters = 132 of 148 SMs resident on a B200), on a second stream.  0 disables; None =
+# spare * r / (spare * r + quad_clusters) with r = 0.40, the measured throughput of one pair cluster relative to one
+# quad cluster (14.3 vs 34.4 tiles/ms, profiles/r1_quad_kernel.md) rounded down: overshooting makes the pair kernel the tail.
+PAIR_SHARE = None
+_side_stream = {}
 
 
 def _mlp_signature(mlp):
@@ -164,16 +172,41 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
 
     if not save and FORWARD_KERNEL in ("quad", "pair") and NV <= 4:
         # inference: CTA-cluster kernels, residual stream in TMEM, lin_out fused (csrc/mlp_pair.cu)
-        n_part = 4 if FORWARD_KERNEL == "quad" else 2
-        part = torch.empty(mv * n_part * 128, 4, **f32)
-        if n_part == 4:
-            _lib.call("dnr_mlp_quad_fwd", p(lat), p(code), pk.w128_ptrs, pk.pair_b_ptrs, p(pk.w_out), NV, mv,
-                      p(part), p(PAIR_PROF), st)
-        else:
-            _lib.call("dnr_mlp_pair_fwd", p(lat), p(code), pk.w_ptrs, pk.pair_b_ptrs, p(pk.w_out), NV, mv,
-                      p(part), p(PAIR_PROF), st)
         out = torch.empty(n_samples, 4, **f32)
-        _lib.call("dnr_head_finalize", p(part), p(pk.b_out), NV, n_samples, n_part, p(out), st)
+        per_tile = 4 * (32 // NV)                                # samples per 128-row view tile (RowMap)
+        mv_q, spare = mv, 0
+        if FORWARD_KERNEL == "quad":
+            n_quad = _lib.load().dnr_mlp_quad_max_clusters(NV)
+            n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
+            spare = max(0, (n_sm - 4 * n_quad) // 2)             # SM pairs the quad kernel leaves idle
+            share = PAIR_SHARE if PAIR_SHARE is not None else 0.40 * spare / (0.40 * spare + n_quad)
+            if share > 0 and spare > 0 and mv >= 64 * spare:
+                mv_q = mv - max(2, int(mv * share)) // 2 * 2
+        else:
+            mv_q = 0
+        cur = torch.cuda.current_stream(dev)
+        side = None
+        if 0 < mv_q < mv:                                        # fork: the pair clusters run beside the quad clusters
+            side = _side_stream.setdefault(str(dev), torch.cuda.Stream(dev))
+            side.wait_stream(cur)
+        if mv_q > 0:
+            part_q = torch.empty(mv_q * 4 * 128, 4, **f32)
+            _lib.call("dnr_mlp_quad_fwd", p(lat), p(code), pk.w128_ptrs, pk.pair_b_ptrs, p(pk.w_out), NV, mv_q,
+                      p(part_q), p(PAIR_PROF), st)
+            _lib.call("dnr_head_finalize", p(part_q), p(pk.b_out), NV, min(n_samples, mv_q * per_tile), 4, p(out), st)
+        if mv_q < mv:
+            n_p = mv - mv_q
+            part_p = torch.empty(n_p * 2 * 128, 4, **f32)
+            s0 = mv_q * per_tile                                 # first sample of the pair clusters' tiles
+            lat_p, code_p, out_p = lat[mv_q * 128 * HID:], code[mv_q * 128 * IN_PAD:], out[s0:]
+            with torch.cuda.stream(side) if side is not None else contextlib.nullcontext():
+                st2 = _lib.stream_ptr()
+                _lib.call("dnr_mlp_pair_fwd", p(lat_p), p(code_p), pk.w_ptrs, pk.pair_b_ptrs, p(pk.w_out), NV, n_p,
+                          spare if side is not None else 0, p(part_p), p(PAIR_PROF) if mv_q == 0 else None, st2,
+                          tag="overlapped" if side is not None else None)
+                _lib.call("dnr_head_finalize", p(part_p), p(pk.b_out), NV, n_samples - s0, 2, p(out_p), st2)
+            if side is not None:
+                cur.wait_stream(side)                            # join
         return out, None
     if not save and FORWARD_KERNEL != "layers":
         # inference: the whole ResnetFC in one persistent kernel, activations stay in L2 (csrc/mlp_fused.cu)

@@ -127,8 +127,8 @@ int dnr_mlp_fused_fwd(const void* lat_pk, const void* code_pk, const void* const
  * cb0 = lin_in+lin_z0, cb1..5 = cb0 plus the cumulative fc_1 (+lin_z[b+1]) biases of blocks 0..4;
  * head_partial: [mv_tiles*2*128] float4, consumed by dnr_head_finalize (sigmoid / relu, pixelnerf.py:137-145). */
 int dnr_mlp_pair_fwd(const void* lat_pk, const void* code_pk, const void* const* weights, const float* const* biases,
-                     const float* w_out, int NV, int mv_tiles, float* head_partial,
-                     long long* prof /* nullable: [grid][16] cycle counters */,
+                     const float* w_out, int NV, int mv_tiles, int max_clusters /* 0 = all SM pairs */,
+                     float* head_partial, long long* prof /* nullable: [grid][16] cycle counters */,
                      dnr_stream_t stream);
 /* The same on clusters of FOUR CTAs (2 row tiles x 2 column halves) with tcgen05.mma.cta_group::2: the two CTAs of a
  * column half share every weight K-block, each streaming half of it, which halves the L2 -> SM traffic that bounds the
@@ -137,6 +137,9 @@ int dnr_mlp_pair_fwd(const void* lat_pk, const void* code_pk, const void* const*
 int dnr_mlp_quad_fwd(const void* lat_pk, const void* code_pk, const void* const* weights_pk128,
                      const float* const* biases, const float* w_out, int NV, int mv_tiles, float* head_partial,
                      long long* prof /* nullable */, dnr_stream_t stream);
+/* Number of 4-CTA clusters the quad kernel keeps resident; SMs beyond 4x that stay idle and can run
+ * dnr_mlp_pair_fwd clusters (max_clusters) on another stream at the same time. */
+int dnr_mlp_quad_max_clusters(int NV);
 /* n_partials = 2 after dnr_mlp_pair_fwd, 4 after dnr_mlp_quad_fwd. */
 int dnr_head_finalize(const float* head_partial, const float* bout, int NV, long long n_samples, int n_partials,
                       float* rgbsigma, dnr_stream_t stream);
