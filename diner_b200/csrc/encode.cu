@@ -87,9 +87,18 @@ __device__ __forceinline__ void row_geometry(const EncodeParams& P, long long sa
 constexpr int kEncWarps = 4;
 constexpr int kLatChunkStride = 144;   // 8 rows * 16 B + 16 B pad -> conflict-free staging
 
+// per-row tap description, produced by one lane per row and read back by the whole warp (broadcast LDS)
+struct __align__(16) RowTaps {
+  uint32_t p00, p01, p10, p11;      // element offsets of the four taps inside the (sb, view) map
+  float w00, w01, w10, w11;
+  float xc, yc, zc, dx, dy, dz, dd;
+  uint32_t map_plus1;               // (sb*NV + view) + 1, 0 = padding row
+};
+
 __global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams P) {
   __shared__ __align__(16) unsigned char stage_lat[kEncWarps][64 * kLatChunkStride];
   __shared__ __align__(16) unsigned char stage_in[kEncWarps][8 * 128];
+  __shared__ RowTaps taps_s[kEncWarps][8];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const RowMap rm = RowMap::make(P.NV);
   const long long group = (long long)blockIdx.x * kEncWarps + warp;   // 8-row group index
@@ -98,27 +107,42 @@ __global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams
   unsigned char* si = stage_in[warp];
   const int L = 512;
 
-  for (int i = 0; i < 8; ++i) {
-    const long long row = row_base + i;
+  // phase 1: lanes 0..7 run the projection chain of one row each (the eight chains overlap instead of running
+  // back to back on all 32 lanes)
+  if (lane < 8) {
     long long sample; int view;
-    const bool valid = rm.decode(row, P.n_samples, sample, view);
-    uint4 o0 = make_uint4(0, 0, 0, 0), o1 = o0;
-    float e0 = 0.f, e1 = 0.f;
-    if (valid) {
+    RowTaps tp;
+    tp.map_plus1 = 0;
+    if (rm.decode(row_base + lane, P.n_samples, sample, view)) {
       RowGeom g;
       row_geometry(P, sample, view, g);
-      const __nv_bfloat16* lat = P.latent + g.map * (size_t)P.Hl * P.Wl * L;
-      const size_t p00 = ((size_t)g.y0 * P.Wl + g.x0) * L, p01 = ((size_t)g.y0 * P.Wl + g.x1) * L;
-      const size_t p10 = ((size_t)g.y1 * P.Wl + g.x0) * L, p11 = ((size_t)g.y1 * P.Wl + g.x1) * L;
-      const float w00 = (1.f - g.wx) * (1.f - g.wy), w01 = g.wx * (1.f - g.wy);
-      const float w10 = (1.f - g.wx) * g.wy, w11 = g.wx * g.wy;
+      tp.p00 = (uint32_t)(((size_t)g.y0 * P.Wl + g.x0) * L); tp.p01 = (uint32_t)(((size_t)g.y0 * P.Wl + g.x1) * L);
+      tp.p10 = (uint32_t)(((size_t)g.y1 * P.Wl + g.x0) * L); tp.p11 = (uint32_t)(((size_t)g.y1 * P.Wl + g.x1) * L);
+      tp.w00 = (1.f - g.wx) * (1.f - g.wy); tp.w01 = g.wx * (1.f - g.wy);
+      tp.w10 = (1.f - g.wx) * g.wy; tp.w11 = g.wx * g.wy;
+      tp.xc = g.xc; tp.yc = g.yc; tp.zc = g.zc; tp.dx = g.dx; tp.dy = g.dy; tp.dz = g.dz; tp.dd = g.dd;
+      tp.map_plus1 = (uint32_t)g.map + 1u;
+    }
+    taps_s[warp][lane] = tp;
+  }
+  __syncwarp();
+
+  // phase 2: the warp gathers row after row, two rows' loads in flight
+#pragma unroll 2
+  for (int i = 0; i < 8; ++i) {
+    const RowTaps tp = taps_s[warp][i];
+    uint4 o0 = make_uint4(0, 0, 0, 0), o1 = o0;
+    float e0 = 0.f, e1 = 0.f;
+    if (tp.map_plus1) {
+      const __nv_bfloat16* lat = P.latent + (size_t)(tp.map_plus1 - 1) * (size_t)P.Hl * P.Wl * L;
+      const float w00 = tp.w00, w01 = tp.w01, w10 = tp.w10, w11 = tp.w11;
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
         const int ch = half * 256 + lane * 8;
-        const uint4 a = __ldg(reinterpret_cast<const uint4*>(lat + p00 + ch));
-        const uint4 b = __ldg(reinterpret_cast<const uint4*>(lat + p01 + ch));
-        const uint4 c = __ldg(reinterpret_cast<const uint4*>(lat + p10 + ch));
-        const uint4 d = __ldg(reinterpret_cast<const uint4*>(lat + p11 + ch));
+        const uint4 a = __ldg(reinterpret_cast<const uint4*>(lat + tp.p00 + ch));
+        const uint4 b = __ldg(reinterpret_cast<const uint4*>(lat + tp.p01 + ch));
+        const uint4 c = __ldg(reinterpret_cast<const uint4*>(lat + tp.p10 + ch));
+        const uint4 d = __ldg(reinterpret_cast<const uint4*>(lat + tp.p11 + ch));
         const uint32_t av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
         const uint32_t cv[4] = {c.x, c.y, c.z, c.w}, dv[4] = {d.x, d.y, d.z, d.w};
         uint32_t r[4];
@@ -137,14 +161,14 @@ __global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams
         float val = 0.f;
         const int npos = 3 + 6 * P.NF;          // 39
         const int ndep = 1 + 2 * P.NF;          // 13
-        if (e < 3) val = e == 0 ? g.xc : (e == 1 ? g.yc : g.zc);
+        if (e < 3) val = e == 0 ? tp.xc : (e == 1 ? tp.yc : tp.zc);
         else if (e < npos) {
           const int q = e - 3, j = q % 3, fs = q / 3;
-          const float x = j == 0 ? g.xc : (j == 1 ? g.yc : g.zc);
+          const float x = j == 0 ? tp.xc : (j == 1 ? tp.yc : tp.zc);
           val = sinf(__fadd_rn(P.phases[fs], __fmul_rn(x, P.freqs[fs])));
-        } else if (e < npos + 3) { const int j = e - npos; val = j == 0 ? g.dx : (j == 1 ? g.dy : g.dz); }
-        else if (e == npos + 3) val = g.dd;
-        else if (e < npos + 3 + ndep) { const int fs = e - (npos + 4); val = sinf(__fadd_rn(P.phases[fs], __fmul_rn(g.dd, P.freqs[fs]))); }
+        } else if (e < npos + 3) { const int j = e - npos; val = j == 0 ? tp.dx : (j == 1 ? tp.dy : tp.dz); }
+        else if (e == npos + 3) val = tp.dd;
+        else if (e < npos + 3 + ndep) { const int fs = e - (npos + 4); val = sinf(__fadd_rn(P.phases[fs], __fmul_rn(tp.dd, P.freqs[fs]))); }
         if (hh == 0) e0 = val; else e1 = val;
       }
     }
