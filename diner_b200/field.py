@@ -180,7 +180,7 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
             n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
             spare = max(0, (n_sm - 4 * n_quad) // 2)             # SM pairs the quad kernel leaves idle
             share = PAIR_SHARE if PAIR_SHARE is not None else 0.40 * spare / (0.40 * spare + n_quad)
-            if share > 0 and spare > 0 and mv >= 64 * spare:
+            if share > 0 and spare > 0 and (PAIR_SHARE is not None or mv >= 64 * spare):
                 mv_q = mv - max(2, int(mv * share)) // 2 * 2
         else:
             mv_q = 0
