@@ -444,10 +444,11 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
   uint64_t* peer_full = bars + 12;        // [6]  (even CTA) the odd CTA's operands of this ring step are in place
   uint64_t* accf = bars + 18;             // [2]  accumulator of op (parity) complete (multicast commit)
   uint64_t* a_peer = bars + 20;           // [2]  exchange partner's K-blocks {0,1} / {2,3} landed
-  uint64_t* a_own = bars + 22;            // [4]  own K-block p written (one arrival per epilogue warp)
+  uint64_t* a_own = bars + 22;            // [4]  own K-block p written (one arrival per epilogue warp; pusher waits here)
+  uint64_t* a_own2 = bars + 32;           // [4]  (even CTA) K-block p written in BOTH CTAs of the MMA pair (16 arrivals)
   uint64_t* pushed = bars + 26;           // [1]  partner received my whole half
   uint64_t* peer_free = bars + 27;        // [1]  partner's A buffer may receive my next operand
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 30);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 40);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t cr = tc::cluster_ctarank();
@@ -462,7 +463,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < kQRing; ++s) { tc::mbar_init(full + s, 1); tc::mbar_init(empty + s, 1); tc::mbar_init(peer_full + s, 1); }
     tc::mbar_init(accf + 0, 1); tc::mbar_init(accf + 1, 1);
-    for (int i = 0; i < 4; ++i) tc::mbar_init(a_own + i, 8);
+    for (int i = 0; i < 4; ++i) { tc::mbar_init(a_own + i, 8); tc::mbar_init(a_own2 + i, 16); }
     tc::mbar_init(a_peer + 0, 1); tc::mbar_init(a_peer + 1, 1);
     tc::mbar_init(pushed, 1); tc::mbar_init(peer_free, 1);
     tc::fence_barrier_init();
@@ -560,7 +561,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
             const uint32_t par = (uint32_t)(aops & 1);
             for (int i = 0; i < 8; ++i) {
               const int kb = pair_kb_order(h, i);
-              if (i < 4) TIMED(w_own, tc::mbar_wait(a_own + i, par));
+              if (i < 4) TIMED(w_own, tc::mbar_wait(a_own2 + i, par));
               if (i == 4) TIMED(w_peer, tc::mbar_wait(a_peer + 0, par));
               if (i == 6) TIMED(w_peer, tc::mbar_wait(a_peer + 1, par));
               TIMED(w_ring, tc::mbar_wait(full + slot, phase));
@@ -605,8 +606,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
           if (d.abuf_w) {
             const uint32_t par = (uint32_t)(aops & 1);
             for (int i = 0; i < 8; ++i) {
-              if (i < 4) tc::mbar_wait(a_own + i, par);
-              if (i == 4) tc::mbar_wait(a_peer + 0, par);
+              if (i == 4) tc::mbar_wait(a_peer + 0, par);     // (own K-blocks: the epilogue warps signal the even CTA directly)
               if (i == 6) tc::mbar_wait(a_peer + 1, par);
               forward();
             }
@@ -688,7 +688,10 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
             tc::fence_before_sync();
             tc::fence_proxy_async();
             __syncwarp();
-            if (lane == 0) tc::mbar_arrive(a_own + st);
+            if (lane == 0) {
+              tc::mbar_arrive(a_own + st);
+              tc::mbar_arrive_remote_relaxed(a_own2 + st, cr & ~1u);     // the MMA issuer of my pair
+            }
           }
         }
         w_kind[d.epi] += clock64() - tl0;
