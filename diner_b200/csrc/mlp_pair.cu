@@ -93,48 +93,52 @@ __device__ __forceinline__ float view_mean(float v, int lane) {
     v += __shfl_xor_sync(0xffffffffu, v, 2);
     return v * 0.25f;
   }
-  const int l0 = lane - lane % NV;
-  float s = __shfl_sync(0xffffffffu, v, l0);
-#pragma unroll
-  for (int dd = 1; dd < NV; ++dd) s += __shfl_sync(0xffffffffu, v, min(l0 + dd, 31));
-  return s / (float)NV;
+  // NV == 3: the two other rows of the sample with two shuffles; every lane adds in view order (a0 + a1) + a2 so the
+  // three rows of a sample hold the same bits.  Lanes 30, 31 are padding rows (SPW = 10).
+  const int r = lane % 3, l0 = lane - r;
+  const float x = __shfl_sync(0xffffffffu, v, min(l0 + (r == 2 ? 0 : r + 1), 31));      // a_{r+1 mod 3}
+  const float y = __shfl_sync(0xffffffffu, v, min(l0 + (r == 0 ? 2 : r - 1), 31));      // a_{r+2 mod 3}
+  const float A = r == 2 ? x : v, B = r == 0 ? x : y, C = r == 0 ? y : (r == 1 ? x : v);
+  return ((A + B) + C) * (1.0f / 3.0f);
 }
 
 // one 32-column piece of an activation epilogue: (+bias, [view mean], relu, bf16) -> resident A buffer
 template <int NV, bool POOLED>
-__device__ __forceinline__ void pair_act_stage(const uint32_t (&acc)[32], const float* __restrict__ bias, int lane,
-                                               unsigned char* dst_s) {
+__device__ __forceinline__ void pair_act_stage(uint32_t (&acc)[32], const float* __restrict__ bias, int lane,
+                                               unsigned char* dst_s, uint32_t taddr) {
+  if (POOLED) {
+    // x (pooled) = mean over the view rows (resnetfc.py:9-14,148-151), taken ONCE: the mean is written back over the
+    // per-view rows of the residual stream in TMEM.  Blocks 3-4 then add identical updates to identical rows, so
+    // every later read of the stream (fc_1 of blocks 3/4, the head) already sees the pooled value in all NV rows.
+#pragma unroll
+    for (int j = 0; j < 32; ++j) acc[j] = __float_as_uint(view_mean<NV>(__uint_as_float(acc[j]), lane));
+    tc::tmem_st32(taddr, acc);
+  }
 #pragma unroll
   for (int g = 0; g < 4; ++g) {
     const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + g * 8));
     const float4 b1 = __ldg(reinterpret_cast<const float4*>(bias + g * 8 + 4));
-    float v[8] = {__uint_as_float(acc[g * 8 + 0]) + b0.x, __uint_as_float(acc[g * 8 + 1]) + b0.y,
-                  __uint_as_float(acc[g * 8 + 2]) + b0.z, __uint_as_float(acc[g * 8 + 3]) + b0.w,
-                  __uint_as_float(acc[g * 8 + 4]) + b1.x, __uint_as_float(acc[g * 8 + 5]) + b1.y,
-                  __uint_as_float(acc[g * 8 + 6]) + b1.z, __uint_as_float(acc[g * 8 + 7]) + b1.w};
-    if (POOLED) {
-      // x (pooled) = mean over the view rows.  The per-view rows keep accumulating the (identical) block-3/4
-      // updates in TMEM, so the mean is re-taken whenever the stream is read (resnetfc.py:9-14,148-151).
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] = view_mean<NV>(v[j], lane);
-    }
+    const float v[8] = {__uint_as_float(acc[g * 8 + 0]) + b0.x, __uint_as_float(acc[g * 8 + 1]) + b0.y,
+                        __uint_as_float(acc[g * 8 + 2]) + b0.z, __uint_as_float(acc[g * 8 + 3]) + b0.w,
+                        __uint_as_float(acc[g * 8 + 4]) + b1.x, __uint_as_float(acc[g * 8 + 5]) + b1.y,
+                        __uint_as_float(acc[g * 8 + 6]) + b1.z, __uint_as_float(acc[g * 8 + 7]) + b1.w};
     const uint32_t w0 = pack_bf16x2(fmaxf(v[0], 0.f), fmaxf(v[1], 0.f)), w1 = pack_bf16x2(fmaxf(v[2], 0.f), fmaxf(v[3], 0.f));
     const uint32_t w2 = pack_bf16x2(fmaxf(v[4], 0.f), fmaxf(v[5], 0.f)), w3 = pack_bf16x2(fmaxf(v[6], 0.f), fmaxf(v[7], 0.f));
     *reinterpret_cast<uint4*>(dst_s + (size_t)g * 2048) = make_uint4(w0, w1, w2, w3);
   }
+  if (POOLED) tc::tmem_st_wait();       // before this warp signals the K-block: the next MMAs on X come after that signal
 }
 
-// one 32-column piece of the head: partial lin_out sums on the bf16-rounded relu(mean x) (contract of dnr_head_fwd)
-template <int NV>
+// one 32-column piece of the head: partial lin_out sums on the bf16-rounded relu(x) (contract of dnr_head_fwd); the
+// stream is already pooled (all NV rows of a sample equal, see pair_act_stage)
 __device__ __forceinline__ void pair_head_stage(const uint32_t (&acc)[32], const float* __restrict__ bias,
-                                                const float* __restrict__ wo, int lane, float& h0, float& h1, float& h2,
+                                                const float* __restrict__ wo, float& h0, float& h1, float& h2,
                                                 float& h3) {
 #pragma unroll
   for (int q = 0; q < 8; ++q) {
     const float4 b = __ldg(reinterpret_cast<const float4*>(bias + q * 4));
-    float v[4] = {__uint_as_float(acc[q * 4 + 0]) + b.x, __uint_as_float(acc[q * 4 + 1]) + b.y,
-                  __uint_as_float(acc[q * 4 + 2]) + b.z, __uint_as_float(acc[q * 4 + 3]) + b.w};
-    for (int j = 0; j < 4; ++j) v[j] = fmaxf(view_mean<NV>(v[j], lane), 0.f);
+    float v[4] = {fmaxf(__uint_as_float(acc[q * 4 + 0]) + b.x, 0.f), fmaxf(__uint_as_float(acc[q * 4 + 1]) + b.y, 0.f),
+                  fmaxf(__uint_as_float(acc[q * 4 + 2]) + b.z, 0.f), fmaxf(__uint_as_float(acc[q * 4 + 3]) + b.w, 0.f)};
     {   // round to bf16 two at a time (one packed convert instead of two quarter-rate scalar ones)
       const uint32_t p01 = pack_bf16x2(v[0], v[1]), p23 = pack_bf16x2(v[2], v[3]);
       v[0] = bf16lo(p01); v[1] = bf16hi(p01); v[2] = bf16lo(p23); v[3] = bf16hi(p23);
@@ -361,7 +365,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
         TIMED(w_acc, tc::mbar_wait(accf + (opc & 1), (uint32_t)((opc >> 1) & 1)));
         tc::fence_after_sync();
         const uint32_t t0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (d.acc_x ? x_col : (256u - x_col));
-        const bool pooled = d.acc_x && o >= 6;                 // residual stream after the view mean
+        const bool pooled = o == 6;                            // fc_1 of block 2: the view mean (taken once, written back)
         // the previous operand has left my half of the A buffer (pusher's bulk stores have read it)
         if (d.epi != EPI_HEAD && xops > 0) TIMED(w_push, tc::mbar_wait(pushed, (uint32_t)((xops - 1) & 1)));
         float hp0 = 0.f, hp1 = 0.f, hp2 = 0.f, hp3 = 0.f;
@@ -377,11 +381,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
           const float* bias = d.bias + (int)rank * 256 + nl0;
           if (d.epi == EPI_HEAD) {
             const float* wo = P.w_out + (int)rank * 256 + nl0;
-            pair_head_stage<NV>(acc, bias, wo, lane, hp0, hp1, hp2, hp3);
+            pair_head_stage(acc, bias, wo, hp0, hp1, hp2, hp3);
           } else {
             unsigned char* dst_s = abuf + ((size_t)rank * 32 + nl0 / 8) * 2048 + (size_t)row * 16;
-            if (pooled) pair_act_stage<NV, true>(acc, bias, lane, dst_s);
-            else pair_act_stage<NV, false>(acc, bias, lane, dst_s);
+            if (pooled) pair_act_stage<NV, true>(acc, bias, lane, dst_s, t0 + nl0);
+            else pair_act_stage<NV, false>(acc, bias, lane, dst_s, t0 + nl0);
             // my part of K-block (half*2 + st) is in shared memory: order it before the MMAs (async proxy) and
             // before the pusher's bulk copy, then one arrival per warp
             const long long t__ = clock64();
@@ -668,7 +672,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
         TIMED(w_acc, tc::mbar_wait(accf + (opc & 1), (uint32_t)((opc >> 1) & 1)));
         tc::fence_after_sync();
         const uint32_t t0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (d.acc_x ? x_col : (256u - x_col));
-        const bool pooled = d.acc_x && o >= 6;
+        const bool pooled = o == 6;
         if (d.epi != EPI_HEAD && xops > 0) tc::mbar_wait(pushed, (uint32_t)((xops - 1) & 1));
         float hp0 = 0.f, hp1 = 0.f, hp2 = 0.f, hp3 = 0.f;
         const long long tl0 = clock64();
@@ -680,11 +684,11 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
           tc::tmem_ld_wait();
           const float* bias = d.bias + h * 256 + nl0;
           if (d.epi == EPI_HEAD) {
-            pair_head_stage<NV>(acc, bias, P.w_out + h * 256 + nl0, lane, hp0, hp1, hp2, hp3);
+            pair_head_stage(acc, bias, P.w_out + h * 256 + nl0, hp0, hp1, hp2, hp3);
           } else {
             unsigned char* dst_s = abuf + ((size_t)h * 32 + nl0 / 8) * 2048 + (size_t)row * 16;
-            if (pooled) pair_act_stage<NV, true>(acc, bias, lane, dst_s);
-            else pair_act_stage<NV, false>(acc, bias, lane, dst_s);
+            if (pooled) pair_act_stage<NV, true>(acc, bias, lane, dst_s, t0 + nl0);
+            else pair_act_stage<NV, false>(acc, bias, lane, dst_s, t0 + nl0);
             tc::fence_before_sync();
             tc::fence_proxy_async();
             __syncwarp();

@@ -5,7 +5,9 @@ import torch
 from diner_b200 import NeRFRendererDGS, field as F_
 from diner_b200.synthetic import make_scene
 
-scene = make_scene("facescape", seed=0)
+scene = make_scene(os.environ.get("DNR_WORKLOAD", "facescape"), seed=0)
+if os.environ.get("DNR_KERNEL"):
+    F_.FORWARD_KERNEL = os.environ["DNR_KERNEL"]
 wl = scene.workload
 m = scene.model.to_device("cuda")
 r = NeRFRendererDGS(wl.n_samples, wl.n_candidates, wl.n_gaussian, white_bkgd=True)
