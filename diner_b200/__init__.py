@@ -1,7 +1,9 @@
 """diner_b200 -- B200-native implementation of DINER's per-ray rendering hot path.
 
-Public API (mirrors the reference plugin, src/models/nerf_renderer.py): `NeRFRendererDGS`.
+Public API (mirrors the reference plugin, src/models/nerf_renderer.py): `NeRFRendererDGS`; and the two input
+producers next to it with the reference's signatures: `gen_rays`, `depth2normal`.
 """
+from .producers import depth2normal, gen_rays  # noqa: F401
 from .renderer import NeRFRendererDGS, RenderResult, sample_rays  # noqa: F401
 
-__all__ = ["NeRFRendererDGS", "RenderResult", "sample_rays"]
+__all__ = ["NeRFRendererDGS", "RenderResult", "sample_rays", "gen_rays", "depth2normal"]

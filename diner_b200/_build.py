@@ -21,6 +21,7 @@ SOURCES = [
     ("mlp_fused.cu", []),
     ("mlp_pair.cu", []),
     ("wgrad.cu", []),
+    ("producers.cu", []),
     ("mlp_misc.cu", []),
 ]
 COMMON = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

@@ -179,6 +179,18 @@ int dnr_composite_bwd(const float* rgbsigma, const float* z, const float* rays, 
                       const float* d_depth, const float* d_weights, int n_rays, int K, int white_bkgd,
                       float* d_rgbsigma, dnr_stream_t stream);
 
+/* ---- input producers next to the path ---------------------------------------------------- */
+
+/* Pixel-centre rays of B target cameras: rays [B,H,W,8] = [origin 3 | unit direction 3 | near | far] from world->cam
+ * extrinsics [B,4,4], intrinsics [B,3,3], z_near / z_far [B].  Replaces gen_rays (src/util/cam_geometry.py:36-79). */
+int dnr_gen_rays(const float* extrinsics, const float* intrinsics, int B, int W, int H, const float* z_near,
+                 const float* z_far, float* rays, dnr_stream_t stream);
+
+/* Camera-space normal maps [N,3,H,W] from depth maps [N,1,H,W] and intrinsics [N,3,3] by central differences of the
+ * back-projected points, with the reference's hole-cleaning rule and NaN behaviour.  Replaces depth2normal
+ * (src/util/depth2normal.py:6-87) including the axis its torch.cross (no dim) takes when N == 3. */
+int dnr_depth2normal(const float* dmap, const float* K, int N, int H, int W, float* normal, dnr_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
