@@ -104,8 +104,9 @@ __device__ __forceinline__ float view_mean(float v, int lane) {
 
 // one 32-column piece of an activation epilogue: (+bias, [view mean], relu, bf16) -> resident A buffer
 template <int NV, bool POOLED>
-__device__ __forceinline__ void pair_act_stage(uint32_t (&acc)[32], const float* __restrict__ bias, int lane,
-                                               unsigned char* dst_s, uint32_t taddr) {
+__device__ __forceinline__ void pair_act_stage(uint32_t (&acc)[32], const float4 (&bq)[8],
+                                               const float* __restrict__ bias, int lane, unsigned char* dst_s,
+                                               uint32_t taddr) {
   if (POOLED) {
     // x (pooled) = mean over the view rows (resnetfc.py:9-14,148-151), taken ONCE: the mean is written back over the
     // per-view rows of the residual stream in TMEM.  Blocks 3-4 then add identical updates to identical rows, so
@@ -116,8 +117,9 @@ __device__ __forceinline__ void pair_act_stage(uint32_t (&acc)[32], const float*
   }
 #pragma unroll
   for (int g = 0; g < 4; ++g) {
-    const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + g * 8));
-    const float4 b1 = __ldg(reinterpret_cast<const float4*>(bias + g * 8 + 4));
+    // biases: prefetched into registers by the caller, except for NV = 3 whose three-way mean needs the registers
+    const float4 b0 = NV == 3 ? __ldg(reinterpret_cast<const float4*>(bias) + 2 * g) : bq[2 * g];
+    const float4 b1 = NV == 3 ? __ldg(reinterpret_cast<const float4*>(bias) + 2 * g + 1) : bq[2 * g + 1];
     const float v[8] = {__uint_as_float(acc[g * 8 + 0]) + b0.x, __uint_as_float(acc[g * 8 + 1]) + b0.y,
                         __uint_as_float(acc[g * 8 + 2]) + b0.z, __uint_as_float(acc[g * 8 + 3]) + b0.w,
                         __uint_as_float(acc[g * 8 + 4]) + b1.x, __uint_as_float(acc[g * 8 + 5]) + b1.y,
@@ -131,12 +133,12 @@ __device__ __forceinline__ void pair_act_stage(uint32_t (&acc)[32], const float*
 
 // one 32-column piece of the head: partial lin_out sums on the bf16-rounded relu(x) (contract of dnr_head_fwd); the
 // stream is already pooled (all NV rows of a sample equal, see pair_act_stage)
-__device__ __forceinline__ void pair_head_stage(const uint32_t (&acc)[32], const float* __restrict__ bias,
+__device__ __forceinline__ void pair_head_stage(const uint32_t (&acc)[32], const float4 (&bq)[8],
                                                 const float* __restrict__ wo, float& h0, float& h1, float& h2,
                                                 float& h3) {
 #pragma unroll
   for (int q = 0; q < 8; ++q) {
-    const float4 b = __ldg(reinterpret_cast<const float4*>(bias + q * 4));
+    const float4 b = bq[q];
     float v[4] = {fmaxf(__uint_as_float(acc[q * 4 + 0]) + b.x, 0.f), fmaxf(__uint_as_float(acc[q * 4 + 1]) + b.y, 0.f),
                   fmaxf(__uint_as_float(acc[q * 4 + 2]) + b.z, 0.f), fmaxf(__uint_as_float(acc[q * 4 + 3]) + b.w, 0.f)};
     {   // round to bf16 two at a time (one packed convert instead of two quarter-rate scalar ones)
@@ -374,18 +376,25 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
         for (int st = 0; st < 4; ++st) {                       // four 32-column pieces; the two halves share K-block st
           uint32_t acc[32];
           const int nl0 = st * 64 + half * 32;                 // first column inside the CTA's 256
-          { const long long t__ = clock64();
           tc::tmem_ld32(t0 + nl0, acc);
+          float4 bq[8];                                        // the piece's biases travel while the TMEM load does
+          if (NV != 3) {                                       // (NV = 3: the three-way mean needs the registers)
+#pragma unroll
+            for (int g = 0; g < 8; ++g) bq[g] = __ldg(reinterpret_cast<const float4*>(d.bias + (int)rank * 256 + nl0) + g);
+          }
           tc::tmem_ld_wait();
-          w_fence += clock64() - t__; }
           const float* bias = d.bias + (int)rank * 256 + nl0;
+          if (NV == 3 && d.epi == EPI_HEAD) {
+#pragma unroll
+            for (int g = 0; g < 8; ++g) bq[g] = __ldg(reinterpret_cast<const float4*>(bias) + g);
+          }
           if (d.epi == EPI_HEAD) {
             const float* wo = P.w_out + (int)rank * 256 + nl0;
-            pair_head_stage(acc, bias, wo, hp0, hp1, hp2, hp3);
+            pair_head_stage(acc, bq, wo, hp0, hp1, hp2, hp3);
           } else {
             unsigned char* dst_s = abuf + ((size_t)rank * 32 + nl0 / 8) * 2048 + (size_t)row * 16;
-            if (pooled) pair_act_stage<NV, true>(acc, bias, lane, dst_s, t0 + nl0);
-            else pair_act_stage<NV, false>(acc, bias, lane, dst_s, t0 + nl0);
+            if (pooled) pair_act_stage<NV, true>(acc, bq, bias, lane, dst_s, t0 + nl0);
+            else pair_act_stage<NV, false>(acc, bq, bias, lane, dst_s, t0 + nl0);
             // my part of K-block (half*2 + st) is in shared memory: order it before the MMAs (async proxy) and
             // before the pusher's bulk copy, then one arrival per warp
             const long long t__ = clock64();
@@ -673,7 +682,6 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
         tc::fence_after_sync();
         const uint32_t t0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (d.acc_x ? x_col : (256u - x_col));
         const bool pooled = o == 6;
-        if (d.epi != EPI_HEAD && xops > 0) tc::mbar_wait(pushed, (uint32_t)((xops - 1) & 1));
         float hp0 = 0.f, hp1 = 0.f, hp2 = 0.f, hp3 = 0.f;
         const long long tl0 = clock64();
 #pragma unroll 1
@@ -681,14 +689,25 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
           uint32_t acc[32];
           const int nl0 = st * 64 + half * 32;
           tc::tmem_ld32(t0 + nl0, acc);
+          float4 bq[8];                                        // the piece's biases travel while the TMEM load does
+          if (NV != 3) {                                       // (NV = 3: the three-way mean needs the registers)
+#pragma unroll
+            for (int g = 0; g < 8; ++g) bq[g] = __ldg(reinterpret_cast<const float4*>(d.bias + h * 256 + nl0) + g);
+          }
+          // the previous operand has left my half of the A buffer (the pusher's bulk copies have read it)
+          if (st == 0 && d.epi != EPI_HEAD && xops > 0) tc::mbar_wait(pushed, (uint32_t)((xops - 1) & 1));
           tc::tmem_ld_wait();
           const float* bias = d.bias + h * 256 + nl0;
+          if (NV == 3 && d.epi == EPI_HEAD) {
+#pragma unroll
+            for (int g = 0; g < 8; ++g) bq[g] = __ldg(reinterpret_cast<const float4*>(bias) + g);
+          }
           if (d.epi == EPI_HEAD) {
-            pair_head_stage(acc, bias, P.w_out + h * 256 + nl0, hp0, hp1, hp2, hp3);
+            pair_head_stage(acc, bq, P.w_out + h * 256 + nl0, hp0, hp1, hp2, hp3);
           } else {
             unsigned char* dst_s = abuf + ((size_t)h * 32 + nl0 / 8) * 2048 + (size_t)row * 16;
-            if (pooled) pair_act_stage<NV, true>(acc, bias, lane, dst_s, t0 + nl0);
-            else pair_act_stage<NV, false>(acc, bias, lane, dst_s, t0 + nl0);
+            if (pooled) pair_act_stage<NV, true>(acc, bq, bias, lane, dst_s, t0 + nl0);
+            else pair_act_stage<NV, false>(acc, bq, bias, lane, dst_s, t0 + nl0);
             tc::fence_before_sync();
             tc::fence_proxy_async();
             __syncwarp();
