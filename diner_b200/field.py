@@ -31,8 +31,9 @@ PAIR_PROF = None             # debug: int64 tensor [148*8] receiving cycle count
 FORWARD_KERNEL = "quad"
 # With "quad": share of a chunk's tiles rendered by 2-CTA clusters on the SMs that the 4-CTA clusters cannot use
 # (the quad kernel keeps 33 clusters = 132 of 148 SMs resident on a B200), on a second stream.  0 disables; None =
-# spare * r / (spare * r + quad_clusters) with r = 0.40, the measured throughput of one pair cluster relative to one
-# quad cluster (14.3 vs 34.4 tiles/ms, profiles/r1_quad_kernel.md) rounded down: overshooting makes the pair kernel the tail.
+# spare * r / (spare * r + quad_clusters) with r = 0.37: one pair cluster renders 0.40-0.42 of what one quad cluster does
+# (14.3 vs 34.4 tiles/ms, profiles/r1_quad_kernel.md); rounded down because a late pair kernel is the tail of the step
+# while an early one only idles 16 SMs.
 PAIR_SHARE = None
 _side_stream = {}
 
@@ -179,7 +180,7 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
             n_quad = _lib.load().dnr_mlp_quad_max_clusters(NV)
             n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
             spare = max(0, (n_sm - 4 * n_quad) // 2)             # SM pairs the quad kernel leaves idle
-            share = PAIR_SHARE if PAIR_SHARE is not None else 0.40 * spare / (0.40 * spare + n_quad)
+            share = PAIR_SHARE if PAIR_SHARE is not None else 0.37 * spare / (0.37 * spare + n_quad)
             if share > 0 and spare > 0 and (PAIR_SHARE is not None or mv >= 64 * spare):
                 mv_q = mv - max(2, int(mv * share)) // 2 * 2
         else:
