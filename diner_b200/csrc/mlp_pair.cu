@@ -20,7 +20,6 @@
 //                 complete one 64-column K-block per piece so the next layer's MMAs start after a quarter epilogue)
 #include "common.cuh"
 #include "tc05.cuh"
-#include <stdlib.h>
 
 namespace dnr {
 
@@ -45,7 +44,6 @@ struct PairParams {
   float4* head_partial;           // [mv_tiles][2][128]: partial lin_out sums of each CTA's 256 columns
   int NV, SPW, mv_tiles;
   long long* prof;                // optional [gridDim][8] cycle counters (debug)
-  int flags;                      // DNR_PAIR_FLAGS (development): bit 0 = probe the latency of one bulk copy from L2
 };
 
 enum { EPI_X = 0, EPI_T = 1, EPI_MEAN = 2, EPI_HEAD = 3 };
@@ -183,7 +181,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
     for (int i = 0; i < 4; ++i) tc::mbar_init(a_own + i, 8);
     tc::mbar_init(a_peer + 0, 1); tc::mbar_init(a_peer + 1, 1);
     tc::mbar_init(pushed, 1); tc::mbar_init(peer_free, 1);
-    tc::mbar_init(bars + 18, 1);
     tc::fence_barrier_init();
   }
   if (warp == 1) tc::tmem_alloc(tmem_slot, 512);
@@ -206,20 +203,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
         if (++slot == kPRing) { slot = 0; phase ^= 1; }
       };
       POp d;
-      if ((P.flags & 1) && P.prof) {          // probe: latency of one bulk copy from L2 into an idle ring slot
-        long long* pr = P.prof + (size_t)blockIdx.x * 16;
-        uint32_t ph = 0;
-        for (int it = 0; it < 6; ++it) {
-          const uint32_t bytes = it < 3 ? 32768u : 16384u;
-          const long long t0 = clock64();
-          tc::mbar_arrive_expect_tx(bars + 18, bytes);
-          tc::bulk_g2s_hint(ring, P.w_0[4] + (size_t)rank * 262144 + (size_t)(it % 3) * 32768, bytes, bars + 18, pol_keep);
-          tc::mbar_wait(bars + 18, ph); ph ^= 1;
-          if (it == 1) pr[13] = clock64() - t0;     // second 32 KB load (first one may miss L2)
-          if (it == 2) pr[14] = clock64() - t0;
-          if (it == 5) pr[15] = clock64() - t0;     // 16 KB load
-        }
-      }
       for (int tile = cluster; tile < P.mv_tiles; tile += n_clusters) {
         const unsigned char* lat = P.lat_pk + (size_t)tile * 131072;
         if (tile + n_clusters < P.mv_tiles) {     // pull the next tile's inputs from HBM into L2 while this one computes
@@ -793,7 +776,6 @@ DNR_EXPORT int dnr_mlp_pair_fwd(const void* lat_pk, const void* code_pk, const v
   for (int i = 0; i < 5; ++i) P.b_0[i] = biases[6 + i];
   P.w_out = w_out; P.head_partial = (float4*)head_partial;
   P.NV = NV; P.SPW = 32 / NV; P.mv_tiles = mv_tiles; P.prof = prof;
-  { const char* e = getenv("DNR_PAIR_FLAGS"); P.flags = e ? atoi(e) : 0; }
   void (*kern)(const dnr::PairParams) = NV == 1 ? dnr::mlp_pair_fwd_kernel<1>
                                          : NV == 2 ? dnr::mlp_pair_fwd_kernel<2>
                                          : NV == 3 ? dnr::mlp_pair_fwd_kernel<3> : dnr::mlp_pair_fwd_kernel<4>;
@@ -856,7 +838,6 @@ DNR_EXPORT int dnr_mlp_quad_fwd(const void* lat_pk, const void* code_pk, const v
   for (int i = 0; i < 5; ++i) P.b_0[i] = biases[6 + i];
   P.w_out = w_out; P.head_partial = (float4*)head_partial;
   P.NV = NV; P.SPW = 32 / NV; P.mv_tiles = mv_tiles; P.prof = prof;
-  { const char* e = getenv("DNR_PAIR_FLAGS"); P.flags = e ? atoi(e) : 0; }
   void (*kern)(const dnr::PairParams) = NV == 1 ? dnr::mlp_quad_fwd_kernel<1>
                                          : NV == 2 ? dnr::mlp_quad_fwd_kernel<2>
                                          : NV == 3 ? dnr::mlp_quad_fwd_kernel<3> : dnr::mlp_quad_fwd_kernel<4>;

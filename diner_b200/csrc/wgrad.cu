@@ -10,7 +10,6 @@
 // extra N=16 MMA per K step against a constant tile of ones.
 #include "common.cuh"
 #include "tc05.cuh"
-#include <stdlib.h>
 
 namespace dnr {
 
@@ -157,9 +156,7 @@ DNR_EXPORT int dnr_mlp_wgrad(const void* dY_pk, int Fy, const void* X_pk, int Fx
   dnr::WgradParams P;
   P.dY = (const unsigned char*)dY_pk; P.X = (const unsigned char*)X_pk; P.Fy = Fy; P.Fx = Fx;
   P.NB = Fx < 256 ? Fx : 256;
-  { const char* e = getenv("DNR_WG_NB"); if (e && Fx >= 256) P.NB = atoi(e); }
   P.copy_piece = P.NB * 256;
-  { const char* e = getenv("DNR_WG_PIECE"); if (e) { int v = atoi(e); if (v > 0 && v < P.copy_piece) P.copy_piece = v; } }
   P.row_tiles = row_tiles; P.dW = dW; P.ldw = ldw; P.n_valid = n_valid; P.k_valid = k_valid; P.db = db;
   const int out_tiles = (Fy / 128) * (Fx / P.NB);
   static int num_sms = 0;
