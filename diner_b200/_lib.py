@@ -11,7 +11,7 @@ import os
 from . import _build
 
 _lib = None
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 # instrumentation used by bench.py: number of kernel launches issued through the ABI, and (when `profile` is a
 # list) one (name, start_event, end_event, tag) record per call for per-kernel CUDA-event timing
@@ -46,7 +46,8 @@ _SIGNATURES = {
     "dnr_mlp_fused_scratch_bytes": (c_ll, [c_i]),
     "dnr_mlp_pair_fwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_p, c_p, c_p]),
     "dnr_mlp_quad_max_clusters": (c_i, [c_i]),
-    "dnr_mlp_quad_fwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_p, c_p, c_p]),
+    "dnr_mlp_quad_scratch_bytes": (c_ll, []),
+    "dnr_mlp_quad_fwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_p, c_p, c_p, c_p]),
     "dnr_head_finalize": (c_i, [c_p, c_p, c_i, c_ll, c_i, c_p, c_p]),
     "dnr_mlp_fused_fwd": (c_i, [c_p, c_p, c_p, c_p, c_i, c_i, c_ll, c_p, c_p, c_i, c_p]),
     "dnr_head_bwd": (c_i, [c_p, c_p, c_p, c_p, c_ll, c_p, c_p, c_p, c_p]),

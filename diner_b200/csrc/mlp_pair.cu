@@ -42,6 +42,7 @@ struct PairParams {
   const float* b_0[5];
   const float* w_out;             // fp32 [4 x 512]
   float4* head_partial;           // [mv_tiles][2][128]: partial lin_out sums of each CTA's 256 columns
+  float* merge_scratch;           // quad kernel, MERGE: [gridDim][128 rows][256] fp32 parked pooled rows
   int NV, SPW, mv_tiles;
   long long* prof;                // optional [gridDim][8] cycle counters (debug)
 };
@@ -429,7 +430,15 @@ constexpr int kQRing = 6;
 constexpr int kQSlot = 16384;
 constexpr size_t kQSmem = (size_t)kPAbuf + kQRing * kQSlot + 512;
 
-template <int NV>
+// MERGE (NV > 1): after the view mean only 128/NV rows of a tile are distinct, so a CTA parks the pooled rows of NV
+// consecutive tiles (fp32, in an L2-resident scratch), merges them into ONE full tile and runs blocks 3-4 + the head
+// once per NV tiles instead of on NV-fold duplicated rows.  `last` = this iteration closes its group.
+template <int NV, bool MERGE>
+__device__ __forceinline__ bool quad_last(int it, int q, int n_clusters, int n_pairs) {
+  return !MERGE || (it % NV) == NV - 1 || q + n_clusters >= n_pairs;
+}
+
+template <int NV, bool MERGE>
 __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_quad_fwd_kernel(const PairParams P) {
   extern __shared__ __align__(128) unsigned char smem[];
   unsigned char* abuf = smem;                                   // 128 KB resident A operand
@@ -486,7 +495,8 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
         if (++slot == kQRing) { slot = 0; phase ^= 1; }
       };
       POp d;
-      for (int q = cluster; q < n_pairs; q += n_clusters) {
+      for (int q = cluster, it = 0; q < n_pairs; q += n_clusters, ++it) {
+        const int n_ops = quad_last<NV, MERGE>(it, q, n_clusters, n_pairs) ? kPOps : 7;
         const int tile = tile_of(q);
         const unsigned char* lat = P.lat_pk + (size_t)tile * 131072;
         if (q + n_clusters < n_pairs) {           // pull the next tile's inputs from HBM into L2 while this one computes
@@ -494,7 +504,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
           tc::bulk_prefetch_l2(P.lat_pk + (size_t)nt * 131072, 131072);
           tc::bulk_prefetch_l2(P.code_pk + (size_t)nt * 16384, 16384);
         }
-        for (int o = 0; o < kPOps; ++o) {
+        for (int o = 0; o < n_ops; ++o) {
           pair_get_op(P, o, d);
           if (d.code) {
             fill(P.code_pk + (size_t)tile * 16384, pol_stream);
@@ -526,7 +536,8 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
       long long w_ring = 0, w_own = 0, w_peer = 0, w_pfull = 0, w_ring_lat = 0, w_pfull_lat = 0, t_start = clock64();
       for (int q = cluster; q < n_pairs; q += n_clusters, ++titer) {
         const uint32_t x_col = (titer & 1) ? 256u : 0u;           // X / T swap regions every tile
-        for (int o = 0; o < kPOps; ++o, ++opc) {
+        const int n_ops = quad_last<NV, MERGE>(titer, q, n_clusters, n_pairs) ? kPOps : 7;
+        for (int o = 0; o < n_ops; ++o, ++opc) {
           pair_get_op(P, o, d);
           const uint32_t d_tmem = tmem_base + (d.acc_x ? x_col : (256u - x_col));
           uint32_t accumulate = d.fresh ? 0u : 1u;
@@ -593,8 +604,9 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
         tc::mbar_arrive_remote_relaxed(peer_full + slot, mma_peer);
         if (++slot == kQRing) { slot = 0; phase ^= 1; }
       };
-      for (int q = cluster; q < n_pairs; q += n_clusters) {
-        for (int o = 0; o < kPOps; ++o) {
+      for (int q = cluster, it = 0; q < n_pairs; q += n_clusters, ++it) {
+        const int n_ops = quad_last<NV, MERGE>(it, q, n_clusters, n_pairs) ? kPOps : 7;
+        for (int o = 0; o < n_ops; ++o) {
           pair_get_op(P, o, d);
           if (d.code) { forward(); forward(); }
           if (d.lat_w)
@@ -617,8 +629,11 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
     if (lane == 0) {
       int xops = 0;
       unsigned char* mine = abuf + (size_t)h * 65536;
-      for (int q = cluster; q < n_pairs; q += n_clusters) {
-        for (int o = 0; o < kPOps - 1; ++o, ++xops) {          // every op but the head produces an A operand
+      for (int q = cluster, it = 0; q < n_pairs; q += n_clusters, ++it) {
+        // A operands produced per iteration: by the epilogues of ops 0..5, and - when the iteration closes its group -
+        // by the merge after op 6 and the epilogues of ops 7..9
+        const int n_events = quad_last<NV, MERGE>(it, q, n_clusters, n_pairs) ? kPOps - 1 : 6;
+        for (int o = 0; o < n_events; ++o, ++xops) {
           for (int st = 0; st < 2; ++st) {
             tc::mbar_wait(a_own + 2 * st + 1, (uint32_t)(xops & 1));
             if (st == 0) tc::mbar_wait(peer_free, (uint32_t)(xops & 1));
@@ -631,9 +646,11 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
     // ================= receiver: arm the landing barriers, grant the credit, acknowledge =================
     if (lane == 0) {
       int opc = 0, xops = 0;
-      for (int q = cluster; q < n_pairs; q += n_clusters) {
-        for (int o = 0; o < kPOps; ++o, ++opc) {
-          if (o == kPOps - 1) continue;
+      for (int q = cluster, it = 0; q < n_pairs; q += n_clusters, ++it) {
+        const bool last = quad_last<NV, MERGE>(it, q, n_clusters, n_pairs);
+        const int n_ops = last ? kPOps : 7;
+        for (int o = 0; o < n_ops; ++o, ++opc) {
+          if (!(o < 6 || (last && o < kPOps - 1))) continue;                  // this op's output is no A operand
           tc::mbar_wait(accf + (opc & 1), (uint32_t)((opc >> 1) & 1));     // the MMAs of this op no longer read my buffer
           tc::mbar_arrive_expect_tx(a_peer + 0, 32768);
           tc::mbar_arrive_expect_tx(a_peer + 1, 32768);
@@ -646,27 +663,111 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
       }
     }
   } else if (warp >= 4) {
-    // ================= epilogue (identical to the pair kernel; column half = h) =================
+    // ================= epilogue (the pair kernel's; column half = h; + park / merge when MERGE) =================
     const int quad = warp & 3;
     const int half = (warp - 4) >> 2;
     const int row = quad * 32 + lane;
     const bool leader = (warp == 4 && lane == 0);
+    constexpr int SPWc = 32 / NV;                    // samples per 32-row slab (RowMap)
+    constexpr int U = 4 * SPWc;                      // distinct (pooled) rows per view tile
+    float* park = MERGE ? P.merge_scratch + (size_t)blockIdx.x * (128 * 256) : nullptr;     // [NV*U <= 128][256] fp32
+    const uint64_t pol_keep = tc::policy_evict_last();
     int opc = 0, xops = 0, titer = 0;
-    long long w_acc = 0, t_epi0 = clock64();
+    long long w_acc = 0, w_merge = 0, w_mbar = 0, w_mld = 0, t_epi0 = clock64();
+    long long w_m[4] = {0, 0, 0, 0};
     long long w_kind[4] = {0, 0, 0, 0};
     POp d;
+    auto signal_kblock = [&](int st) {               // my part of own K-block st is in shared memory
+      tc::fence_before_sync();
+      tc::fence_proxy_async();                       // generic smem writes -> async proxy (MMA reads, pusher's bulk copy)
+      __syncwarp();
+      if (lane == 0) {
+        tc::mbar_arrive(a_own + st);
+        tc::mbar_arrive_remote_relaxed(a_own2 + st, cr & ~1u);     // the MMA issuer of my pair
+      }
+    };
     for (int q = cluster; q < n_pairs; q += n_clusters, ++titer) {
       const int tile = tile_of(q);
       const bool valid = 2 * q + t < P.mv_tiles;
       const uint32_t x_col = (titer & 1) ? 256u : 0u;
-      for (int o = 0; o < kPOps; ++o, ++opc) {
+      const int pos = MERGE ? titer % NV : 0;                     // position of this tile in its merge group
+      const bool last = quad_last<NV, MERGE>(titer, q, n_clusters, n_pairs);
+      const int n_ops = last ? kPOps : 7;
+      for (int o = 0; o < n_ops; ++o, ++opc) {
         pair_get_op(P, o, d);
         TIMED(w_acc, tc::mbar_wait(accf + (opc & 1), (uint32_t)((opc >> 1) & 1)));
         tc::fence_after_sync();
         const uint32_t t0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (d.acc_x ? x_col : (256u - x_col));
-        const bool pooled = o == 6;
-        float hp0 = 0.f, hp1 = 0.f, hp2 = 0.f, hp3 = 0.f;
         const long long tl0 = clock64();
+        if (MERGE && o == 6) {
+          // ---- park: mean over the view rows (resnetfc.py:9-14,148-151); the first row of every sample stores it
+          const bool first_view = (lane % NV == 0) && (lane / NV < SPWc);
+          const int j_own = quad * SPWc + lane / NV;
+#pragma unroll 1
+          for (int st = 0; st < 4; ++st) {
+            uint32_t acc[32];
+            const int nl0 = st * 64 + half * 32;
+            tc::tmem_ld32(t0 + nl0, acc);
+            tc::tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) acc[j] = __float_as_uint(view_mean<NV>(__uint_as_float(acc[j]), lane));
+            if (first_view) {
+              // scratch layout [64 column chunks of 4][128 merged rows] x 16 B: the lanes of a warp write (and the
+              // merge reads) consecutive 16-byte words; evict_last keeps it in L2 against the streaming operands
+              uint4* dst = reinterpret_cast<uint4*>(park) + (size_t)(nl0 / 4) * 128 + (pos * U + j_own);
+#pragma unroll
+              for (int g = 0; g < 8; ++g)
+                tc::st_hint_v4(dst + (size_t)g * 128, acc[4 * g], acc[4 * g + 1], acc[4 * g + 2], acc[4 * g + 3], pol_keep);
+            }
+          }
+          w_kind[EPI_MEAN] += clock64() - tl0;
+          if (!last) continue;
+          const long long tm0 = clock64();
+          bar_sync_epi();
+          w_mbar += clock64() - tm0;                  // the parked rows of the whole group are visible to all epilogue threads
+          // ---- merge: thread = row m of the merged tile = pooled row (m % U) of the group's tile (m / U)
+          const int i_src = row / U, j_src = row % U;
+          const bool have = i_src <= pos;
+          const uint4* src_row = reinterpret_cast<const uint4*>(park) + (i_src * U + j_src);     // (+ chunk * 128)
+          uint4 nxt[8];                    // the next piece's rows travel from L2 while this piece is processed
+          auto fetch = [&](int st) {
+#pragma unroll
+            for (int g = 0; g < 8; ++g)
+              nxt[g] = have ? tc::ld_cg_hint_v4(src_row + (size_t)((st * 64 + half * 32) / 4 + g) * 128, pol_keep)
+                            : make_uint4(0, 0, 0, 0);
+          };
+          fetch(0);
+#pragma unroll 1                   // (compact code: this path runs once per group and is cold in the instruction cache)
+          for (int st = 0; st < 4; ++st) {
+            uint32_t acc[32];
+            const int nl0 = st * 64 + half * 32;
+#pragma unroll
+            for (int g = 0; g < 8; ++g) { acc[4 * g] = nxt[g].x; acc[4 * g + 1] = nxt[g].y; acc[4 * g + 2] = nxt[g].z; acc[4 * g + 3] = nxt[g].w; }
+            long long c0 = clock64();
+            if (st < 3) fetch(st + 1);
+            float4 bq[8];
+            const float* bias = d.bias + h * 256 + nl0;
+#pragma unroll
+            for (int g = 0; g < 8; ++g) bq[g] = __ldg(reinterpret_cast<const float4*>(bias) + g);
+            { const long long cp = clock64();
+            if (st == 0 && xops > 0) tc::mbar_wait(pushed, (uint32_t)((xops - 1) & 1));
+            w_mbar += clock64() - cp; }
+            long long c1 = clock64(); w_m[0] += c1 - c0;
+            tc::tmem_st32(t0 + nl0, acc);                           // the merged tile's residual stream
+            unsigned char* dst_s = abuf + ((size_t)h * 32 + nl0 / 8) * 2048 + (size_t)row * 16;
+            pair_act_stage<1, false>(acc, bq, bias, lane, dst_s, t0 + nl0);
+            long long c2 = clock64(); w_m[1] += c2 - c1;
+            tc::tmem_st_wait();
+            long long c3 = clock64(); w_m[2] += c3 - c2;
+            signal_kblock(st);
+            w_m[3] += clock64() - c3;
+          }
+          w_merge += clock64() - tm0;
+          ++xops;
+          continue;
+        }
+        const bool pooled = !MERGE && o == 6;
+        float hp0 = 0.f, hp1 = 0.f, hp2 = 0.f, hp3 = 0.f;
 #pragma unroll 1
         for (int st = 0; st < 4; ++st) {
           uint32_t acc[32];
@@ -691,21 +792,25 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
             unsigned char* dst_s = abuf + ((size_t)h * 32 + nl0 / 8) * 2048 + (size_t)row * 16;
             if (pooled) pair_act_stage<NV, true>(acc, bq, bias, lane, dst_s, t0 + nl0);
             else pair_act_stage<NV, false>(acc, bq, bias, lane, dst_s, t0 + nl0);
-            tc::fence_before_sync();
-            tc::fence_proxy_async();
-            __syncwarp();
-            if (lane == 0) {
-              tc::mbar_arrive(a_own + st);
-              tc::mbar_arrive_remote_relaxed(a_own2 + st, cr & ~1u);     // the MMA issuer of my pair
-            }
+            signal_kblock(st);
           }
         }
         w_kind[d.epi] += clock64() - tl0;
         if (d.epi == EPI_HEAD) {
           tc::fence_before_sync();
           // the two column groups of a row are summed by head_finalize (4 partials per row and tile)
-          if (valid)
-            P.head_partial[(((size_t)tile * 2 + h) * 2 + half) * 128 + row] = make_float4(hp0, hp1, hp2, hp3);
+          if (!MERGE) {
+            if (valid)
+              P.head_partial[(((size_t)tile * 2 + h) * 2 + half) * 128 + row] = make_float4(hp0, hp1, hp2, hp3);
+          } else {
+            // merged row -> the first view row of its sample in the tile it came from (what head_finalize reads)
+            const int i_src = row / U, j_src = row % U;
+            const int x = 2 * (q - (pos - i_src) * n_clusters) + t;
+            if (i_src <= pos && x < P.mv_tiles) {
+              const int lrow = (j_src / SPWc) * 32 + (j_src % SPWc) * NV;
+              P.head_partial[(((size_t)x * 2 + h) * 2 + half) * 128 + lrow] = make_float4(hp0, hp1, hp2, hp3);
+            }
+          }
         } else {
           ++xops;
         }
@@ -713,7 +818,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
     }
     if (leader && P.prof) {
       long long* pr = P.prof + (size_t)blockIdx.x * 16;
-      pr[4] = clock64() - t_epi0; pr[5] = w_acc;
+      pr[4] = clock64() - t_epi0; pr[5] = w_acc; pr[12] = w_merge; pr[6] = w_m[0]; pr[7] = w_m[1]; pr[13] = w_m[2]; pr[14] = w_m[3]; pr[15] = w_mbar;
       pr[8] = w_kind[0]; pr[9] = w_kind[1]; pr[10] = w_kind[2]; pr[11] = w_kind[3];
     }
   }
@@ -794,13 +899,21 @@ DNR_EXPORT int dnr_mlp_pair_fwd(const void* lat_pk, const void* code_pk, const v
 
 namespace dnr {
 // how many 4-CTA clusters the device holds at once (GPCs whose SM count is not a multiple of 4 leave SMs idle); -1 on error
+typedef void (*QuadKernel)(const PairParams);
+static QuadKernel quad_kernel(int NV, bool merge) {
+  if (merge) return NV == 2 ? mlp_quad_fwd_kernel<2, true> : NV == 3 ? mlp_quad_fwd_kernel<3, true> : mlp_quad_fwd_kernel<4, true>;
+  return NV == 1 ? mlp_quad_fwd_kernel<1, false> : NV == 2 ? mlp_quad_fwd_kernel<2, false>
+         : NV == 3 ? mlp_quad_fwd_kernel<3, false> : mlp_quad_fwd_kernel<4, false>;
+}
 static int quad_max_clusters(int NV) {
   static int cached[5] = {0, 0, 0, 0, 0};
   if (NV < 1 || NV > 4) return -1;
   if (cached[NV]) return cached[NV];
-  void (*kern)(const PairParams) = NV == 1 ? mlp_quad_fwd_kernel<1> : NV == 2 ? mlp_quad_fwd_kernel<2>
-                                   : NV == 3 ? mlp_quad_fwd_kernel<3> : mlp_quad_fwd_kernel<4>;
+  QuadKernel kern = quad_kernel(NV, false);
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kQSmem) != cudaSuccess) return -1;
+  if (NV > 1 && cudaFuncSetAttribute(quad_kernel(NV, true), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kQSmem) !=
+                    cudaSuccess)
+    return -1;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(4 * 37, 1, 1); cfg.blockDim = dim3(kPThreads, 1, 1); cfg.dynamicSmemBytes = kQSmem;
   cudaLaunchAttribute attr[1];
@@ -818,12 +931,16 @@ static int quad_max_clusters(int NV) {
 // run dnr_mlp_pair_fwd clusters concurrently.  Negative on error.
 DNR_EXPORT int dnr_mlp_quad_max_clusters(int NV) { return dnr::quad_max_clusters(NV); }
 
+// Bytes of the scratch that enables the quad kernel's merge of pooled rows (see MERGE above).
+DNR_EXPORT long long dnr_mlp_quad_scratch_bytes(void) { return 148LL * 128 * 256 * 4; }
+
 // The quad variant (clusters of 4 CTAs, tcgen05 cta_group::2; see above).  weights: the same 14 matrices as
 // dnr_mlp_pair_fwd but in the PK128 layout [N/128][K/8][128][8]; head_partial: [mv_tiles*4*128] float4
-// (dnr_head_finalize with n_partials = 4).
+// (dnr_head_finalize with n_partials = 4); merge_scratch: null, or dnr_mlp_quad_scratch_bytes() bytes -> blocks 3-4 and
+// the head run once per NV tiles on merged pooled rows (NV > 1; the partial sums land where they would otherwise).
 DNR_EXPORT int dnr_mlp_quad_fwd(const void* lat_pk, const void* code_pk, const void* const* weights_pk128,
                                 const float* const* biases, const float* w_out, int NV, int mv_tiles,
-                                float* head_partial, long long* prof, cudaStream_t stream) {
+                                void* merge_scratch, float* head_partial, long long* prof, cudaStream_t stream) {
   DNR_REQUIRE(NV >= 1 && NV <= 4, "dnr_mlp_quad_fwd: NV must be in [1,4]");
   DNR_REQUIRE(lat_pk && code_pk && weights_pk128 && biases && w_out && head_partial, "dnr_mlp_quad_fwd: null argument");
   if (mv_tiles <= 0) return 0;
@@ -838,9 +955,8 @@ DNR_EXPORT int dnr_mlp_quad_fwd(const void* lat_pk, const void* code_pk, const v
   for (int i = 0; i < 5; ++i) P.b_0[i] = biases[6 + i];
   P.w_out = w_out; P.head_partial = (float4*)head_partial;
   P.NV = NV; P.SPW = 32 / NV; P.mv_tiles = mv_tiles; P.prof = prof;
-  void (*kern)(const dnr::PairParams) = NV == 1 ? dnr::mlp_quad_fwd_kernel<1>
-                                         : NV == 2 ? dnr::mlp_quad_fwd_kernel<2>
-                                         : NV == 3 ? dnr::mlp_quad_fwd_kernel<3> : dnr::mlp_quad_fwd_kernel<4>;
+  P.merge_scratch = (float*)merge_scratch;
+  dnr::QuadKernel kern = dnr::quad_kernel(NV, merge_scratch != nullptr && NV > 1);
   const int max_cl = dnr::quad_max_clusters(NV);
   DNR_REQUIRE(max_cl >= 1, "dnr_mlp_quad_fwd: the device cannot hold a cluster of 4 CTAs with 225 KB of shared memory each");
   const int n_pairs = (mv_tiles + 1) / 2;

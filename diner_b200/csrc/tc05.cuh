@@ -90,6 +90,15 @@ __device__ __forceinline__ void st_hint_v4(void* p, uint32_t a, uint32_t b, uint
                "l"(policy)
                : "memory");
 }
+// L2-only load (bypasses L1) with an eviction-priority hint
+__device__ __forceinline__ uint4 ld_cg_hint_v4(const void* p, uint64_t policy) {
+  uint4 v;
+  asm volatile("ld.global.cg.L2::cache_hint.v4.b32 {%0, %1, %2, %3}, [%4], %5;"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p), "l"(policy)
+               : "memory");
+  return v;
+}
 
 // ---- tensor memory -------------------------------------------------------------------------------
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_result, uint32_t ncols) {   // whole warp

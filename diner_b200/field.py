@@ -31,10 +31,13 @@ PAIR_PROF = None             # debug: int64 tensor [148*8] receiving cycle count
 FORWARD_KERNEL = "quad"
 # With "quad": share of a chunk's tiles rendered by 2-CTA clusters on the SMs that the 4-CTA clusters cannot use
 # (the quad kernel keeps 33 clusters = 132 of 148 SMs resident on a B200), on a second stream.  0 disables; None =
-# spare * r / (spare * r + quad_clusters) with r = 0.37: one pair cluster renders 0.40-0.42 of what one quad cluster does
-# (14.3 vs 34.4 tiles/ms, profiles/r1_quad_kernel.md); rounded down because a late pair kernel is the tail of the step
-# while an early one only idles 16 SMs.
+# spare * r / (spare * r + quad_clusters), r = throughput of one pair cluster relative to one quad cluster, measured
+# on the BASELINE.json shapes (profiles/r1_quad_kernel.md) and rounded down: a late pair kernel is the tail of the
+# step while an early one only idles 16 SMs.  The quad kernel merges pooled rows (MERGE_POOLED), the pair kernel does
+# not, so r falls with the view count.
+PAIR_RATE = {1: 0.37, 2: 0.34, 3: 0.32, 4: 0.30}
 PAIR_SHARE = None
+MERGE_POOLED = True          # quad kernel: run blocks 3-4 + head once per NV tiles on merged pooled rows (NV > 1)
 _side_stream = {}
 
 
@@ -115,6 +118,14 @@ def get_packed(mlp, need_transposed: bool) -> PackedMLP:
 _scratch: dict = {}
 
 
+def _quad_scratch(dev) -> torch.Tensor:
+    """Parking space of the quad kernel's pooled rows (128 KB per CTA, L2-resident)."""
+    k = "quad" + str(dev)
+    if k not in _scratch:
+        _scratch[k] = torch.zeros(_lib.load().dnr_mlp_quad_scratch_bytes(), device=dev, dtype=torch.uint8)
+    return _scratch[k]
+
+
 def _fused_scratch(dev) -> torch.Tensor:
     """Per-CTA activation scratch of the fused forward kernel (1 MB per SM; re-used by every tile, L2-resident)."""
     k = str(dev)
@@ -180,7 +191,8 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
             n_quad = _lib.load().dnr_mlp_quad_max_clusters(NV)
             n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
             spare = max(0, (n_sm - 4 * n_quad) // 2)             # SM pairs the quad kernel leaves idle
-            share = PAIR_SHARE if PAIR_SHARE is not None else 0.37 * spare / (0.37 * spare + n_quad)
+            r = PAIR_RATE[NV] if MERGE_POOLED else 0.37
+            share = PAIR_SHARE if PAIR_SHARE is not None else r * spare / (r * spare + n_quad)
             if share > 0 and spare > 0 and (PAIR_SHARE is not None or mv >= 64 * spare):
                 mv_q = mv - max(2, int(mv * share)) // 2 * 2
         else:
@@ -193,7 +205,7 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
         if mv_q > 0:
             part_q = torch.empty(mv_q * 4 * 128, 4, **f32)
             _lib.call("dnr_mlp_quad_fwd", p(lat), p(code), pk.w128_ptrs, pk.pair_b_ptrs, p(pk.w_out), NV, mv_q,
-                      p(part_q), p(PAIR_PROF), st)
+                      p(_quad_scratch(dev)) if MERGE_POOLED and NV > 1 else None, p(part_q), p(PAIR_PROF), st)
             _lib.call("dnr_head_finalize", p(part_q), p(pk.b_out), NV, min(n_samples, mv_q * per_tile), 4, p(out), st)
         if mv_q < mv:
             n_p = mv - mv_q

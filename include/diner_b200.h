@@ -133,10 +133,14 @@ int dnr_mlp_pair_fwd(const void* lat_pk, const void* code_pk, const void* const*
 /* The same on clusters of FOUR CTAs (2 row tiles x 2 column halves) with tcgen05.mma.cta_group::2: the two CTAs of a
  * column half share every weight K-block, each streaming half of it, which halves the L2 -> SM traffic that bounds the
  * pair kernel.  weights_pk128: the same 14 matrices in the PK128 layout [N/128][K/8][128][8] bf16;
- * head_partial: [mv_tiles*4*128] float4. */
+ * head_partial: [mv_tiles*4*128] float4.
+ * merge_scratch: null, or dnr_mlp_quad_scratch_bytes() bytes of device memory: for NV > 1 every CTA then parks the
+ * pooled rows (128/NV distinct rows per tile after the view mean) of NV consecutive tiles, merges them into one full tile
+ * and runs blocks 3-4 and lin_out once per NV tiles instead of on NV-fold duplicated rows. */
+long long dnr_mlp_quad_scratch_bytes(void);
 int dnr_mlp_quad_fwd(const void* lat_pk, const void* code_pk, const void* const* weights_pk128,
-                     const float* const* biases, const float* w_out, int NV, int mv_tiles, float* head_partial,
-                     long long* prof /* nullable */, dnr_stream_t stream);
+                     const float* const* biases, const float* w_out, int NV, int mv_tiles, void* merge_scratch,
+                     float* head_partial, long long* prof /* nullable */, dnr_stream_t stream);
 /* Number of 4-CTA clusters the quad kernel keeps resident; SMs beyond 4x that stay idle and can run
  * dnr_mlp_pair_fwd clusters (max_clusters) on another stream at the same time. */
 int dnr_mlp_quad_max_clusters(int NV);
