@@ -673,8 +673,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
     float* park = MERGE ? P.merge_scratch + (size_t)blockIdx.x * (128 * 256) : nullptr;     // [NV*U <= 128][256] fp32
     const uint64_t pol_keep = tc::policy_evict_last();
     int opc = 0, xops = 0, titer = 0;
-    long long w_acc = 0, w_merge = 0, w_mbar = 0, w_mld = 0, t_epi0 = clock64();
-    long long w_m[4] = {0, 0, 0, 0};
+    long long w_acc = 0, w_merge = 0, t_epi0 = clock64();
     long long w_kind[4] = {0, 0, 0, 0};
     POp d;
     auto signal_kblock = [&](int st) {               // my part of own K-block st is in shared memory
@@ -723,8 +722,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
           w_kind[EPI_MEAN] += clock64() - tl0;
           if (!last) continue;
           const long long tm0 = clock64();
-          bar_sync_epi();
-          w_mbar += clock64() - tm0;                  // the parked rows of the whole group are visible to all epilogue threads
+          bar_sync_epi();                  // the parked rows of the whole group are visible to all epilogue threads
           // ---- merge: thread = row m of the merged tile = pooled row (m % U) of the group's tile (m / U)
           const int i_src = row / U, j_src = row % U;
           const bool have = i_src <= pos;
@@ -743,24 +741,17 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
             const int nl0 = st * 64 + half * 32;
 #pragma unroll
             for (int g = 0; g < 8; ++g) { acc[4 * g] = nxt[g].x; acc[4 * g + 1] = nxt[g].y; acc[4 * g + 2] = nxt[g].z; acc[4 * g + 3] = nxt[g].w; }
-            long long c0 = clock64();
             if (st < 3) fetch(st + 1);
             float4 bq[8];
             const float* bias = d.bias + h * 256 + nl0;
 #pragma unroll
             for (int g = 0; g < 8; ++g) bq[g] = __ldg(reinterpret_cast<const float4*>(bias) + g);
-            { const long long cp = clock64();
             if (st == 0 && xops > 0) tc::mbar_wait(pushed, (uint32_t)((xops - 1) & 1));
-            w_mbar += clock64() - cp; }
-            long long c1 = clock64(); w_m[0] += c1 - c0;
             tc::tmem_st32(t0 + nl0, acc);                           // the merged tile's residual stream
             unsigned char* dst_s = abuf + ((size_t)h * 32 + nl0 / 8) * 2048 + (size_t)row * 16;
             pair_act_stage<1, false>(acc, bq, bias, lane, dst_s, t0 + nl0);
-            long long c2 = clock64(); w_m[1] += c2 - c1;
             tc::tmem_st_wait();
-            long long c3 = clock64(); w_m[2] += c3 - c2;
             signal_kblock(st);
-            w_m[3] += clock64() - c3;
           }
           w_merge += clock64() - tm0;
           ++xops;
@@ -818,7 +809,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
     }
     if (leader && P.prof) {
       long long* pr = P.prof + (size_t)blockIdx.x * 16;
-      pr[4] = clock64() - t_epi0; pr[5] = w_acc; pr[12] = w_merge; pr[6] = w_m[0]; pr[7] = w_m[1]; pr[13] = w_m[2]; pr[14] = w_m[3]; pr[15] = w_mbar;
+      pr[4] = clock64() - t_epi0; pr[5] = w_acc; pr[12] = w_merge;
       pr[8] = w_kind[0]; pr[9] = w_kind[1]; pr[10] = w_kind[2]; pr[11] = w_kind[3];
     }
   }

@@ -20,6 +20,6 @@ torch.cuda.synchronize()
 p = F_.PAIR_PROF.view(148, 16).double().cpu()
 p = p[p[:, 4] > 0]            # CTAs that ran (the quad kernel may leave SMs idle)
 print('CTAs reporting:', p.shape[0]); lead = p[p[:, 0] > 0]
-names = ["mma_total", "mma_wait_ring", "mma_wait_own", "mma_wait_peer", "epi_total", "epi_wait_accf", "merge_fetch_pushed", "merge_st_stage", "loop_EPI_X(4/tile)", "loop_EPI_T(5/tile)", "loop_EPI_MEAN(1)", "loop_EPI_HEAD(1)", "epi_merge", "merge_st_wait", "merge_signal", "merge_pushed_wait"]
+names = ["mma_total", "mma_wait_ring", "mma_wait_own", "mma_wait_peer", "epi_total", "epi_wait_accf", "-", "-", "loop_EPI_X(4/tile)", "loop_EPI_T(5/tile)", "loop_EPI_PARK(1)", "loop_EPI_HEAD(1)", "epi_merge", "wait_peer_full", "ring_lat", "pfull_lat"]
 for i, n in enumerate(names):
     print(f"{n:16s} mean {p[:, i].mean():14.0f} cyc  ({100 * p[:, i].mean() / max(lead[:, 0].mean(), 1):5.1f}% of mma_total)  min {p[:, i].min():.0f} max {p[:, i].max():.0f}")
