@@ -244,11 +244,11 @@ def test_inference_kernels_agree(golden_cache, name):
         scene.model.to_device("cpu")
 
 
-@pytest.mark.parametrize("NV,n_rays", [(1, 37), (2, 333), (3, 130), (4, 515)])
+@pytest.mark.parametrize("NV,n_rays", [(1, 37), (2, 333), (3, 130), (4, 515), (2, 3), (2, 576), (3, 7), (3, 576), (4, 41)])
 def test_cluster_kernels_all_view_counts(NV, n_rays):
     """The 2-CTA and 4-CTA cluster kernels for every view count they accept, on ragged ray counts (odd and
-    single-tile launches, a last tile that is mostly padding): against the per-layer path and against the
-    precision-contract oracle."""
+    single-tile launches, a last tile that is mostly padding, merge groups of the quad kernel that end early or hold
+    a single tile): against the per-layer path and against the precision-contract oracle."""
     dev = _cuda()
     import dataclasses
     from diner_b200 import field as F_
@@ -291,8 +291,8 @@ def test_cluster_kernels_all_view_counts(NV, n_rays):
             d = (outs[kern] - want).abs()
             err[kern] = (float(d[:, :3].max()), float(d[:, :3].mean()), float(d[:, 3].max()) / smax, float(d[:, 3].mean()) / smax)
         assert err["layers"][0] < 3e-2 and err["layers"][1] < 1e-3 and err["layers"][2] < 2e-2 and err["layers"][3] < 1e-3, err
-        for a, b in zip(err["pair"], err["layers"]):
-            assert a < 1.5 * b + 1e-4, err
+        for k, (a, b) in enumerate(zip(err["pair"], err["layers"])):
+            assert a < (2.0 * b + 2e-3 if k % 2 == 0 else 1.5 * b + 1e-4), err      # (max | mean) of (rgb, sigma)
         dk = (outs["pair"] - outs["layers"]).abs()
         assert float(dk[:, :3].mean()) < 1e-3 and float(dk[:, 3].mean()) < 1e-3 * smax
     finally:
