@@ -37,6 +37,11 @@ FORWARD_KERNEL = "quad"
 # not, so r falls with the view count.
 PAIR_RATE = {1: 0.37, 2: 0.34, 3: 0.32, 4: 0.30}
 PAIR_SHARE = None
+# The split adapts itself: both kernels of a chunk are bracketed by CUDA events, and once a pair of timings has
+# completed (polled without synchronising) the rate of that (device, NV) moves towards the measured one.  The split
+# never changes the result (both kernels produce the same bits, tests/test_gpu_field.py), only the balance.
+ADAPT_SPLIT = True
+_split_state = {}            # (device, NV) -> dict(rate=float, pending=[(e_q0, e_q1, e_p0, e_p1, tiles_q, tiles_p)])
 MERGE_POOLED = True          # quad kernel: run blocks 3-4 + head once per NV tiles on merged pooled rows (NV > 1)
 _side_stream = {}
 
@@ -118,6 +123,23 @@ def get_packed(mlp, need_transposed: bool) -> PackedMLP:
 _scratch: dict = {}
 
 
+def _update_split(state: dict, spare: int, n_quad: int) -> None:
+    """Fold completed (quad, pair) timings into the pair rate: rate = (tiles_p / t_p / spare) / (tiles_q / t_q / n_quad)."""
+    keep = []
+    for rec in state["pending"]:
+        e_q0, e_q1, e_p0, e_p1, tiles_q, tiles_p = rec
+        if not (e_q1.query() and e_p1.query()):
+            keep.append(rec)
+            continue
+        t_q, t_p = e_q0.elapsed_time(e_q1), e_p0.elapsed_time(e_p1)
+        if t_q > 0.05 and t_p > 0.05 and spare > 0:            # ignore launches too small to time
+            measured = (tiles_p / t_p / spare) / (tiles_q / t_q / n_quad)
+            measured = min(max(measured, 0.15), 0.6)
+            # move a third of the way, aim 3 % low: a late pair kernel is the tail, an early one only idles 16 SMs
+            state["rate"] += (0.97 * measured - state["rate"]) / 3.0
+    state["pending"] = keep
+
+
 def _quad_scratch(dev) -> torch.Tensor:
     """Parking space of the quad kernel's pooled rows (128 KB per CTA, L2-resident)."""
     k = "quad" + str(dev)
@@ -191,7 +213,10 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
             n_quad = _lib.load().dnr_mlp_quad_max_clusters(NV)
             n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
             spare = max(0, (n_sm - 4 * n_quad) // 2)             # SM pairs the quad kernel leaves idle
-            r = PAIR_RATE[NV] if MERGE_POOLED else 0.37
+            state = _split_state.setdefault((str(dev), NV, MERGE_POOLED),
+                                            dict(rate=PAIR_RATE[NV] if MERGE_POOLED else 0.37, pending=[]))
+            _update_split(state, spare, n_quad)
+            r = state["rate"]
             share = PAIR_SHARE if PAIR_SHARE is not None else r * spare / (r * spare + n_quad)
             if share > 0 and spare > 0 and (PAIR_SHARE is not None or mv >= 64 * spare):
                 mv_q = mv - max(2, int(mv * share)) // 2 * 2
@@ -202,10 +227,16 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
         if 0 < mv_q < mv:                                        # fork: the pair clusters run beside the quad clusters
             side = _side_stream.setdefault(str(dev), torch.cuda.Stream(dev))
             side.wait_stream(cur)
+        timing = side is not None and ADAPT_SPLIT and PAIR_SHARE is None and len(state["pending"]) < 8
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)] if timing else None
         if mv_q > 0:
             part_q = torch.empty(mv_q * 4 * 128, 4, **f32)
+            if timing:
+                ev[0].record(cur)
             _lib.call("dnr_mlp_quad_fwd", p(lat), p(code), pk.w128_ptrs, pk.pair_b_ptrs, p(pk.w_out), NV, mv_q,
                       p(_quad_scratch(dev)) if MERGE_POOLED and NV > 1 else None, p(part_q), p(PAIR_PROF), st)
+            if timing:
+                ev[1].record(cur)
             _lib.call("dnr_head_finalize", p(part_q), p(pk.b_out), NV, min(n_samples, mv_q * per_tile), 4, p(out), st)
         if mv_q < mv:
             n_p = mv - mv_q
@@ -214,9 +245,14 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
             lat_p, code_p, out_p = lat[mv_q * 128 * HID:], code[mv_q * 128 * IN_PAD:], out[s0:]
             with torch.cuda.stream(side) if side is not None else contextlib.nullcontext():
                 st2 = _lib.stream_ptr()
+                if timing:
+                    ev[2].record(side)
                 _lib.call("dnr_mlp_pair_fwd", p(lat_p), p(code_p), pk.w_ptrs, pk.pair_b_ptrs, p(pk.w_out), NV, n_p,
                           spare if side is not None else 0, p(part_p), p(PAIR_PROF) if mv_q == 0 else None, st2,
                           tag="overlapped" if side is not None else None)
+                if timing:
+                    ev[3].record(side)
+                    state["pending"].append((*ev, mv_q, n_p))
                 _lib.call("dnr_head_finalize", p(part_p), p(pk.b_out), NV, n_samples - s0, 2, p(out_p), st2)
             if side is not None:
                 cur.wait_stream(side)                            # join
