@@ -192,6 +192,13 @@ class NeRFRendererDGS(torch.nn.Module):
             raise ValueError(f"rays batch {SB} does not match the encoded scenes {sc.SB}")
         rays = rays.detach().to(torch.float32).contiguous()
         K = self.n_samples
+        if NR == 0:                                  # nothing to render: empty results of the right shapes
+            empty = RenderResult(rgb=rays.new_zeros(SB, 0, 3), depth=rays.new_zeros(SB, 0))
+            if want_weights:
+                empty.weights = rays.new_zeros(SB, 0, K)
+            if return_samples:
+                empty.z = rays.new_zeros(SB, 0, K)
+            return RenderResult(fine=empty)
         if noise is not None and noise.get("z") is not None:
             # parity hook: evaluate field + compositing on externally supplied (sorted) sample depths
             z = noise["z"].detach().to(device=rays.device, dtype=torch.float32).reshape(SB * NR, K).contiguous()

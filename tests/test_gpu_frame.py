@@ -135,3 +135,33 @@ def test_training_step_shape():
     out = r(m, rays, noise=None)
     torch.nn.functional.mse_loss(out.fine.rgb, gt).backward()
     assert float((m.mlp_fine.lin_out.weight.grad - g1).abs().sum()) > 0
+
+
+def test_empty_and_tiny_ray_batches():
+    """Zero rays give empty outputs of the right shapes; 1, 2 and 129 rays (less than one tile, ragged) render and
+    back-propagate; a renderer whose n_samples / n_gaussian were mutated after construction (as
+    python_scripts/create_prediction_folder.py:51-52 does) uses the new values."""
+    dev = _cuda()
+    from diner_b200 import NeRFRendererDGS
+    from diner_b200.synthetic import make_scene
+    scene = make_scene("tiny", seed=0)
+    wl = scene.workload
+    m = scene.model.to_device(dev)
+    r = NeRFRendererDGS(wl.n_samples, wl.n_candidates, wl.n_gaussian, white_bkgd=True)
+    for n in (0, 1, 2, 129):
+        rays = scene.rays[:, :n].contiguous().to(dev)
+        with torch.no_grad():
+            out = r(m, rays, want_weights=True)
+        assert out.fine.rgb.shape == (1, n, 3) and out.fine.depth.shape == (1, n)
+        assert out.fine.weights.shape == (1, n, wl.n_samples) and torch.isfinite(out.fine.rgb).all()
+        m.encoder.latent = m.encoder.latent.detach().requires_grad_(True)
+        out2 = r(m, rays, want_weights=True)
+        if n:
+            (out2.fine.rgb.sum() + out2.fine.depth.sum()).backward()
+            assert torch.isfinite(m.encoder.latent.grad).all()
+        m.encoder.latent = m.encoder.latent.detach()
+    r.n_samples, r.n_gaussian = 24, 8
+    with torch.no_grad():
+        out = r(m, scene.rays[:, :50].contiguous().to(dev), want_weights=True, return_samples=True)
+    assert out.fine.weights.shape == (1, 50, 24) and out.fine.z.shape == (1, 50, 24)
+    assert bool((out.fine.z[..., 1:] >= out.fine.z[..., :-1]).all()) and torch.isfinite(out.fine.rgb).all()
