@@ -142,15 +142,15 @@ def _update_split(state: dict, spare: int, n_quad: int) -> None:
 
 def _quad_scratch(dev) -> torch.Tensor:
     """Parking space of the quad kernel's pooled rows (128 KB per CTA, L2-resident)."""
-    k = "quad" + str(dev)
-    if k not in _scratch:
+    k = ("quad", str(dev), torch.cuda.current_stream(dev).cuda_stream)      # one per stream: launches on different
+    if k not in _scratch:                                                   # streams may overlap
         _scratch[k] = torch.zeros(_lib.load().dnr_mlp_quad_scratch_bytes(), device=dev, dtype=torch.uint8)
     return _scratch[k]
 
 
 def _fused_scratch(dev) -> torch.Tensor:
     """Per-CTA activation scratch of the fused forward kernel (1 MB per SM; re-used by every tile, L2-resident)."""
-    k = str(dev)
+    k = ("chain", str(dev), torch.cuda.current_stream(dev).cuda_stream)
     if k not in _scratch:
         n = _lib.load().dnr_mlp_fused_scratch_bytes(0)
         _scratch[k] = torch.zeros(n, device=dev, dtype=torch.uint8)
