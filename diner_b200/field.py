@@ -219,7 +219,7 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
             r = state["rate"]
             share = PAIR_SHARE if PAIR_SHARE is not None else r * spare / (r * spare + n_quad)
             if share > 0 and spare > 0 and (PAIR_SHARE is not None or mv >= 64 * spare):
-                mv_q = mv - max(2, int(mv * share)) // 2 * 2
+                mv_q = max(0, mv - max(2, int(mv * share)) // 2 * 2)
         else:
             mv_q = 0
         cur = torch.cuda.current_stream(dev)

@@ -244,7 +244,7 @@ def test_inference_kernels_agree(golden_cache, name):
         scene.model.to_device("cpu")
 
 
-@pytest.mark.parametrize("NV,n_rays", [(1, 37), (2, 333), (3, 130), (4, 515), (2, 3), (2, 576), (3, 7), (3, 576), (4, 41)])
+@pytest.mark.parametrize("NV,n_rays", [(1, 37), (2, 333), (3, 130), (4, 515), (2, 3), (2, 576), (3, 7), (3, 576), (4, 41), (1, 3)])
 def test_cluster_kernels_all_view_counts(NV, n_rays):
     """The 2-CTA and 4-CTA cluster kernels for every view count they accept, on ragged ray counts (odd and
     single-tile launches, a last tile that is mostly padding, merge groups of the quad kernel that end early or hold
