@@ -297,6 +297,22 @@ def main():
                     launches_per_step=gemm_launches, kernel_ms_per_step=gemm_ms,
                     algorithmic_flops_per_step=gemm_flops)
 
+    # the other stages against the memory roofline (SURVEY.md 8d algorithmic bytes; HBM level and L2 level)
+    def _gbs(nbytes, key):
+        ms = breakdown.get(key, {}).get("ms_per_step", 0.0)
+        return nbytes / (ms * 1e-3) / 1e9 if ms > 0 else None
+    rows = n_samples * wl.NV
+    stage_rooflines = dict(
+        encode=dict(kernel="encode_fwd_kernel", hbm_gbs=_gbs(rows * 1152.0, "dnr_encode_fwd"),
+                    l2_gbs=_gbs(rows * (4100.0 + 1152.0), "dnr_encode_fwd"), hbm_peak_gbs=peaks["hbm_gbs"],
+                    note="HBM: 1152 B written per view row (operands of the MLP); L2: + 4 bilinear taps x 1 KB read "
+                         "from the L2-resident bf16 latent; issue-bound (ncu: 60 % issue slots), not memory-bound"),
+        composite=dict(kernel="composite_fwd_kernel", hbm_gbs=_gbs(n_rays * 1008.0, "dnr_composite_fwd"),
+                       hbm_peak_gbs=peaks["hbm_gbs"], note="1008 B per ray; ~10 us launches, latency-bound at this size"),
+        sampler=dict(kernel="sampler_kernel", hbm_gbs=_gbs(n_rays * 192.0, "dnr_sampler_fwd"),
+                     l2_gbs=_gbs(n_rays * wl.NV * wl.n_candidates * 20.0, "dnr_sampler_fwd"),
+                     note="not memory-bound: NV*C candidate-view evaluations per ray on cache-resident maps"))
+
     if rank == 0:
         ms_per_step = total_ms / args.steps
         value = n_rays * world / (ms_per_step * 1e-3)
@@ -313,7 +329,8 @@ def main():
                     e2e=dict(value=e2e_value, unit="rays/s", h2d_bytes_per_step=rays_host.numel() * 4,
                              d2h_bytes_per_step=(rgb_host.numel() + depth_host.numel()) * 4,
                              ms_per_step=e2e_ms / args.steps),
-                    gpu_launches=launches, clocks=clk, roofline=roofline, breakdown_ms=breakdown)
+                    gpu_launches=launches, clocks=clk, roofline=roofline, stage_rooflines=stage_rooflines,
+                    breakdown_ms=breakdown)
         if world == 1 and not args.no_cpu_baseline:
             rate, n, threads, times = cpu_oracle_rate(args.workload, args.cpu_rays)
             line["cpu_baseline"] = dict(value=rate, unit="rays/s", cores=threads, kind="port",
