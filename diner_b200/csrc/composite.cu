@@ -150,6 +150,157 @@ __global__ void __launch_bounds__(256) composite_bwd_kernel(
   }
 }
 
+// ---- K even and <= 64: two adjacent samples per lane, every load of a ray issued before the first use -----------
+// (the generic kernels below walk 32-sample chunks one after the other: two dependent HBM round trips at K = 40)
+
+__device__ __forceinline__ float warp_excl_prod1(float v, int lane) {
+  float x = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    float y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= o) x *= y;
+  }
+  float e = __shfl_up_sync(0xffffffffu, x, 1);
+  return lane == 0 ? 1.0f : e;
+}
+
+__device__ __forceinline__ float warp_excl_suffix_sum1(float v, int lane) {
+  float x = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    float y = __shfl_down_sync(0xffffffffu, x, o);
+    if (lane + o < 32) x += y;
+  }
+  float e = __shfl_down_sync(0xffffffffu, x, 1);
+  return lane == 31 ? 0.0f : e;
+}
+
+struct PairRaw { float4 c0, c1; float2 zz; float far; };
+struct PairSamples {
+  float4 c0, c1;
+  float z0, z1, delta0, delta1, alpha0, alpha1, t0, t1;
+};
+
+// samples (2*lane, 2*lane+1) of one ray: the loads ...
+__device__ __forceinline__ PairRaw load_pair(const float4* __restrict__ rgbsigma, const float* __restrict__ z,
+                                             const float* __restrict__ rays, long long ray, int K, int lane) {
+  PairRaw r;
+  r.far = __ldg(rays + ray * 8 + 7);
+  r.zz = make_float2(0.f, 0.f);
+  r.c0 = make_float4(0.f, 0.f, 0.f, 0.f); r.c1 = r.c0;
+  if (2 * lane < K) {
+    r.zz = __ldg(reinterpret_cast<const float2*>(z + ray * K) + lane);
+    r.c0 = __ldg(rgbsigma + ray * K + 2 * lane);
+    r.c1 = __ldg(rgbsigma + ray * K + 2 * lane + 1);
+  }
+  return r;
+}
+
+// ... and their per-sample terms (nerf_renderer.py:299-301, :344-349)
+__device__ __forceinline__ PairSamples derive_pair(const PairRaw& r, int K, int lane) {
+  PairSamples s;
+  const bool valid = 2 * lane < K;
+  float zn1 = __shfl_down_sync(0xffffffffu, r.zz.x, 1);
+  if (2 * lane + 2 >= K) zn1 = r.far;
+  s.c0 = r.c0; s.c1 = r.c1;
+  s.z0 = r.zz.x; s.z1 = r.zz.y;
+  s.delta0 = __fsub_rn(r.zz.y, r.zz.x);
+  s.delta1 = __fsub_rn(zn1, r.zz.y);
+  s.alpha0 = valid ? __fsub_rn(1.0f, expf(-__fmul_rn(s.delta0, fmaxf(s.c0.w, 0.f)))) : 0.f;
+  s.alpha1 = valid ? __fsub_rn(1.0f, expf(-__fmul_rn(s.delta1, fmaxf(s.c1.w, 0.f)))) : 0.f;
+  s.t0 = valid ? __fadd_rn(__fsub_rn(1.0f, s.alpha0), 1e-10f) : 1.0f;
+  s.t1 = valid ? __fadd_rn(__fsub_rn(1.0f, s.alpha1), 1e-10f) : 1.0f;
+  return s;
+}
+
+constexpr int kRaysInFlight = 2;   // rays per warp whose loads are issued together (bytes in flight per SM)
+
+__global__ void __launch_bounds__(256) composite_fwd2_kernel(
+    const float4* __restrict__ rgbsigma, const float* __restrict__ z, const float* __restrict__ rays,
+    int n_rays, int K, int white_bkgd, float* __restrict__ weights, float* __restrict__ rgb, float* __restrict__ depth)
+{
+  const int lane = threadIdx.x & 31;
+  const long long stride = (long long)gridDim.x * (blockDim.x >> 5);
+  for (long long ray0 = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); ray0 < n_rays;
+       ray0 += stride * kRaysInFlight) {
+    PairRaw raw[kRaysInFlight];
+#pragma unroll
+    for (int u = 0; u < kRaysInFlight; ++u)
+      if (ray0 + u * stride < n_rays) raw[u] = load_pair(rgbsigma, z, rays, ray0 + u * stride, K, lane);
+#pragma unroll
+    for (int u = 0; u < kRaysInFlight; ++u) {
+      const long long ray = ray0 + u * stride;
+      if (ray >= n_rays) break;
+      const PairSamples s = derive_pair(raw[u], K, lane);
+      const float T0 = warp_excl_prod1(s.t0 * s.t1, lane);
+      const float T1 = T0 * s.t0;
+      const float w0 = s.alpha0 * T0, w1 = s.alpha1 * T1;
+      if (weights && 2 * lane < K)
+        reinterpret_cast<float2*>(weights + ray * K)[lane] = make_float2(w0, w1);
+      float ar = fmaf(w1, s.c1.x, w0 * s.c0.x), ag = fmaf(w1, s.c1.y, w0 * s.c0.y), ab = fmaf(w1, s.c1.z, w0 * s.c0.z);
+      float ad = fmaf(w1, s.z1, w0 * s.z0), aw = w0 + w1;
+      ar = warp_sum(ar); ag = warp_sum(ag); ab = warp_sum(ab); ad = warp_sum(ad);
+      if (white_bkgd) aw = warp_sum(aw);
+      if (lane == 0) {
+        if (white_bkgd) { ar = ar + 1.f - aw; ag = ag + 1.f - aw; ab = ab + 1.f - aw; }
+        rgb[ray * 3 + 0] = ar; rgb[ray * 3 + 1] = ag; rgb[ray * 3 + 2] = ab;
+        depth[ray] = ad;
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) composite_bwd2_kernel(
+    const float4* __restrict__ rgbsigma, const float* __restrict__ z, const float* __restrict__ rays,
+    const float* __restrict__ d_rgb, const float* __restrict__ d_depth, const float* __restrict__ d_weights,
+    int n_rays, int K, int white_bkgd, float4* __restrict__ d_rgbsigma)
+{
+  const int lane = threadIdx.x & 31;
+  const bool valid = 2 * lane < K;
+  const long long stride = (long long)gridDim.x * (blockDim.x >> 5);
+  for (long long ray0 = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); ray0 < n_rays;
+       ray0 += stride * kRaysInFlight) {
+    PairRaw raw[kRaysInFlight];
+    float2 dws[kRaysInFlight];
+    float4 gs[kRaysInFlight];            // d_rgb (3) and d_depth of the ray
+#pragma unroll
+    for (int u = 0; u < kRaysInFlight; ++u) {
+      const long long ray = ray0 + u * stride;
+      if (ray >= n_rays) continue;
+      raw[u] = load_pair(rgbsigma, z, rays, ray, K, lane);
+      dws[u] = make_float2(0.f, 0.f);
+      if (d_weights && valid) dws[u] = __ldg(reinterpret_cast<const float2*>(d_weights + ray * K) + lane);
+      gs[u] = make_float4(__ldg(d_rgb + ray * 3 + 0), __ldg(d_rgb + ray * 3 + 1), __ldg(d_rgb + ray * 3 + 2),
+                          d_depth ? __ldg(d_depth + ray) : 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < kRaysInFlight; ++u) {
+      const long long ray = ray0 + u * stride;
+      if (ray >= n_rays) break;
+      const PairSamples s = derive_pair(raw[u], K, lane);
+      const float gr = gs[u].x, gg = gs[u].y, gb = gs[u].z, gd = gs[u].w;
+      const float2 dw = dws[u];
+      const float gbg = white_bkgd ? (gr + gg + gb) : 0.f;
+      const float T0 = warp_excl_prod1(s.t0 * s.t1, lane);
+      const float T1 = T0 * s.t0;
+      const float w0 = s.alpha0 * T0, w1 = s.alpha1 * T1;
+      const float g0 = gr * s.c0.x + gg * s.c0.y + gb * s.c0.z + gd * s.z0 - gbg + dw.x;
+      const float g1 = gr * s.c1.x + gg * s.c1.y + gb * s.c1.z + gd * s.z1 - gbg + dw.y;
+      const float gw0 = valid ? g0 * w0 : 0.f, gw1 = valid ? g1 * w1 : 0.f;
+      const float S1 = warp_excl_suffix_sum1(gw0 + gw1, lane);   // sum over the samples after 2*lane+1
+      const float S0 = S1 + gw1;
+      if (valid) {
+        const float da0 = g0 * T0 - S0 / s.t0, da1 = g1 * T1 - S1 / s.t1;
+        const float ds0 = (s.c0.w > 0.f) ? da0 * s.delta0 * (1.0f - s.alpha0) : 0.f;
+        const float ds1 = (s.c1.w > 0.f) ? da1 * s.delta1 * (1.0f - s.alpha1) : 0.f;
+        float4* o = d_rgbsigma + ray * K + 2 * lane;
+        o[0] = make_float4(w0 * gr, w0 * gg, w0 * gb, ds0);
+        o[1] = make_float4(w1 * gr, w1 * gg, w1 * gb, ds1);
+      }
+    }
+  }
+}
+
 }  // namespace dnr
 
 // C ABI -- replaces NeRFRendererDGS.composite's blending tail (nerf_renderer.py:344-365).
@@ -159,9 +310,9 @@ DNR_EXPORT int dnr_composite_fwd(const float* rgbsigma, const float* z, const fl
   if (n_rays <= 0) return 0;
   const int wpb = 8;
   int blocks = (int)((n_rays + wpb - 1) / wpb);
-  if (blocks > 148 * 16) blocks = 148 * 16;
-  dnr::composite_fwd_kernel<<<blocks, wpb * 32, 0, stream>>>((const float4*)rgbsigma, z, rays, n_rays, K, white_bkgd,
-                                                            weights, rgb, depth);
+  if (blocks > 148 * 8) blocks = 148 * 8;      // one resident wave (2 048 threads per SM), grid-stride over the rays
+  auto kern = (K % 2 == 0 && K <= 64) ? dnr::composite_fwd2_kernel : dnr::composite_fwd_kernel;
+  kern<<<blocks, wpb * 32, 0, stream>>>((const float4*)rgbsigma, z, rays, n_rays, K, white_bkgd, weights, rgb, depth);
   DNR_CHECK_LAUNCH("dnr_composite_fwd");
   return 0;
 }
@@ -173,9 +324,10 @@ DNR_EXPORT int dnr_composite_bwd(const float* rgbsigma, const float* z, const fl
   if (n_rays <= 0) return 0;
   const int wpb = 8;
   int blocks = (int)((n_rays + wpb - 1) / wpb);
-  if (blocks > 148 * 16) blocks = 148 * 16;
-  dnr::composite_bwd_kernel<<<blocks, wpb * 32, 0, stream>>>((const float4*)rgbsigma, z, rays, d_rgb, d_depth,
-                                                            d_weights, n_rays, K, white_bkgd, (float4*)d_rgbsigma);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  auto kern = (K % 2 == 0 && K <= 64) ? dnr::composite_bwd2_kernel : dnr::composite_bwd_kernel;
+  kern<<<blocks, wpb * 32, 0, stream>>>((const float4*)rgbsigma, z, rays, d_rgb, d_depth, d_weights, n_rays, K, white_bkgd,
+                                        (float4*)d_rgbsigma);
   DNR_CHECK_LAUNCH("dnr_composite_bwd");
   return 0;
 }

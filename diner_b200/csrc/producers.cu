@@ -1,11 +1,30 @@
 // Input producers next to the hot path, one thread per pixel, HBM-bound:
 //   gen_rays      reference src/util/cam_geometry.py:36-79   32 B written per ray, nothing read but the camera
+//   gen_rays_at   the same for selected pixels (diner.py:229-258): 8 B index read + 32 B written per ray
 //   depth2normal  reference src/util/depth2normal.py:6-87    4 B read (+ cached neighbours), 12 B written per pixel
 // Every fp32 operation of the reference is one rounding here (explicit __f*_rn, no contraction), so the maps agree
 // with torch to the last bits except where torch's own reduction order is free (3-term sums, the 3x3 rotation).
 #include "common.cuh"
 
 namespace dnr {
+
+// ray of pixel (x, y) of camera (e, k): pixel centre -> camera plane -> unit direction (cam_geometry.py:57-63),
+// world direction = R^T d_cam, camera centre = -R^T t (:66-70)
+__device__ __forceinline__ void ray_of_pixel(const float* __restrict__ e, const float* __restrict__ k, int x, int y,
+                                             float z_near, float z_far, float4* __restrict__ out) {
+  const float px = __fdiv_rn(__fsub_rn((float)x + 0.5f, k[2]), k[0]);
+  const float py = __fdiv_rn(__fsub_rn((float)y + 0.5f, k[5]), k[4]);
+  const float nrm = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(px, px), __fmul_rn(py, py)), 1.0f));
+  const float dx = __fdiv_rn(px, nrm), dy = __fdiv_rn(py, nrm), dz = __fdiv_rn(1.0f, nrm);
+  const float wx = fmaf(e[8], dz, fmaf(e[4], dy, __fmul_rn(e[0], dx)));
+  const float wy = fmaf(e[9], dz, fmaf(e[5], dy, __fmul_rn(e[1], dx)));
+  const float wz = fmaf(e[10], dz, fmaf(e[6], dy, __fmul_rn(e[2], dx)));
+  const float ox = -fmaf(e[8], e[11], fmaf(e[4], e[7], __fmul_rn(e[0], e[3])));
+  const float oy = -fmaf(e[9], e[11], fmaf(e[5], e[7], __fmul_rn(e[1], e[3])));
+  const float oz = -fmaf(e[10], e[11], fmaf(e[6], e[7], __fmul_rn(e[2], e[3])));
+  out[0] = make_float4(ox, oy, oz, wx);
+  out[1] = make_float4(wy, wz, z_near, z_far);
+}
 
 __global__ void gen_rays_kernel(const float* __restrict__ E, const float* __restrict__ K, int B, int W, int H,
                                 const float* __restrict__ z_near, const float* __restrict__ z_far,
@@ -15,23 +34,22 @@ __global__ void gen_rays_kernel(const float* __restrict__ E, const float* __rest
   if (idx >= per * B) return;
   const int b = (int)(idx / per);
   const int rem = (int)(idx % per);
-  const int y = rem / W, x = rem % W;
-  const float* e = E + (size_t)b * 16;
-  const float* k = K + (size_t)b * 9;
-  // pixel centre -> camera plane -> unit direction (cam_geometry.py:57-63)
-  const float px = __fdiv_rn(__fsub_rn((float)x + 0.5f, k[2]), k[0]);
-  const float py = __fdiv_rn(__fsub_rn((float)y + 0.5f, k[5]), k[4]);
-  const float nrm = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(px, px), __fmul_rn(py, py)), 1.0f));
-  const float dx = __fdiv_rn(px, nrm), dy = __fdiv_rn(py, nrm), dz = __fdiv_rn(1.0f, nrm);
-  // world direction = R^T d_cam, camera centre = -R^T t (:66-70)
-  const float wx = fmaf(e[8], dz, fmaf(e[4], dy, __fmul_rn(e[0], dx)));
-  const float wy = fmaf(e[9], dz, fmaf(e[5], dy, __fmul_rn(e[1], dx)));
-  const float wz = fmaf(e[10], dz, fmaf(e[6], dy, __fmul_rn(e[2], dx)));
-  const float ox = -fmaf(e[8], e[11], fmaf(e[4], e[7], __fmul_rn(e[0], e[3])));
-  const float oy = -fmaf(e[9], e[11], fmaf(e[5], e[7], __fmul_rn(e[1], e[3])));
-  const float oz = -fmaf(e[10], e[11], fmaf(e[6], e[7], __fmul_rn(e[2], e[3])));
-  rays[idx * 2 + 0] = make_float4(ox, oy, oz, wx);
-  rays[idx * 2 + 1] = make_float4(wy, wz, z_near[b], z_far[b]);
+  ray_of_pixel(E + (size_t)b * 16, K + (size_t)b * 9, rem % W, rem / W, z_near[b], z_far[b], rays + idx * 2);
+}
+
+// rays of SELECTED pixels: rays[b, i] = gen_rays(...)[b].view(H*W, 8)[pix[b, i]]  (the caller's gather, diner.py:229-258)
+__global__ void gen_rays_at_kernel(const float* __restrict__ E, const float* __restrict__ K, int B, int W, int H,
+                                   const float* __restrict__ z_near, const float* __restrict__ z_far,
+                                   const long long* __restrict__ pix, int n, float4* __restrict__ rays,
+                                   int* __restrict__ bad) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)n * B) return;
+  const int b = (int)(idx / n);
+  long long p = pix[idx];
+  const long long per = (long long)H * W;
+  if (p < 0) p += per;                                  // torch indexing accepts negative indices
+  if (p < 0 || p >= per) { if (bad) atomicExch(bad, 1); p = 0; }
+  ray_of_pixel(E + (size_t)b * 16, K + (size_t)b * 9, (int)(p % W), (int)(p / W), z_near[b], z_far[b], rays + idx * 2);
 }
 
 struct D2NParams {
@@ -112,6 +130,22 @@ DNR_EXPORT int dnr_gen_rays(const float* extrinsics, const float* intrinsics, in
   dnr::gen_rays_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(extrinsics, intrinsics, B, W, H, z_near, z_far,
                                                                         (float4*)rays);
   DNR_CHECK_LAUNCH("dnr_gen_rays");
+  return 0;
+}
+
+// Rays of n selected pixels per camera (flat indices y*W+x, int64 [B,n]); same arithmetic as dnr_gen_rays, so
+// rays[b,i] == dnr_gen_rays(...)[b, pix[b,i]] bit for bit.  Replaces gen_rays + the advanced-index gather of
+// DINER.calc_losses (diner.py:222-258).  `bad_flag` (device int, nullable) is set to 1 if an index is out of range.
+DNR_EXPORT int dnr_gen_rays_at(const float* extrinsics, const float* intrinsics, int B, int W, int H, const float* z_near,
+                               const float* z_far, const long long* pix_idx, int n, float* rays, int* bad_flag,
+                               cudaStream_t stream) {
+  DNR_REQUIRE(B >= 0 && W >= 1 && H >= 1 && n >= 0, "dnr_gen_rays_at: bad sizes");
+  const long long tot = (long long)B * n;
+  if (tot == 0) return 0;
+  DNR_REQUIRE(extrinsics && intrinsics && z_near && z_far && rays && pix_idx, "dnr_gen_rays_at: null argument");
+  dnr::gen_rays_at_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, stream>>>(extrinsics, intrinsics, B, W, H, z_near, z_far,
+                                                                          pix_idx, n, (float4*)rays, bad_flag);
+  DNR_CHECK_LAUNCH("dnr_gen_rays_at");
   return 0;
 }
 

@@ -2,6 +2,7 @@
 (SURVEY.md 8f rows 1-2):
 
     gen_rays(extrinsics, intrinsics, W, H, z_near, z_far)   src/util/cam_geometry.py:36-79
+    gen_rays_at(..., pix_idcs)                               the same for selected pixels (src/models/diner.py:222-258)
     depth2normal(dmap, K)                                    src/util/depth2normal.py:6-87
 
 Both call the CUDA kernels in csrc/producers.cu through the C ABI; CPU tensors raise (there is no CPU path).
@@ -21,9 +22,7 @@ def _dev_f32(t: torch.Tensor, name: str, shape_tail) -> torch.Tensor:
     return t.detach().to(torch.float32).contiguous()
 
 
-def gen_rays(extrinsics, intrinsics, W, H, z_near, z_far) -> torch.Tensor:
-    """(B,4,4) world->cam extrinsics, (B,3,3) intrinsics, z_near / z_far (B,) -> rays (B,H,W,8) =
-    [origin(3), direction(3), near, far] through the pixel centres (OpenCV convention)."""
+def _camera_args(extrinsics, intrinsics, W, H, z_near, z_far):
     E = _dev_f32(extrinsics, "extrinsics", (4, 4))
     K = _dev_f32(intrinsics, "intrinsics", (3, 3))
     B = E.shape[0]
@@ -36,10 +35,38 @@ def gen_rays(extrinsics, intrinsics, W, H, z_near, z_far) -> torch.Tensor:
     zf = torch.as_tensor(z_far, dtype=torch.float32, device=E.device).reshape(-1).contiguous()
     if zn.numel() != B or zf.numel() != B:
         raise ValueError("z_near and z_far must hold one value per camera")
+    return E, K, B, W, H, zn, zf
+
+
+def gen_rays(extrinsics, intrinsics, W, H, z_near, z_far) -> torch.Tensor:
+    """(B,4,4) world->cam extrinsics, (B,3,3) intrinsics, z_near / z_far (B,) -> rays (B,H,W,8) =
+    [origin(3), direction(3), near, far] through the pixel centres (OpenCV convention)."""
+    E, K, B, W, H, zn, zf = _camera_args(extrinsics, intrinsics, W, H, z_near, z_far)
     rays = torch.empty(B, H, W, 8, device=E.device, dtype=torch.float32)
     with torch.cuda.device(E.device):
         _lib.call("dnr_gen_rays", _lib.ptr(E), _lib.ptr(K), B, W, H, _lib.ptr(zn), _lib.ptr(zf), _lib.ptr(rays),
                   _lib.stream_ptr())
+    return rays
+
+
+def gen_rays_at(extrinsics, intrinsics, W, H, z_near, z_far, pix_idcs, check_bounds: bool = True) -> torch.Tensor:
+    """Rays of selected pixels: `gen_rays(...).view(B, H*W, 8)[arange(B)[:, None], pix_idcs]` (the gather of
+    DINER.calc_losses, diner.py:256-257) without materialising the full-frame ray tensor.  pix_idcs (B, n) integer flat
+    pixel indices y*W+x.  `check_bounds` reads one flag back (a sync) and raises IndexError like the gather would."""
+    E, K, B, W, H, zn, zf = _camera_args(extrinsics, intrinsics, W, H, z_near, z_far)
+    if not isinstance(pix_idcs, torch.Tensor) or pix_idcs.dim() != 2 or pix_idcs.shape[0] != B:
+        raise ValueError("pix_idcs must have shape (B, n)")
+    if pix_idcs.dtype.is_floating_point or pix_idcs.dtype == torch.bool:
+        raise IndexError("pix_idcs must be an integer tensor")
+    pix = pix_idcs.to(device=E.device, dtype=torch.int64).contiguous()
+    n = pix.shape[1]
+    rays = torch.empty(B, n, 8, device=E.device, dtype=torch.float32)
+    bad = torch.zeros(1, device=E.device, dtype=torch.int32) if check_bounds else None
+    with torch.cuda.device(E.device):
+        _lib.call("dnr_gen_rays_at", _lib.ptr(E), _lib.ptr(K), B, W, H, _lib.ptr(zn), _lib.ptr(zf), _lib.ptr(pix), n,
+                  _lib.ptr(rays), _lib.ptr(bad), _lib.stream_ptr())
+    if check_bounds and int(bad.item()):
+        raise IndexError(f"pix_idcs out of range for an image of {H}x{W} pixels")
     return rays
 
 

@@ -190,6 +190,13 @@ int dnr_composite_bwd(const float* rgbsigma, const float* z, const float* rays, 
 int dnr_gen_rays(const float* extrinsics, const float* intrinsics, int B, int W, int H, const float* z_near,
                  const float* z_far, float* rays, dnr_stream_t stream);
 
+/* Rays of n selected pixels per camera: pix_idx int64 [B,n] holds flat pixel indices y*W+x (negative indices count from
+ * the end, as in torch); rays [B,n,8] equal dnr_gen_rays(...)[b, pix_idx[b,i]] bit for bit.  Replaces gen_rays followed by
+ * the advanced-index gather of DINER.calc_losses (src/models/diner.py:222-258).  bad_flag (device int, nullable) is set to
+ * 1 when an index is out of range (that ray is then generated for pixel 0). */
+int dnr_gen_rays_at(const float* extrinsics, const float* intrinsics, int B, int W, int H, const float* z_near,
+                    const float* z_far, const long long* pix_idx, int n, float* rays, int* bad_flag, dnr_stream_t stream);
+
 /* Camera-space normal maps [N,3,H,W] from depth maps [N,1,H,W] and intrinsics [N,3,3] by central differences of the
  * back-projected points, with the reference's hole-cleaning rule and NaN behaviour.  Replaces depth2normal
  * (src/util/depth2normal.py:6-87) including the axis its torch.cross (no dim) takes when N == 3. */

@@ -91,3 +91,40 @@ def depth2normal(dmap, K):
             res[d[n, 0] == 0] = 0                                                           # :78
             out[n] = res
     return out.transpose(0, 3, 1, 2).copy()                                                 # :84
+
+
+# ---- caller-side ray handling (reference src/models/diner.py; not importable here: pytorch_lightning is absent, so
+# ---- these two are restated from the cited lines and "parity unpinned" by a run of the reference) -----------------
+
+def rays_at(extrinsics, intrinsics, W, H, z_near, z_far, pix_idcs):
+    """rays.view(SB, H*W, 8)[arange(SB)[:, None], pix_idcs] -- diner.py:256-257."""
+    rays = gen_rays(extrinsics, intrinsics, W, H, z_near, z_far).reshape(len(extrinsics), H * W, 8)
+    pix = np.asarray(pix_idcs, np.int64)
+    return rays[np.arange(rays.shape[0])[:, None], pix]
+
+
+def patch_pixel_indices(centers, W, patch):
+    """Flat pixel indices of the patch around each centre -- diner.py:234,238-247, loop form.
+    centers: (SB,) flat indices as torch.multinomial returns them."""
+    pad = (patch + 1) // 2                                   # :234
+    out = np.empty((len(centers), patch * patch), np.int64)
+    for n, c in enumerate(np.asarray(centers, np.int64).reshape(-1)):
+        cx, cy = c % W, c // W                               # :239
+        i = 0
+        for h in range(patch):                               # pix_coords[h, w] = (x=w, y=h) - pad  (:240-243)
+            for w in range(patch):
+                x, y = cx + (w - pad), cy + (h - pad)        # :244
+                out[n, i] = x + y * W                        # :245
+                i += 1
+    return out
+
+
+def eligible_patch_centres(alpha, patch):
+    """The mask torch.multinomial draws from (:232-237): foreground minus a border of pad pixels."""
+    fg = np.array(alpha[:, 0], np.float32, copy=True)
+    pad = (patch + 1) // 2
+    fg[..., :pad] = 0
+    fg[..., :pad, :] = 0
+    fg[..., -pad:] = 0
+    fg[..., -pad:, :] = 0
+    return fg

@@ -149,3 +149,24 @@ def test_sharded_render_gloo_world2():
     for p in procs:
         p.join(timeout=60)
     assert res == [(0, True), (1, True)]
+
+
+def test_patch_selection_host_logic_matches_loop_restatement():
+    """callers.patch_pixels is torch index arithmetic (no kernel): check it on the CPU against the loop form of
+    diner.py:231-247 in oracle/producers_oracle.py."""
+    import numpy as np
+    from diner_b200.callers import patch_pixels, patch_pixels_at, random_pixels
+    from oracle import producers_oracle as P
+    SB, H, W = 4, 40, 56
+    torch.manual_seed(0)
+    alpha = (torch.rand(SB, 1, H, W) > 0.5).float()
+    for patch in (1, 4, 9, 16):
+        idx, centres = patch_pixels(alpha, patch, generator=torch.Generator().manual_seed(patch))
+        flat = (centres[:, 0] + centres[:, 1] * W).numpy()
+        assert np.array_equal(idx.numpy(), P.patch_pixel_indices(flat, W, patch))
+        assert np.array_equal(patch_pixels_at(torch.from_numpy(flat), W, patch).numpy(), idx.numpy())
+        elig = P.eligible_patch_centres(alpha.numpy(), patch)
+        assert all(elig[s, int(centres[s, 1]), int(centres[s, 0])] > 0 for s in range(SB))
+        assert int(idx.min()) >= 0 and int(idx.max()) < H * W
+    pix = random_pixels(SB, H, W, 128, generator=torch.Generator().manual_seed(1))
+    assert pix.shape == (SB, 128) and int(pix.min()) >= 0 and int(pix.max()) < H * W
