@@ -102,58 +102,99 @@ __global__ void __launch_bounds__(kSamplerWarps * 32) sampler_kernel(SamplerPara
   Philox rng(P.seed);
 
   // ---- 1. candidates and their likelihoods, compacted to the non-zero ones (in index order) ----
+  // A lane scores four consecutive candidates per pass: one Philox call yields the four uniforms of candidates
+  // 4j..4j+3 (counter i >> 2, component i & 3), and the compaction keeps index order (lane-major, q-minor).
+  // Per view the four candidates go through the taps stage by stage (std -> depth -> normal -> erf), so that the four
+  // map loads of a stage are in flight together instead of one dependent L2 round trip per candidate; the float
+  // operations of a candidate are the same, in the same order, as in the one-candidate form.
   int n_nz = 0;
-  for (int i0 = 0; i0 < C; i0 += 32) {
-    const int i = i0 + lane;
-    float p = 0.0f, zc = 0.0f;
-    if (i < C) {
-      float u;
-      if (P.u_coarse) u = P.u_coarse[ray * C + i];
-      else { uint4 r = rng((uint32_t)ray, (uint32_t)(ray >> 32), (uint32_t)(i >> 2), 0u);
-             u = u01((i & 3) == 0 ? r.x : (i & 3) == 1 ? r.y : (i & 3) == 2 ? r.z : r.w); }
-      float s = P.lin_tab[i] + u * P.inv_c_step;       // :55-57
-      zc = near * (1.0f - s) + far * s;                 // :60
-      const float x0 = o0 + zc * d0, x1 = o1 + zc * d1, x2 = o2 + zc * d2;   // :96
-      for (int v = 0; v < NV; ++v) {
-        const float* cv = cam + v * 20;
-        const float xc = fmaf(cv[2], x2, fmaf(cv[1], x1, cv[0] * x0)) + cv[9];    // :100-101
-        const float yc = fmaf(cv[5], x2, fmaf(cv[4], x1, cv[3] * x0)) + cv[10];
-        const float zcam = fmaf(cv[8], x2, fmaf(cv[7], x1, cv[6] * x0)) + cv[11];
-        float uu = xc / zcam, vv = yc / zcam;          // :107
-        uu = uu * cv[15]; vv = vv * cv[16];            // :108
-        uu = uu + cv[17]; vv = vv + cv[18];            // :109
-        uu = uu / P.img_w * 2.0f - 1.0f;               // :110
-        vv = vv / P.img_h * 2.0f - 1.0f;
-        // depth std first: background (std == 0) candidates are dropped without more taps
-        const int sx = nearest_zeros(uu * P.std_sx, Wp), sy = nearest_zeros(vv * P.std_sy, Hp);
-        if (sx < 0 || sy < 0) continue;
-        const float sref = __ldg(P.stdpad + ((size_t)sb * NV + v) * pad_sz + (size_t)sy * Wp + sx);
-        if (sref == 0.0f) continue;                    // bg_mask :123
-        const int ix = nearest_border(uu, W), iy = nearest_border(vv, H);
-        const float dref = __ldg(P.depth + ((size_t)sb * NV + v) * map_sz + (size_t)iy * W + ix);
-        if (!(fabsf(dref - zcam) < P.depth_diff_max)) continue;   // :122
-        const int nx = nearest_zeros(uu, W), ny = nearest_zeros(vv, H);
-        float n0 = 0.f, n1 = 0.f, n2 = 0.f;
-        if (nx >= 0 && ny >= 0) {
-          const float* np_ = P.normal + ((size_t)sb * NV + v) * 3 * map_sz + (size_t)ny * W + nx;
-          n0 = __ldg(np_); n1 = __ldg(np_ + map_sz); n2 = __ldg(np_ + 2 * map_sz);
-        }
-        const float cosd = cv[12] * n0 + cv[13] * n1 + cv[14] * n2;   // :119
-        if (!(cosd <= 0.0f)) continue;                 // :121
-        const float den = sref * sqrt2;
-        const float a = erff((zcam + half_step - dref) / den);
-        const float b = erff((zcam - half_step - dref) / den);
-        const float pv = fabsf(0.5f * (a - b));        // :125-128
-        p = fmaxf(p, pv);                              // :129
+  const unsigned lt_mask = (1u << lane) - 1u;
+  for (int i0 = 0; i0 < C; i0 += 128) {
+    const int ib = i0 + 4 * lane;
+    float pq[4], zq[4], x0[4], x1[4], x2[4];
+    uint4 r = make_uint4(0u, 0u, 0u, 0u);
+    if (!P.u_coarse && ib < C) r = rng((uint32_t)ray, (uint32_t)(ray >> 32), (uint32_t)(ib >> 2), 0u);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int i = ib + q;
+      pq[q] = 0.0f; zq[q] = 0.0f; x0[q] = x1[q] = x2[q] = 0.0f;
+      if (i < C) {
+        const float u = P.u_coarse ? P.u_coarse[ray * C + i] : u01(q == 0 ? r.x : q == 1 ? r.y : q == 2 ? r.z : r.w);
+        float s = P.lin_tab[i] + u * P.inv_c_step;       // :55-57
+        const float zc = near * (1.0f - s) + far * s;     // :60
+        zq[q] = zc;
+        x0[q] = o0 + zc * d0; x1[q] = o1 + zc * d1; x2[q] = o2 + zc * d2;   // :96
       }
     }
-    if (P.p_out && i < C) P.p_out[ray * C + i] = p;
-    const unsigned nzmask = __ballot_sync(0xffffffffu, p != 0.0f);
-    if (p != 0.0f) {
-      const int pos = n_nz + __popc(nzmask & ((1u << lane) - 1u));
-      lp[pos] = p; lz[pos] = zc; lidx[pos] = (unsigned short)i;
+    for (int v = 0; v < NV; ++v) {
+      const float* cv = cam + v * 20;
+      const float* std_v = P.stdpad + ((size_t)sb * NV + v) * pad_sz;
+      const float* depth_v = P.depth + ((size_t)sb * NV + v) * map_sz;
+      const float* normal_v = P.normal + ((size_t)sb * NV + v) * 3 * map_sz;
+      float zcam[4], uu[4], vv[4], sref[4], dref[4];
+      bool ok[4];
+      // stage A: project, tap the padded std map (background candidates, std == 0, need nothing else)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float xc = fmaf(cv[2], x2[q], fmaf(cv[1], x1[q], cv[0] * x0[q])) + cv[9];    // :100-101
+        const float yc = fmaf(cv[5], x2[q], fmaf(cv[4], x1[q], cv[3] * x0[q])) + cv[10];
+        zcam[q] = fmaf(cv[8], x2[q], fmaf(cv[7], x1[q], cv[6] * x0[q])) + cv[11];
+        float a = xc / zcam[q], b = yc / zcam[q];      // :107
+        a = a * cv[15]; b = b * cv[16];                // :108
+        a = a + cv[17]; b = b + cv[18];                // :109
+        uu[q] = a / P.img_w * 2.0f - 1.0f;             // :110
+        vv[q] = b / P.img_h * 2.0f - 1.0f;
+        const int sx = nearest_zeros(uu[q] * P.std_sx, Wp), sy = nearest_zeros(vv[q] * P.std_sy, Hp);
+        ok[q] = (ib + q < C) && sx >= 0 && sy >= 0;
+        sref[q] = ok[q] ? __ldg(std_v + (size_t)sy * Wp + sx) : 0.0f;
+      }
+      // stage B: depth tap and the depth-difference gate
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        ok[q] = ok[q] && sref[q] != 0.0f;              // bg_mask :123
+        const int ix = nearest_border(uu[q], W), iy = nearest_border(vv[q], H);
+        dref[q] = ok[q] ? __ldg(depth_v + (size_t)iy * W + ix) : 0.0f;
+      }
+      bool any_ok = false;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        ok[q] = ok[q] && (fabsf(dref[q] - zcam[q]) < P.depth_diff_max);   // :122
+        any_ok = any_ok || ok[q];
+      }
+      if (!__any_sync(0xffffffffu, any_ok)) continue;
+      // stage C: normal tap, facing test; stage D: likelihood
+      float n0[4], n1[4], n2[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int nx = nearest_zeros(uu[q], W), ny = nearest_zeros(vv[q], H);
+        const bool tap = ok[q] && nx >= 0 && ny >= 0;
+        const float* np_ = normal_v + (size_t)ny * W + nx;
+        n0[q] = tap ? __ldg(np_) : 0.f; n1[q] = tap ? __ldg(np_ + map_sz) : 0.f; n2[q] = tap ? __ldg(np_ + 2 * map_sz) : 0.f;
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float cosd = cv[12] * n0[q] + cv[13] * n1[q] + cv[14] * n2[q];   // :119
+        if (ok[q] && cosd <= 0.0f) {                   // :121
+          const float den = sref[q] * sqrt2;
+          const float a = erff((zcam[q] + half_step - dref[q]) / den);
+          const float b = erff((zcam[q] - half_step - dref[q]) / den);
+          const float pv = fabsf(0.5f * (a - b));      // :125-128
+          pq[q] = fmaxf(pq[q], pv);                    // :129
+        }
+      }
     }
-    n_nz += __popc(nzmask);
+    if (P.p_out) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        if (ib + q < C) P.p_out[ray * C + ib + q] = pq[q];
+    }
+    const unsigned b0 = __ballot_sync(0xffffffffu, pq[0] != 0.0f), b1 = __ballot_sync(0xffffffffu, pq[1] != 0.0f);
+    const unsigned b2 = __ballot_sync(0xffffffffu, pq[2] != 0.0f), b3 = __ballot_sync(0xffffffffu, pq[3] != 0.0f);
+    int pos = n_nz + __popc(b0 & lt_mask) + __popc(b1 & lt_mask) + __popc(b2 & lt_mask) + __popc(b3 & lt_mask);
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      if (pq[q] != 0.0f) { lp[pos] = pq[q]; lz[pos] = zq[q]; lidx[pos] = (unsigned short)(ib + q); ++pos; }
+    n_nz += __popc(b0) + __popc(b1) + __popc(b2) + __popc(b3);
   }
   __syncwarp();
 

@@ -159,6 +159,37 @@ def test_sampler_packed_reference_noise_vs_golden(golden_cache, name):
         scene.model.to_device("cpu")
 
 
+def test_sampler_philox_jitter_equals_explicit_uniforms():
+    """Performance mode (in-kernel Philox, four candidates per call) scores exactly the candidates the parity mode
+    scores when it is handed the same uniforms: likelihoods and shortlist indices bit-equal."""
+    dev = _cuda()
+    from diner_b200 import sample_rays
+    from diner_b200.scene import get_scene
+    from diner_b200.synthetic import make_scene
+    from oracle.philox import philox4x32_10 as _philox4x32_10
+    scene = make_scene("tiny", seed=0, calibrate=False)
+    wl = scene.workload
+    scene.model.to_device(dev)
+    rays = scene.rays.to(dev)
+    sc = get_scene(scene.model)
+    K, C, G = wl.n_samples, wl.n_candidates, wl.n_gaussian
+    n = rays.shape[0] * rays.shape[1]
+    for C_ in (C, 998, 130):                         # C not a multiple of 4 / of 128: ragged last pass
+        seed = 0x1234_5678_9ABC_DEF0 + C_
+        _, d = sample_rays(sc, rays, K, C_, G, seed=seed, want_debug=True)
+        ray = np.arange(n, dtype=np.uint64)[:, None]
+        blk = np.arange((C_ + 3) // 4, dtype=np.uint64)[None, :]
+        r = _philox4x32_10(ray & np.uint64(0xFFFFFFFF), ray >> np.uint64(32), blk + 0 * ray, 0 * blk + 0 * ray,
+                           seed & 0xFFFFFFFF, seed >> 32)
+        u = np.stack(r, -1).reshape(n, -1)[:, :C_]
+        u = ((u & np.uint64(0xFFFFFF)).astype(np.float32) * np.float32(1.0 / 16777216.0)).astype(np.float32)
+        noise = dict(u_coarse=torch.from_numpy(u), n_gauss_full=torch.zeros(n, G), u_fill_full=torch.zeros(n, K))
+        _, d2 = sample_rays(sc, rays, K, C_, G, noise=noise, want_debug=True)
+        assert int((d["p"] != 0).sum()) > 0
+        assert torch.equal(d["p"], d2["p"]) and torch.equal(d["sel_idx"], d2["sel_idx"])
+        assert torch.equal(d["ray_mask"], d2["ray_mask"])
+
+
 def test_sampler_background_rays_are_stratified_uniform():
     """A ray that sees no depth (std == 0 everywhere) gets K stratified samples in [near, far)."""
     dev = _cuda()

@@ -170,3 +170,11 @@ def test_patch_selection_host_logic_matches_loop_restatement():
         assert int(idx.min()) >= 0 and int(idx.max()) < H * W
     pix = random_pixels(SB, H, W, 128, generator=torch.Generator().manual_seed(1))
     assert pix.shape == (SB, 128) and int(pix.min()) >= 0 and int(pix.max()) < H * W
+
+
+def test_numpy_philox_known_answers():
+    """Random123's kat_vectors for philox4x32-10: all-zero and all-one counter/key."""
+    from oracle.philox import philox4x32_10
+    assert [int(x) for x in philox4x32_10(0, 0, 0, 0, 0, 0)] == [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]
+    f = 0xffffffff
+    assert [int(x) for x in philox4x32_10(f, f, f, f, f, f)] == [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]
