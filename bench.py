@@ -196,14 +196,28 @@ def main():
     depth_host = torch.empty(rays_cpu.shape[0], rays_cpu.shape[1]).pin_memory()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
 
+    enc_bucket = None
     if args.train:
         model.encoder.latent = model.encoder.latent.detach().requires_grad_(True)
+        if world > 1:
+            # DDP of the reference all-reduces every parameter gradient (configs/train_diner_facescape.yaml:87,
+            # 11.67 M fp32 = 46.7 MB).  The MLP's 3.45 M gradients come from our backward; the
+            # encoder trunk is stock PyTorch and not part of this bench, so a bucket of its size stands in for it.
+            from diner_b200.sharding import allreduce_gradients
+            n_mlp = sum(p.numel() for p in model.mlp_fine.parameters())
+            enc_bucket = torch.zeros(max(0, 11_670_000 - n_mlp), device=dev)
+
+    def train_allreduce():
+        if world > 1:
+            allreduce_gradients(list(model.mlp_fine.parameters()))
+            dist.all_reduce(enc_bucket)
 
     def step_device():
         if args.train:
             out = renderer(model, rays_dev)
             loss = out.fine.rgb.square().mean()
             loss.backward()
+            train_allreduce()
             return out
         with torch.no_grad():
             return renderer(model, rays_dev)
@@ -213,6 +227,7 @@ def main():
         if args.train:
             out = renderer(model, rays_stage)
             out.fine.rgb.square().mean().backward()
+            train_allreduce()
         else:
             with torch.no_grad():
                 out = renderer(model, rays_stage)
@@ -324,7 +339,9 @@ def main():
                                 rays_per_gpu_per_step=n_rays, samples_per_ray=wl.n_samples,
                                 n_candidates=wl.n_candidates, n_gaussian=wl.n_gaussian, n_views=wl.NV,
                                 source_hw=[wl.H, wl.W], l2="flushed between timed steps (256 MiB write)",
-                                parallelism=f"rays sharded, dp{world}"),
+                                parallelism=f"rays sharded, dp{world}" + (
+                                    ", NCCL all-reduce of 46.7 MB gradients per step (MLP grads + encoder-sized bucket)"
+                                    if args.train and world > 1 else "")),
                     msamples_per_s=value * wl.n_samples / 1e6,
                     e2e=dict(value=e2e_value, unit="rays/s", h2d_bytes_per_step=rays_host.numel() * 4,
                              d2h_bytes_per_step=(rgb_host.numel() + depth_host.numel()) * 4,

@@ -202,40 +202,80 @@ __device__ __forceinline__ void red_add_v4(float* addr, float4 v) {
                : "memory");
 }
 
-// One lane per row (a 32-row slab per warp): d_latent[tap] += w_tap * d_feature, 4 channels per red.
+// Backward scatter d_latent[tap] += w_tap * d_feature.  One CTA per 32-row slab; warp w owns channels
+// [128 w, 128 w + 128).  The slab's gradient rows arrive in XR order (one row per lane, coalesced), are transposed
+// through shared memory, and the warp then walks the rows view by view in sample order with the channels across
+// lanes: consecutive samples of a ray that fall into the same bilinear footprint of a view (most of the
+// depth-guided samples do: they cluster within a few std of the surface) are summed in registers and leave as
+// ONE set of four 512-byte-contiguous vector reductions per warp instead of one 16-byte reduction per lane and row.
+constexpr int kBwdRowStride = 33;      // float4 per staged row: 32 + 1 pad -> conflict-free 128-bit stores
+constexpr int kBwdSmemBytes = 4 * 32 * kBwdRowStride * 16;
+
 __global__ void __launch_bounds__(128) encode_bwd_kernel(EncodeParams P) {
+  extern __shared__ float4 bwd_stage[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const RowMap rm = RowMap::make(P.NV);
-  const long long slab = (long long)blockIdx.x * 4 + warp;
+  const long long slab = blockIdx.x;
   const long long row = slab * 32 + lane;
   long long sample; int view;
   const bool valid = rm.decode(row, P.n_samples, sample, view);
   if (!__any_sync(0xffffffffu, valid)) return;
   const int L = 512;
-  RowGeom g;
-  float w00 = 0.f, w01 = 0.f, w10 = 0.f, w11 = 0.f;
-  float *q00 = nullptr, *q01 = nullptr, *q10 = nullptr, *q11 = nullptr;
+  uint32_t kx = 0, ky = 0, km = 0;
+  float wx = 0.f, wy = 0.f;
   if (valid) {
+    RowGeom g;
     row_geometry(P, sample, view, g);
-    float* dl = P.d_latent + g.map * (size_t)P.Hl * P.Wl * L;
-    q00 = dl + ((size_t)g.y0 * P.Wl + g.x0) * L; q01 = dl + ((size_t)g.y0 * P.Wl + g.x1) * L;
-    q10 = dl + ((size_t)g.y1 * P.Wl + g.x0) * L; q11 = dl + ((size_t)g.y1 * P.Wl + g.x1) * L;
-    w00 = (1.f - g.wx) * (1.f - g.wy); w01 = g.wx * (1.f - g.wy); w10 = (1.f - g.wx) * g.wy; w11 = g.wx * g.wy;
+    kx = (uint32_t)g.x0 | ((uint32_t)g.x1 << 16);
+    ky = (uint32_t)g.y0 | ((uint32_t)g.y1 << 16);
+    km = (uint32_t)g.map + 1u;
+    wx = g.wx; wy = g.wy;
   }
-  const long long tile = row / 128;
-  const int rr = (int)(row % 128);
-  const float4* src = reinterpret_cast<const float4*>(P.d_lat_xr) + (size_t)tile * (L / 4) * 128 + rr;
-#pragma unroll 4
-  for (int n4 = 0; n4 < L / 4; ++n4) {
-    const float4 d = src[(size_t)n4 * 128];
-    if (valid) {
-      const int ch = n4 * 4;
-      if (w00 != 0.f) red_add_v4(q00 + ch, make_float4(d.x * w00, d.y * w00, d.z * w00, d.w * w00));
-      if (w01 != 0.f) red_add_v4(q01 + ch, make_float4(d.x * w01, d.y * w01, d.z * w01, d.w * w01));
-      if (w10 != 0.f) red_add_v4(q10 + ch, make_float4(d.x * w10, d.y * w10, d.z * w10, d.w * w10));
-      if (w11 != 0.f) red_add_v4(q11 + ch, make_float4(d.x * w11, d.y * w11, d.z * w11, d.w * w11));
+  // stage this warp's 128 channels of the 32 rows: st[row][n4]
+  float4* st = bwd_stage + warp * 32 * kBwdRowStride;
+  {
+    const long long tile = row / 128;
+    const int rr = (int)(row % 128);
+    const float4* src = reinterpret_cast<const float4*>(P.d_lat_xr) + ((size_t)tile * (L / 4) + warp * 32) * 128 + rr;
+#pragma unroll 8
+    for (int n4 = 0; n4 < 32; ++n4) st[lane * kBwdRowStride + n4] = src[(size_t)n4 * 128];
+  }
+  __syncwarp();
+  float4 a00 = make_float4(0.f, 0.f, 0.f, 0.f), a01 = a00, a10 = a00, a11 = a00;
+  uint32_t cx = 0, cy = 0, cm = 0;
+  const int ch = warp * 128 + lane * 4;
+  auto flush = [&]() {
+    if (cm == 0) return;
+    float* dl = P.d_latent + (size_t)(cm - 1) * P.Hl * P.Wl * L + ch;
+    const size_t x0 = cx & 0xffffu, x1 = cx >> 16, y0 = cy & 0xffffu, y1 = cy >> 16;
+    red_add_v4(dl + (y0 * P.Wl + x0) * L, a00);
+    if (x1 != x0) red_add_v4(dl + (y0 * P.Wl + x1) * L, a01);
+    if (y1 != y0) {
+      red_add_v4(dl + (y1 * P.Wl + x0) * L, a10);
+      if (x1 != x0) red_add_v4(dl + (y1 * P.Wl + x1) * L, a11);
+    }
+  };
+  for (int v = 0; v < rm.NV; ++v) {
+    for (int s = 0; s < rm.SPW; ++s) {
+      const int l = s * rm.NV + v;
+      const uint32_t m = __shfl_sync(0xffffffffu, km, l);
+      if (m == 0) continue;                              // padding row (warp-uniform)
+      const uint32_t x = __shfl_sync(0xffffffffu, kx, l), y = __shfl_sync(0xffffffffu, ky, l);
+      const float fx = __shfl_sync(0xffffffffu, wx, l), fy = __shfl_sync(0xffffffffu, wy, l);
+      if (m != cm || x != cx || y != cy) {
+        flush();
+        a00 = make_float4(0.f, 0.f, 0.f, 0.f); a01 = a00; a10 = a00; a11 = a00;
+        cm = m; cx = x; cy = y;
+      }
+      const float4 d = st[l * kBwdRowStride + lane];
+      const float w00 = (1.f - fx) * (1.f - fy), w01 = fx * (1.f - fy), w10 = (1.f - fx) * fy, w11 = fx * fy;
+      a00.x = fmaf(d.x, w00, a00.x); a00.y = fmaf(d.y, w00, a00.y); a00.z = fmaf(d.z, w00, a00.z); a00.w = fmaf(d.w, w00, a00.w);
+      a01.x = fmaf(d.x, w01, a01.x); a01.y = fmaf(d.y, w01, a01.y); a01.z = fmaf(d.z, w01, a01.z); a01.w = fmaf(d.w, w01, a01.w);
+      a10.x = fmaf(d.x, w10, a10.x); a10.y = fmaf(d.y, w10, a10.y); a10.z = fmaf(d.z, w10, a10.z); a10.w = fmaf(d.w, w10, a10.w);
+      a11.x = fmaf(d.x, w11, a11.x); a11.y = fmaf(d.y, w11, a11.y); a11.z = fmaf(d.z, w11, a11.z); a11.w = fmaf(d.w, w11, a11.w);
     }
   }
+  flush();
 }
 
 // latent (N,C,H,W) fp32 -> (N,H,W,C) bf16, tiled transpose through shared memory
@@ -331,7 +371,11 @@ DNR_EXPORT int dnr_encode_bwd(const float* rays, const float* z, const float* po
   P.d_lat_xr = d_lat_xr; P.d_latent = d_latent_nhwc;
   if (P.n_samples <= 0) return 0;
   const int tiles = dnr::RowMap::make(NV).tiles_for(P.n_samples);
-  dnr::encode_bwd_kernel<<<tiles, 128, 0, stream>>>(P);
+  DNR_CHECK(cudaFuncSetAttribute(dnr::encode_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 dnr::kBwdSmemBytes), "dnr_encode_bwd");
+  const long long slabs = (P.n_samples + dnr::RowMap::make(NV).SPW - 1) / dnr::RowMap::make(NV).SPW;
+  (void)tiles;
+  dnr::encode_bwd_kernel<<<(unsigned)slabs, 128, dnr::kBwdSmemBytes, stream>>>(P);
   DNR_CHECK_LAUNCH("dnr_encode_bwd");
   return 0;
 }

@@ -7,7 +7,7 @@
 // image, so every pipeline stage is filled by two cp.async.bulk copies (TMA engine) and consumed by
 // four tcgen05.mma (M=128, N=256, K=16) issued by one thread; accumulators are double-buffered in TMEM
 // (2 x 256 columns) so the epilogue of tile i overlaps the main loop of tile i+1.  Persistent kernel:
-// one CTA per SM, 6 warps = {bulk-copy producer, MMA issuer, 4 epilogue warps (one per TMEM lane quadrant)}.
+// one CTA per SM, 10 warps = {bulk-copy producer, MMA issuer, 8 epilogue warps (two per TMEM lane quadrant)}.
 #include "common.cuh"
 #include "tc05.cuh"
 
@@ -17,7 +17,7 @@ constexpr int kBM = 128, kBN = 256, kBK = 64;
 constexpr int kStages = 4;
 constexpr int kAStage = kBM * kBK * 2;          // 16 KB
 constexpr int kBStage = kBN * kBK * 2;          // 32 KB
-constexpr int kGemmThreads = 192;
+constexpr int kGemmThreads = 320;     // producer, MMA issuer, 8 epilogue warps (two per TMEM lane quadrant)
 constexpr size_t kGemmSmem = (size_t)kStages * (kAStage + kBStage) + 256;
 
 struct GemmSeg {
@@ -42,8 +42,29 @@ struct GemmParams {
   long long n_samples;
 };
 
+// Global operands of one 32-column epilogue chunk (residual stream, ReLU mask): loaded one chunk ahead of the
+// TMEM read so that their HBM latency overlaps the previous chunk (and, for the first chunk, the wait for the MMAs).
+struct EpiOperands {
+  float4 r[8];
+  uint4 m[4];
+};
+__device__ __forceinline__ void epilogue_prefetch(const GemmParams& P, int m_tile, int n0, int row_in_tile,
+                                                  EpiOperands& e) {
+  const int N = P.N;
+  if (P.mask_pk) {
+    const unsigned char* mp = P.mask_pk + ((size_t)((size_t)m_tile * (N / 8) + n0 / 8) * 128 + row_in_tile) * 16;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) e.m[c] = __ldg(reinterpret_cast<const uint4*>(mp + (size_t)c * 2048));
+  }
+  if (P.res_in) {
+    const float4* rp = reinterpret_cast<const float4*>(P.res_in) + ((size_t)m_tile * (N / 4) + n0 / 4) * 128 + row_in_tile;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) e.r[c] = __ldg(rp + (size_t)c * 128);
+  }
+}
+
 __device__ __forceinline__ void epilogue_chunk(const GemmParams& P, int m_tile, int n0, int row_in_tile, int lane,
-                                               uint32_t (&acc)[32]) {
+                                               uint32_t (&acc)[32], const EpiOperands& e) {
   const int N = P.N;
   float v[32];
 #pragma unroll
@@ -56,10 +77,9 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& P, int m_tile, 
     }
   }
   if (P.mask_pk) {
-    const unsigned char* mp = P.mask_pk + ((size_t)((size_t)m_tile * (N / 8) + n0 / 8) * 128 + row_in_tile) * 16;
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
-      const uint4 m = __ldg(reinterpret_cast<const uint4*>(mp + (size_t)c * 2048));
+      const uint4 m = e.m[c];
       const uint32_t mv[4] = {m.x, m.y, m.z, m.w};
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
@@ -69,10 +89,9 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& P, int m_tile, 
     }
   }
   if (P.res_in) {
-    const float4* rp = reinterpret_cast<const float4*>(P.res_in) + ((size_t)m_tile * (N / 4) + n0 / 4) * 128 + row_in_tile;
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
-      const float4 r = __ldg(rp + (size_t)c * 128);
+      const float4 r = e.r[c];
       v[c * 4] += r.x; v[c * 4 + 1] += r.y; v[c * 4 + 2] += r.z; v[c * 4 + 3] += r.w;
     }
   }
@@ -139,7 +158,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) mlp_gemm_kernel(const GemmPar
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < kStages; ++s) { tc::mbar_init(full + s, 1); tc::mbar_init(empty + s, 1); }
-    for (int b = 0; b < 2; ++b) { tc::mbar_init(tfull + b, 1); tc::mbar_init(tempty + b, 128); }
+    for (int b = 0; b < 2; ++b) { tc::mbar_init(tfull + b, 1); tc::mbar_init(tempty + b, 256); }
     tc::fence_barrier_init();
   }
   if (warp == 1) tc::tmem_alloc(tmem_slot, 512);
@@ -203,21 +222,28 @@ __global__ void __launch_bounds__(kGemmThreads, 1) mlp_gemm_kernel(const GemmPar
     }
   } else {
     // ================= epilogue: TMEM -> registers -> HBM =================
+    // two warps per TMEM lane quadrant; each takes four of the tile's eight 32-column chunks
     const int quad = warp & 3;                 // TMEM lane quadrant this warp may access
+    const int half = (warp - 2) >> 2;
     const int row_in_tile = quad * 32 + lane;
+    constexpr int kChunksPerWarp = kBN / 32 / 2;
     int it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
       const int m_tile = tile / n_tiles_n, n_tile = tile % n_tiles_n;
       const int buf = it & 1;
+      const int n_base = n_tile * kBN + half * kChunksPerWarp * 32;
+      EpiOperands e[2];
+      epilogue_prefetch(P, m_tile, n_base, row_in_tile, e[0]);
       tc::mbar_wait(tfull + buf, (it >> 1) & 1);
       tc::fence_after_sync();
-      const uint32_t t0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)buf * kBN;
-#pragma unroll 1
-      for (int ch = 0; ch < kBN / 32; ++ch) {
+      const uint32_t t0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)buf * kBN + half * kChunksPerWarp * 32;
+#pragma unroll
+      for (int ch = 0; ch < kChunksPerWarp; ++ch) {
         uint32_t acc[32];
         tc::tmem_ld32(t0 + ch * 32, acc);
+        if (ch + 1 < kChunksPerWarp) epilogue_prefetch(P, m_tile, n_base + (ch + 1) * 32, row_in_tile, e[(ch + 1) & 1]);
         tc::tmem_ld_wait();
-        epilogue_chunk(P, m_tile, n_tile * kBN + ch * 32, row_in_tile, lane, acc);
+        epilogue_chunk(P, m_tile, n_base + ch * 32, row_in_tile, lane, acc, e[ch & 1]);
       }
       tc::fence_before_sync();
       tc::mbar_arrive(tempty + buf);
