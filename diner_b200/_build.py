@@ -22,6 +22,7 @@ SOURCES = [
     ("mlp_pair.cu", []),
     ("wgrad.cu", []),
     ("producers.cu", []),
+    ("depth_format.cu", []),
     ("mlp_misc.cu", []),
 ]
 COMMON = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

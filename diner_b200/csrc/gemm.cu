@@ -99,18 +99,28 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& P, int m_tile, 
   long long out_row = (long long)m_tile * 128 + row_in_tile;
   bool write = true;
   if (P.mean_nv) {
-    // rows of one sample are NV consecutive lanes of this warp (RowMap): sum them, leader lane keeps it
+    // rows of one sample are NV consecutive lanes of this warp (RowMap): average them (resnetfc.py:9-14, torch.mean
+    // over views; same association as view_mean of the cluster kernels), the leader lane writes
     const int NV = P.mean_nv, SPW = 32 / NV;
-    float s[32];
+    if (NV == 2) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) s[j] = v[j];
-    for (int d = 1; d < NV; ++d) {
+      for (int j = 0; j < 32; ++j) v[j] = (v[j] + __shfl_xor_sync(0xffffffffu, v[j], 1)) * 0.5f;
+    } else if (NV == 4) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) s[j] += __shfl_down_sync(0xffffffffu, v[j], d);
+      for (int j = 0; j < 32; ++j) {
+        float t = v[j] + __shfl_xor_sync(0xffffffffu, v[j], 1);
+        t += __shfl_xor_sync(0xffffffffu, t, 2);
+        v[j] = t * 0.25f;
+      }
+    } else if (NV > 1) {
+      const float nv = (float)NV;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        float t = v[j];
+        for (int d = 1; d < NV; ++d) t += __shfl_down_sync(0xffffffffu, v[j], d);
+        v[j] = t / nv;                                               // same bits as the chain kernel (mlp_fused.cu)
+      }
     }
-    const float nv = (float)NV;
-#pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] = s[j] / nv;                 // resnetfc.py:9-14 (torch.mean over views)
     const long long slab = (long long)m_tile * 4 + (row_in_tile >> 5);
     const long long sample = slab * SPW + lane / NV;
     write = (lane % NV == 0) && (lane < SPW * NV) && (sample < P.n_samples);

@@ -104,7 +104,13 @@ class _FieldFn(torch.autograd.Function):
         sc, mlp = ctx.sc, ctx.mlp
         dev = d_out.device
         params = dict(mlp.named_parameters())
-        grads = {n: torch.zeros(params[n].shape, device=dev, dtype=torch.float32) for n in ctx.names}
+        # one zero fill for all parameter gradients (views into a flat buffer, 16-byte aligned starts)
+        offs, total = {}, 0
+        for n in ctx.names:
+            offs[n] = total
+            total += (params[n].numel() + 3) // 4 * 4
+        flat = torch.zeros(total, device=dev, dtype=torch.float32)
+        grads = {n: flat[offs[n]:offs[n] + params[n].numel()].view(params[n].shape) for n in ctx.names}
         d_lat_nhwc = None
         if ctx.needs_input_grad[7]:
             d_lat_nhwc = torch.zeros(sc.SB, sc.NV, sc.Hl, sc.Wl, sc.L, device=dev, dtype=torch.float32)

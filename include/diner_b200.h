@@ -202,6 +202,22 @@ int dnr_gen_rays_at(const float* extrinsics, const float* intrinsics, int B, int
  * (src/util/depth2normal.py:6-87) including the axis its torch.cross (no dim) takes when N == 3. */
 int dnr_depth2normal(const float* dmap, const float* K, int N, int H, int W, float* normal, dnr_stream_t stream);
 
+/* On-disk depth format: decoded uint16 PNG planes in units of `scale` (1e-4 m) -> fp32 depth
+ * [N,H,W] and depth-std [N,H,W] maps in one pass.  `pred` / `conf` point at the first pixel of the MVS depth /
+ * confidence plane of image 0 (FaceScape triptych [gt|pred|conf]: tri + W and tri + 2 W, row_stride = 3 W,
+ * img_stride = 3 W H; dense images: row_stride = W, img_stride = W H); `mesh` is a dense [N,H,W] plane.
+ * depth_type 0 = MVS planes ("original"), 1 = mesh depth with confidence 0.8 where it is non-zero, 2 = mesh with its
+ * holes filled from the MVS planes ("merge").  depth = u16 * scale [/ div0 * mul1]; std = std_a * conf + std_b.
+ * flags: 1 clip std at 0; 2 std = 0 where depth == 0; 4 conf is rescaled (/ div0 * mul1) like depth; 8 std = std_const.
+ * Every operation is a separate fp32 rounding in the reference's order.  Replaces FacescapeDataSet.read_depth +
+ * conf2std (src/data/facescape.py:54-56,69-106,266), the PNG branch of DTUDataSet.read_depth + conf2std
+ * (src/data/dtu.py:68-70,104-107,119,221-223) and MultiFaceDataset.read_depth + std law (src/data/multiface.py:103-109,
+ * 305-311).  PNG inflation stays in the host image library. */
+int dnr_decode_depth_u16(const uint16_t* pred, const uint16_t* conf, long long img_stride, int row_stride,
+                         const uint16_t* mesh, int N, int H, int W, int depth_type, float scale, float div0, float mul1,
+                         float std_a, float std_b, float std_const, int flags, float* depth_out, float* std_out,
+                         dnr_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
