@@ -127,12 +127,42 @@ __global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams
   }
   __syncwarp();
 
+  // phase 1b: the 55-wide geometric code of the 8 rows (zero-padded to 64).  The 48 sines of a row are spread over the
+  // warp as 8 x 48 = 384 = 12 full-warp evaluations, one branch-free sinf each; the 16 plain elements follow.
+  {
+    constexpr int NF = 6;                    // required by fill_encode_params (55-wide code)
+    constexpr int npos = 3 + 6 * NF;         // 39
+    constexpr int nsin_pos = 6 * NF, nsin = 8 * NF;      // 36, 48
+#pragma unroll 4
+    for (int t = lane; t < 8 * nsin; t += 32) {
+      const int i = t / nsin, q = t - i * nsin;
+      const RowTaps& tp = taps_s[warp][i];
+      int e, fs; float x;
+      if (q < nsin_pos) { const int j = q % 3; fs = q / 3; e = 3 + q; x = j == 0 ? tp.xc : (j == 1 ? tp.yc : tp.zc); }
+      else { fs = q - nsin_pos; e = npos + 4 + fs; x = tp.dd; }
+      float val = sinf(__fadd_rn(P.phases[fs], __fmul_rn(x, P.freqs[fs])));
+      if (!tp.map_plus1) val = 0.f;
+      reinterpret_cast<__nv_bfloat16*>(si + (e >> 3) * 128 + i * 16)[e & 7] = __float2bfloat16_rn(val);
+    }
+    constexpr int nraw = 64 - nsin;          // 16: x_cam 3 | dir_cam 3 | depth distance 1 | 9 zeros
+    for (int t = lane; t < 8 * nraw; t += 32) {
+      const int i = t / nraw, r = t - i * nraw;
+      const RowTaps& tp = taps_s[warp][i];
+      int e; float val = 0.f;
+      if (r < 3) { e = r; val = r == 0 ? tp.xc : (r == 1 ? tp.yc : tp.zc); }
+      else if (r < 6) { e = npos + (r - 3); val = r == 3 ? tp.dx : (r == 4 ? tp.dy : tp.dz); }
+      else if (r == 6) { e = npos + 3; val = tp.dd; }
+      else e = npos + 4 + 2 * NF + (r - 7);
+      if (!tp.map_plus1) val = 0.f;
+      reinterpret_cast<__nv_bfloat16*>(si + (e >> 3) * 128 + i * 16)[e & 7] = __float2bfloat16_rn(val);
+    }
+  }
+
   // phase 2: the warp gathers row after row, two rows' loads in flight
 #pragma unroll 2
   for (int i = 0; i < 8; ++i) {
     const RowTaps tp = taps_s[warp][i];
     uint4 o0 = make_uint4(0, 0, 0, 0), o1 = o0;
-    float e0 = 0.f, e1 = 0.f;
     if (tp.map_plus1) {
       const __nv_bfloat16* lat = P.latent + (size_t)(tp.map_plus1 - 1) * (size_t)P.Hl * P.Wl * L;
       const float w00 = tp.w00, w01 = tp.w01, w10 = tp.w10, w11 = tp.w11;
@@ -154,28 +184,9 @@ __global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams
         }
         if (half == 0) o0 = make_uint4(r[0], r[1], r[2], r[3]); else o1 = make_uint4(r[0], r[1], r[2], r[3]);
       }
-      // geometric code, two elements per lane (e = lane, lane + 32)
-#pragma unroll
-      for (int hh = 0; hh < 2; ++hh) {
-        const int e = lane + hh * 32;
-        float val = 0.f;
-        const int npos = 3 + 6 * P.NF;          // 39
-        const int ndep = 1 + 2 * P.NF;          // 13
-        if (e < 3) val = e == 0 ? tp.xc : (e == 1 ? tp.yc : tp.zc);
-        else if (e < npos) {
-          const int q = e - 3, j = q % 3, fs = q / 3;
-          const float x = j == 0 ? tp.xc : (j == 1 ? tp.yc : tp.zc);
-          val = sinf(__fadd_rn(P.phases[fs], __fmul_rn(x, P.freqs[fs])));
-        } else if (e < npos + 3) { const int j = e - npos; val = j == 0 ? tp.dx : (j == 1 ? tp.dy : tp.dz); }
-        else if (e == npos + 3) val = tp.dd;
-        else if (e < npos + 3 + ndep) { const int fs = e - (npos + 4); val = sinf(__fadd_rn(P.phases[fs], __fmul_rn(tp.dd, P.freqs[fs]))); }
-        if (hh == 0) e0 = val; else e1 = val;
-      }
     }
     *reinterpret_cast<uint4*>(sl + lane * kLatChunkStride + i * 16) = o0;
     *reinterpret_cast<uint4*>(sl + (32 + lane) * kLatChunkStride + i * 16) = o1;
-    reinterpret_cast<__nv_bfloat16*>(si + (lane >> 3) * 128 + i * 16)[lane & 7] = __float2bfloat16_rn(e0);
-    reinterpret_cast<__nv_bfloat16*>(si + (4 + (lane >> 3)) * 128 + i * 16)[lane & 7] = __float2bfloat16_rn(e1);
   }
   __syncwarp();
   // write-out: every 8 lanes move one 128-byte line (8 rows x 16 B of one feature chunk)
