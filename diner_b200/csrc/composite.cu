@@ -250,6 +250,107 @@ __global__ void __launch_bounds__(256) composite_fwd2_kernel(
   }
 }
 
+// ---- K <= 48 (the reference's K = 40): one ray per HALF warp, three adjacent samples per lane ---------------------
+// At K = 40 the two-samples-per-lane kernel leaves 12 of 32 lanes idle and spends ~31 shuffles per ray (one 32-lane
+// scan + five 32-lane sums): it is issue-bound (ncu: 68 % issue slots, 194 warp instructions per ray, 58 % of the HBM
+// roofline at 1 M rays).  Here a warp blends two rays at once: 16-lane scan (4 shuffles), the four outputs reduced
+// together by a butterfly that halves the number of live values per step (5 shuffles for 4 sums), so a pair of rays
+// costs 14 shuffles.
+struct TriRaw { float4 c0, c1, c2; float z0, z1, z2; float far; };
+
+__device__ __forceinline__ TriRaw load_tri(const float4* __restrict__ rgbsigma, const float* __restrict__ z,
+                                           const float* __restrict__ rays, long long ray, int K, int l16) {
+  TriRaw r;
+  r.far = __ldg(rays + ray * 8 + 7);
+  const int k = 3 * l16;
+  const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+  r.c0 = zero; r.c1 = zero; r.c2 = zero; r.z0 = 0.f; r.z1 = 0.f; r.z2 = 0.f;
+  const float* zr = z + ray * K;
+  const float4* cr = rgbsigma + ray * K;
+  if (k < K) { r.z0 = __ldg(zr + k); r.c0 = __ldg(cr + k); }
+  if (k + 1 < K) { r.z1 = __ldg(zr + k + 1); r.c1 = __ldg(cr + k + 1); }
+  if (k + 2 < K) { r.z2 = __ldg(zr + k + 2); r.c2 = __ldg(cr + k + 2); }
+  return r;
+}
+
+__device__ __forceinline__ void tri_term(bool valid, float zk, float znext, float sigma, float& alpha, float& t) {
+  const float delta = __fsub_rn(znext, zk);
+  alpha = valid ? __fsub_rn(1.0f, expf(-__fmul_rn(delta, fmaxf(sigma, 0.f)))) : 0.f;      // nerf_renderer.py:344-346
+  t = valid ? __fadd_rn(__fsub_rn(1.0f, alpha), 1e-10f) : 1.0f;                             // :347
+}
+
+__global__ void __launch_bounds__(256) composite_fwd3_kernel(
+    const float4* __restrict__ rgbsigma, const float* __restrict__ z, const float* __restrict__ rays,
+    int n_rays, int K, int white_bkgd, float* __restrict__ weights, float* __restrict__ rgb, float* __restrict__ depth)
+{
+  const int lane = threadIdx.x & 31, l16 = lane & 15, half = lane >> 4;
+  const long long n_pairs = ((long long)n_rays + 1) >> 1;
+  const long long stride = (long long)gridDim.x * (blockDim.x >> 5);
+  for (long long p0 = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); p0 < n_pairs;
+       p0 += stride * kRaysInFlight) {
+    TriRaw raw[kRaysInFlight];
+#pragma unroll
+    for (int u = 0; u < kRaysInFlight; ++u) {
+      const long long ray = 2 * (p0 + u * stride) + half;
+      if (ray < n_rays) raw[u] = load_tri(rgbsigma, z, rays, ray, K, l16);
+    }
+#pragma unroll
+    for (int u = 0; u < kRaysInFlight; ++u) {
+      if (p0 + u * stride >= n_pairs) break;                    // warp-uniform
+      const long long ray = 2 * (p0 + u * stride) + half;
+      const bool live = ray < n_rays;                           // odd n_rays: the last pair has one ray
+      TriRaw r = raw[u];
+      if (!live) { r.c0 = make_float4(0.f, 0.f, 0.f, 0.f); r.c1 = r.c0; r.c2 = r.c0; r.z0 = r.z1 = r.z2 = 0.f; r.far = 0.f; }
+      const int k = 3 * l16;
+      float zn = __shfl_down_sync(0xffffffffu, r.z0, 1, 16);    // first sample of the next lane of this ray
+      const bool v0 = live && k < K, v1 = live && k + 1 < K, v2 = live && k + 2 < K;
+      const float n0 = (k + 1 < K) ? r.z1 : r.far, n1 = (k + 2 < K) ? r.z2 : r.far, n2 = (k + 3 < K) ? zn : r.far;
+      float a0, a1, a2, t0, t1, t2;
+      tri_term(v0, r.z0, n0, r.c0.w, a0, t0);
+      tri_term(v1, r.z1, n1, r.c1.w, a1, t1);
+      tri_term(v2, r.z2, n2, r.c2.w, a2, t2);
+      // exclusive transmittance: 16-lane product scan of the per-lane products (nerf_renderer.py:348-349)
+      float x = (t0 * t1) * t2;
+#pragma unroll
+      for (int o = 1; o < 16; o <<= 1) {
+        const float y = __shfl_up_sync(0xffffffffu, x, o, 16);
+        if (l16 >= o) x *= y;
+      }
+      const float e = __shfl_up_sync(0xffffffffu, x, 1, 16);
+      const float T0 = l16 == 0 ? 1.0f : e;
+      const float T1 = T0 * t0, T2 = T1 * t1;
+      const float w0 = a0 * T0, w1 = a1 * T1, w2 = a2 * T2;
+      if (weights) {
+        float* wr = weights + ray * K + k;
+        if (v0) wr[0] = w0;
+        if (v1) wr[1] = w1;
+        if (v2) wr[2] = w2;
+      }
+      float ar = fmaf(w2, r.c2.x, fmaf(w1, r.c1.x, w0 * r.c0.x));
+      float ag = fmaf(w2, r.c2.y, fmaf(w1, r.c1.y, w0 * r.c0.y));
+      float ab = fmaf(w2, r.c2.z, fmaf(w1, r.c1.z, w0 * r.c0.z));
+      float ad = fmaf(w2, r.z2, fmaf(w1, r.z1, w0 * r.z0));
+      // butterfly: (ar, ab) and (ag, ad) fold over bit 3, the two results over bit 2, then bits 1, 0:
+      // lanes 0-3 of the half warp end with sum(ar), 4-7 sum(ag), 8-11 sum(ab), 12-15 sum(ad)
+      const bool b3 = l16 & 8, b2 = l16 & 4;
+      float A = (b3 ? ab : ar) + __shfl_xor_sync(0xffffffffu, b3 ? ar : ab, 8, 16);
+      float B = (b3 ? ad : ag) + __shfl_xor_sync(0xffffffffu, b3 ? ag : ad, 8, 16);
+      float V = (b2 ? B : A) + __shfl_xor_sync(0xffffffffu, b2 ? A : B, 4, 16);
+      V += __shfl_xor_sync(0xffffffffu, V, 2, 16);
+      V += __shfl_xor_sync(0xffffffffu, V, 1, 16);
+      if (white_bkgd) {
+        float aw = (w0 + w1) + w2;
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) aw += __shfl_xor_sync(0xffffffffu, aw, o, 16);
+        if (l16 < 12) V = V + 1.f - aw;                         // nerf_renderer.py:361-363
+      }
+      if (live && (l16 & 3) == 0) {
+        if (l16 < 12) rgb[ray * 3 + (l16 >> 2)] = V; else depth[ray] = V;
+      }
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256) composite_bwd2_kernel(
     const float4* __restrict__ rgbsigma, const float* __restrict__ z, const float* __restrict__ rays,
     const float* __restrict__ d_rgb, const float* __restrict__ d_depth, const float* __restrict__ d_weights,
@@ -311,7 +412,12 @@ DNR_EXPORT int dnr_composite_fwd(const float* rgbsigma, const float* z, const fl
   const int wpb = 8;
   int blocks = (int)((n_rays + wpb - 1) / wpb);
   if (blocks > 148 * 8) blocks = 148 * 8;      // one resident wave (2 048 threads per SM), grid-stride over the rays
-  auto kern = (K % 2 == 0 && K <= 64) ? dnr::composite_fwd2_kernel : dnr::composite_fwd_kernel;
+  auto kern = K <= 48 ? dnr::composite_fwd3_kernel
+                      : (K % 2 == 0 && K <= 64) ? dnr::composite_fwd2_kernel : dnr::composite_fwd_kernel;
+  if (K <= 48) {                                 // two rays per warp, three resident blocks per SM (80 registers)
+    blocks = (int)(((n_rays + 1) / 2 + wpb - 1) / wpb);
+    if (blocks > 148 * 3) blocks = 148 * 3;
+  }
   kern<<<blocks, wpb * 32, 0, stream>>>((const float4*)rgbsigma, z, rays, n_rays, K, white_bkgd, weights, rgb, depth);
   DNR_CHECK_LAUNCH("dnr_composite_fwd");
   return 0;

@@ -45,7 +45,8 @@ def _oracle_sampler(model, rays, wl, noise):
 # ---------------------------------------------------------------------------------------------------------
 
 @pytest.mark.parametrize("n,K,white", [(1000, 40, True), (1000, 40, False), (37, 1, True), (129, 33, False),
-                                       (64, 100, True)])
+                                       (64, 100, True), (1001, 40, True), (1, 40, True), (77, 48, True),
+                                       (77, 47, False), (50, 2, True), (33, 50, True), (33, 64, False)])
 def test_composite_fwd_bwd_matches_oracle(n, K, white):
     dev = _cuda()
     from diner_b200.renderer import _CompositeFn
@@ -212,3 +213,82 @@ def test_sampler_background_rays_are_stratified_uniform():
     assert torch.equal(z, z2), "Philox jitter must be deterministic for a fixed seed"
     z3 = sample_rays(get_scene(scene.model), rays, wl.n_samples, wl.n_candidates, wl.n_gaussian, seed=8)
     assert not torch.equal(z, z3)
+
+
+# ------------------------------------------------------------------------------------------------ gather stage
+@pytest.mark.parametrize("NV,n_rays", [(1, 37), (2, 100), (3, 45), (4, 64), (2, 1)])
+def test_encode_stage_fwd_bwd_all_view_counts(NV, n_rays):
+    """Projection + gather + geometric code (dnr_encode_fwd) and its backward scatter (dnr_encode_bwd) for every view
+    count, on ragged sample counts (padding rows in the last slab / tile): forward against the fp32 oracle's
+    field_inputs (bf16 rounding of the operands is the only difference), backward against autograd through the oracle's
+    grid_sample on the same upstream gradient."""
+    dev = _cuda()
+    import dataclasses
+    from diner_b200 import _lib
+    from diner_b200.field import _encode_args
+    from diner_b200.scene import get_scene
+    from diner_b200.synthetic import WORKLOADS, make_scene
+    from oracle import dgs_oracle as O
+    wl = dataclasses.replace(WORKLOADS["tiny"], name=f"enc_nv{NV}", NV=NV, tgt_H=16, tgt_W=16)
+    scene = make_scene(wl, seed=10 + NV)
+    K = wl.n_samples
+    rays = scene.rays[:, :n_rays].contiguous()
+    gen = torch.Generator().manual_seed(NV)
+    # depth-guided-like samples: most of a ray's samples cluster (shared bilinear footprints), the rest spread out
+    u = torch.cat([0.45 + 0.02 * torch.rand(1, n_rays, K - 10, generator=gen), torch.rand(1, n_rays, 10, generator=gen)], -1)
+    z = rays[..., 6:7] + (rays[..., 7:8] - rays[..., 6:7]) * u.sort(-1).values
+    SB, NR = 1, n_rays
+    pts = (rays[..., None, :3] + z.unsqueeze(-1) * rays[..., None, 3:6]).reshape(SB, NR * K, 3)
+    dirs = rays[..., None, 3:6].expand(-1, -1, K, -1).reshape(SB, NR * K, 3)
+    m = scene.model
+    lat_leaf = m.encoder.latent.detach().clone().requires_grad_(True)
+    m.encoder.latent = lat_leaf
+    zx = O.field_inputs(m, pts, dirs)                                  # SB,NV,B,567 (fp32, torch CPU)
+    G = torch.randn(SB, NV, NR * K, 512, generator=gen)
+    (zx[..., :512] * G).sum().backward()
+    want_dlat = lat_leaf.grad.clone()                                  # SB,NV,512,Hl,Wl
+    m.encoder.latent = lat_leaf.detach()
+    m.to_device(dev)
+    try:
+        sc = get_scene(m)
+        p, st = _lib.ptr, _lib.stream_ptr()
+        ns = NR * K
+        mv = _lib.load().dnr_view_row_tiles(ns, NV)
+        lat = torch.empty(mv * 128 * 512, device=dev, dtype=torch.bfloat16)
+        code = torch.empty(mv * 128 * 64, device=dev, dtype=torch.bfloat16)
+        r_d, z_d = rays.view(-1, 8).to(dev), z.view(-1, K).to(dev)
+        _lib.call("dnr_encode_fwd", p(r_d), p(z_d), p(sc.poses), p(sc.focal), p(sc.cxy), p(sc.depth), p(sc.latent_nhwc),
+                  p(sc.freqs), p(sc.phases), *_encode_args(sc, NR, K, 0, NR), p(lat), p(code), st)
+        lat_rows = torch.empty(mv * 128, 512, device=dev)
+        code_rows = torch.empty(mv * 128, 64, device=dev)
+        _lib.call("dnr_unpack_rows", p(lat), mv * 128, 512, p(lat_rows), st)
+        _lib.call("dnr_unpack_rows", p(code), mv * 128, 64, p(code_rows), st)
+        spw = 32 // NV
+        s_ = torch.arange(ns)
+        g_rows = torch.zeros(mv * 128, 512)
+        valid = torch.zeros(mv * 128, dtype=torch.bool)
+        for v in range(NV):
+            row = (s_ // spw) * 32 + (s_ % spw) * NV + v
+            valid[row] = True
+            w = zx[0, v].detach()
+            got_l, got_c = lat_rows[row.to(dev)].cpu(), code_rows[row.to(dev)].cpu()
+            # operands are bf16: relative 2^-9 of the value, plus the latent itself stored in bf16 before blending
+            assert (got_l - w[:, :512]).abs().max() <= 2.0 ** -7 * w[:, :512].abs().max() + 1e-6
+            assert torch.allclose(got_c[:, :55], w[:, 512:], rtol=2.0 ** -8, atol=2e-3)      # sin of large arguments
+            assert (got_c[:, 55:] == 0).all()
+            g_rows[row] = G[0, v]
+        assert (lat_rows[(~valid).to(dev)] == 0).all() and (code_rows[(~valid).to(dev)] == 0).all()    # padding rows
+        # backward: upstream gradient in XR layout -> NHWC fp32 latent gradient
+        g_xr = torch.empty(mv * 128 * 512, device=dev)
+        _lib.call("dnr_rows_to_xr", p(g_rows.to(dev).contiguous()), mv * 128, 512, mv * 128, p(g_xr), st)
+        d_nhwc = torch.zeros(sc.SB, sc.NV, sc.Hl, sc.Wl, sc.L, device=dev)
+        _lib.call("dnr_encode_bwd", p(r_d), p(z_d), p(sc.poses), p(sc.focal), p(sc.cxy), p(sc.depth), p(sc.freqs),
+                  p(sc.phases), *_encode_args(sc, NR, K, 0, NR), p(g_xr), p(d_nhwc), st)
+        torch.cuda.synchronize()
+        got = d_nhwc.permute(0, 1, 4, 2, 3).cpu()
+        assert got.shape == want_dlat.shape
+        err = (got - want_dlat).abs().max().item()
+        assert err <= 1e-4 * max(want_dlat.abs().max().item(), 1.0), err      # fp32 sums in a different order
+        assert (got != 0).sum() > 0 and ((got != 0) == (want_dlat != 0)).float().mean() > 0.999
+    finally:
+        m.to_device("cpu")
