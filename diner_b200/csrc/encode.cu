@@ -84,6 +84,20 @@ __device__ __forceinline__ void row_geometry(const EncodeParams& P, long long sa
   g.wx = fx - flx; g.wy = fy - fly;     // weight of the +1 neighbour (0 when it is out of range)
 }
 
+// packed fp32 pairs (Blackwell FMUL2 / FFMA2): the two channels of a bf16x2 word travel together
+__device__ __forceinline__ uint64_t splat_f32x2(float w) {
+  uint64_t r; asm("mov.b64 %0, {%1, %1};" : "=l"(r) : "f"(w)); return r;
+}
+__device__ __forceinline__ uint64_t bf16x2_to_f32x2(uint32_t v) {
+  uint64_t r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(v << 16), "r"(v & 0xffff0000u)); return r;
+}
+__device__ __forceinline__ uint64_t mul_f32x2(uint64_t a, uint64_t b) {
+  uint64_t r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r;
+}
+__device__ __forceinline__ uint64_t fma_f32x2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r;
+}
+
 constexpr int kEncWarps = 4;
 constexpr int kLatChunkStride = 144;   // 8 rows * 16 B + 16 B pad -> conflict-free staging
 
@@ -165,7 +179,7 @@ __global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams
     uint4 o0 = make_uint4(0, 0, 0, 0), o1 = o0;
     if (tp.map_plus1) {
       const __nv_bfloat16* lat = P.latent + (size_t)(tp.map_plus1 - 1) * (size_t)P.Hl * P.Wl * L;
-      const float w00 = tp.w00, w01 = tp.w01, w10 = tp.w10, w11 = tp.w11;
+      const uint64_t W00 = splat_f32x2(tp.w00), W01 = splat_f32x2(tp.w01), W10 = splat_f32x2(tp.w10), W11 = splat_f32x2(tp.w11);
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
         const int ch = half * 256 + lane * 8;
@@ -178,8 +192,14 @@ __global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams
         uint32_t r[4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          const float lo = bf16lo(av[q]) * w00 + bf16lo(bv[q]) * w01 + bf16lo(cv[q]) * w10 + bf16lo(dv[q]) * w11;
-          const float hi = bf16hi(av[q]) * w00 + bf16hi(bv[q]) * w01 + bf16hi(cv[q]) * w10 + bf16hi(dv[q]) * w11;
+          // both channels of a bf16x2 word in one packed fp32 operation (FMUL2 / FFMA2): a*w00, then fma by fma in
+          // tap order -- the same roundings as the scalar chain
+          uint64_t acc = mul_f32x2(bf16x2_to_f32x2(av[q]), W00);
+          acc = fma_f32x2(bf16x2_to_f32x2(bv[q]), W01, acc);
+          acc = fma_f32x2(bf16x2_to_f32x2(cv[q]), W10, acc);
+          acc = fma_f32x2(bf16x2_to_f32x2(dv[q]), W11, acc);
+          float lo, hi;
+          asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(acc));
           r[q] = pack_bf16x2(lo, hi);
         }
         if (half == 0) o0 = make_uint4(r[0], r[1], r[2], r[3]); else o1 = make_uint4(r[0], r[1], r[2], r[3]);
