@@ -163,6 +163,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-rays", type=int, default=4096)
     ap.add_argument("--train", action="store_true", help="time forward+backward of the workload's ray batch instead")
+    ap.add_argument("--shard-frame", action="store_true",
+                    help="N > 1: all ranks render ONE frame (contiguous ray slices, all-gather of rgb/depth): strong scaling")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -179,14 +181,17 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
+    from types import SimpleNamespace
     from diner_b200 import NeRFRendererDGS, _lib
+    from diner_b200.sharding import render_sharded
     from diner_b200.synthetic import make_scene, target_rays
 
     scene = make_scene(args.workload, seed=0)
     wl = scene.workload
     model = scene.model.to_device(dev)
     # every rank renders its own frame of a camera sweep around the scene
-    rays_cpu = target_rays(scene, azimuth_deg=2.0 + 6.0 * rank, elevation_deg=8.0)
+    shard = args.shard_frame and world > 1 and not args.train
+    rays_cpu = target_rays(scene, azimuth_deg=2.0 + (0.0 if shard else 6.0 * rank), elevation_deg=8.0)
     n_rays = rays_cpu.shape[0] * rays_cpu.shape[1]
     renderer = NeRFRendererDGS(wl.n_samples, wl.n_candidates, wl.n_gaussian, white_bkgd=wl.white_bkgd)
     rays_dev = rays_cpu.to(dev)
@@ -219,11 +224,19 @@ def main():
             loss.backward()
             train_allreduce()
             return out
+        if shard:        # one frame for all ranks: diner_b200.sharding splits the rays and all-gathers rgb / depth (NCCL)
+            rgb, depth = render_sharded(renderer, model, rays_dev)
+            return SimpleNamespace(fine=SimpleNamespace(rgb=rgb, depth=depth))
         with torch.no_grad():
             return renderer(model, rays_dev)
 
     def step_e2e():
         rays_stage.copy_(rays_host, non_blocking=True)
+        if shard:
+            rgb, depth = render_sharded(renderer, model, rays_stage)
+            rgb_host.copy_(rgb, non_blocking=True)
+            depth_host.copy_(depth, non_blocking=True)
+            return None
         if args.train:
             out = renderer(model, rays_stage)
             out.fine.rgb.square().mean().backward()
@@ -288,7 +301,8 @@ def main():
     breakdown = {k: dict(ms_per_step=v[0] / prof_steps, launches_per_step=v[1] // prof_steps) for k, v in per.items()}
 
     peaks = load_peaks()
-    n_samples = n_rays * wl.n_samples
+    n_local = n_rays // world if shard else n_rays          # rays this rank renders per step
+    n_samples = n_local * wl.n_samples
     gemm_flops = 2.0 * (wl.NV * (55 * 512 + 9 * 512 * 512) + 4 * 512 * 512) * n_samples * (3.0 if args.train else 1.0)
     # every C-ABI call whose kernel runs the MLP's tcgen05 GEMMs (inference: one fused launch per chunk)
     gemm_names = ("dnr_mlp_quad_fwd", "dnr_mlp_pair_fwd", "dnr_mlp_fused_fwd", "dnr_mlp_gemm", "dnr_mlp_wgrad")
@@ -322,24 +336,26 @@ def main():
                     l2_gbs=_gbs(rows * (4100.0 + 1152.0), "dnr_encode_fwd"), hbm_peak_gbs=peaks["hbm_gbs"],
                     note="HBM: 1152 B written per view row (operands of the MLP); L2: + 4 bilinear taps x 1 KB read "
                          "from the L2-resident bf16 latent; issue-bound (ncu: 60 % issue slots), not memory-bound"),
-        composite=dict(kernel="composite_fwd3_kernel", hbm_gbs=_gbs(n_rays * 1008.0, "dnr_composite_fwd"),
+        composite=dict(kernel="composite_fwd3_kernel", hbm_gbs=_gbs(n_local * 1008.0, "dnr_composite_fwd"),
                        hbm_peak_gbs=peaks["hbm_gbs"], note="1008 B per ray; ~10 us launches, latency-bound at this size"),
-        sampler=dict(kernel="sampler_kernel", hbm_gbs=_gbs(n_rays * 192.0, "dnr_sampler_fwd"),
-                     l2_gbs=_gbs(n_rays * wl.NV * wl.n_candidates * 20.0, "dnr_sampler_fwd"),
+        sampler=dict(kernel="sampler_kernel", hbm_gbs=_gbs(n_local * 192.0, "dnr_sampler_fwd"),
+                     l2_gbs=_gbs(n_local * wl.NV * wl.n_candidates * 20.0, "dnr_sampler_fwd"),
                      note="not memory-bound: NV*C candidate-view evaluations per ray on cache-resident maps"))
 
     if rank == 0:
         ms_per_step = total_ms / args.steps
-        value = n_rays * world / (ms_per_step * 1e-3)
-        e2e_value = n_rays * world / (e2e_ms / args.steps * 1e-3)
+        frames = 1 if shard else world
+        value = n_rays * frames / (ms_per_step * 1e-3)
+        e2e_value = n_rays * frames / (e2e_ms / args.steps * 1e-3)
         line = dict(metric="render_rays_per_s", value=value, unit="rays/s", n_gpus=world, steps=args.steps,
-                    warmup=args.warmup, ms_per_step=ms_per_step, higher_is_better=True, scaling="weak",
-                    vs_baseline=None, dtype="bf16", data="synthetic",
+                    warmup=args.warmup, ms_per_step=ms_per_step, higher_is_better=True,
+                    scaling="strong" if shard else "weak", vs_baseline=None, dtype="bf16", data="synthetic",
                     config=dict(workload=args.workload + ("_train_fwd_bwd" if args.train else "_eval"),
-                                rays_per_gpu_per_step=n_rays, samples_per_ray=wl.n_samples,
+                                rays_per_gpu_per_step=n_rays // world if shard else n_rays, samples_per_ray=wl.n_samples,
                                 n_candidates=wl.n_candidates, n_gaussian=wl.n_gaussian, n_views=wl.NV,
                                 source_hw=[wl.H, wl.W], l2="flushed between timed steps (256 MiB write)",
-                                parallelism=f"rays sharded, dp{world}" + (
+                                parallelism=(f"one frame, rays sharded over {world} ranks, all-gather of rgb/depth" if shard
+                                             else f"rays sharded, dp{world}") + (
                                     ", NCCL all-reduce of 46.7 MB gradients per step (MLP grads + encoder-sized bucket)"
                                     if args.train and world > 1 else "")),
                     msamples_per_s=value * wl.n_samples / 1e6,
