@@ -75,8 +75,12 @@ def test_gemm_view_mean_epilogue(NV):
     torch.testing.assert_close(_xr_to_rows(xm, ns, 512), ref, rtol=1e-4, atol=1e-4)
 
 
-@pytest.mark.parametrize("rows,Fx,kv", [(1000, 512, 512), (4000, 64, 55), (38400, 512, 512)])
+@pytest.mark.parametrize("rows,Fx,kv", [(1000, 512, 512), (4000, 64, 55), (38400, 512, 512), (100, 512, 512),
+                                        (2500, 512, 512), (2500, 256, 256), (300, 64, 55)])
 def test_wgrad_matches_torch(rows, Fx, kv):
+    """512 x 512 (and 512 x 256) layers run on CTA pairs (mlp_wgrad2_kernel), Fx = 64 on the single-CTA kernel.  2 500
+    rows = 20 batch tiles over 18 splits leaves splits without work (the early-out path of a whole cluster); 100 rows is
+    a single, mostly padded tile."""
     dev = _cuda()
     from diner_b200 import _lib
     from tools.gpu_diag import _pack_rows
