@@ -32,6 +32,7 @@ struct SamplerParams {
   unsigned long long seed;
   int SB, NV, NR, H, W, C, K, G, P;
   float depth_diff_max, img_w, img_h, std_sx, std_sy, inv_c_step;
+  float inv_w, inv_h;     // exact reciprocals when img_w / img_h are powers of two (x / 2^k == x * 2^-k bit for bit), else 0
   int count_only;
   int unpacked;           // n_gauss is [SB*NR, G] and u_fill is [SB*NR, K] (indexed by ray / sorted slot)
   float* z_out;           // [SB*NR, K]
@@ -142,8 +143,8 @@ __global__ void __launch_bounds__(kSamplerWarps * 32) sampler_kernel(SamplerPara
         float a = xc / zcam[q], b = yc / zcam[q];      // :107
         a = a * cv[15]; b = b * cv[16];                // :108
         a = a + cv[17]; b = b + cv[18];                // :109
-        uu[q] = a / P.img_w * 2.0f - 1.0f;             // :110
-        vv[q] = b / P.img_h * 2.0f - 1.0f;
+        uu[q] = (P.inv_w != 0.0f ? a * P.inv_w : a / P.img_w) * 2.0f - 1.0f;   // :110
+        vv[q] = (P.inv_h != 0.0f ? b * P.inv_h : b / P.img_h) * 2.0f - 1.0f;
         const int sx = nearest_zeros(uu[q] * P.std_sx, Wp), sy = nearest_zeros(vv[q] * P.std_sy, Hp);
         ok[q] = (ib + q < C) && sx >= 0 && sy >= 0;
         sref[q] = ok[q] ? __ldg(std_v + (size_t)sy * Wp + sx) : 0.0f;
@@ -363,6 +364,11 @@ DNR_EXPORT int dnr_sampler_fwd(const float* rays, const float* poses, const floa
   P.gauss_off = gauss_off; P.fill_off = fill_off; P.seed = seed;
   P.SB = SB; P.NV = NV; P.NR = NR; P.H = H; P.W = W; P.C = C; P.K = K; P.G = G; P.P = pad;
   P.depth_diff_max = depth_diff_max; P.img_w = img_w; P.img_h = img_h; P.std_sx = std_sx; P.std_sy = std_sy;
+  {
+    int ew = 0, eh = 0;
+    P.inv_w = (img_w >= 1.0f && frexpf(img_w, &ew) == 0.5f) ? 1.0f / img_w : 0.0f;
+    P.inv_h = (img_h >= 1.0f && frexpf(img_h, &eh) == 0.5f) ? 1.0f / img_h : 0.0f;
+  }
   P.inv_c_step = (float)(1.0 / (double)C);
   P.count_only = count_only; P.unpacked = unpacked_noise; P.z_out = z_out; P.ray_mask_out = ray_mask_out; P.n_missing_out = n_missing_out;
   P.sel_idx_out = sel_idx_out; P.p_out = p_out;
