@@ -292,12 +292,16 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
                 net = new_act(mv)
         else:
             # last per-view block: the epilogue averages the NV rows of each sample (resnetfc.py:147-151)
-            xm = torch.zeros(ms * 128 * HID, **f32)
-            xam = torch.zeros(ms * 128 * HID, **bf)
+            # the mean epilogue writes the rows of valid samples only: the padding rows of the LAST pooled tile (both
+            # layouts keep a tile contiguous) must be zero -- they are read again as wgrad operands (0 x NaN = NaN)
+            xm = torch.empty(ms * 128 * HID, **f32)
+            xam = torch.empty(ms * 128 * HID, **bf)
+            xm[(ms - 1) * 128 * HID:].zero_()
+            xam[(ms - 1) * 128 * HID:].zero_()
             _gemm(net, pk.w_1[b], HID, mv, bias=pk.b_1[b], res_in=x, res_out=xm, act_out=xam, relu=1, mean_nv=NV,
                   n_samples=n_samples)
     del x
-    xa, net = xam, torch.zeros(ms * 128 * HID, **bf)
+    xa, net = xam, torch.empty(ms * 128 * HID, **bf)      # fc_0 writes every row of every tile
     for b in (3, 4):
         if save:
             sv.xa.append(xa)
