@@ -708,8 +708,19 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
             const int nl0 = st * 64 + half * 32;
             tc::tmem_ld32(t0 + nl0, acc);
             tc::tmem_ld_wait();
+            if (NV == 3) {
+              // only the first row of a sample is parked: (a0 + a1) + a2 from the two lanes below -- the bits view_mean<3>
+              // gives that row, without its per-lane operand selection
 #pragma unroll
-            for (int j = 0; j < 32; ++j) acc[j] = __float_as_uint(view_mean<NV>(__uint_as_float(acc[j]), lane));
+              for (int j = 0; j < 32; ++j) {
+                const float v = __uint_as_float(acc[j]);
+                const float x = __shfl_down_sync(0xffffffffu, v, 1), y = __shfl_down_sync(0xffffffffu, v, 2);
+                acc[j] = __float_as_uint(((v + x) + y) * (1.0f / 3.0f));
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) acc[j] = __float_as_uint(view_mean<NV>(__uint_as_float(acc[j]), lane));
+            }
             if (first_view) {
               // scratch layout [64 column chunks of 4][128 merged rows] x 16 B: the lanes of a warp write (and the
               // merge reads) consecutive 16-byte words; evict_last keeps it in L2 against the streaming operands
