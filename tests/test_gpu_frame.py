@@ -165,3 +165,52 @@ def test_empty_and_tiny_ray_batches():
         out = r(m, scene.rays[:, :50].contiguous().to(dev), want_weights=True, return_samples=True)
     assert out.fine.weights.shape == (1, 50, 24) and out.fine.z.shape == (1, 50, 24)
     assert bool((out.fine.z[..., 1:] >= out.fine.z[..., :-1]).all()) and torch.isfinite(out.fine.rgb).all()
+
+
+@pytest.mark.parametrize("workload,max_rays", [("dtu", None), ("multiface", 131072)])
+def test_full_frame_properties_other_shapes(workload, max_rays):
+    """BASELINE.json configs 2 and 5: DTU shape (3 views of 300 x 400, black background, near / far 0.32 / 1.20) at its
+    full 120 000 rays, Multiface shape (4 views of 1024 x 672, std 1e-3) on 131 072 of its 1 M rays -- the same
+    size-independent properties as the FaceScape frame, plus agreement of the three inference MLP kernels."""
+    dev = _cuda()
+    from diner_b200 import NeRFRendererDGS, field as F_, sample_rays
+    from diner_b200.scene import get_scene
+    from diner_b200.synthetic import make_scene
+    scene = make_scene(workload, seed=0)
+    m = scene.model.to_device(dev)
+    try:
+        wl = scene.workload
+        rays = scene.rays.to(dev)
+        if max_rays is not None:                                   # a centred band of the frame
+            mid = rays.shape[1] // 2
+            rays = rays[:, mid - max_rays // 2: mid + max_rays // 2].contiguous()
+        K = wl.n_samples
+        sc = get_scene(m)
+        z, d = sample_rays(sc, rays, K, wl.n_candidates, wl.n_gaussian, seed=3, want_debug=True)
+        assert bool((z[:, 1:] >= z[:, :-1]).all())
+        fg = d["ray_mask"].bool()
+        assert 0.05 < fg.float().mean().item() < 0.95
+        bgz = z[~fg]
+        assert bool((bgz >= wl.near).all()) and bool((bgz < wl.far + 1e-5).all())
+        r = NeRFRendererDGS(K, wl.n_candidates, wl.n_gaussian, white_bkgd=wl.white_bkgd)
+        outs = {}
+        keep = F_.FORWARD_KERNEL
+        try:
+            for kern in ("quad", "pair"):
+                F_.FORWARD_KERNEL = kern
+                with torch.no_grad():
+                    outs[kern] = r(m, rays, want_weights=True, noise=dict(z=z))
+        finally:
+            F_.FORWARD_KERNEL = keep
+        o = outs["quad"]
+        assert torch.equal(o.fine.rgb, outs["pair"].fine.rgb) and torch.equal(o.fine.weights, outs["pair"].fine.weights)
+        w = o.fine.weights
+        sw = w.sum(-1)
+        assert torch.isfinite(o.fine.rgb).all() and torch.isfinite(o.fine.depth).all()
+        assert float(w.min()) >= 0 and float(sw.max()) <= 1 + 1e-4
+        assert float(sw.max()) > 0.9                               # the calibrated density head is live
+        if not wl.white_bkgd:                                      # black background: colour bounded by the weight sum
+            assert bool((o.fine.rgb.amax(-1) <= sw + 1e-5).all())
+        assert float(o.fine.depth.max()) <= wl.far + 1e-3 and float(o.fine.depth.min()) >= 0
+    finally:
+        m.to_device("cpu")
