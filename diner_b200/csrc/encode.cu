@@ -147,16 +147,32 @@ __global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams
     constexpr int NF = 6;                    // required by fill_encode_params (55-wide code)
     constexpr int npos = 3 + 6 * NF;         // 39
     constexpr int nsin_pos = 6 * NF, nsin = 8 * NF;      // 36, 48
-#pragma unroll 4
-    for (int t = lane; t < 8 * nsin; t += 32) {
-      const int i = t / nsin, q = t - i * nsin;
-      const RowTaps& tp = taps_s[warp][i];
-      int e, fs; float x;
-      if (q < nsin_pos) { const int j = q % 3; fs = q / 3; e = 3 + q; x = j == 0 ? tp.xc : (j == 1 ? tp.yc : tp.zc); }
-      else { fs = q - nsin_pos; e = npos + 4 + fs; x = tp.dd; }
-      float val = sinf(__fadd_rn(P.phases[fs], __fmul_rn(x, P.freqs[fs])));
-      if (!tp.map_plus1) val = 0.f;
-      reinterpret_cast<__nv_bfloat16*>(si + (e >> 3) * 128 + i * 16)[e & 7] = __float2bfloat16_rn(val);
+    // 3 x 32 lanes cover the 2 x 48 sines of a row pair, so a lane meets only three (element, frequency, coordinate)
+    // combinations: q = lane (row 2m), lane + 32 or lane - 16 (row 2m or 2m + 1), lane + 16 (row 2m + 1).  Everything
+    // that depends on q alone is hoisted out of the loop over the four row pairs.
+    int q3[3] = {lane, lane < 16 ? lane + 32 : lane - 16, lane + 16};
+    const int r3[3] = {0, lane < 16 ? 0 : 1, 1};                    // row of the pair
+    int foff[3], sto[3]; float fr[3], ph[3];
+#pragma unroll
+    for (int u = 0; u < 3; ++u) {
+      const int q = q3[u];
+      int e, fs;
+      if (q < nsin_pos) { fs = q / 3; e = 3 + q; foff[u] = q % 3; }            // xc, yc, zc
+      else { fs = q - nsin_pos; e = npos + 4 + fs; foff[u] = 6; }              // dd
+      fr[u] = P.freqs[fs]; ph[u] = P.phases[fs];
+      sto[u] = (e >> 3) * 128 + (e & 7) * 2;                                    // byte offset inside the staged code tile
+    }
+#pragma unroll
+    for (int m = 0; m < 4; ++m) {
+#pragma unroll
+      for (int u = 0; u < 3; ++u) {
+        const int i = 2 * m + r3[u];
+        const RowTaps& tp = taps_s[warp][i];
+        const float x = (&tp.xc)[foff[u]];
+        float val = sinf(__fadd_rn(ph[u], __fmul_rn(x, fr[u])));
+        if (!tp.map_plus1) val = 0.f;
+        *reinterpret_cast<__nv_bfloat16*>(si + sto[u] + i * 16) = __float2bfloat16_rn(val);
+      }
     }
     constexpr int nraw = 64 - nsin;          // 16: x_cam 3 | dir_cam 3 | depth distance 1 | 9 zeros
     for (int t = lane; t < 8 * nraw; t += 32) {
