@@ -335,7 +335,7 @@ def main():
         encode=dict(kernel="encode_fwd_kernel", hbm_gbs=_gbs(rows * 1152.0, "dnr_encode_fwd"),
                     l2_gbs=_gbs(rows * (4100.0 + 1152.0), "dnr_encode_fwd"), hbm_peak_gbs=peaks["hbm_gbs"],
                     note="HBM: 1152 B written per view row (operands of the MLP); L2: + 4 bilinear taps x 1 KB read "
-                         "from the L2-resident bf16 latent; issue-bound (ncu: 60 % issue slots), not memory-bound"),
+                         "from the L2-resident bf16 latent; the L2-level figure is what the L2 -> SM fabric (12-13 TB/s chip-wide, DESIGN.md) bounds"),
         composite=dict(kernel="composite_fwd3_kernel", hbm_gbs=_gbs(n_local * 1008.0, "dnr_composite_fwd"),
                        hbm_peak_gbs=peaks["hbm_gbs"], note="1008 B per ray; ~10 us launches, latency-bound at this size"),
         sampler=dict(kernel="sampler_kernel", hbm_gbs=_gbs(n_local * 192.0, "dnr_sampler_fwd"),

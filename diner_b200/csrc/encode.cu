@@ -103,7 +103,7 @@ constexpr int kLatChunkStride = 144;   // 8 rows * 16 B + 16 B pad -> conflict-f
 
 // per-row tap description, produced by one lane per row and read back by the whole warp (broadcast LDS)
 struct __align__(16) RowTaps {
-  uint32_t p00, p01, p10, p11;      // element offsets of the four taps inside the (sb, view) map
+  uint32_t p00, p01, p10, p11;      // element offsets of the four taps inside the whole latent (all maps)
   float w00, w01, w10, w11;
   float xc, yc, zc, dx, dy, dz, dd;
   uint32_t map_plus1;               // (sb*NV + view) + 1, 0 = padding row
@@ -130,8 +130,9 @@ __global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams
     if (rm.decode(row_base + lane, P.n_samples, sample, view)) {
       RowGeom g;
       row_geometry(P, sample, view, g);
-      tp.p00 = (uint32_t)(((size_t)g.y0 * P.Wl + g.x0) * L); tp.p01 = (uint32_t)(((size_t)g.y0 * P.Wl + g.x1) * L);
-      tp.p10 = (uint32_t)(((size_t)g.y1 * P.Wl + g.x0) * L); tp.p11 = (uint32_t)(((size_t)g.y1 * P.Wl + g.x1) * L);
+      const size_t mb = g.map * (size_t)P.Hl * P.Wl;          // texels before this (scene, view) map; the whole latent holds < 2^32 elements
+      tp.p00 = (uint32_t)((mb + (size_t)g.y0 * P.Wl + g.x0) * L); tp.p01 = (uint32_t)((mb + (size_t)g.y0 * P.Wl + g.x1) * L);
+      tp.p10 = (uint32_t)((mb + (size_t)g.y1 * P.Wl + g.x0) * L); tp.p11 = (uint32_t)((mb + (size_t)g.y1 * P.Wl + g.x1) * L);
       tp.w00 = (1.f - g.wx) * (1.f - g.wy); tp.w01 = g.wx * (1.f - g.wy);
       tp.w10 = (1.f - g.wx) * g.wy; tp.w11 = g.wx * g.wy;
       tp.xc = g.xc; tp.yc = g.yc; tp.zc = g.zc; tp.dx = g.dx; tp.dy = g.dy; tp.dz = g.dz; tp.dd = g.dd;
@@ -174,17 +175,24 @@ __global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams
         *reinterpret_cast<__nv_bfloat16*>(si + sto[u] + i * 16) = __float2bfloat16_rn(val);
       }
     }
-    constexpr int nraw = 64 - nsin;          // 16: x_cam 3 | dir_cam 3 | depth distance 1 | 9 zeros
-    for (int t = lane; t < 8 * nraw; t += 32) {
-      const int i = t / nraw, r = t - i * nraw;
-      const RowTaps& tp = taps_s[warp][i];
-      int e; float val = 0.f;
-      if (r < 3) { e = r; val = r == 0 ? tp.xc : (r == 1 ? tp.yc : tp.zc); }
-      else if (r < 6) { e = npos + (r - 3); val = r == 3 ? tp.dx : (r == 4 ? tp.dy : tp.dz); }
-      else if (r == 6) { e = npos + 3; val = tp.dd; }
+    // the 16 plain elements of a row (x_cam 3 | dir_cam 3 | depth distance 1 | 9 zeros): lane & 15 fixes the element, two
+    // rows per iteration
+    {
+      const int r = lane & 15;
+      int e, fo = -1;                                              // fo: field offset from RowTaps::xc, -1 = zero padding
+      if (r < 3) { e = r; fo = r; }                                // xc, yc, zc
+      else if (r < 6) { e = npos + (r - 3); fo = r; }              // dx, dy, dz
+      else if (r == 6) { e = npos + 3; fo = 6; }                   // dd
       else e = npos + 4 + 2 * NF + (r - 7);
-      if (!tp.map_plus1) val = 0.f;
-      reinterpret_cast<__nv_bfloat16*>(si + (e >> 3) * 128 + i * 16)[e & 7] = __float2bfloat16_rn(val);
+      const int so = (e >> 3) * 128 + (e & 7) * 2;
+#pragma unroll
+      for (int m = 0; m < 4; ++m) {
+        const int i = 2 * m + (lane >> 4);
+        const RowTaps& tp = taps_s[warp][i];
+        float val = fo >= 0 ? (&tp.xc)[fo] : 0.f;
+        if (!tp.map_plus1) val = 0.f;
+        *reinterpret_cast<__nv_bfloat16*>(si + so + i * 16) = __float2bfloat16_rn(val);
+      }
     }
   }
 
@@ -194,7 +202,7 @@ __global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams
     const RowTaps tp = taps_s[warp][i];
     uint4 o0 = make_uint4(0, 0, 0, 0), o1 = o0;
     if (tp.map_plus1) {
-      const __nv_bfloat16* lat = P.latent + (size_t)(tp.map_plus1 - 1) * (size_t)P.Hl * P.Wl * L;
+      const __nv_bfloat16* lat = P.latent;
       const uint64_t W00 = splat_f32x2(tp.w00), W01 = splat_f32x2(tp.w01), W10 = splat_f32x2(tp.w10), W11 = splat_f32x2(tp.w11);
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
@@ -395,6 +403,8 @@ DNR_EXPORT int dnr_encode_fwd(const float* rays, const float* z, const float* po
   int rc = fill_encode_params(P, rays, z, poses, focal, cxy, depth, latent_nhwc_bf16, freqs, phases, SB, NV, NR, K, H,
                               W, Hl, Wl, L, NF, ray_offset, n_rays, img_w, img_h, lat_sx, lat_sy);
   if (rc) return rc;
+  DNR_REQUIRE((unsigned long long)SB * NV * Hl * Wl * L < (1ull << 32),
+              "dnr_encode_fwd: the latent holds 2^32 elements or more (tap offsets are 32-bit); render fewer scenes per call");
   P.lat_pk = (unsigned char*)lat_pk; P.in_pk = (unsigned char*)in_pk;
   if (P.n_samples <= 0) return 0;
   const int tiles = dnr::RowMap::make(NV).tiles_for(P.n_samples);
