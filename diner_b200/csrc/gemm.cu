@@ -39,6 +39,7 @@ struct GemmParams {
   int relu_act;             // act_out = relu(v) instead of v
   // view mean-pool (combine layer): outputs are indexed by sample instead of by (sample, view) row
   int mean_nv;              // 0 = off, else NV
+  int res_in_nv;            // > 0: res_in is indexed by SAMPLE and enters as res_in / NV (backward of the view mean)
   long long n_samples;
 };
 
@@ -56,7 +57,20 @@ __device__ __forceinline__ void epilogue_prefetch(const GemmParams& P, int m_til
 #pragma unroll
     for (int c = 0; c < 4; ++c) e.m[c] = __ldg(reinterpret_cast<const uint4*>(mp + (size_t)c * 2048));
   }
-  if (P.res_in) {
+  if (P.res_in && P.res_in_nv) {
+    // d_x[(sample, view)] = d_mean[sample] / NV (resnetfc.py:9-14): the NV rows of a sample read the same pooled row
+    const int NV = P.res_in_nv, SPW = 32 / NV, l = row_in_tile & 31;
+    const long long sample = ((long long)m_tile * 4 + (row_in_tile >> 5)) * SPW + l / NV;
+    const bool ok = l < SPW * NV && sample < P.n_samples;
+    const float4* rp = reinterpret_cast<const float4*>(P.res_in) + ((size_t)(sample >> 7) * (N / 4) + n0 / 4) * 128 + (sample & 127);
+    const float inv = 1.f / (float)NV;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      float4 r = ok ? __ldg(rp + (size_t)c * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
+      r.x *= inv; r.y *= inv; r.z *= inv; r.w *= inv;
+      e.r[c] = r;
+    }
+  } else if (P.res_in) {
     const float4* rp = reinterpret_cast<const float4*>(P.res_in) + ((size_t)m_tile * (N / 4) + n0 / 4) * 128 + row_in_tile;
 #pragma unroll
     for (int c = 0; c < 8; ++c) e.r[c] = __ldg(rp + (size_t)c * 128);
@@ -274,7 +288,8 @@ DNR_EXPORT int dnr_mlp_gemm(const void* A0, const void* B0, int K0, const void* 
   DNR_REQUIRE(N > 0 && N % dnr::kBN == 0, "dnr_mlp_gemm: N must be a multiple of 256");
   DNR_REQUIRE(A0 && B0 && K0 > 0 && K0 % dnr::kBK == 0, "dnr_mlp_gemm: segment 0 invalid (K multiple of 64)");
   DNR_REQUIRE(K1 % dnr::kBK == 0 && K2 % dnr::kBK == 0, "dnr_mlp_gemm: K must be a multiple of 64");
-  DNR_REQUIRE(mean_nv >= 0 && mean_nv <= 8, "dnr_mlp_gemm: mean_nv must be in [0,8]");
+  DNR_REQUIRE(mean_nv >= -8 && mean_nv <= 8, "dnr_mlp_gemm: mean_nv must be in [-8,8]");
+  DNR_REQUIRE(mean_nv >= 0 || res_in != nullptr, "dnr_mlp_gemm: mean_nv < 0 (pooled residual input) needs res_in");
   if (m_tiles <= 0) return 0;
   dnr::GemmParams P;
   P.seg[0] = {(const unsigned char*)A0, (const unsigned char*)B0, K0};
@@ -283,7 +298,8 @@ DNR_EXPORT int dnr_mlp_gemm(const void* A0, const void* B0, int K0, const void* 
   P.nseg = 1 + (A1 != nullptr && K1 > 0 ? 1 : 0);
   if (P.nseg == 2 && A2 != nullptr && K2 > 0) P.nseg = 3;
   P.m_tiles = m_tiles; P.N = N; P.bias = bias; P.mask_pk = (const unsigned char*)mask_pk; P.res_in = res_in;
-  P.res_out = res_out; P.act_out = (unsigned char*)act_out; P.relu_act = relu_act; P.mean_nv = mean_nv;
+  P.res_out = res_out; P.act_out = (unsigned char*)act_out; P.relu_act = relu_act;
+  P.mean_nv = mean_nv > 0 ? mean_nv : 0; P.res_in_nv = mean_nv < 0 ? -mean_nv : 0;
   P.n_samples = n_samples;
   static bool configured = false;
   static int num_sms = 148;

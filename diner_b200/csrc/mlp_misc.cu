@@ -120,8 +120,7 @@ __global__ void __launch_bounds__(128) mean_bwd_kernel(const float* __restrict__
     float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
     if (valid) { a = __ldg(src + (size_t)(c * 2) * 128); b = __ldg(src + (size_t)(c * 2 + 1) * 128); }
     a.x *= inv; a.y *= inv; a.z *= inv; a.w *= inv; b.x *= inv; b.y *= inv; b.z *= inv; b.w *= inv;
-    xr[(size_t)(c * 2) * 128] = a;
-    xr[(size_t)(c * 2 + 1) * 128] = b;
+    if (dx_xr) { xr[(size_t)(c * 2) * 128] = a; xr[(size_t)(c * 2 + 1) * 128] = b; }
     *reinterpret_cast<uint4*>(pb + (size_t)c * 2048) =
         make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y), pack_bf16x2(b.z, b.w));
   }

@@ -348,26 +348,35 @@ def field_backward(sc: SceneBuffers, pk: PackedMLP, mlp, sv: FieldSaved, rays, z
               p(draw), st)
     _wgrad(draw, 128, sv.xa[5], HID, ms, G("lin_out.weight"), 4, HID, G("lin_out.bias"))
 
-    def block_bwd(b, tiles, dx, dx_pk):
-        """dx = d x_{b+1} -> returns d x_b' (gradient at the block's input, after its lin_z was added)."""
+    def block_bwd(b, tiles, dx, dx_pk, pooled_dx=None):
+        """dx = d x_{b+1} -> returns d x_b' (gradient at the block's input, after its lin_z was added).  With
+        `pooled_dx` the fp32 stream entering the block is the POOLED gradient of the view mean: the dgrad epilogue
+        reads row (sample, view) as pooled_dx[sample] / NV and writes the per-view stream for the first time."""
         _wgrad(dx_pk, HID, sv.net[b], HID, tiles, G(f"blocks.{b}.fc_1.weight"), HID, HID, G(f"blocks.{b}.fc_1.bias"))
         dnet = torch.empty(tiles * 128 * HID, **bf)
         _gemm(dx_pk, pk.wt_1[b], HID, tiles, mask=sv.net[b], act_out=dnet)
         _wgrad(dnet, HID, sv.xa[b], HID, tiles, G(f"blocks.{b}.fc_0.weight"), HID, HID, G(f"blocks.{b}.fc_0.bias"))
         dx_pk2 = torch.empty(tiles * 128 * HID, **bf)
-        _gemm(dnet, pk.wt_0[b], HID, tiles, mask=sv.xa[b], res_in=dx, res_out=dx, act_out=dx_pk2)
+        if pooled_dx is not None:
+            dx = torch.empty(tiles * 128 * HID, **f32)
+            _gemm(dnet, pk.wt_0[b], HID, tiles, mask=sv.xa[b], res_in=pooled_dx, res_out=dx, act_out=dx_pk2,
+                  mean_nv=-NV, n_samples=n_samples)
+        else:
+            _gemm(dnet, pk.wt_0[b], HID, tiles, mask=sv.xa[b], res_in=dx, res_out=dx, act_out=dx_pk2)
         return dx, dx_pk2
 
     for b in (4, 3):
         dx, dx_pk = block_bwd(b, ms, dx, dx_pk)
     # ---- view mean ----
-    dxv = torch.empty(mv * 128 * HID, **f32)
+    # only the bf16 operand image of d x / NV is materialised per view row; the fp32 stream is read from the pooled
+    # gradient by block 2's dgrad epilogue (2 KB per view row less to write and to read back)
     dxv_pk = torch.empty(mv * 128 * HID, **bf)
-    _lib.call("dnr_mean_bwd", p(dx), NV, n_samples, mv, p(dxv), p(dxv_pk), st)
-    del dx, dx_pk
+    _lib.call("dnr_mean_bwd", p(dx), NV, n_samples, mv, None, p(dxv_pk), st)
+    pooled, dxv = dx, None
+    del dx_pk
     dz_pk = [None, None, None]
     for b in (2, 1, 0):
-        dxv, dxv_pk = block_bwd(b, mv, dxv, dxv_pk)
+        dxv, dxv_pk = block_bwd(b, mv, dxv, dxv_pk, pooled_dx=pooled if b == 2 else None)
         dz_pk[b] = dxv_pk
         _wgrad(dxv_pk, HID, sv.lat, HID, mv, G(f"lin_z.{b}.weight"), HID, HID, G(f"lin_z.{b}.bias"))
     _wgrad(dz_pk[0], HID, sv.code, IN_PAD, mv, G("lin_in.weight"), HID, mlp.d_in, G("lin_in.bias"))

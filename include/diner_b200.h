@@ -101,7 +101,8 @@ int dnr_pack_weight(const float* W, int rows_w, int cols_w, int ld, int transpos
  * epilogue: + bias[N]; * [mask_pk > 0] (ReLU backward); + res_in (XR); optional mean over the NV view rows of
  * each sample (combine(), resnetfc.py:9-14; outputs then indexed by sample); outputs res_out (XR fp32) and/or
  * act_out (PK128 bf16, relu_act=1 applies ReLU).  A: PK128, B: PK256, K multiple of 64, N multiple of 256.
- * max_ctas > 0 caps the persistent grid. */
+ * max_ctas > 0 caps the persistent grid.  mean_nv < 0 is the backward of that mean: res_in is a POOLED stream indexed by
+ * sample, and row (sample, view) receives res_in[sample] / |mean_nv| (n_samples bounds the valid rows). */
 int dnr_mlp_gemm(const void* A0, const void* B0, int K0, const void* A1, const void* B1, int K1, const void* A2,
                  const void* B2, int K2, int m_tiles, int N, const float* bias, const void* mask_pk,
                  const float* res_in, float* res_out, void* act_out, int relu_act, int mean_nv, long long n_samples,
@@ -163,6 +164,8 @@ int dnr_head_fwd(const void* xa_pk, const float* Wout, const float* bout, long l
 int dnr_head_bwd(const void* xa_pk, const float* Wout, const float* rgbsigma, const float* d_rgbsigma,
                  long long n_samples, float* dx_xr, void* dx_pk, void* draw_pk, dnr_stream_t stream);
 /* Backward of the view mean (resnetfc.py:9-14): d_x[(sample,view)] = d_mean[sample] / NV. */
+/* dx_xr may be null (only the bf16 operand image is written; the fp32 stream is then folded into the next dgrad GEMM
+ * through dnr_mlp_gemm's mean_nv < 0). */
 int dnr_mean_bwd(const float* dmean_xr, int NV, long long n_samples, int view_tiles, float* dx_xr, void* dx_pk,
                  dnr_stream_t stream);
 
