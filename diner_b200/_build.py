@@ -23,6 +23,7 @@ SOURCES = [
     ("wgrad.cu", []),
     ("producers.cu", []),
     ("depth_format.cu", []),
+    ("deform.cu", []),
     ("mlp_misc.cu", []),
 ]
 COMMON = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

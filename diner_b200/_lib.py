@@ -11,7 +11,7 @@ import os
 from . import _build
 
 _lib = None
-ABI_VERSION = 9
+ABI_VERSION = 10
 
 # instrumentation used by bench.py: number of kernel launches issued through the ABI, and (when `profile` is a
 # list) one (name, start_event, end_event, tag) record per call for per-kernel CUDA-event timing
@@ -33,6 +33,7 @@ _SIGNATURES = {
     "dnr_gen_rays_at": (c_i, [c_p, c_p, c_i, c_i, c_i, c_p, c_p, c_p, c_i, c_p, c_p, c_p]),
     "dnr_depth2normal": (c_i, [c_p, c_p, c_i, c_i, c_i, c_p, c_p]),
     "dnr_decode_depth_u16": (c_i, [c_p, c_p, c_ll, c_i, c_p, c_i, c_i, c_i, c_i] + [c_f] * 6 + [c_i, c_p, c_p, c_p]),
+    "dnr_deform_points": (c_i, [c_p, c_p, c_p, c_i, c_ll, c_i, c_p, c_p, c_p, c_p]),
     "dnr_pad_depth_std": (c_i, [c_p, c_p, c_i, c_i, c_i, c_i, c_p, c_p]),
     "dnr_sampler_fwd": (c_i, [c_p] * 13 + [c_ull] + [c_i] * 9 + [c_f] * 5 + [c_i, c_i] + [c_p] * 6),
     "dnr_view_row_tiles": (c_i, [c_ll, c_i]),

@@ -11,4 +11,4 @@ void set_last_error_msg(const char* msg) { snprintf(g_last_error, sizeof(g_last_
 }  // namespace dnr
 
 DNR_EXPORT const char* dnr_last_error() { return dnr::g_last_error; }
-DNR_EXPORT int dnr_abi_version() { return 9; }
+DNR_EXPORT int dnr_abi_version() { return 10; }

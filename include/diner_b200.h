@@ -221,6 +221,14 @@ int dnr_decode_depth_u16(const uint16_t* pred, const uint16_t* conf, long long i
                          float std_a, float std_b, float std_const, int flags, float* depth_out, float* std_out,
                          dnr_stream_t stream);
 
+/* Nearest-vertex deformation (first piece): out[sb,i] = points[sb,i] + offsets[sb, argmin_v
+ * |points[sb,i] - vertices[sb,v]|^2] (brute-force K = 1 search, squared distance accumulated x, y, z in fp32, the lowest index
+ * wins a tie).  points / out [SB,B,3], vertices / offsets [SB,V,3]; idx_out [SB,B] int32 and dist_out [SB,B] (squared) are
+ * optional.  Replaces NeRFRendererDGS.deform_points of the NOVEL variants (src/models/novel/nerf_novel_renderer.py:40-50,
+ * pytorch3d.ops.knn_points + gather + add).  Parity with pytorch3d is unpinned: it is not installed in the build image. */
+int dnr_deform_points(const float* points, const float* vertices, const float* offsets, int SB, long long B, int V,
+                      float* out, int* idx_out, float* dist_out, dnr_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
