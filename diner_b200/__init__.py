@@ -7,5 +7,6 @@ format in `diner_b200.depth_format`.
 """
 from .producers import depth2normal, gen_rays, gen_rays_at  # noqa: F401
 from .renderer import NeRFRendererDGS, RenderResult, sample_rays  # noqa: F401
+from .scene import invalidate  # noqa: F401
 
-__all__ = ["NeRFRendererDGS", "RenderResult", "sample_rays", "gen_rays", "gen_rays_at", "depth2normal"]
+__all__ = ["NeRFRendererDGS", "RenderResult", "sample_rays", "gen_rays", "gen_rays_at", "depth2normal", "invalidate"]

@@ -37,19 +37,46 @@ def _nvcc() -> str:
     raise RuntimeError("nvcc not found")
 
 
+HASH_PATH = LIB_PATH + ".srchash"
+
+
+def source_hash() -> str:
+    """Digest of every file under csrc/ and of the compile flags (mtimes do not survive a snapshot copy to another box;
+    contents do)."""
+    import hashlib
+    h = hashlib.sha256(repr((SOURCES, COMMON)).encode())
+    for name in sorted(os.listdir(CSRC)):
+        with open(os.path.join(CSRC, name), "rb") as f:
+            h.update(name.encode() + b"\0" + f.read())
+    return h.hexdigest()
+
+
 def needs_build() -> bool:
-    if not os.path.exists(LIB_PATH):
+    """True when the library is missing or was built from other sources than the ones in the tree."""
+    if not (os.path.exists(LIB_PATH) and os.path.exists(HASH_PATH)):
         return True
-    t = os.path.getmtime(LIB_PATH)
-    for name in os.listdir(CSRC):
-        if os.path.getmtime(os.path.join(CSRC, name)) > t:
-            return True
-    return False
+    with open(HASH_PATH) as f:
+        return f.read().strip() != source_hash()
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
+    """Build the library if it is missing or older than a source.  Safe under torchrun: an exclusive file lock
+    serialises the ranks (the first one builds, the others find the library up to date), objects go to a per-process
+    directory and the library is moved into place atomically."""
     if not force and not needs_build():
         return LIB_PATH
+    import fcntl
+    with open(os.path.join(HERE, ".build.lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and not needs_build():      # another process built it while we waited
+                return LIB_PATH
+            return _build_locked(verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(verbose: bool) -> str:
     nvcc = _nvcc()
     objdir = os.path.join(HERE, "build")
     os.makedirs(objdir, exist_ok=True)
@@ -66,10 +93,14 @@ def build(force: bool = False, verbose: bool = False) -> str:
             raise RuntimeError("nvcc failed: " + " ".join(cmd) + "\n" + out)
         if verbose and out.strip():
             print(out)
-    cmd = [nvcc, "-shared", "-o", LIB_PATH, *objs, "-lcudart"]
+    tmp = LIB_PATH + f".tmp{os.getpid()}"
+    cmd = [nvcc, "-shared", "-o", tmp, *objs, "-lcudart"]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed: " + " ".join(cmd) + "\n" + r.stdout)
+    os.replace(tmp, LIB_PATH)
+    with open(HASH_PATH, "w") as f:
+        f.write(source_hash())
     return LIB_PATH
 
 

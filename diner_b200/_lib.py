@@ -11,7 +11,7 @@ import os
 from . import _build
 
 _lib = None
-ABI_VERSION = 10
+ABI_VERSION = 11
 
 # instrumentation used by bench.py: number of kernel launches issued through the ABI, and (when `profile` is a
 # list) one (name, start_event, end_event, tag) record per call for per-kernel CUDA-event timing
@@ -38,14 +38,15 @@ _SIGNATURES = {
     "dnr_sampler_fwd": (c_i, [c_p] * 13 + [c_ull] + [c_i] * 9 + [c_f] * 5 + [c_i, c_i] + [c_p] * 6),
     "dnr_view_row_tiles": (c_i, [c_ll, c_i]),
     "dnr_encode_fwd": (c_i, [c_p] * 9 + [c_i] * 10 + [c_ll, c_ll] + [c_f] * 4 + [c_p, c_p, c_p]),
+    "dnr_encode_fwd_split": (c_i, [c_p] * 10 + [c_i] * 10 + [c_ll, c_ll] + [c_f] * 4 + [c_p] * 5),
     "dnr_encode_bwd": (c_i, [c_p] * 8 + [c_i] * 10 + [c_ll, c_ll] + [c_f] * 4 + [c_p, c_p, c_p]),
     "dnr_pack_latent_nhwc": (c_i, [c_p, c_i, c_i, c_i, c_i, c_p, c_p]),
     "dnr_unpack_dlatent_nchw": (c_i, [c_p, c_i, c_i, c_i, c_i, c_p, c_p]),
-    "dnr_mlp_gemm": (c_i, [c_p, c_p, c_i, c_p, c_p, c_i, c_p, c_p, c_i, c_i, c_i, c_p, c_p, c_p, c_p, c_p, c_i, c_i,
+    "dnr_mlp_gemm": (c_i, [c_p, c_p, c_i, c_p, c_p, c_i, c_p, c_p, c_i, c_i, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i,
                            c_ll, c_i, c_p]),
     "dnr_mlp_wgrad": (c_i, [c_p, c_i, c_p, c_i, c_i, c_p, c_i, c_i, c_i, c_p, c_p]),
     "dnr_pack_weight": (c_i, [c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_p, c_p]),
-    "dnr_head_fwd": (c_i, [c_p, c_p, c_p, c_ll, c_i, c_p, c_p]),
+    "dnr_head_fwd": (c_i, [c_p, c_p, c_p, c_p, c_ll, c_i, c_p, c_p]),
     "dnr_mlp_fused_scratch_bytes": (c_ll, [c_i]),
     "dnr_mlp_pair_fwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_p, c_p, c_p]),
     "dnr_mlp_quad_max_clusters": (c_i, [c_i]),
@@ -73,10 +74,10 @@ def load(build_if_missing: bool = True):
     if _lib is not None:
         return _lib
     path = _build.LIB_PATH
-    if not os.path.exists(path):
-        if not build_if_missing:
-            raise RuntimeError(f"{path} is missing and building was disabled; diner_b200 has no CPU fallback")
-        _build.build()
+    if build_if_missing:
+        _build.build()          # no-op when the library is newer than every source; file-locked against other ranks
+    elif not os.path.exists(path):
+        raise RuntimeError(f"{path} is missing and building was disabled; diner_b200 has no CPU fallback")
     lib = C.CDLL(path)
     for name, (res, args) in _SIGNATURES.items():
         fn = getattr(lib, name)
@@ -113,5 +114,7 @@ def call(name: str, *args, tag=None):
 
 
 def stream_ptr():
+    """Current stream of the current device (NeRFRendererDGS.forward and the autograd backwards run inside
+    `torch.cuda.device(rays.device)`, so this is the stream of the device the tensors live on)."""
     import torch
     return torch.cuda.current_stream().cuda_stream

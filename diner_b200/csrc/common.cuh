@@ -41,6 +41,18 @@ void set_last_error_msg(const char* msg);
     }                                                            \
   } while (0)
 
+// ---- per-device launch state ---------------------------------------------------------------------
+// cudaFuncSetAttribute and the SM count are per DEVICE: one process may render on several GPUs in turn, so nothing of
+// this lives in function-local statics.  device_info() returns the slot of the calling thread's current device
+// (nullptr when there is none); the flags are idempotent, so unsynchronised first use from two threads is harmless.
+struct DeviceInfo {
+  int num_sms;
+  bool gemm_configured, fused_configured, wgrad2_configured, pair_configured[5];
+  size_t sampler_smem, wgrad_smem;
+  int quad_clusters[5];
+};
+DeviceInfo* device_info();
+
 // ---- row tiling of the MLP batch ------------------------------------------------------------
 // Per-view rows are ordered sample-major / view-minor and grouped so that the NV rows of one
 // sample never straddle a warp of the GEMM epilogue (32 TMEM lanes): each warp-slab of 32 rows

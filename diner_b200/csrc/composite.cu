@@ -410,13 +410,18 @@ DNR_EXPORT int dnr_composite_fwd(const float* rgbsigma, const float* z, const fl
   DNR_REQUIRE(K >= 1 && K <= 256, "dnr_composite_fwd: K must be in [1,256]");
   if (n_rays <= 0) return 0;
   const int wpb = 8;
+  dnr::DeviceInfo* di = dnr::device_info();
+  DNR_REQUIRE(di != nullptr, "dnr_composite_fwd: no current CUDA device");
+  const int sms = di->num_sms;
   int blocks = (int)((n_rays + wpb - 1) / wpb);
-  if (blocks > 148 * 8) blocks = 148 * 8;      // one resident wave (2 048 threads per SM), grid-stride over the rays
+  if (blocks > sms * 8) blocks = sms * 8;      // one resident wave (2 048 threads per SM), grid-stride over the rays
+  // K <= 48: one ray per half warp, three samples per lane (fwd3); 48 < K <= 64, K even: two samples per lane (fwd2);
+  // otherwise the generic one-warp-per-ray kernel
   auto kern = K <= 48 ? dnr::composite_fwd3_kernel
                       : (K % 2 == 0 && K <= 64) ? dnr::composite_fwd2_kernel : dnr::composite_fwd_kernel;
   if (K <= 48) {                                 // two rays per warp, three resident blocks per SM (80 registers)
     blocks = (int)(((n_rays + 1) / 2 + wpb - 1) / wpb);
-    if (blocks > 148 * 3) blocks = 148 * 3;
+    if (blocks > sms * 3) blocks = sms * 3;
   }
   kern<<<blocks, wpb * 32, 0, stream>>>((const float4*)rgbsigma, z, rays, n_rays, K, white_bkgd, weights, rgb, depth);
   DNR_CHECK_LAUNCH("dnr_composite_fwd");
@@ -429,8 +434,10 @@ DNR_EXPORT int dnr_composite_bwd(const float* rgbsigma, const float* z, const fl
   DNR_REQUIRE(K >= 1 && K <= 256, "dnr_composite_bwd: K must be in [1,256]");
   if (n_rays <= 0) return 0;
   const int wpb = 8;
+  dnr::DeviceInfo* di = dnr::device_info();
+  DNR_REQUIRE(di != nullptr, "dnr_composite_bwd: no current CUDA device");
   int blocks = (int)((n_rays + wpb - 1) / wpb);
-  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks > di->num_sms * 8) blocks = di->num_sms * 8;
   auto kern = (K % 2 == 0 && K <= 64) ? dnr::composite_bwd2_kernel : dnr::composite_bwd_kernel;
   kern<<<blocks, wpb * 32, 0, stream>>>((const float4*)rgbsigma, z, rays, d_rgb, d_depth, d_weights, n_rays, K, white_bkgd,
                                         (float4*)d_rgbsigma);

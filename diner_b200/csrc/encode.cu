@@ -99,9 +99,13 @@ __device__ __forceinline__ uint64_t fma_f32x2(uint64_t a, uint64_t b, uint64_t c
 }
 
 constexpr int kEncWarps = 4;
-constexpr int kLatChunkStride = 144;   // 8 rows * 16 B + 16 B pad -> conflict-free staging
+// staging of one 32-row slab in the PK<128> order: [feature chunk of 8][32 rows] x 16 B, i.e. the 512 contiguous bytes a
+// slab owns of every chunk in global memory; + 16 B pad per chunk -> conflict-free 8-byte stores and 16-byte loads
+constexpr int kLatChunkStride = 32 * 16 + 16;
+constexpr int kEncLatBytes = 64 * kLatChunkStride;       // 33 792
+constexpr int kEncInBytes = 8 * kLatChunkStride;         //  4 224
 
-// per-row tap description, produced by one lane per row and read back by the whole warp (broadcast LDS)
+// per-row tap description, produced by one lane per row and read back by the whole CTA (broadcast LDS)
 struct __align__(16) RowTaps {
   uint32_t p00, p01, p10, p11;      // element offsets of the four taps inside the whole latent (all maps)
   float w00, w01, w10, w11;
@@ -109,25 +113,51 @@ struct __align__(16) RowTaps {
   uint32_t map_plus1;               // (sb*NV + view) + 1, 0 = padding row
 };
 
-__global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams P) {
-  __shared__ __align__(16) unsigned char stage_lat[kEncWarps][64 * kLatChunkStride];
-  __shared__ __align__(16) unsigned char stage_in[kEncWarps][8 * 128];
-  __shared__ RowTaps taps_s[kEncWarps][8];
+__device__ __forceinline__ float blend4_lo(uint32_t a, uint32_t b, uint32_t c, uint32_t d, uint64_t W00, uint64_t W01,
+                                           uint64_t W10, uint64_t W11, float& hi) {
+  // both channels of a bf16x2 word in one packed fp32 operation (FMUL2 / FFMA2): a*w00, then fma by fma in tap order --
+  // the same roundings as the scalar chain
+  uint64_t acc = mul_f32x2(bf16x2_to_f32x2(a), W00);
+  acc = fma_f32x2(bf16x2_to_f32x2(b), W01, acc);
+  acc = fma_f32x2(bf16x2_to_f32x2(c), W10, acc);
+  acc = fma_f32x2(bf16x2_to_f32x2(d), W11, acc);
+  float lo;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(acc));
+  return lo;
+}
+
+// One CTA per 32-row slab (floor(32/NV) samples x NV views); warp w owns feature channels [128 w, 128 w + 128), four per
+// lane.  The warp walks the slab's rows VIEW BY VIEW in sample order: consecutive samples of a ray project into the same
+// bilinear footprint of a source view most of the time (the depth-guided samples cluster within a few std of the
+// surface, and the latent has half the image resolution), so the four taps stay in registers across such a run and only
+// the blend weights change -- the L2 -> SM tap traffic falls from 4 KB per row to 4 KB per footprint run.  Same blend
+// order as before (mul, fma, fma, fma in tap order): bit-identical outputs.
+// SPLIT (verification mode): the latent is a bf16 hi + lo pair, the blended feature and the geometric code leave as
+// hi + lo pairs of operand images (v_hi = bf16(v), v_lo = bf16(v - v_hi)).
+template <bool SPLIT>
+__global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams P, const __nv_bfloat16* latent_lo,
+                                                                    unsigned char* lat_pk_lo, unsigned char* in_pk_lo) {
+  extern __shared__ __align__(16) unsigned char enc_smem[];
+  unsigned char* sl = enc_smem;                                   // [64][kLatChunkStride]
+  unsigned char* si = enc_smem + kEncLatBytes;                    // [8][kLatChunkStride]
+  RowTaps* taps_s = reinterpret_cast<RowTaps*>(si + kEncInBytes); // [32]
+  unsigned char* sl_lo = reinterpret_cast<unsigned char*>(taps_s + 32);     // SPLIT only
+  unsigned char* si_lo = sl_lo + kEncLatBytes;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const RowMap rm = RowMap::make(P.NV);
-  const long long group = (long long)blockIdx.x * kEncWarps + warp;   // 8-row group index
-  const long long row_base = group * 8;
-  unsigned char* sl = stage_lat[warp];
-  unsigned char* si = stage_in[warp];
+  const long long row_base = (long long)blockIdx.x * 32;
   const int L = 512;
 
-  // phase 1: lanes 0..7 run the projection chain of one row each (the eight chains overlap instead of running
+  // phase 1: lanes 0..7 of warp w run the projection chain of rows 8w..8w+7 (the eight chains overlap instead of running
   // back to back on all 32 lanes)
   if (lane < 8) {
     long long sample; int view;
     RowTaps tp;
     tp.map_plus1 = 0;
-    if (rm.decode(row_base + lane, P.n_samples, sample, view)) {
+    tp.p00 = tp.p01 = tp.p10 = tp.p11 = 0u;
+    tp.w00 = tp.w01 = tp.w10 = tp.w11 = 0.f;
+    tp.xc = tp.yc = tp.zc = tp.dx = tp.dy = tp.dz = tp.dd = 0.f;
+    if (rm.decode(row_base + warp * 8 + lane, P.n_samples, sample, view)) {
       RowGeom g;
       row_geometry(P, sample, view, g);
       const size_t mb = g.map * (size_t)P.Hl * P.Wl;          // texels before this (scene, view) map; the whole latent holds < 2^32 elements
@@ -138,16 +168,16 @@ __global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams
       tp.xc = g.xc; tp.yc = g.yc; tp.zc = g.zc; tp.dx = g.dx; tp.dy = g.dy; tp.dz = g.dz; tp.dd = g.dd;
       tp.map_plus1 = (uint32_t)g.map + 1u;
     }
-    taps_s[warp][lane] = tp;
+    taps_s[warp * 8 + lane] = tp;
   }
   __syncwarp();
 
-  // phase 1b: the 55-wide geometric code of the 8 rows (zero-padded to 64).  The 48 sines of a row are spread over the
-  // warp as 8 x 48 = 384 = 12 full-warp evaluations, one branch-free sinf each; the 16 plain elements follow.
+  // phase 1b: the 55-wide geometric code of the warp's 8 rows (zero-padded to 64).  The 48 sines of a row are spread
+  // over the warp as 8 x 48 = 384 = 12 full-warp evaluations, one branch-free sinf each; the 16 plain elements follow.
   {
     constexpr int NF = 6;                    // required by fill_encode_params (55-wide code)
     constexpr int npos = 3 + 6 * NF;         // 39
-    constexpr int nsin_pos = 6 * NF, nsin = 8 * NF;      // 36, 48
+    constexpr int nsin_pos = 6 * NF;         // 36
     // 3 x 32 lanes cover the 2 x 48 sines of a row pair, so a lane meets only three (element, frequency, coordinate)
     // combinations: q = lane (row 2m), lane + 32 or lane - 16 (row 2m or 2m + 1), lane + 16 (row 2m + 1).  Everything
     // that depends on q alone is hoisted out of the loop over the four row pairs.
@@ -161,18 +191,23 @@ __global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams
       if (q < nsin_pos) { fs = q / 3; e = 3 + q; foff[u] = q % 3; }            // xc, yc, zc
       else { fs = q - nsin_pos; e = npos + 4 + fs; foff[u] = 6; }              // dd
       fr[u] = P.freqs[fs]; ph[u] = P.phases[fs];
-      sto[u] = (e >> 3) * 128 + (e & 7) * 2;                                    // byte offset inside the staged code tile
+      sto[u] = (e >> 3) * kLatChunkStride + (e & 7) * 2;                        // byte offset inside the staged code slab
     }
+    auto put = [&](int off, float val) {
+      const __nv_bfloat16 hi = __float2bfloat16_rn(val);
+      *reinterpret_cast<__nv_bfloat16*>(si + off) = hi;
+      if (SPLIT) *reinterpret_cast<__nv_bfloat16*>(si_lo + off) = __float2bfloat16_rn(val - __bfloat162float(hi));
+    };
 #pragma unroll
     for (int m = 0; m < 4; ++m) {
 #pragma unroll
       for (int u = 0; u < 3; ++u) {
-        const int i = 2 * m + r3[u];
-        const RowTaps& tp = taps_s[warp][i];
+        const int i = warp * 8 + 2 * m + r3[u];
+        const RowTaps& tp = taps_s[i];
         const float x = (&tp.xc)[foff[u]];
         float val = sinf(__fadd_rn(ph[u], __fmul_rn(x, fr[u])));
         if (!tp.map_plus1) val = 0.f;
-        *reinterpret_cast<__nv_bfloat16*>(si + sto[u] + i * 16) = __float2bfloat16_rn(val);
+        put(sto[u] + i * 16, val);
       }
     }
     // the 16 plain elements of a row (x_cam 3 | dir_cam 3 | depth distance 1 | 9 zeros): lane & 15 fixes the element, two
@@ -184,71 +219,100 @@ __global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams
       else if (r < 6) { e = npos + (r - 3); fo = r; }              // dx, dy, dz
       else if (r == 6) { e = npos + 3; fo = 6; }                   // dd
       else e = npos + 4 + 2 * NF + (r - 7);
-      const int so = (e >> 3) * 128 + (e & 7) * 2;
+      const int so = (e >> 3) * kLatChunkStride + (e & 7) * 2;
 #pragma unroll
       for (int m = 0; m < 4; ++m) {
-        const int i = 2 * m + (lane >> 4);
-        const RowTaps& tp = taps_s[warp][i];
+        const int i = warp * 8 + 2 * m + (lane >> 4);
+        const RowTaps& tp = taps_s[i];
         float val = fo >= 0 ? (&tp.xc)[fo] : 0.f;
         if (!tp.map_plus1) val = 0.f;
-        *reinterpret_cast<__nv_bfloat16*>(si + so + i * 16) = __float2bfloat16_rn(val);
+        put(so + i * 16, val);
       }
     }
   }
+  __syncthreads();
 
-  // phase 2: the warp gathers row after row, two rows' loads in flight
+  // phase 2: gather.  Lane's channels: 128 warp + 4 lane .. + 3 = 8 bytes of feature chunk c = 16 warp + lane / 2.
+  {
+    const int ch = warp * 128 + lane * 4;
+    unsigned char* dst0 = sl + (warp * 16 + (lane >> 1)) * kLatChunkStride + (lane & 1) * 8;
+    unsigned char* dst0_lo = sl_lo + (warp * 16 + (lane >> 1)) * kLatChunkStride + (lane & 1) * 8;
+    const __nv_bfloat16* lat = P.latent + ch;
+    const __nv_bfloat16* lat_lo = SPLIT ? latent_lo + ch : nullptr;
+    uint2 a = make_uint2(0, 0), b = a, c = a, d = a;              // the four taps of the current footprint
+    uint2 al = a, bl = a, cl = a, dl = a;
+    uint32_t cur00 = 0xffffffffu, cur11 = 0xffffffffu;
+    const int n_live = rm.SPW * rm.NV;
+    for (int v = 0; v < rm.NV; ++v) {
 #pragma unroll 2
-  for (int i = 0; i < 8; ++i) {
-    const RowTaps tp = taps_s[warp][i];
-    uint4 o0 = make_uint4(0, 0, 0, 0), o1 = o0;
-    if (tp.map_plus1) {
-      const __nv_bfloat16* lat = P.latent;
-      const uint64_t W00 = splat_f32x2(tp.w00), W01 = splat_f32x2(tp.w01), W10 = splat_f32x2(tp.w10), W11 = splat_f32x2(tp.w11);
-#pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        const int ch = half * 256 + lane * 8;
-        const uint4 a = __ldg(reinterpret_cast<const uint4*>(lat + tp.p00 + ch));
-        const uint4 b = __ldg(reinterpret_cast<const uint4*>(lat + tp.p01 + ch));
-        const uint4 c = __ldg(reinterpret_cast<const uint4*>(lat + tp.p10 + ch));
-        const uint4 d = __ldg(reinterpret_cast<const uint4*>(lat + tp.p11 + ch));
-        const uint32_t av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
-        const uint32_t cv[4] = {c.x, c.y, c.z, c.w}, dv[4] = {d.x, d.y, d.z, d.w};
-        uint32_t r[4];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          // both channels of a bf16x2 word in one packed fp32 operation (FMUL2 / FFMA2): a*w00, then fma by fma in
-          // tap order -- the same roundings as the scalar chain
-          uint64_t acc = mul_f32x2(bf16x2_to_f32x2(av[q]), W00);
-          acc = fma_f32x2(bf16x2_to_f32x2(bv[q]), W01, acc);
-          acc = fma_f32x2(bf16x2_to_f32x2(cv[q]), W10, acc);
-          acc = fma_f32x2(bf16x2_to_f32x2(dv[q]), W11, acc);
-          float lo, hi;
-          asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(acc));
-          r[q] = pack_bf16x2(lo, hi);
+      for (int s = 0; s < rm.SPW; ++s) {
+        const int l = s * rm.NV + v;
+        const uint4 pp = *reinterpret_cast<const uint4*>(&taps_s[l].p00);
+        const float4 ww = *reinterpret_cast<const float4*>(&taps_s[l].w00);
+        const uint32_t live = taps_s[l].map_plus1;
+        uint2 o = make_uint2(0, 0), o_lo = o;
+        if (live) {                                                // (warp-uniform)
+          if (pp.x != cur00 || pp.w != cur11) {                    // a new footprint: p00 fixes (map, x0, y0), p11 the clamps
+            a = __ldg(reinterpret_cast<const uint2*>(lat + pp.x)); b = __ldg(reinterpret_cast<const uint2*>(lat + pp.y));
+            c = __ldg(reinterpret_cast<const uint2*>(lat + pp.z)); d = __ldg(reinterpret_cast<const uint2*>(lat + pp.w));
+            if (SPLIT) {
+              al = __ldg(reinterpret_cast<const uint2*>(lat_lo + pp.x)); bl = __ldg(reinterpret_cast<const uint2*>(lat_lo + pp.y));
+              cl = __ldg(reinterpret_cast<const uint2*>(lat_lo + pp.z)); dl = __ldg(reinterpret_cast<const uint2*>(lat_lo + pp.w));
+            }
+            cur00 = pp.x; cur11 = pp.w;
+          }
+          const uint64_t W00 = splat_f32x2(ww.x), W01 = splat_f32x2(ww.y), W10 = splat_f32x2(ww.z), W11 = splat_f32x2(ww.w);
+          float v0, v1, v2, v3;
+          v0 = blend4_lo(a.x, b.x, c.x, d.x, W00, W01, W10, W11, v1);
+          v2 = blend4_lo(a.y, b.y, c.y, d.y, W00, W01, W10, W11, v3);
+          if (SPLIT) {
+            float u0, u1, u2, u3;
+            u0 = blend4_lo(al.x, bl.x, cl.x, dl.x, W00, W01, W10, W11, u1);
+            u2 = blend4_lo(al.y, bl.y, cl.y, dl.y, W00, W01, W10, W11, u3);
+            v0 += u0; v1 += u1; v2 += u2; v3 += u3;
+          }
+          o = make_uint2(pack_bf16x2(v0, v1), pack_bf16x2(v2, v3));
+          if (SPLIT)
+            o_lo = make_uint2(pack_bf16x2(v0 - bf16lo(o.x), v1 - bf16hi(o.x)), pack_bf16x2(v2 - bf16lo(o.y), v3 - bf16hi(o.y)));
         }
-        if (half == 0) o0 = make_uint4(r[0], r[1], r[2], r[3]); else o1 = make_uint4(r[0], r[1], r[2], r[3]);
+        *reinterpret_cast<uint2*>(dst0 + l * 16) = o;
+        if (SPLIT) *reinterpret_cast<uint2*>(dst0_lo + l * 16) = o_lo;
       }
     }
-    *reinterpret_cast<uint4*>(sl + lane * kLatChunkStride + i * 16) = o0;
-    *reinterpret_cast<uint4*>(sl + (32 + lane) * kLatChunkStride + i * 16) = o1;
+    for (int l = n_live; l < 32; ++l) {                            // padding rows of the slab (NV = 3: rows 30, 31)
+      *reinterpret_cast<uint2*>(dst0 + l * 16) = make_uint2(0, 0);
+      if (SPLIT) *reinterpret_cast<uint2*>(dst0_lo + l * 16) = make_uint2(0, 0);
+    }
   }
-  __syncwarp();
-  // write-out: every 8 lanes move one 128-byte line (8 rows x 16 B of one feature chunk)
+  __syncthreads();
+  // write-out: a warp moves the slab's 512 contiguous bytes of one feature chunk per instruction
   const long long tile = row_base / 128;
   const int rr = (int)(row_base % 128);
-  unsigned char* lat_tile = P.lat_pk + (size_t)tile * (512 / 8) * 2048;
-  unsigned char* in_tile = P.in_pk + (size_t)tile * (64 / 8) * 2048;
+  {
+    unsigned char* lat_tile = P.lat_pk + (size_t)tile * (512 / 8) * 2048 + (size_t)(rr + lane) * 16;
+    unsigned char* in_tile = P.in_pk + (size_t)tile * (64 / 8) * 2048 + (size_t)(rr + lane) * 16;
 #pragma unroll 4
-  for (int it = 0; it < 16; ++it) {
-    const int c = it * 4 + (lane >> 3), i = lane & 7;
-    const uint4 v = *reinterpret_cast<const uint4*>(sl + c * kLatChunkStride + i * 16);
-    *reinterpret_cast<uint4*>(lat_tile + (size_t)c * 2048 + (size_t)(rr + i) * 16) = v;
-  }
+    for (int it = 0; it < 16; ++it) {
+      const int c = it * 4 + warp;
+      *reinterpret_cast<uint4*>(lat_tile + (size_t)c * 2048) = *reinterpret_cast<const uint4*>(sl + c * kLatChunkStride + lane * 16);
+    }
 #pragma unroll
-  for (int it = 0; it < 2; ++it) {
-    const int c = it * 4 + (lane >> 3), i = lane & 7;
-    const uint4 v = *reinterpret_cast<const uint4*>(si + c * 128 + i * 16);
-    *reinterpret_cast<uint4*>(in_tile + (size_t)c * 2048 + (size_t)(rr + i) * 16) = v;
+    for (int it = 0; it < 2; ++it) {
+      const int c = it * 4 + warp;
+      *reinterpret_cast<uint4*>(in_tile + (size_t)c * 2048) = *reinterpret_cast<const uint4*>(si + c * kLatChunkStride + lane * 16);
+    }
+  }
+  if (SPLIT) {
+    unsigned char* lat_tile = lat_pk_lo + (size_t)tile * (512 / 8) * 2048 + (size_t)(rr + lane) * 16;
+    unsigned char* in_tile = in_pk_lo + (size_t)tile * (64 / 8) * 2048 + (size_t)(rr + lane) * 16;
+    for (int it = 0; it < 16; ++it) {
+      const int c = it * 4 + warp;
+      *reinterpret_cast<uint4*>(lat_tile + (size_t)c * 2048) = *reinterpret_cast<const uint4*>(sl_lo + c * kLatChunkStride + lane * 16);
+    }
+    for (int it = 0; it < 2; ++it) {
+      const int c = it * 4 + warp;
+      *reinterpret_cast<uint4*>(in_tile + (size_t)c * 2048) = *reinterpret_cast<const uint4*>(si_lo + c * kLatChunkStride + lane * 16);
+    }
   }
 }
 
@@ -392,6 +456,24 @@ DNR_EXPORT int dnr_view_row_tiles(long long n_samples, int NV) {
   return dnr::RowMap::make(NV).tiles_for(n_samples);
 }
 
+static int launch_encode_fwd(dnr::EncodeParams& P, int NV, const void* latent_lo, void* lat_pk_lo, void* in_pk_lo,
+                             cudaStream_t stream) {
+  if (P.n_samples <= 0) return 0;
+  const bool split = latent_lo != nullptr;
+  const int tiles = dnr::RowMap::make(NV).tiles_for(P.n_samples);
+  const int slabs = tiles * 4;
+  const int smem = (dnr::kEncLatBytes + dnr::kEncInBytes) * (split ? 2 : 1) + 32 * (int)sizeof(dnr::RowTaps);
+  if (split) {
+    DNR_CHECK(cudaFuncSetAttribute(dnr::encode_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
+              "dnr_encode_fwd_split/attr");
+    dnr::encode_fwd_kernel<true><<<slabs, dnr::kEncWarps * 32, smem, stream>>>(
+        P, (const __nv_bfloat16*)latent_lo, (unsigned char*)lat_pk_lo, (unsigned char*)in_pk_lo);
+  } else {
+    dnr::encode_fwd_kernel<false><<<slabs, dnr::kEncWarps * 32, smem, stream>>>(P, nullptr, nullptr, nullptr);
+  }
+  return 0;
+}
+
 // Replaces PixelNeRF.forward's projection / gather / encoding (pixelnerf.py:91-128).
 DNR_EXPORT int dnr_encode_fwd(const float* rays, const float* z, const float* poses, const float* focal,
                               const float* cxy, const float* depth, const void* latent_nhwc_bf16, const float* freqs,
@@ -405,12 +487,32 @@ DNR_EXPORT int dnr_encode_fwd(const float* rays, const float* z, const float* po
   if (rc) return rc;
   DNR_REQUIRE((unsigned long long)SB * NV * Hl * Wl * L < (1ull << 32),
               "dnr_encode_fwd: the latent holds 2^32 elements or more (tap offsets are 32-bit); render fewer scenes per call");
+  DNR_REQUIRE(latent_nhwc_bf16 && lat_pk && in_pk, "dnr_encode_fwd: null argument");
   P.lat_pk = (unsigned char*)lat_pk; P.in_pk = (unsigned char*)in_pk;
-  if (P.n_samples <= 0) return 0;
-  const int tiles = dnr::RowMap::make(NV).tiles_for(P.n_samples);
-  const int groups = tiles * 16;
-  dnr::encode_fwd_kernel<<<groups / dnr::kEncWarps, dnr::kEncWarps * 32, 0, stream>>>(P);
+  rc = launch_encode_fwd(P, NV, nullptr, nullptr, nullptr, stream);
+  if (rc) return rc;
   DNR_CHECK_LAUNCH("dnr_encode_fwd");
+  return 0;
+}
+
+// Verification-mode variant (NeRFRendererDGS(precision="split")): the latent and both outputs are bf16 hi + lo pairs
+// (x ~ hi + lo to 2^-17 relative), otherwise identical to dnr_encode_fwd.
+DNR_EXPORT int dnr_encode_fwd_split(const float* rays, const float* z, const float* poses, const float* focal,
+                                    const float* cxy, const float* depth, const void* latent_hi, const void* latent_lo,
+                                    const float* freqs, const float* phases, int SB, int NV, int NR, int K, int H, int W,
+                                    int Hl, int Wl, int L, int NF, long long ray_offset, long long n_rays, float img_w,
+                                    float img_h, float lat_sx, float lat_sy, void* lat_pk_hi, void* in_pk_hi,
+                                    void* lat_pk_lo, void* in_pk_lo, cudaStream_t stream) {
+  dnr::EncodeParams P;
+  int rc = fill_encode_params(P, rays, z, poses, focal, cxy, depth, latent_hi, freqs, phases, SB, NV, NR, K, H,
+                              W, Hl, Wl, L, NF, ray_offset, n_rays, img_w, img_h, lat_sx, lat_sy);
+  if (rc) return rc;
+  DNR_REQUIRE((unsigned long long)SB * NV * Hl * Wl * L < (1ull << 32), "dnr_encode_fwd_split: latent too large");
+  DNR_REQUIRE(latent_hi && latent_lo && lat_pk_hi && in_pk_hi && lat_pk_lo && in_pk_lo, "dnr_encode_fwd_split: null argument");
+  P.lat_pk = (unsigned char*)lat_pk_hi; P.in_pk = (unsigned char*)in_pk_hi;
+  rc = launch_encode_fwd(P, NV, latent_lo, lat_pk_lo, in_pk_lo, stream);
+  if (rc) return rc;
+  DNR_CHECK_LAUNCH("dnr_encode_fwd_split");
   return 0;
 }
 

@@ -36,6 +36,7 @@ struct GemmParams {
   const float* res_in;      // XR [rows x N] fp32 added to the result, or null
   float* res_out;           // XR [rows x N] fp32, or null
   unsigned char* act_out;   // PK<128> [rows x N] bf16, or null
+  unsigned char* act_lo_out;  // verification mode: PK<128> bf16 image of (v - bf16(v)) beside act_out, or null
   int relu_act;             // act_out = relu(v) instead of v
   // view mean-pool (combine layer): outputs are indexed by sample instead of by (sample, view) row
   int mean_nv;              // 0 = off, else NV
@@ -149,7 +150,8 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& P, int m_tile, 
     for (int c = 0; c < 8; ++c) op[(size_t)c * 128] = make_float4(v[c * 4], v[c * 4 + 1], v[c * 4 + 2], v[c * 4 + 3]);
   }
   if (P.act_out) {
-    unsigned char* ap = P.act_out + ((size_t)((size_t)ot * (N / 8) + n0 / 8) * 128 + orow) * 16;
+    const size_t aoff = ((size_t)((size_t)ot * (N / 8) + n0 / 8) * 128 + orow) * 16;
+    unsigned char* ap = P.act_out + aoff;
     const bool relu = P.relu_act != 0;
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
@@ -159,8 +161,13 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& P, int m_tile, 
         float a = v[c * 8 + q * 2], b = v[c * 8 + q * 2 + 1];
         if (relu) { a = fmaxf(a, 0.f); b = fmaxf(b, 0.f); }
         w[q] = pack_bf16x2(a, b);
+        v[c * 8 + q * 2] = a - bf16lo(w[q]); v[c * 8 + q * 2 + 1] = b - bf16hi(w[q]);      // residue (read below only)
       }
       *reinterpret_cast<uint4*>(ap + (size_t)c * 2048) = make_uint4(w[0], w[1], w[2], w[3]);
+      if (P.act_lo_out)
+        *reinterpret_cast<uint4*>(P.act_lo_out + aoff + (size_t)c * 2048) =
+            make_uint4(pack_bf16x2(v[c * 8], v[c * 8 + 1]), pack_bf16x2(v[c * 8 + 2], v[c * 8 + 3]),
+                       pack_bf16x2(v[c * 8 + 4], v[c * 8 + 5]), pack_bf16x2(v[c * 8 + 6], v[c * 8 + 7]));
     }
   }
 }
@@ -283,8 +290,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) mlp_gemm_kernel(const GemmPar
 // One fused linear layer of the field MLP (forward or dgrad), see GemmParams.
 DNR_EXPORT int dnr_mlp_gemm(const void* A0, const void* B0, int K0, const void* A1, const void* B1, int K1,
                             const void* A2, const void* B2, int K2, int m_tiles, int N, const float* bias,
-                            const void* mask_pk, const float* res_in, float* res_out, void* act_out, int relu_act,
-                            int mean_nv, long long n_samples, int max_ctas, cudaStream_t stream) {
+                            const void* mask_pk, const float* res_in, float* res_out, void* act_out, void* act_lo_out,
+                            int relu_act, int mean_nv, long long n_samples, int max_ctas, cudaStream_t stream) {
   DNR_REQUIRE(N > 0 && N % dnr::kBN == 0, "dnr_mlp_gemm: N must be a multiple of 256");
   DNR_REQUIRE(A0 && B0 && K0 > 0 && K0 % dnr::kBK == 0, "dnr_mlp_gemm: segment 0 invalid (K multiple of 64)");
   DNR_REQUIRE(K1 % dnr::kBK == 0 && K2 % dnr::kBK == 0, "dnr_mlp_gemm: K must be a multiple of 64");
@@ -298,19 +305,18 @@ DNR_EXPORT int dnr_mlp_gemm(const void* A0, const void* B0, int K0, const void* 
   P.nseg = 1 + (A1 != nullptr && K1 > 0 ? 1 : 0);
   if (P.nseg == 2 && A2 != nullptr && K2 > 0) P.nseg = 3;
   P.m_tiles = m_tiles; P.N = N; P.bias = bias; P.mask_pk = (const unsigned char*)mask_pk; P.res_in = res_in;
-  P.res_out = res_out; P.act_out = (unsigned char*)act_out; P.relu_act = relu_act;
+  P.res_out = res_out; P.act_out = (unsigned char*)act_out; P.act_lo_out = (unsigned char*)act_lo_out; P.relu_act = relu_act;
+  DNR_REQUIRE(act_lo_out == nullptr || act_out != nullptr, "dnr_mlp_gemm: act_lo_out needs act_out");
   P.mean_nv = mean_nv > 0 ? mean_nv : 0; P.res_in_nv = mean_nv < 0 ? -mean_nv : 0;
   P.n_samples = n_samples;
-  static bool configured = false;
-  static int num_sms = 148;
-  if (!configured) {
+  dnr::DeviceInfo* di = dnr::device_info();
+  DNR_REQUIRE(di != nullptr, "dnr_mlp_gemm: no current CUDA device");
+  if (!di->gemm_configured) {          // function attributes are per device
     DNR_CHECK(cudaFuncSetAttribute(dnr::mlp_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)dnr::kGemmSmem), "dnr_mlp_gemm/attr");
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    configured = true;
+    di->gemm_configured = true;
   }
+  const int num_sms = di->num_sms;
   int grid = m_tiles * (N / dnr::kBN);
   int cap = (max_ctas > 0 && max_ctas < num_sms) ? max_ctas : num_sms;
   if (grid > cap) grid = cap;

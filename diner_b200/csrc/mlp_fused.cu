@@ -358,16 +358,14 @@ DNR_EXPORT int dnr_mlp_fused_fwd(const void* lat_pk, const void* code_pk, const 
   for (int i = 0; i < 5; ++i) { P.b_0[i] = biases[1 + i]; P.b_1[i] = biases[6 + i]; }
   P.scratch = (unsigned char*)scratch; P.xa_out = (unsigned char*)xa_out;
   P.NV = NV; P.SPW = 32 / NV; P.mv_tiles = mv_tiles; P.n_groups = (mv_tiles + NV - 1) / NV; P.n_samples = n_samples;
-  static bool configured = false;
-  static int num_sms = 148;
-  if (!configured) {
+  dnr::DeviceInfo* di = dnr::device_info();
+  DNR_REQUIRE(di != nullptr, "dnr_mlp_fused_fwd: no current CUDA device");
+  if (!di->fused_configured) {
     DNR_CHECK(cudaFuncSetAttribute(dnr::mlp_fused_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)dnr::kFSmem), "dnr_mlp_fused_fwd/attr");
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    configured = true;
+    di->fused_configured = true;
   }
+  const int num_sms = di->num_sms;
   int grid = P.n_groups;
   int cap = num_sms < 148 ? num_sms : 148;
   if (max_ctas > 0 && max_ctas < cap) cap = max_ctas;

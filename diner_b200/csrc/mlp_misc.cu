@@ -29,6 +29,7 @@ constexpr int kHid = 512;
 
 // out[s, 0:3] = sigmoid(lin_out(xa)[0:3]),  out[s, 3] = relu(lin_out(xa)[3]); xa = relu(x) is PK<128> bf16.
 __global__ void __launch_bounds__(128) head_fwd_kernel(const unsigned char* __restrict__ xa_pk,
+                                                       const unsigned char* __restrict__ xa_lo_pk,   // or null
                                                        const float* __restrict__ Wout,  // [4,512]
                                                        const float* __restrict__ bout,  // [4]
                                                        long long n_samples, int samples_per_tile,
@@ -46,9 +47,12 @@ __global__ void __launch_bounds__(128) head_fwd_kernel(const unsigned char* __re
   for (int c = 0; c < kHid / 8; ++c) {
     const uint4 p = __ldg(reinterpret_cast<const uint4*>(base + (size_t)c * 2048));
     const uint32_t pv[4] = {p.x, p.y, p.z, p.w};
+    uint4 pl = make_uint4(0u, 0u, 0u, 0u);
+    if (xa_lo_pk) pl = __ldg(reinterpret_cast<const uint4*>(xa_lo_pk + (base - xa_pk) + (size_t)c * 2048));
+    const uint32_t plv[4] = {pl.x, pl.y, pl.z, pl.w};
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-      const float x0 = bf16lo(pv[q]), x1 = bf16hi(pv[q]);
+      const float x0 = bf16lo(pv[q]) + bf16lo(plv[q]), x1 = bf16hi(pv[q]) + bf16hi(plv[q]);     // (+ 0 without a lo image)
       const int k = c * 8 + q * 2;
       a0 = fmaf(x0, sw[k], a0); a0 = fmaf(x1, sw[k + 1], a0);
       a1 = fmaf(x0, sw[kHid + k], a1); a1 = fmaf(x1, sw[kHid + k + 1], a1);
@@ -187,12 +191,13 @@ DNR_EXPORT int dnr_pack_weight(const float* W, int rows_w, int cols_w, int ld, i
 }
 
 // lin_out + sigmoid/relu (resnetfc.py:158, pixelnerf.py:137-145).
-DNR_EXPORT int dnr_head_fwd(const void* xa_pk, const float* Wout, const float* bout, long long n_samples,
-                            int samples_per_tile, float* rgbsigma, cudaStream_t stream) {
+DNR_EXPORT int dnr_head_fwd(const void* xa_pk, const void* xa_lo_pk, const float* Wout, const float* bout,
+                            long long n_samples, int samples_per_tile, float* rgbsigma, cudaStream_t stream) {
   DNR_REQUIRE(samples_per_tile >= 1 && samples_per_tile <= 128, "dnr_head_fwd: samples_per_tile must be in [1,128]");
   if (n_samples <= 0) return 0;
   const int tiles = (int)((n_samples + samples_per_tile - 1) / samples_per_tile);
-  dnr::head_fwd_kernel<<<tiles, 128, 0, stream>>>((const unsigned char*)xa_pk, Wout, bout, n_samples, samples_per_tile,
+  dnr::head_fwd_kernel<<<tiles, 128, 0, stream>>>((const unsigned char*)xa_pk, (const unsigned char*)xa_lo_pk, Wout, bout,
+                                                  n_samples, samples_per_tile,
                                                   (float4*)rgbsigma);
   DNR_CHECK_LAUNCH("dnr_head_fwd");
   return 0;

@@ -886,13 +886,15 @@ DNR_EXPORT int dnr_mlp_pair_fwd(const void* lat_pk, const void* code_pk, const v
   void (*kern)(const dnr::PairParams) = NV == 1 ? dnr::mlp_pair_fwd_kernel<1>
                                          : NV == 2 ? dnr::mlp_pair_fwd_kernel<2>
                                          : NV == 3 ? dnr::mlp_pair_fwd_kernel<3> : dnr::mlp_pair_fwd_kernel<4>;
-  static bool configured[5] = {false, false, false, false, false};
-  if (!configured[NV]) {
+  dnr::DeviceInfo* di = dnr::device_info();
+  DNR_REQUIRE(di != nullptr, "dnr_mlp_pair_fwd: no current CUDA device");
+  if (!di->pair_configured[NV]) {
     DNR_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dnr::kPSmem),
               "dnr_mlp_pair_fwd/attr");
-    configured[NV] = true;
+    di->pair_configured[NV] = true;
   }
-  const int cap = max_clusters > 0 && max_clusters < 74 ? max_clusters : 74;
+  const int all_pairs = di->num_sms / 2;
+  const int cap = max_clusters > 0 && max_clusters < all_pairs ? max_clusters : all_pairs;
   int clusters = mv_tiles < cap ? mv_tiles : cap;
   kern<<<2 * clusters, dnr::kPThreads, dnr::kPSmem, stream>>>(P);
   DNR_CHECK_LAUNCH("dnr_mlp_pair_fwd");
@@ -907,9 +909,12 @@ static QuadKernel quad_kernel(int NV, bool merge) {
   return NV == 1 ? mlp_quad_fwd_kernel<1, false> : NV == 2 ? mlp_quad_fwd_kernel<2, false>
          : NV == 3 ? mlp_quad_fwd_kernel<3, false> : mlp_quad_fwd_kernel<4, false>;
 }
+constexpr int kQuadMaxClusters = 37;      // merge scratch: 4 * 37 CTAs x 128 KB (dnr_mlp_quad_scratch_bytes)
 static int quad_max_clusters(int NV) {
-  static int cached[5] = {0, 0, 0, 0, 0};
   if (NV < 1 || NV > 4) return -1;
+  DeviceInfo* di = device_info();
+  if (!di) return -1;
+  int* cached = di->quad_clusters;
   if (cached[NV]) return cached[NV];
   QuadKernel kern = quad_kernel(NV, false);
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kQSmem) != cudaSuccess) return -1;
@@ -917,13 +922,14 @@ static int quad_max_clusters(int NV) {
                     cudaSuccess)
     return -1;
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(4 * 37, 1, 1); cfg.blockDim = dim3(kPThreads, 1, 1); cfg.dynamicSmemBytes = kQSmem;
+  cfg.gridDim = dim3(4 * kQuadMaxClusters, 1, 1); cfg.blockDim = dim3(kPThreads, 1, 1); cfg.dynamicSmemBytes = kQSmem;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 4; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
   int n = 0;
   if (cudaOccupancyMaxActiveClusters(&n, (const void*)kern, &cfg) != cudaSuccess) return -1;
+  if (n > kQuadMaxClusters) n = kQuadMaxClusters;       // the parking scratch is sized for 4 * 37 CTAs
   cached[NV] = n;
   return n;
 }
@@ -934,7 +940,7 @@ static int quad_max_clusters(int NV) {
 DNR_EXPORT int dnr_mlp_quad_max_clusters(int NV) { return dnr::quad_max_clusters(NV); }
 
 // Bytes of the scratch that enables the quad kernel's merge of pooled rows (see MERGE above).
-DNR_EXPORT long long dnr_mlp_quad_scratch_bytes(void) { return 148LL * 128 * 256 * 4; }
+DNR_EXPORT long long dnr_mlp_quad_scratch_bytes(void) { return 4LL * dnr::kQuadMaxClusters * 128 * 256 * 4; }
 
 // The quad variant (clusters of 4 CTAs, tcgen05 cta_group::2; see above).  weights: the same 14 matrices as
 // dnr_mlp_pair_fwd but in the PK128 layout [N/128][K/8][128][8]; head_partial: [mv_tiles*4*128] float4

@@ -373,11 +373,12 @@ DNR_EXPORT int dnr_sampler_fwd(const float* rays, const float* poses, const floa
   P.count_only = count_only; P.unpacked = unpacked_noise; P.z_out = z_out; P.ray_mask_out = ray_mask_out; P.n_missing_out = n_missing_out;
   P.sel_idx_out = sel_idx_out; P.p_out = p_out;
   const size_t smem = dnr::sampler_smem_bytes(C, K);
-  static size_t configured = 0;
-  if (smem > configured) {
+  dnr::DeviceInfo* di = dnr::device_info();
+  DNR_REQUIRE(di != nullptr, "dnr_sampler_fwd: no current CUDA device");
+  if (smem > di->sampler_smem) {
     DNR_CHECK(cudaFuncSetAttribute(dnr::sampler_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
               "dnr_sampler_fwd/attr");
-    configured = smem;
+    di->sampler_smem = smem;
   }
   const int blocks = (int)((n_rays + dnr::kSamplerWarps - 1) / dnr::kSamplerWarps);
   dnr::sampler_kernel<<<blocks, dnr::kSamplerWarps * 32, smem, stream>>>(P);

@@ -286,8 +286,9 @@ DNR_EXPORT int dnr_mlp_wgrad(const void* dY_pk, int Fy, const void* X_pk, int Fx
   P.NB = Fx < 256 ? Fx : 256;
   P.copy_piece = P.NB * 256;
   P.row_tiles = row_tiles; P.dW = dW; P.ldw = ldw; P.n_valid = n_valid; P.k_valid = k_valid; P.db = db;
-  static int num_sms = 0;
-  if (!num_sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev); }
+  dnr::DeviceInfo* di = dnr::device_info();
+  DNR_REQUIRE(di != nullptr, "dnr_mlp_wgrad: no current CUDA device");
+  const int num_sms = di->num_sms;
   if (Fy % 256 == 0 && Fx % 256 == 0) {
     // CTA pairs sharing the X operand (cta_group::2)
     const int out_pairs = (Fy / 256) * (Fx / 256);
@@ -296,11 +297,10 @@ DNR_EXPORT int dnr_mlp_wgrad(const void* dY_pk, int Fy, const void* X_pk, int Fx
     if (splits > row_tiles) splits = row_tiles;
     P.splits = splits;
     const size_t smem2 = (size_t)dnr::kW2Stages * 2 * dnr::kW2Op + 4096 + 256;
-    static bool configured2 = false;
-    if (!configured2) {
+    if (!di->wgrad2_configured) {
       DNR_CHECK(cudaFuncSetAttribute(dnr::mlp_wgrad2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2),
                 "dnr_mlp_wgrad/attr2");
-      configured2 = true;
+      di->wgrad2_configured = true;
     }
     dnr::mlp_wgrad2_kernel<<<out_pairs * splits * 2, dnr::kWgThreads, smem2, stream>>>(P);
     DNR_CHECK_LAUNCH("dnr_mlp_wgrad");
@@ -312,11 +312,10 @@ DNR_EXPORT int dnr_mlp_wgrad(const void* dY_pk, int Fy, const void* X_pk, int Fx
   if (splits > row_tiles) splits = row_tiles;
   P.splits = splits;
   const size_t smem = (size_t)dnr::kWgStages * (dnr::kWgAStage + (size_t)P.NB * 256) + 4096 + 256;
-  static size_t configured = 0;
-  if (smem > configured) {
+  if (smem > di->wgrad_smem) {
     DNR_CHECK(cudaFuncSetAttribute(dnr::mlp_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
               "dnr_mlp_wgrad/attr");
-    configured = smem;
+    di->wgrad_smem = smem;
   }
   dnr::mlp_wgrad_kernel<<<out_tiles * splits, dnr::kWgThreads, smem, stream>>>(P);
   DNR_CHECK_LAUNCH("dnr_mlp_wgrad");

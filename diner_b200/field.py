@@ -44,6 +44,7 @@ ADAPT_SPLIT = True
 _split_state = {}            # (device, NV) -> dict(rate=float, pending=[(e_q0, e_q1, e_p0, e_p1, tiles_q, tiles_p)])
 MERGE_POOLED = True          # quad kernel: run blocks 3-4 + head once per NV tiles on merged pooled rows (NV > 1)
 _side_stream = {}
+LAST_SPLIT = {}              # bench instrumentation: tiles of the most recent inference MLP launch (main / side kernel)
 
 
 def _mlp_signature(mlp):
@@ -53,10 +54,11 @@ def _mlp_signature(mlp):
 class PackedMLP:
     """bf16 tensor-core images of the ResnetFC weights (W for forward, W^T for dgrad) + fp32 biases."""
 
-    def __init__(self, mlp, need_transposed: bool):
+    def __init__(self, mlp, need_transposed: bool, split: bool = False):
         dev = mlp.lin_out.weight.device
         self.sig = _mlp_signature(mlp)
         self.has_t = need_transposed
+        self.has_split = split
         st = _lib.stream_ptr()
 
         def pack(w, transpose=False):
@@ -105,19 +107,35 @@ class PackedMLP:
             self.wt_z = [pack(l.weight, True) for l in mlp.lin_z]
             self.wt_0 = [pack(b.fc_0.weight, True) for b in mlp.blocks]
             self.wt_1 = [pack(b.fc_1.weight, True) for b in mlp.blocks]
+        if split:
+            # verification mode: the rounding residue W - bf16(W) as a second bf16 image of every forward weight
+            lo = lambda w: pack(w.detach().float() - w.detach().float().bfloat16().float())
+            self.lo_in = lo(mlp.lin_in.weight)
+            self.lo_z = [lo(l.weight) for l in mlp.lin_z]
+            self.lo_0 = [lo(b.fc_0.weight) for b in mlp.blocks]
+            self.lo_1 = [lo(b.fc_1.weight) for b in mlp.blocks]
 
 
 _packed_cache: dict = {}
 
 
-def get_packed(mlp, need_transposed: bool) -> PackedMLP:
+def get_packed(mlp, need_transposed: bool, split: bool = False) -> PackedMLP:
+    """Packed weights of `mlp`, cached on the parameters' (data_ptr, _version).  Writers that bypass the version counter
+    (`p.data.copy_`, c10d broadcasts, fused optimizers working on .data) must call `invalidate_caches()`."""
     hit = _packed_cache.get(id(mlp))
-    if hit is not None and hit.sig == _mlp_signature(mlp) and (hit.has_t or not need_transposed):
+    if (hit is not None and hit.sig == _mlp_signature(mlp) and (hit.has_t or not need_transposed)
+            and (hit.has_split or not split)):
         return hit
-    pk = PackedMLP(mlp, need_transposed)
+    pk = PackedMLP(mlp, need_transposed or (hit is not None and hit.sig == _mlp_signature(mlp) and hit.has_t),
+                   split or (hit is not None and hit.sig == _mlp_signature(mlp) and hit.has_split))
     _packed_cache.clear()
     _packed_cache[id(mlp)] = pk
     return pk
+
+
+def invalidate_caches() -> None:
+    """Forget the packed weights (and, via scene.invalidate, the per-scene repacks)."""
+    _packed_cache.clear()
 
 
 _scratch: dict = {}
@@ -158,10 +176,17 @@ def _fused_scratch(dev) -> torch.Tensor:
 
 
 def _gemm(A0, B0, K0, m_tiles, N=HID, A1=None, B1=None, K1=0, A2=None, B2=None, K2=0, bias=None, mask=None,
-          res_in=None, res_out=None, act_out=None, relu=0, mean_nv=0, n_samples=0, max_ctas=0):
+          res_in=None, res_out=None, act_out=None, relu=0, mean_nv=0, n_samples=0, max_ctas=0, act_lo=None):
     p = _lib.ptr
     _lib.call("dnr_mlp_gemm", p(A0), p(B0), K0, p(A1), p(B1), K1, p(A2), p(B2), K2, m_tiles, N, p(bias), p(mask),
-              p(res_in), p(res_out), p(act_out), relu, mean_nv, n_samples, max_ctas, _lib.stream_ptr())
+              p(res_in), p(res_out), p(act_out), p(act_lo), relu, mean_nv, n_samples, max_ctas, _lib.stream_ptr())
+
+
+def _gemm3(A, W, K, m_tiles, **kw):
+    """Verification mode: A = (hi, lo), W = (hi, lo) bf16 pairs; A W^T ~ hi hi^T + hi lo^T + lo hi^T as the three K
+    segments of ONE launch (the lo lo^T term is 2^-16 of the product and dropped)."""
+    (ah, al), (wh, wl) = A, W
+    _gemm(ah, wh, K, m_tiles, A1=ah, B1=wl, K1=K, A2=al, B2=wh, K2=K, **kw)
 
 
 @dataclass
@@ -183,11 +208,12 @@ def _encode_args(sc: SceneBuffers, NR: int, K: int, ray0: int, n_rays: int):
 
 
 def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.Tensor, NR: int, ray0: int,
-                  save: bool):
+                  save: bool, out: torch.Tensor = None, precision: str = "bf16"):
     """Evaluate the field on one chunk of rays.
 
     rays (n,8) / z (n,K) are the chunk's rows of the flattened (SB*NR) batch, `ray0` the index of its first
-    ray in that batch (the scene of a ray is ray // NR).  Returns (rgbsigma (n*K,4) fp32, FieldSaved | None).
+    ray in that batch (the scene of a ray is ray // NR).  Returns (rgbsigma (n*K,4) fp32, FieldSaved | None);
+    `out` (contiguous (n*K,4) fp32) receives the result in place when given.
     """
     p, st = _lib.ptr, _lib.stream_ptr()
     dev = rays.device
@@ -198,6 +224,11 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
     ms = (n_samples + 127) // 128
     bf = dict(device=dev, dtype=torch.bfloat16)
     f32 = dict(device=dev, dtype=torch.float32)
+    if out is None:
+        out = torch.empty(n_samples, 4, **f32)
+    assert out.is_contiguous() and out.shape == (n_samples, 4) and out.dtype == torch.float32
+    if precision == "split":
+        return _field_forward_split(sc, pk, rays, z, NR, ray0, save, out)
 
     lat = torch.empty(mv * 128 * HID, **bf)
     code = torch.empty(mv * 128 * IN_PAD, **bf)
@@ -206,7 +237,6 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
 
     if not save and FORWARD_KERNEL in ("quad", "pair") and NV <= 4:
         # inference: CTA-cluster kernels, residual stream in TMEM, lin_out fused (csrc/mlp_pair.cu)
-        out = torch.empty(n_samples, 4, **f32)
         per_tile = 4 * (32 // NV)                                # samples per 128-row view tile (RowMap)
         mv_q, spare = mv, 0
         if FORWARD_KERNEL == "quad":
@@ -222,6 +252,8 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
                 mv_q = max(0, mv - max(2, int(mv * share)) // 2 * 2)
         else:
             mv_q = 0
+        LAST_SPLIT.update(tiles_main=mv_q if mv_q > 0 else mv, tiles_side=mv - mv_q if mv_q > 0 else 0, tiles=mv,
+                          kernel=FORWARD_KERNEL)
         cur = torch.cuda.current_stream(dev)
         side = None
         if 0 < mv_q < mv:                                        # fork: the pair clusters run beside the quad clusters
@@ -264,8 +296,7 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
         xa = torch.empty(groups * 128 * HID, **bf)
         _lib.call("dnr_mlp_fused_fwd", p(lat), p(code), pk.w_ptrs, pk.b_ptrs, NV, mv, n_samples,
                   p(_fused_scratch(dev)), p(xa), 0, st)
-        out = torch.empty(n_samples, 4, **f32)
-        _lib.call("dnr_head_fwd", p(xa), p(pk.w_out), p(pk.b_out), n_samples, S, p(out), st)
+        _lib.call("dnr_head_fwd", p(xa), None, p(pk.w_out), p(pk.b_out), n_samples, S, p(out), st)
         return out, None
     sv = FieldSaved(n_samples=n_samples, mv=mv, ms=ms, lat=lat, code=code) if save else None
     x = torch.empty(mv * 128 * HID, **f32)                      # residual stream, XR layout (updated in place)
@@ -313,10 +344,75 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
         xa = xa_next
         if save and b == 3:
             net = new_act(ms)
-    out = torch.empty(n_samples, 4, **f32)
-    _lib.call("dnr_head_fwd", p(xa), p(pk.w_out), p(pk.b_out), n_samples, 128, p(out), st)
+    _lib.call("dnr_head_fwd", p(xa), None, p(pk.w_out), p(pk.b_out), n_samples, 128, p(out), st)
     if save:
         sv.xa.append(xa)
+        sv.out = out
+    return out, sv
+
+
+def _field_forward_split(sc: SceneBuffers, pk: PackedMLP, rays, z, NR: int, ray0: int, save: bool, out):
+    """Verification mode of field_forward (NeRFRendererDGS(precision="split")): the same kernels, operand layouts,
+    row maps and epilogues as the per-layer path, but every bf16 operand x is carried as a pair (hi = bf16(x),
+    lo = bf16(x - hi)) and every product as hi*hi + hi*lo + lo*hi -- 2^-16 relative per product instead of 2^-8, so the
+    result can be held to ~1e-4 against the fp32 reference and an indexing error cannot hide in the bf16 budget.
+    The backward pass (when `save`) runs on the hi images, i.e. it is the ordinary bf16 backward."""
+    p, st = _lib.ptr, _lib.stream_ptr()
+    dev = rays.device
+    n, K = z.shape
+    n_samples = n * K
+    NV = sc.NV
+    mv = _lib.load().dnr_view_row_tiles(n_samples, NV)
+    ms = (n_samples + 127) // 128
+    bf = dict(device=dev, dtype=torch.bfloat16)
+    f32 = dict(device=dev, dtype=torch.float32)
+    pair = lambda tiles, width=HID: (torch.empty(tiles * 128 * width, **bf), torch.empty(tiles * 128 * width, **bf))
+    lat, code = pair(mv), pair(mv, IN_PAD)
+    _lib.call("dnr_encode_fwd_split", p(rays), p(z), p(sc.poses), p(sc.focal), p(sc.cxy), p(sc.depth),
+              p(sc.latent_nhwc), p(sc.latent_lo()), p(sc.freqs), p(sc.phases), *_encode_args(sc, NR, K, ray0, n),
+              p(lat[0]), p(code[0]), p(lat[1]), p(code[1]), st)
+    sv = FieldSaved(n_samples=n_samples, mv=mv, ms=ms, lat=lat[0], code=code[0]) if save else None
+    x = torch.empty(mv * 128 * HID, **f32)
+    xa = pair(mv)
+    # x0 = lin_in(code) + lin_z[0](lat)
+    _gemm3(code, (pk.w_in, pk.lo_in), IN_PAD, mv, bias=pk.b_first, res_out=x)
+    _gemm3(lat, (pk.w_z[0], pk.lo_z[0]), HID, mv, res_in=x, res_out=x, act_out=xa[0], act_lo=xa[1], relu=1)
+    xm = xam = None
+    for b in range(3):
+        if save:
+            sv.xa.append(xa[0])
+        net = pair(mv)
+        _gemm3(xa, (pk.w_0[b], pk.lo_0[b]), HID, mv, bias=pk.b_0[b], act_out=net[0], act_lo=net[1], relu=1)
+        if save:
+            sv.net.append(net[0])
+        if b < 2:
+            xa = pair(mv)
+            _gemm3(net, (pk.w_1[b], pk.lo_1[b]), HID, mv, bias=pk.b_1[b], res_in=x, res_out=x)
+            _gemm3(lat, (pk.w_z[b + 1], pk.lo_z[b + 1]), HID, mv, res_in=x, res_out=x, act_out=xa[0], act_lo=xa[1],
+                   relu=1)
+        else:
+            xm = torch.empty(ms * 128 * HID, **f32)
+            xam = pair(ms)
+            xm[(ms - 1) * 128 * HID:].zero_()
+            xam[0][(ms - 1) * 128 * HID:].zero_()
+            xam[1][(ms - 1) * 128 * HID:].zero_()
+            _gemm3(net, (pk.w_1[b], pk.lo_1[b]), HID, mv, bias=pk.b_1[b], res_in=x, res_out=xm, act_out=xam[0],
+                   act_lo=xam[1], relu=1, mean_nv=NV, n_samples=n_samples)
+    del x
+    xa = xam
+    for b in (3, 4):
+        if save:
+            sv.xa.append(xa[0])
+        net = pair(ms)
+        _gemm3(xa, (pk.w_0[b], pk.lo_0[b]), HID, ms, bias=pk.b_0[b], act_out=net[0], act_lo=net[1], relu=1)
+        if save:
+            sv.net.append(net[0])
+        xa = pair(ms)
+        _gemm3(net, (pk.w_1[b], pk.lo_1[b]), HID, ms, bias=pk.b_1[b], res_in=xm, res_out=xm, act_out=xa[0],
+               act_lo=xa[1], relu=1)
+    _lib.call("dnr_head_fwd", p(xa[0]), p(xa[1]), p(pk.w_out), p(pk.b_out), n_samples, 128, p(out), st)
+    if save:
+        sv.xa.append(xa[0])
         sv.out = out
     return out, sv
 

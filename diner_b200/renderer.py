@@ -23,7 +23,13 @@ from .scene import DEPTH_DIFF_MAX, STD_PAD, SceneBuffers, get_scene, lin_table
 
 class RenderResult(dict):
     """Attribute-access dict (stands in for dotmap.DotMap, nerf_renderer.py:421-430)."""
-    __getattr__ = dict.__getitem__
+
+    def __getattr__(self, name):
+        try:
+            return self[name]
+        except KeyError:
+            raise AttributeError(name) from None       # hasattr / getattr-with-default / copy / pickle rely on this
+
     __setattr__ = dict.__setitem__
 
 
@@ -87,15 +93,23 @@ def sample_rays(sc: SceneBuffers, rays: torch.Tensor, K: int, C: int, G: int, no
 
 
 class _FieldFn(torch.autograd.Function):
-    """rgbsigma = field(rays, z); differentiable w.r.t. encoder.latent and the 30 MLP parameter tensors."""
+    """rgbsigma = field(rays, z) over all ray chunks of one forward call; differentiable w.r.t. encoder.latent and
+    the 30 MLP parameter tensors.  The chunks only tile the work: one flat parameter-gradient buffer and one feature
+    gradient map are zero-filled, accumulated into by every chunk and unpacked ONCE per backward call."""
 
     @staticmethod
-    def forward(ctx, sc, mlp, names, rays, z, NR, ray0, latent, *params):
-        need_grad = any(ctx.needs_input_grad[7:])
-        pk = F_.get_packed(mlp, need_transposed=need_grad)
-        out, saved = F_.field_forward(sc, pk, rays, z, NR, ray0, save=need_grad)
+    def forward(ctx, sc, mlp, names, rays, z, NR, chunks, precision, latent, *params):
+        need_grad = any(ctx.needs_input_grad[8:])
+        pk = F_.get_packed(mlp, need_transposed=need_grad, split=precision == "split")
+        out = torch.empty(z.shape[0] * z.shape[1], 4, device=z.device, dtype=torch.float32)
+        K = z.shape[1]
+        saved = []
+        for r0, r1 in chunks:
+            _, sv = F_.field_forward(sc, pk, rays[r0:r1], z[r0:r1], NR, r0, save=need_grad, out=out[r0 * K:r1 * K],
+                                     precision=precision)
+            saved.append(sv)
         ctx.sc, ctx.mlp, ctx.names, ctx.pk, ctx.saved = sc, mlp, names, pk, saved
-        ctx.rays, ctx.z, ctx.NR, ctx.ray0 = rays, z, NR, ray0
+        ctx.rays, ctx.z, ctx.NR, ctx.chunks = rays, z, NR, chunks
         ctx.latent_shape = latent.shape
         return out
 
@@ -103,27 +117,32 @@ class _FieldFn(torch.autograd.Function):
     def backward(ctx, d_out):
         sc, mlp = ctx.sc, ctx.mlp
         dev = d_out.device
-        params = dict(mlp.named_parameters())
-        # one zero fill for all parameter gradients (views into a flat buffer, 16-byte aligned starts)
-        offs, total = {}, 0
-        for n in ctx.names:
-            offs[n] = total
-            total += (params[n].numel() + 3) // 4 * 4
-        flat = torch.zeros(total, device=dev, dtype=torch.float32)
-        grads = {n: flat[offs[n]:offs[n] + params[n].numel()].view(params[n].shape) for n in ctx.names}
-        d_lat_nhwc = None
-        if ctx.needs_input_grad[7]:
-            d_lat_nhwc = torch.zeros(sc.SB, sc.NV, sc.Hl, sc.Wl, sc.L, device=dev, dtype=torch.float32)
-        F_.field_backward(sc, ctx.pk, mlp, ctx.saved, ctx.rays, ctx.z, ctx.NR, ctx.ray0, d_out, grads, d_lat_nhwc)
-        d_latent = None
-        if d_lat_nhwc is not None:
-            d_latent = torch.empty(ctx.latent_shape, device=dev, dtype=torch.float32)
-            _lib.call("dnr_unpack_dlatent_nchw", _lib.ptr(d_lat_nhwc), sc.SB * sc.NV, sc.L, sc.Hl, sc.Wl,
-                      _lib.ptr(d_latent), _lib.stream_ptr())
-        ctx.saved = None
-        pg = tuple(grads[n].to(params[n].dtype) if ctx.needs_input_grad[8 + i] else None
-                   for i, n in enumerate(ctx.names))
-        return (None, None, None, None, None, None, None, d_latent, *pg)
+        with torch.cuda.device(dev):
+            params = dict(mlp.named_parameters())
+            # one zero fill for all parameter gradients (views into a flat buffer, 16-byte aligned starts)
+            offs, total = {}, 0
+            for n in ctx.names:
+                offs[n] = total
+                total += (params[n].numel() + 3) // 4 * 4
+            flat = torch.zeros(total, device=dev, dtype=torch.float32)
+            grads = {n: flat[offs[n]:offs[n] + params[n].numel()].view(params[n].shape) for n in ctx.names}
+            d_lat_nhwc = None
+            if ctx.needs_input_grad[8]:
+                d_lat_nhwc = torch.zeros(sc.SB, sc.NV, sc.Hl, sc.Wl, sc.L, device=dev, dtype=torch.float32)
+            d_out = d_out.contiguous()
+            K = ctx.z.shape[1]
+            for (r0, r1), sv in zip(ctx.chunks, ctx.saved):
+                F_.field_backward(sc, ctx.pk, mlp, sv, ctx.rays[r0:r1], ctx.z[r0:r1], ctx.NR, r0,
+                                  d_out[r0 * K:r1 * K], grads, d_lat_nhwc)
+            d_latent = None
+            if d_lat_nhwc is not None:
+                d_latent = torch.empty(ctx.latent_shape, device=dev, dtype=torch.float32)
+                _lib.call("dnr_unpack_dlatent_nchw", _lib.ptr(d_lat_nhwc), sc.SB * sc.NV, sc.L, sc.Hl, sc.Wl,
+                          _lib.ptr(d_latent), _lib.stream_ptr())
+            ctx.saved = None
+            pg = tuple(grads[n].to(params[n].dtype) if ctx.needs_input_grad[9 + i] else None
+                       for i, n in enumerate(ctx.names))
+        return (None, None, None, None, None, None, None, None, d_latent, *pg)
 
 
 class _CompositeFn(torch.autograd.Function):
@@ -157,6 +176,19 @@ class _CompositeFn(torch.autograd.Function):
         return d, None, None, None
 
 
+def balanced_chunks(n_rays: int, per_chunk: int):
+    """[(r0, r1)] covering n_rays in ceil(n_rays / per_chunk) chunks whose sizes differ by at most one ray (no
+    degenerate tail chunk: 65 536 rays at 13 107 per chunk are 6 chunks of 10 922 / 10 923, not 5 + one ray)."""
+    n_chunks = max(1, -(-n_rays // max(1, per_chunk)))
+    base, extra = divmod(n_rays, n_chunks)
+    out, r0 = [], 0
+    for i in range(n_chunks):
+        r1 = r0 + base + (1 if i < extra else 0)
+        out.append((r0, r1))
+        r0 = r1
+    return out
+
+
 class NeRFRendererDGS(torch.nn.Module):
     """NeRF renderer with depth-guided sampling on hand-written sm_100a kernels (see module docstring).
 
@@ -166,17 +198,27 @@ class NeRFRendererDGS(torch.nn.Module):
     :param eval_batch_size: kept for signature compatibility (the reference chunks the MLP batch with it,
            nerf_renderer.py:325-333); chunking here is by `rows_per_chunk` rows of the per-view MLP batch
     :param white_bkgd: composite onto white (True) or black
+    :param rows_per_chunk: per-view MLP rows evaluated per kernel sequence; None = ROWS_INFERENCE without autograd
+           (1 152 B of packed operands per row), ROWS_TRAINING with (every layer's operands are kept for backward)
+    :param precision: "bf16" (default: bf16 x bf16 -> fp32 tensor-core MLP) | "split" (verification mode: every MLP
+           operand is carried as a bf16 hi + lo pair and every product as hi*hi + hi*lo + lo*hi on the same kernels,
+           layouts and epilogues -- ~2^-16 relative per product instead of 2^-8; about 3.5x slower)
     """
+    ROWS_INFERENCE = 1 << 22
+    ROWS_TRAINING = 1 << 20
 
     def __init__(self, n_samples=40, n_depth_candidates=1000, n_gaussian=15, eval_batch_size=100000, white_bkgd=True,
-                 rows_per_chunk=1 << 20):
+                 rows_per_chunk=None, precision="bf16"):
         super().__init__()
+        if precision not in ("bf16", "split"):
+            raise ValueError("precision must be 'bf16' or 'split'")
         self.n_samples = n_samples
         self.n_depth_candidates = n_depth_candidates
         self.n_gaussian = n_gaussian
         self.eval_batch_size = eval_batch_size
         self.white_bkgd = white_bkgd
         self.rows_per_chunk = rows_per_chunk
+        self.precision = precision
 
     def forward(self, model, rays, want_weights=False, noise=None, return_samples=False):
         """
@@ -192,6 +234,13 @@ class NeRFRendererDGS(torch.nn.Module):
             raise RuntimeError("diner_b200.NeRFRendererDGS needs CUDA tensors (no CPU path)")
         if rays.shape[-1] != 8:
             raise ValueError("rays must be (SB, B, 8)")
+        lat_dev = model.encoder.latent.device
+        if lat_dev != rays.device:
+            raise RuntimeError(f"diner_b200: rays live on {rays.device} but the encoded scene on {lat_dev}")
+        with torch.cuda.device(rays.device):     # every launch goes to the stream / context of the rays' device
+            return self._forward(model, rays, want_weights, noise, return_samples)
+
+    def _forward(self, model, rays, want_weights, noise, return_samples):
         SB, NR, _ = rays.shape
         sc = get_scene(model)
         if SB != sc.SB:
@@ -214,25 +263,27 @@ class NeRFRendererDGS(torch.nn.Module):
         mlp = model.mlp_fine
         names = [n for n, _ in mlp.named_parameters()]
         params = [q for _, q in mlp.named_parameters()]
+        if params[0].device != rays.device:
+            raise RuntimeError(f"diner_b200: rays live on {rays.device} but model.mlp_fine on {params[0].device}")
         latent = model.encoder.latent
         flat = rays.view(SB * NR, 8)
         n_rays = SB * NR
-        per_chunk = max(1, self.rows_per_chunk // (K * sc.NV))
         track = torch.is_grad_enabled() and (latent.requires_grad or any(q.requires_grad for q in params))
-        rgbs, depths, weights = [], [], []
-        for r0 in range(0, n_rays, per_chunk):
-            r1 = min(n_rays, r0 + per_chunk)
-            rc, zc = flat[r0:r1], z[r0:r1]
-            if track:
-                rgbsigma = _FieldFn.apply(sc, mlp, names, rc, zc, NR, r0, latent, *params)
-            else:       # inference: nothing is saved, the MLP runs as one persistent kernel
-                rgbsigma, _ = F_.field_forward(sc, F_.get_packed(mlp, need_transposed=False), rc, zc, NR, r0, save=False)
-            rgb, depth, w = _CompositeFn.apply(rgbsigma, zc, rc, self.white_bkgd)
-            rgbs.append(rgb); depths.append(depth); weights.append(w)
-        cat = (lambda xs: xs[0] if len(xs) == 1 else torch.cat(xs, 0))
-        out = RenderResult(rgb=cat(rgbs).view(SB, NR, 3), depth=cat(depths).view(SB, NR))
+        rows = self.rows_per_chunk or (self.ROWS_TRAINING if track or self.precision == "split" else self.ROWS_INFERENCE)
+        chunks = balanced_chunks(n_rays, max(1, rows // (K * sc.NV)))
+        if track:
+            rgbsigma = _FieldFn.apply(sc, mlp, names, flat, z, NR, chunks, self.precision, latent, *params)
+        else:           # inference: nothing is saved, the MLP runs as one persistent kernel per chunk
+            pk = F_.get_packed(mlp, need_transposed=False, split=self.precision == "split")
+            rgbsigma = torch.empty(n_rays * K, 4, device=rays.device, dtype=torch.float32)
+            for r0, r1 in chunks:
+                F_.field_forward(sc, pk, flat[r0:r1], z[r0:r1], NR, r0, save=False, out=rgbsigma[r0 * K:r1 * K],
+                                 precision=self.precision)
+        # one compositing launch per call (nerf_renderer.py:344-365), whatever the chunking of the field
+        rgb, depth, w = _CompositeFn.apply(rgbsigma, z, flat, self.white_bkgd)
+        out = RenderResult(rgb=rgb.view(SB, NR, 3), depth=depth.view(SB, NR))
         if want_weights:
-            out.weights = cat(weights).view(SB, NR, K)
+            out.weights = w.view(SB, NR, K)
         if return_samples:
             out.z = z.view(SB, NR, K)
         return RenderResult(fine=out)

@@ -16,6 +16,7 @@ The repack is cached on the tensors' identity and version counters, so it is red
 from __future__ import annotations
 
 import math
+import weakref
 from dataclasses import dataclass
 
 import numpy as np
@@ -58,6 +59,23 @@ class SceneBuffers:
     lat_sx: float
     lat_sy: float
     key: tuple
+    _latent_ref: object = None         # weak reference to encoder.latent (the cache must not keep the scene alive)
+    _latent_lo: torch.Tensor = None
+
+    def latent_lo(self) -> torch.Tensor:
+        """Verification mode (precision="split"): the bf16 image of latent - bf16(latent), channels-last; built on
+        first use."""
+        if self._latent_lo is None:
+            lat = self._latent_ref() if self._latent_ref is not None else None
+            if lat is None:
+                raise RuntimeError("diner_b200: encoder.latent was released; call encode() again")
+            lat32 = _f32c(lat).view(self.SB * self.NV, self.L, self.Hl, self.Wl)
+            res = (lat32 - lat32.to(torch.bfloat16).to(torch.float32)).contiguous()
+            out = torch.empty(self.SB, self.NV, self.Hl, self.Wl, self.L, device=lat32.device, dtype=torch.bfloat16)
+            _lib.call("dnr_pack_latent_nhwc", _lib.ptr(res), self.SB * self.NV, self.L, self.Hl, self.Wl, _lib.ptr(out),
+                      _lib.stream_ptr())
+            self._latent_lo = out
+        return self._latent_lo
 
 
 _lin_tabs: dict = {}
@@ -113,8 +131,18 @@ def _key(model):
     return tuple((t.data_ptr(), t._version, tuple(t.shape)) for t in ts)
 
 
+def invalidate() -> None:
+    """Forget the cached per-scene repacks AND the packed MLP weights.  The caches key on (data_ptr, _version, shape) of
+    the source tensors; writers that do not bump the version counter -- `t.data.copy_`, c10d broadcasts into existing
+    storage, external kernels, optimizers that step on `.data` -- leave stale repacks behind, so they must call this
+    (`diner_b200.sharding.broadcast_scene` does)."""
+    from . import field
+    _cache.clear()
+    field.invalidate_caches()
+
+
 def get_scene(model) -> SceneBuffers:
-    """Device buffers for the scene currently encoded in `model` (cached until the next encode())."""
+    """Device buffers for the scene currently encoded in `model` (cached until the next encode(); see invalidate())."""
     key = _key(model)
     ck = id(model)
     hit = _cache.get(ck)
@@ -161,7 +189,7 @@ def get_scene(model) -> SceneBuffers:
         img_w=float(image_shape[0]), img_h=float(image_shape[1]),
         std_sx=float(std_scale[0]), std_sy=float(std_scale[1]),
         lat_sx=float(lat_scale[0].float()), lat_sy=float(lat_scale[1].float()),
-        key=key)
+        key=key, _latent_ref=weakref.ref(lat))
     if sc.poses.shape != (SB, NV, 4, 4):
         raise ValueError(f"model.poses must be (SB,NV,4,4), got {tuple(sc.poses.shape)}")
     _cache.clear()

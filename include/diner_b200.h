@@ -82,6 +82,14 @@ int dnr_encode_fwd(const float* rays, const float* z, const float* poses, const 
                    int NV, int NR, int K, int H, int W, int Hl, int Wl, int L, int NF, long long ray_offset,
                    long long n_rays, float img_w, float img_h, float lat_sx, float lat_sy, void* lat_pk, void* in_pk,
                    dnr_stream_t stream);
+/* Verification-mode variant (NeRFRendererDGS(precision="split"), DESIGN.md "Precision contract"): the latent is a
+ * bf16 hi + lo pair (x ~ hi + lo to 2^-17 relative) and both operands leave as hi + lo pairs of PK128 images;
+ * otherwise identical to dnr_encode_fwd. */
+int dnr_encode_fwd_split(const float* rays, const float* z, const float* poses, const float* focal, const float* cxy,
+                         const float* depth, const void* latent_hi, const void* latent_lo, const float* freqs,
+                         const float* phases, int SB, int NV, int NR, int K, int H, int W, int Hl, int Wl, int L, int NF,
+                         long long ray_offset, long long n_rays, float img_w, float img_h, float lat_sx, float lat_sy,
+                         void* lat_pk_hi, void* in_pk_hi, void* lat_pk_lo, void* in_pk_lo, dnr_stream_t stream);
 /* Backward of SpatialEncoder.index w.r.t. the latent map (grid_sample bilinear backward,
  * image_encoder.py:117-123): d_latent_nhwc [SB,NV,Hl,Wl,512] fp32 += scatter(d_lat_xr XR[rows x 512]). */
 int dnr_encode_bwd(const float* rays, const float* z, const float* poses, const float* focal, const float* cxy,
@@ -100,13 +108,14 @@ int dnr_pack_weight(const float* W, int rows_w, int cols_w, int ld, int transpos
  *   D[rows x N] = sum_{seg<3} A_seg[rows x K_seg] * B_seg[N x K_seg]^T   (bf16 in, fp32 accumulate in TMEM)
  * epilogue: + bias[N]; * [mask_pk > 0] (ReLU backward); + res_in (XR); optional mean over the NV view rows of
  * each sample (combine(), resnetfc.py:9-14; outputs then indexed by sample); outputs res_out (XR fp32) and/or
- * act_out (PK128 bf16, relu_act=1 applies ReLU).  A: PK128, B: PK256, K multiple of 64, N multiple of 256.
+ * act_out (PK128 bf16, relu_act=1 applies ReLU; act_lo_out, nullable, receives the bf16 image of the rounding residue
+ * v - bf16(v) for the verification mode).  A: PK128, B: PK256, K multiple of 64, N multiple of 256.
  * max_ctas > 0 caps the persistent grid.  mean_nv < 0 is the backward of that mean: res_in is a POOLED stream indexed by
  * sample, and row (sample, view) receives res_in[sample] / |mean_nv| (n_samples bounds the valid rows). */
 int dnr_mlp_gemm(const void* A0, const void* B0, int K0, const void* A1, const void* B1, int K1, const void* A2,
                  const void* B2, int K2, int m_tiles, int N, const float* bias, const void* mask_pk,
-                 const float* res_in, float* res_out, void* act_out, int relu_act, int mean_nv, long long n_samples,
-                 int max_ctas, dnr_stream_t stream);
+                 const float* res_in, float* res_out, void* act_out, void* act_lo_out, int relu_act, int mean_nv,
+                 long long n_samples, int max_ctas, dnr_stream_t stream);
 
 /* Whole ResnetFC forward in ONE persistent kernel (inference): all 13 linear layers of resnetfc.py:129-159 with
  * the view mean (combine(), :9-14) fused, activations kept in an L2-resident per-CTA scratch instead of HBM.
@@ -157,9 +166,10 @@ int dnr_mlp_wgrad(const void* dY_pk, int Fy, const void* X_pk, int Fx, int row_t
 
 /* lin_out + activations: rgbsigma[s] = [sigmoid(o0..2), relu(o3)], o = lin_out(xa)
  * (resnetfc.py:158, src/models/pixelnerf.py:137-145); xa = relu(x) PK128[tiles*128 x 512], tile t holding samples
- * [t*samples_per_tile, (t+1)*samples_per_tile) in its first rows (128 for the per-layer path). */
-int dnr_head_fwd(const void* xa_pk, const float* Wout, const float* bout, long long n_samples, int samples_per_tile,
-                 float* rgbsigma, dnr_stream_t stream);
+ * [t*samples_per_tile, (t+1)*samples_per_tile) in its first rows (128 for the per-layer path); xa_lo_pk (nullable):
+ * the residue image of the verification mode, xa = hi + lo. */
+int dnr_head_fwd(const void* xa_pk, const void* xa_lo_pk, const float* Wout, const float* bout, long long n_samples,
+                 int samples_per_tile, float* rgbsigma, dnr_stream_t stream);
 /* Backward of the head: dx (XR fp32 + PK128 bf16) and d_raw as PK128[rows x 128] (columns 0..3) for wgrad. */
 int dnr_head_bwd(const void* xa_pk, const float* Wout, const float* rgbsigma, const float* d_rgbsigma,
                  long long n_samples, float* dx_xr, void* dx_pk, void* draw_pk, dnr_stream_t stream);

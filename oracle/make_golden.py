@@ -3,7 +3,7 @@
     python -m oracle.make_golden            # writes tests/golden/{tiny,tiny3,plumbing64}.npz
 
 For each case the synthetic scene is rebuilt deterministically from (workload, seed) by
-diner_b200.synthetic.make_scene, its tensors are injected into the reference's own PixelNeRF
+tools.synthetic.make_scene, its tensors are injected into the reference's own PixelNeRF
 (so the reference's index_* / forward / ResnetFC code runs on them), the reference
 NeRFRendererDGS.forward is run under torch's CPU backend with the three random draws recorded,
 and inputs-by-seed + noise + outputs (+ gradients) are stored.  Test infrastructure.
@@ -18,7 +18,7 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
-from diner_b200.synthetic import make_scene  # noqa: E402
+from tools.synthetic import make_scene  # noqa: E402
 from oracle import ref_shim  # noqa: E402
 
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")

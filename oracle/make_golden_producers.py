@@ -16,7 +16,7 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
-from diner_b200.synthetic import make_scene  # noqa: E402
+from tools.synthetic import make_scene  # noqa: E402
 from oracle import ref_shim  # noqa: E402
 
 OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "producers.npz")

@@ -18,7 +18,7 @@ def pytest_configure(config):
 
 def load_golden(name):
     """Golden vectors written by oracle/make_golden.py (outputs of the unmodified reference)."""
-    from diner_b200.synthetic import make_scene
+    from tools.synthetic import make_scene
     g = dict(np.load(os.path.join(GOLDEN_DIR, f"{name}.npz"), allow_pickle=False))
     scene = make_scene(str(g["workload"]), seed=int(g["seed"]))
     rays = scene.rays

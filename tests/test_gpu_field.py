@@ -120,8 +120,8 @@ def test_field_forward_and_backward(golden_cache, name):
         mlp = m.mlp_fine
         names = [n for n, _ in mlp.named_parameters()]
         params = [q for _, q in mlp.named_parameters()]
-        out = _FieldFn.apply(get_scene(m), mlp, names, rays_d.view(-1, 8), z_d.view(-1, K), NR, 0, m.encoder.latent,
-                             *params)
+        out = _FieldFn.apply(get_scene(m), mlp, names, rays_d.view(-1, 8), z_d.view(-1, K), NR, [(0, SB * NR)], "bf16",
+                             m.encoder.latent, *params)
         # --- checker: precision-contract oracle on torch CUDA ops, autograd for the gradients ---
         lat_ref = lat.clone().requires_grad_(True)
         cuda_latent = m.encoder.latent
@@ -257,7 +257,7 @@ def test_cluster_kernels_all_view_counts(NV, n_rays):
     import dataclasses
     from diner_b200 import field as F_
     from diner_b200.scene import get_scene
-    from diner_b200.synthetic import WORKLOADS, make_scene
+    from tools.synthetic import WORKLOADS, make_scene
     from oracle import bf16_field as B
     wl = dataclasses.replace(WORKLOADS["tiny"], name=f"tiny_nv{NV}", NV=NV, tgt_H=24, tgt_W=24)
     scene = make_scene(wl, seed=NV)

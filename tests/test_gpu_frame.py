@@ -21,7 +21,7 @@ def _cuda():
 
 @pytest.fixture(scope="module")
 def facescape():
-    from diner_b200.synthetic import make_scene
+    from tools.synthetic import make_scene
     dev = _cuda()
     scene = make_scene("facescape", seed=0)
     scene.model.to_device(dev)
@@ -111,7 +111,7 @@ def test_training_step_shape():
     """BASELINE config 4: SB=2 scenes, one 64x64 patch each, forward + backward through all four stages."""
     dev = _cuda()
     from diner_b200 import NeRFRendererDGS
-    from diner_b200.synthetic import make_scene
+    from tools.synthetic import make_scene
     scene = make_scene("facescape_train", seed=0)
     wl = scene.workload
     m = scene.model.to_device(dev)
@@ -143,7 +143,7 @@ def test_empty_and_tiny_ray_batches():
     python_scripts/create_prediction_folder.py:51-52 does) uses the new values."""
     dev = _cuda()
     from diner_b200 import NeRFRendererDGS
-    from diner_b200.synthetic import make_scene
+    from tools.synthetic import make_scene
     scene = make_scene("tiny", seed=0)
     wl = scene.workload
     m = scene.model.to_device(dev)
@@ -175,7 +175,7 @@ def test_full_frame_properties_other_shapes(workload, max_rays):
     dev = _cuda()
     from diner_b200 import NeRFRendererDGS, field as F_, sample_rays
     from diner_b200.scene import get_scene
-    from diner_b200.synthetic import make_scene
+    from tools.synthetic import make_scene
     scene = make_scene(workload, seed=0)
     m = scene.model.to_device(dev)
     try:

@@ -1,0 +1,301 @@
+"""Round-2 GPU parity tests (run with `-m gpu` on a B200), all through the C ABI:
+
+  * BASELINE.json configs 2 / 3 / 5 (DTU 300 x 400 NV = 3 black background, FaceScape, Multiface 1024 x 672 NV = 4):
+    256 strided rays of the full-size scene against the oracle -- sampler indices bit for bit against the oracle on
+    torch CUDA ops, >= 0.9 of the rays against the oracle on torch CPU ops, rgb / depth on the oracle's samples
+  * the CUDA backward against the UNMODIFIED reference's gradients in tests/golden/*.npz
+  * BASELINE config 4 (SB = 2 x 4 096 rays) forward + backward against the fp32 oracle on the whole batch
+  * exponential std padding with a live border against the reference golden; sampler on a scene whose foreground
+    runs over the image border
+  * the verification mode (precision="split"): rgb / depth within 1e-4 of the fp32 reference goldens
+Tolerances were chosen from tools/parity_probe.py on a B200 (profiles/r2_parity_probe.json) with ~2x margin.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import parity_metrics as PM
+
+pytestmark = pytest.mark.gpu
+
+
+def _cuda():
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    from diner_b200 import _lib
+    _lib.load()
+    return torch.device("cuda", 0)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# configs 2, 3, 5 at their real map sizes
+# ------------------------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("workload", ["facescape", "dtu", "multiface"])
+def test_strided_rays_against_oracle_at_config_shapes(workload):
+    dev = _cuda()
+    r = PM.config_shape_parity(workload, dev, n_rays=256)
+    assert 0.05 < r["frac_fg"] < 0.95 and r["p_nonzero"] > 1000, r          # the subset sees object and background
+    # north_star: sample indices, sort order and merge order bit-exact (against the backend the reference deploys on)
+    assert r["p_equal"], "per-candidate likelihoods differ from the oracle on torch CUDA ops"
+    assert r["idx_equal"], "shortlist indices / rank order differ from the oracle on torch CUDA ops"
+    assert r["mask_equal"], "ray masks / fill counts differ from the oracle on torch CUDA ops"
+    assert r["sorted"]
+    assert r["z_vs_cuda_oracle"]["max"] < 1e-5 * 2.5 + 1e-6, r["z_vs_cuda_oracle"]     # gaussian moments: reduction order only
+    assert r["rays_equal_cpu_oracle"] >= 0.9, r                              # rest: torch's own CPU-vs-CUDA rounding
+    # stated tolerance of the bf16 MLP on the oracle's own samples (mean + tail bound)
+    for k in ("rgb", "depth"):
+        assert r[k]["mean"] < 3e-3 and r[k]["q99"] < 3e-2, (k, r[k])
+    # verification mode: within 1e-4 (relative to the value range, rgb in [0,1], depth <= far) of the fp32 oracle
+    assert r["rgb_split"]["max"] < 1e-4 and r["depth_split"]["rel_max"] < 1e-4, (r["rgb_split"], r["depth_split"])
+
+
+# ------------------------------------------------------------------------------------------------------------
+# backward vs the reference's golden gradients
+# ------------------------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("name", ["tiny", "tiny3", "plumbing64"])
+@pytest.mark.parametrize("precision", ["bf16", "split"])
+def test_backward_against_reference_golden_gradients(golden_cache, name, precision):
+    """loss = sum(rgb * w_rgb) + sum(depth * w_dep) on the reference's own samples; the reference's gradients of that
+    loss are in the golden files.  The CUDA backward multiplies in bf16 (gradients are rounded to bf16 between layers),
+    so single entries carry ~1 % noise; a systematic error shows in the norm ratio and the cosine, which are tight."""
+    dev = _cuda()
+    g, scene, rays, _ = golden_cache(name)
+    r = PM.golden_gradient_metrics(scene, rays, g, dev, precision)
+    assert r["loss"] < (1e-4 if precision == "split" else 5e-3), r["loss"]
+    for k, v in r.items():
+        if k.startswith("full."):
+            assert v["rel_l2"] < 5e-2 and v["cos"] > 0.9985 and abs(v["ratio"] - 1) < 2e-2, (k, v)
+        elif k.startswith("norm."):
+            assert abs(v - 1) < 2e-2, (k, v)
+    assert r["glat.picked"]["rel_l2"] < 5e-2 and r["glat.picked"]["cos"] > 0.9985, r["glat.picked"]
+    assert abs(r["glat.norm"] - 1) < 2e-2 and abs(r["glat.sum"]) < 2e-2, (r["glat.norm"], r["glat.sum"])
+
+
+@pytest.mark.parametrize("precision", ["bf16"])
+def test_training_step_gradients_against_oracle(precision):
+    """BASELINE config 4: SB = 2 scenes x 4 096 rays (one 64 x 64 patch each), MSE loss, the whole batch."""
+    dev = _cuda()
+    r = PM.train_shape_gradient_metrics(dev, precision)
+    assert r["rgb"]["mean"] < 3e-3, r["rgb"]
+    assert r["latent_per_scene_nonzero"]
+    for k, v in r.items():
+        if isinstance(v, dict) and "cos" in v:
+            assert v["rel_l2"] < 6e-2 and v["cos"] > 0.998 and abs(v["ratio"] - 1) < 2e-2, (k, v)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# exponential padding with a live border
+# ------------------------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("case", ["a", "b"])
+def test_pad_depth_std_matches_reference_golden(case):
+    """dnr_pad_depth_std against the unmodified reference's exponential_padding (torch_helpers.py:100-122) on std maps
+    whose border pixels are non-zero (the gain 2^(e/12) multiplies live values): bit for bit."""
+    dev = _cuda()
+    from diner_b200 import _lib
+    from diner_b200.scene import STD_PAD, gain_table
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "exp_padding.npz"))
+    std = torch.from_numpy(g[case + "_std"]).to(dev)                # N,1,H,W
+    N, _, H, W = std.shape
+    out = torch.empty(N, H + 2 * STD_PAD, W + 2 * STD_PAD, device=dev)
+    _lib.call("dnr_pad_depth_std", _lib.ptr(std.view(N, H, W).contiguous()), _lib.ptr(gain_table(dev)), N, H, W, STD_PAD,
+              _lib.ptr(out), _lib.stream_ptr())
+    want = torch.from_numpy(g[case + "_padded"])[:, 0]
+    assert torch.equal(out.cpu(), want)
+    ring = out[:, :STD_PAD].cpu()
+    assert float((ring != 0).float().mean()) > 0.5                  # the padded ring really carries amplified values
+
+
+@pytest.mark.parametrize("NV", [2, 3])
+def test_sampler_foreground_touching_the_border(NV):
+    """Source views zoomed in until the object runs over the image border: candidates that project into the padded ring
+    see std * 2^(e/12), border-clamped depth and zero normals.  Likelihoods, shortlist, masks: bit for bit against the
+    oracle on torch CUDA ops; most rays against the oracle on torch CPU ops."""
+    dev = _cuda()
+    import dataclasses
+    from diner_b200 import sample_rays
+    from diner_b200.scene import get_scene
+    from tools.synthetic import WORKLOADS, make_scene
+    wl = dataclasses.replace(WORKLOADS["tiny"], name=f"border_nv{NV}", NV=NV, tgt_H=20, tgt_W=20)
+    scene = PM.zoom_sources(make_scene(wl, seed=3, calibrate=False), 2.2)
+    std = scene.model.encoder.depths_std
+    assert float((std[..., 0, :] != 0).float().mean()) > 0.5         # live border
+    rays = scene.rays
+    noise = PM.unpacked_noise(rays.shape[0] * rays.shape[1], wl, seed=13)
+    oc = PM.oracle_sampler(scene.model, rays, wl, noise)
+    m = scene.model.to_device(dev)
+    try:
+        nd = {k: v.to(dev) for k, v in noise.items()}
+        og = PM.oracle_sampler(m, rays.to(dev), wl, nd)
+        z, d = sample_rays(get_scene(m), rays.to(dev), wl.n_samples, wl.n_candidates, wl.n_gaussian, noise=nd,
+                           want_debug=True)
+        # candidates outside every source image (|u| or |v| > 1) must contribute: that is the padded ring at work
+        from oracle import dgs_oracle as O
+        zc, _ = O.coarse_candidates(rays, wl.n_candidates, noise["u_coarse"])
+        xyz = rays[..., None, :3] + zc.unsqueeze(-1) * rays[..., None, 3:6]
+        _, uv = O.project_to_views(_cpu_view(m), xyz.reshape(1, -1, 3))
+        outside = (uv.abs() > 1).any(-1).all(1).view(-1, wl.n_candidates)         # outside ALL views
+        assert int(((oc["p"] != 0) & outside).sum()) > 50
+        assert torch.equal(d["p"], og["p"])
+        assert torch.equal(d["sel_idx"].long(), og["idx"])
+        assert torch.equal(d["ray_mask"], og["rm"]) and torch.equal(d["n_missing"], og["nm"])
+        torch.testing.assert_close(z, og["z"], rtol=1e-5, atol=1e-6)
+        assert torch.isclose(z.cpu(), oc["z"], rtol=1e-5, atol=1e-6).all(-1).float().mean().item() >= 0.9
+    finally:
+        m.to_device("cpu")
+
+
+def _cpu_view(m):
+    """The cameras of a model that currently lives on the GPU, as a CPU stand-in for oracle.project_to_views."""
+    from types import SimpleNamespace
+    return SimpleNamespace(poses=m.poses.cpu(), focal=m.focal.cpu(), c=m.c.cpu(), image_shape=m.image_shape.cpu())
+
+
+# ------------------------------------------------------------------------------------------------------------
+# verification mode: the same kernels / layouts / epilogues at ~2^-16 per product
+# ------------------------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("name", ["tiny", "tiny3", "plumbing64"])
+def test_split_precision_matches_fp32_reference_goldens(golden_cache, name):
+    """precision="split" on the reference's own samples vs. the unmodified fp32 reference (golden rgb / depth /
+    weights): <= 1e-4, the bar north_star sets for fp32 compositing -- no sample is hiding an indexing or layout error
+    inside the bf16 budget.  The default bf16 mode on the same inputs: mean AND tail bounds."""
+    dev = _cuda()
+    g, scene, rays, _ = golden_cache(name)
+    far = scene.workload.far
+    out, m = PM.render_on_golden_z(scene, rays, g, dev, "split")
+    try:
+        e_rgb = PM.error_metrics(out.fine.rgb, torch.from_numpy(g["rgb"]))
+        e_dep = PM.error_metrics(out.fine.depth, torch.from_numpy(g["depth"]))
+        e_w = PM.error_metrics(out.fine.weights, torch.from_numpy(g["weights"]))
+        assert e_rgb["max"] < 1e-4 and e_dep["max"] < 1e-4 * far and e_w["max"] < 1e-4, (e_rgb, e_dep, e_w)
+    finally:
+        m.to_device("cpu")
+    out, m = PM.render_on_golden_z(scene, rays, g, dev, "bf16")
+    try:
+        for key in ("rgb", "depth", "weights"):
+            e = PM.error_metrics(out.fine[key], torch.from_numpy(g[key]))
+            assert e["mean"] < 3e-3 and e["q99"] < 3e-2 and e["max"] < 0.25, (key, e)
+    finally:
+        m.to_device("cpu")
+
+
+@pytest.mark.parametrize("NV,n_rays", [(1, 33), (2, 100), (3, 45), (4, 64)])
+def test_encode_split_operands(NV, n_rays):
+    """dnr_encode_fwd_split: hi images equal dnr_encode_fwd's for the code and are the bf16 rounding of the fp32-latent
+    blend for the feature; hi + lo reproduces the fp32 oracle's field_inputs to ~2^-16."""
+    dev = _cuda()
+    import dataclasses
+    from diner_b200 import _lib
+    from diner_b200.field import _encode_args
+    from diner_b200.scene import get_scene
+    from oracle import dgs_oracle as O
+    from tools.synthetic import WORKLOADS, make_scene
+    wl = dataclasses.replace(WORKLOADS["tiny"], name=f"encs_nv{NV}", NV=NV, tgt_H=16, tgt_W=16)
+    scene = make_scene(wl, seed=20 + NV, calibrate=False)
+    K = wl.n_samples
+    rays = scene.rays[:, :n_rays].contiguous()
+    gen = torch.Generator().manual_seed(NV)
+    u = torch.cat([0.45 + 0.02 * torch.rand(1, n_rays, K - 10, generator=gen), torch.rand(1, n_rays, 10, generator=gen)], -1)
+    z = rays[..., 6:7] + (rays[..., 7:8] - rays[..., 6:7]) * u.sort(-1).values
+    pts = (rays[..., None, :3] + z.unsqueeze(-1) * rays[..., None, 3:6]).reshape(1, n_rays * K, 3)
+    dirs = rays[..., None, 3:6].expand(-1, -1, K, -1).reshape(1, n_rays * K, 3)
+    with torch.no_grad():
+        zx = O.field_inputs(scene.model, pts, dirs)                         # 1,NV,B,567 fp32
+    m = scene.model.to_device(dev)
+    try:
+        sc = get_scene(m)
+        p, st = _lib.ptr, _lib.stream_ptr()
+        ns = n_rays * K
+        mv = _lib.load().dnr_view_row_tiles(ns, NV)
+        bufs = {k: torch.empty(mv * 128 * w, device=dev, dtype=torch.bfloat16)
+                for k, w in dict(lat=512, code=64, lat_hi=512, code_hi=64, lat_lo=512, code_lo=64).items()}
+        r_d, z_d = rays.view(-1, 8).to(dev), z.view(-1, K).to(dev)
+        args = _encode_args(sc, n_rays, K, 0, n_rays)
+        _lib.call("dnr_encode_fwd", p(r_d), p(z_d), p(sc.poses), p(sc.focal), p(sc.cxy), p(sc.depth), p(sc.latent_nhwc),
+                  p(sc.freqs), p(sc.phases), *args, p(bufs["lat"]), p(bufs["code"]), st)
+        _lib.call("dnr_encode_fwd_split", p(r_d), p(z_d), p(sc.poses), p(sc.focal), p(sc.cxy), p(sc.depth),
+                  p(sc.latent_nhwc), p(sc.latent_lo()), p(sc.freqs), p(sc.phases), *args, p(bufs["lat_hi"]),
+                  p(bufs["code_hi"]), p(bufs["lat_lo"]), p(bufs["code_lo"]), st)
+        rows = {}
+        for k, t in bufs.items():
+            w = 512 if k.startswith("lat") else 64
+            rows[k] = torch.empty(mv * 128, w, device=dev)
+            _lib.call("dnr_unpack_rows", p(t), mv * 128, w, p(rows[k]), st)
+        torch.cuda.synchronize()
+        assert torch.equal(rows["code_hi"], rows["code"])                    # same fp32 code, same rounding
+        spw = 32 // NV
+        s_ = torch.arange(ns)
+        for v in range(NV):
+            row = ((s_ // spw) * 32 + (s_ % spw) * NV + v).to(dev)
+            want = zx[0, v]
+            lat = (rows["lat_hi"][row] + rows["lat_lo"][row]).cpu()
+            code = (rows["code_hi"][row] + rows["code_lo"][row]).cpu()
+            assert (lat - want[:, :512]).abs().max() <= 2.0 ** -14 * want[:, :512].abs().max()
+            # the code: sin of arguments up to ~500 rad evaluated by two different sinf implementations
+            assert torch.allclose(code[:, :55], want[:, 512:], rtol=2.0 ** -14, atol=2e-4)
+    finally:
+        m.to_device("cpu")
+
+
+def test_second_device_in_one_process():
+    """Launch configuration (function attributes, SM counts, cluster occupancy) is per device: render on cuda:1 after
+    cuda:0 in ONE process (skipped on a single-GPU box)."""
+    _cuda()
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    from diner_b200 import NeRFRendererDGS
+    from tools.synthetic import make_scene
+    outs = []
+    for i in (0, 1):
+        dev = torch.device("cuda", i)
+        scene = make_scene("tiny", seed=0)
+        wl = scene.workload
+        m = scene.model.to_device(dev)
+        r = NeRFRendererDGS(wl.n_samples, wl.n_candidates, wl.n_gaussian, white_bkgd=True)
+        gen = torch.Generator().manual_seed(1)
+        zz = torch.rand(1, scene.rays.shape[1], wl.n_samples, generator=gen).sort(-1).values * 1.5 + 1.0
+        with torch.no_grad():
+            out = r(m, scene.rays.to(dev), noise=dict(z=zz))                 # current device stays cuda:0
+        m.encoder.latent = m.encoder.latent.detach().requires_grad_(True)
+        o2 = r(m, scene.rays.to(dev), noise=dict(z=zz))
+        o2.fine.rgb.sum().backward()
+        assert torch.isfinite(m.encoder.latent.grad).all()
+        outs.append(out.fine.rgb.cpu())
+        with pytest.raises(RuntimeError, match="rays live on"):
+            r(m, scene.rays.to(torch.device("cuda", 1 - i)))
+    assert torch.equal(outs[0], outs[1])
+
+
+def test_in_place_writes_need_invalidate():
+    """The per-scene / per-weights caches key on (data_ptr, _version): a write through `.data` (what a c10d broadcast
+    or a fused optimizer does) is invisible to them, `diner_b200.invalidate()` makes the renderer see it."""
+    dev = _cuda()
+    import diner_b200
+    from diner_b200 import NeRFRendererDGS
+    from tools.synthetic import make_scene
+    scene = make_scene("tiny", seed=0)
+    other = make_scene("tiny", seed=5)
+    wl = scene.workload
+    m, m2 = scene.model.to_device(dev), other.model.to_device(dev)
+    r = NeRFRendererDGS(wl.n_samples, wl.n_candidates, wl.n_gaussian, white_bkgd=True)
+    rays = scene.rays.to(dev)
+    gen = torch.Generator().manual_seed(1)
+    zz = dict(z=torch.rand(1, rays.shape[1], wl.n_samples, generator=gen).sort(-1).values * 1.5 + 1.0)
+    with torch.no_grad():
+        a = r(m, rays, noise=zz).fine.rgb.clone()
+        want = r(m2, rays, noise=zz).fine.rgb.clone()
+        r(m, rays, noise=zz)                                          # caches now hold m's repacks again
+        # overwrite scene and weights in place WITHOUT touching the version counters
+        m.encoder.latent.data.copy_(m2.encoder.latent)
+        for p, q in zip(m.mlp_fine.parameters(), m2.mlp_fine.parameters()):
+            p.data.copy_(q.data)
+        stale = r(m, rays, noise=zz).fine.rgb.clone()
+        diner_b200.invalidate()
+        fresh = r(m, rays, noise=zz).fine.rgb.clone()
+    assert torch.equal(stale, a)                 # documented hazard: the cache cannot see the write
+    assert not torch.equal(fresh, a) and torch.equal(fresh, want)

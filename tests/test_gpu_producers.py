@@ -63,7 +63,7 @@ def test_producers_full_frame_properties_and_renderer_round_trip():
     rendered from the host-generated rays of the scene generator."""
     dev = _cuda()
     from diner_b200 import NeRFRendererDGS, depth2normal, gen_rays
-    from diner_b200.synthetic import make_scene
+    from tools.synthetic import make_scene
     scene = make_scene("facescape", seed=0)
     wl = scene.workload
     m = scene.model.to_device(dev)
@@ -175,7 +175,7 @@ def test_predict_imgs_and_sweep_match_direct_renderer_calls():
     dev = _cuda()
     from diner_b200 import NeRFRendererDGS, gen_rays
     from diner_b200.callers import predict_imgs, render_sweep
-    from diner_b200.synthetic import make_scene
+    from tools.synthetic import make_scene
     scene = make_scene("tiny", seed=0)
     wl = scene.workload
     model = scene.model.to_device(dev)

@@ -166,7 +166,7 @@ def test_sampler_philox_jitter_equals_explicit_uniforms():
     dev = _cuda()
     from diner_b200 import sample_rays
     from diner_b200.scene import get_scene
-    from diner_b200.synthetic import make_scene
+    from tools.synthetic import make_scene
     from oracle.philox import philox4x32_10 as _philox4x32_10
     scene = make_scene("tiny", seed=0, calibrate=False)
     wl = scene.workload
@@ -196,7 +196,7 @@ def test_sampler_background_rays_are_stratified_uniform():
     dev = _cuda()
     from diner_b200 import sample_rays
     from diner_b200.scene import get_scene
-    from diner_b200.synthetic import make_scene
+    from tools.synthetic import make_scene
     scene = make_scene("tiny", seed=0, calibrate=False)
     scene.model.encoder.depths_std = torch.zeros_like(scene.model.encoder.depths_std)
     wl = scene.workload
@@ -227,7 +227,7 @@ def test_encode_stage_fwd_bwd_all_view_counts(NV, n_rays):
     from diner_b200 import _lib
     from diner_b200.field import _encode_args
     from diner_b200.scene import get_scene
-    from diner_b200.synthetic import WORKLOADS, make_scene
+    from tools.synthetic import WORKLOADS, make_scene
     from oracle import dgs_oracle as O
     wl = dataclasses.replace(WORKLOADS["tiny"], name=f"enc_nv{NV}", NV=NV, tgt_H=16, tgt_W=16)
     scene = make_scene(wl, seed=10 + NV)

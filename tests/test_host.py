@@ -50,8 +50,8 @@ def test_argument_validation_needs_no_gpu():
     assert lib.dnr_view_row_tiles(10, 9) == -1
     rc = lib.dnr_composite_fwd(None, None, None, 10, 0, 1, None, None, None, None)
     assert rc == 1 and b"K must be" in lib.dnr_last_error()
-    rc = lib.dnr_mlp_gemm(None, None, 64, None, None, 0, None, None, 0, 1, 100, None, None, None, None, None, 0, 0, 0, 0,
-                          None)
+    rc = lib.dnr_mlp_gemm(None, None, 64, None, None, 0, None, None, 0, 1, 100, None, None, None, None, None, None, 0, 0,
+                          0, 0, None)
     assert rc == 1 and b"multiple of 256" in lib.dnr_last_error()
     with pytest.raises(RuntimeError, match="dnr_mlp_wgrad failed"):
         _lib.call("dnr_mlp_wgrad", None, 100, None, 64, 1, None, 64, 1, 1, None, None)
@@ -61,7 +61,7 @@ def test_renderer_signature_and_errors():
     import inspect
     from diner_b200 import NeRFRendererDGS, RenderResult
     from diner_b200.scene import validate_model
-    from diner_b200.synthetic import make_scene
+    from tools.synthetic import make_scene
     sig = inspect.signature(NeRFRendererDGS.__init__)
     # reference constructor (src/models/nerf_renderer.py:23-30): same names, same defaults
     want = dict(n_samples=40, n_depth_candidates=1000, n_gaussian=15, eval_batch_size=100000, white_bkgd=True)
@@ -127,9 +127,22 @@ def _worker(rank, world, port, q):
                                 depths_std=torch.randn(1, 2, 1, 4, 4), normals=torch.randn(1, 2, 3, 4, 4))
     model = types.SimpleNamespace(encoder=enc, poses=torch.randn(1, 2, 4, 4), focal=torch.randn(1, 2, 2),
                                   c=torch.randn(1, 2, 2), image_shape=torch.randn(2), mlp_fine=torch.nn.Linear(4, 4))
+    from diner_b200 import field as F_, scene as S_
+    S_._cache[123] = "stale scene repack"                      # c10d broadcasts / .data writes do not bump _version:
+    F_._packed_cache[456] = "stale packed weights"             # broadcast_scene must drop the renderer's caches itself
+    w_before = model.mlp_fine.weight.detach().clone()
     broadcast_scene(model, src=0)
+    ok = ok and len(S_._cache) == 0 and len(F_._packed_cache) == 0
     torch.manual_seed(0)
-    ok = ok and torch.equal(model.encoder.latent, torch.randn(1, 2, 8, 4, 4))
+    want = dict(latent=torch.randn(1, 2, 8, 4, 4), depths=torch.randn(1, 2, 1, 4, 4), depths_std=torch.randn(1, 2, 1, 4, 4),
+                normals=torch.randn(1, 2, 3, 4, 4))
+    for k, v in want.items():                                   # every tensor of the flat bucket lands in its slot
+        ok = ok and torch.equal(getattr(model.encoder, k), v)
+    want_m = dict(poses=torch.randn(1, 2, 4, 4), focal=torch.randn(1, 2, 2), c=torch.randn(1, 2, 2), image_shape=torch.randn(2))
+    for k, v in want_m.items():
+        ok = ok and torch.equal(getattr(model, k), v)
+    w0 = torch.nn.Linear(4, 4).weight.detach()                  # rank 0's Linear, drawn right after the tensors above
+    ok = ok and torch.equal(model.mlp_fine.weight.detach(), w0) and (rank == 0 or not torch.equal(w_before, w0))
     # gradient all-reduce (mean)
     p = torch.nn.Parameter(torch.zeros(3)); p.grad = torch.full((3,), float(rank + 1))
     allreduce_gradients([p])

@@ -5,7 +5,7 @@ import json, os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from diner_b200 import NeRFRendererDGS
-from diner_b200.synthetic import make_scene
+from tools.synthetic import make_scene
 
 scene = make_scene("facescape", seed=0)
 wl = scene.workload

@@ -352,7 +352,8 @@ def stage_fieldgrad():
         mlp = m.mlp_fine
         names = [n for n, _ in mlp.named_parameters()]
         params = [q for _, q in mlp.named_parameters()]
-        out = _FieldFn.apply(sc, mlp, names, rays.view(-1, 8).cuda(), z.view(-1, K).cuda(), NR, 0, m.encoder.latent, *params)
+        out = _FieldFn.apply(sc, mlp, names, rays.view(-1, 8).cuda(), z.view(-1, K).cuda(), NR, [(0, rays.shape[0] * rays.shape[1])], "bf16",
+                             m.encoder.latent, *params)
         (out * d_out.cuda()).sum().backward()
         torch.cuda.synchronize()
         print(f" [{name}]")

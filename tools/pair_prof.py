@@ -3,7 +3,7 @@ import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from diner_b200 import NeRFRendererDGS, field as F_
-from diner_b200.synthetic import make_scene
+from tools.synthetic import make_scene
 
 scene = make_scene(os.environ.get("DNR_WORKLOAD", "facescape"), seed=0)
 if os.environ.get("DNR_KERNEL"):

@@ -5,7 +5,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from diner_b200 import field as F_
 from diner_b200.scene import get_scene
-from diner_b200.synthetic import WORKLOADS, make_scene
+from tools.synthetic import WORKLOADS, make_scene
 
 budget = float(sys.argv[1]) if len(sys.argv) > 1 else 60.0
 dev = torch.device("cuda", 0)

@@ -8,7 +8,7 @@ figure of SURVEY.md 8(d); the CUDA path of this repo never touches it.
 import json, os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
-from diner_b200.synthetic import make_scene
+from tools.synthetic import make_scene
 from oracle import dgs_oracle as O
 
 workload = sys.argv[1] if len(sys.argv) > 1 else "facescape"
