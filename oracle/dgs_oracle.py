@@ -147,14 +147,18 @@ def coarse_candidates(rays, n_cand, u_coarse=None):
     return z.view(*shp[:-1], n_cand), u_coarse
 
 
-def candidate_likelihood(model, rays, z_cand, depth_diff_max=0.05):
+def candidate_likelihood(model, rays, z_cand, depth_diff_max=0.05, deform=None):
     """Per-candidate surface likelihood, max over views, and its occlusion-aware version
-    (nerf_renderer.py:95-132)."""
+    (nerf_renderer.py:95-132).  `deform` (NOVEL variant, novel/nerf_novel_renderer.py:104-107): a map applied to the
+    candidate positions (SB,B,3) before they are projected into the source views."""
     SB, NR, C = z_cand.shape
     NV = model.poses.shape[1]
     step = (rays[..., -1] - rays[..., -2]) / C                                   # SB,NR
     xyz = rays[..., None, :3] + z_cand.unsqueeze(-1) * rays[..., None, 3:6]
-    x_cam, uv = project_to_views(model, xyz.reshape(SB, -1, 3))                  # SB,NV,B,3 / 2
+    xyz = xyz.reshape(SB, -1, 3)
+    if deform is not None:
+        xyz = deform(xyz)
+    x_cam, uv = project_to_views(model, xyz)                                     # SB,NV,B,3 / 2
     dirs_cam = rotate_to_views(model, rays[..., 3:6]).repeat_interleave(C, dim=-2)
 
     d_ref = tap_depth(model, uv)                                                 # SB,NV,1,B
@@ -184,12 +188,12 @@ def weighted_moments(x, w):
     return mean, std
 
 
-def sample_depthguided(model, rays, n_samples, n_cand, n_gaussian, depth_diff_max=0.05, noise=None):
+def sample_depthguided(model, rays, n_samples, n_cand, n_gaussian, depth_diff_max=0.05, noise=None, deform=None):
     """nerf_renderer.py:65-284.  Returns z (SB,NR,K) with zeros in unfilled slots plus debug info."""
     noise = dict(noise or {})
     SB, NR = rays.shape[:2]
     z_cand, noise["u_coarse"] = coarse_candidates(rays, n_cand, noise.get("u_coarse"))
-    p, p_opq = candidate_likelihood(model, rays, z_cand, depth_diff_max)
+    p, p_opq = candidate_likelihood(model, rays, z_cand, depth_diff_max, deform=deform)
 
     order = p.argsort(dim=-1, descending=True)[..., :n_samples]                 # nerf_renderer.py:172
     p_sel = torch.gather(p, -1, order)

@@ -55,6 +55,37 @@ def load():
                                  gen_rays=gen_rays, DotMap=_AttrDict)
 
 
+def knn_points_k1(p1, p2, K=1, **_):
+    """Stand-in for `pytorch3d.ops.knn.knn_points(p1, p2, K=1)` (pytorch3d is absent from the build image): the published
+    semantics -- squared L2 distance, the FIRST minimum (lowest index) on ties -- returning (dists (N,P1,1),
+    idx (N,P1,1) int64, None); arithmetic of oracle/novel_oracle.nearest_vertex."""
+    import torch
+    from oracle.novel_oracle import nearest_vertex
+    assert K == 1
+    res = [nearest_vertex(a, b) for a, b in zip(p1, p2)]
+    return torch.stack([d for _, d in res]).unsqueeze(-1), torch.stack([i for i, _ in res]).unsqueeze(-1), None
+
+
+def load_novel():
+    """The reference's NOVEL renderer variant and its PixelNeRF (src/models/novel/), UNMODIFIED, with
+    `pytorch3d.ops.knn.knn_points` replaced by knn_points_k1 (the one dependency that cannot be imported here)."""
+    if not available():
+        raise RuntimeError(f"reference sources not found under {REF_ROOT}")
+    _install_stubs()
+    for name in ("pytorch3d", "pytorch3d.ops", "pytorch3d.ops.knn"):
+        if name not in sys.modules:
+            sys.modules[name] = types.ModuleType(name)
+    sys.modules["pytorch3d.ops.knn"].knn_points = knn_points_k1
+    sys.modules["pytorch3d.ops"].knn = sys.modules["pytorch3d.ops.knn"]
+    sys.modules["pytorch3d.ops"].knn_points = knn_points_k1
+    sys.modules["pytorch3d"].ops = sys.modules["pytorch3d.ops"]
+    if REF_ROOT not in sys.path:
+        sys.path.insert(0, REF_ROOT)
+    from src.models.novel.nerf_novel_renderer import NeRFRendererDGS
+    from src.models.novel.novel_pixelnerf import PixelNeRF
+    return types.SimpleNamespace(NeRFRendererDGS=NeRFRendererDGS, PixelNeRF=PixelNeRF, DotMap=_AttrDict)
+
+
 @contextmanager
 def record_noise(store: dict):
     """Record the three random tensors the reference draws, in order:

@@ -397,3 +397,42 @@ def calibrate_sigma(scene, seed=0, n_rays=256, target_std=150.0):
     w, b = model.mlp_fine.lin_out.weight, model.mlp_fine.lin_out.bias
     w[3] *= s
     b[3] = b[3] * s - med * s
+
+
+# ----------------------------------------------------------------------------------------
+# NOVEL variant inputs: a target mesh with per-vertex offsets, the generic camera and the learned
+# second feature map of novel_pixelnerf.py:34-46,73-80.  Input producers only.
+# ----------------------------------------------------------------------------------------
+
+def add_novel_inputs(scene, n_vertices: int = 400, seed: int = 0, offset_std: float = 0.004, gen_hw=None):
+    """Adds scene.target_vertices / tgt_in_offsets / tgt_gen_offsets (SB,V,3) and model.gen_poses (SB,1,4,4),
+    gen_focal / gen_c (SB,1,2), gen_image_shape (2,), gen_latent (512,Hg,Wg) to a scene from make_scene."""
+    wl, m = scene.workload, scene.model
+    g = torch.Generator().manual_seed(9000 + seed)
+    a = torch.tensor(_SEMI_AXES) * wl.scale
+    # vertices: quasi-uniform directions on the ellipsoid (the "mesh" the offsets live on)
+    u = torch.randn(wl.SB, n_vertices, 3, generator=g)
+    u = u / u.norm(dim=-1, keepdim=True)
+    scene.target_vertices = (u * a).contiguous()
+    scene.tgt_in_offsets = (torch.randn(wl.SB, n_vertices, 3, generator=g) * offset_std * wl.scale).contiguous()
+    scene.tgt_gen_offsets = (torch.randn(wl.SB, n_vertices, 3, generator=g) * offset_std * wl.scale).contiguous()
+    dist = 0.5 * (wl.near + wl.far)
+    E = torch.stack([look_at_extrinsics(_cam_center(0.0, 0.0, dist)).float() for _ in range(wl.SB)])
+    K = _intrinsics(wl.H, wl.W, dist, wl.scale).float()
+    m.gen_poses = E.unsqueeze(1).contiguous()                                        # SB,1,4,4
+    m.gen_focal = torch.stack((K[0, 0], K[1, 1])).view(1, 1, 2).expand(wl.SB, 1, 2).contiguous()
+    m.gen_c = K[:2, 2].view(1, 1, 2).expand(wl.SB, 1, 2).contiguous()
+    m.gen_image_shape = torch.tensor([float(wl.W), float(wl.H)])
+    Hg, Wg = gen_hw or ((wl.H + 128) // 2 - 8, (wl.W + 128) // 2 + 8)                  # its own size on purpose
+    m.gen_latent = (torch.randn(512, Hg, Wg, generator=g) * 0.5).contiguous()
+    return scene
+
+
+def novel_to_device(scene, device):
+    m = scene.model
+    for k in ("gen_poses", "gen_focal", "gen_c", "gen_image_shape", "gen_latent"):
+        setattr(m, k, getattr(m, k).to(device))
+    for k in ("target_vertices", "tgt_in_offsets", "tgt_gen_offsets"):
+        setattr(scene, k, getattr(scene, k).to(device))
+    m.to_device(device)
+    return scene
