@@ -24,6 +24,7 @@ SOURCES = [
     ("producers.cu", []),
     ("depth_format.cu", []),
     ("deform.cu", []),
+    ("novel.cu", ["--fmad=false"]),
     ("mlp_misc.cu", []),
 ]
 COMMON = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

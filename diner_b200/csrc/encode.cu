@@ -33,6 +33,15 @@ struct EncodeParams {
   unsigned char* in_pk;  // PK<128> [rows_pad x 64] bf16
   float* d_latent;       // bwd: [SB,NV,Hl,Wl,L] fp32 (accumulated into)
   const float* d_lat_xr; // bwd: XR [rows_pad x 512] fp32
+  // NOVEL variant (src/models/novel/novel_pixelnerf.py:143-196), all null / 0 otherwise
+  const float* pts_in;   // [n_samples, 3] `in`-deformed sample points: replace o + z d in the projection chain
+  const float* pts_gen;  // [n_samples, 3] `gen`-deformed sample points, projected by the ONE generic camera
+  const float* gen_poses;   // [SB,1,4,4]
+  const float* gen_focal;   // [SB,1,2]
+  const float* gen_cxy;     // [SB,1,2]
+  const __nv_bfloat16* gen_latent;  // [Hg,Wg,L] channels-last, shared by all scenes and views
+  int Hg, Wg;
+  float gen_img_w, gen_img_h, gen_sx, gen_sy;
 };
 
 struct RowGeom {
@@ -47,10 +56,15 @@ __device__ __forceinline__ void row_geometry(const EncodeParams& P, long long sa
   const long long ray = sample / P.K;
   const int sb = (int)((ray + P.ray_offset) / P.NR);
   const float* rp = P.rays + ray * 8;
-  const float zs = P.z[sample];
-  const float x0 = __fadd_rn(rp[0], __fmul_rn(zs, rp[3]));
-  const float x1 = __fadd_rn(rp[1], __fmul_rn(zs, rp[4]));
-  const float x2 = __fadd_rn(rp[2], __fmul_rn(zs, rp[5]));
+  float x0, x1, x2;
+  if (P.pts_in) {          // NOVEL variant: the (deformed) point is given
+    x0 = P.pts_in[sample * 3 + 0]; x1 = P.pts_in[sample * 3 + 1]; x2 = P.pts_in[sample * 3 + 2];
+  } else {
+    const float zs = P.z[sample];
+    x0 = __fadd_rn(rp[0], __fmul_rn(zs, rp[3]));
+    x1 = __fadd_rn(rp[1], __fmul_rn(zs, rp[4]));
+    x2 = __fadd_rn(rp[2], __fmul_rn(zs, rp[5]));
+  }
   g.map = (size_t)sb * P.NV + view;
   const float* E = P.poses + g.map * 16;
   g.xc = __fadd_rn(fmaf(E[2], x2, fmaf(E[1], x1, __fmul_rn(E[0], x0))), E[3]);
@@ -82,6 +96,37 @@ __device__ __forceinline__ void row_geometry(const EncodeParams& P, long long sa
   g.x0 = (int)flx; g.y0 = (int)fly;
   g.x1 = min(g.x0 + 1, P.Wl - 1); g.y1 = min(g.y0 + 1, P.Hl - 1);
   g.wx = fx - flx; g.wy = fy - fly;     // weight of the +1 neighbour (0 when it is out of range)
+}
+
+// NOVEL variant: bilinear footprint of the `gen`-deformed point in the learned map (novel_pixelnerf.py:163-165,186-189,
+// index :108-141): one generic camera per scene, the same for every source view.
+struct GenTaps {
+  uint32_t p00, p01, p10, p11;      // element offsets inside gen_latent
+  float w00, w01, w10, w11;
+};
+__device__ __forceinline__ void gen_geometry(const EncodeParams& P, long long sample, int sb, GenTaps& t) {
+  const float x0 = P.pts_gen[sample * 3 + 0], x1 = P.pts_gen[sample * 3 + 1], x2 = P.pts_gen[sample * 3 + 2];
+  const float* E = P.gen_poses + (size_t)sb * 16;
+  const float xc = __fadd_rn(fmaf(E[2], x2, fmaf(E[1], x1, __fmul_rn(E[0], x0))), E[3]);
+  const float yc = __fadd_rn(fmaf(E[6], x2, fmaf(E[5], x1, __fmul_rn(E[4], x0))), E[7]);
+  const float zc = __fadd_rn(fmaf(E[10], x2, fmaf(E[9], x1, __fmul_rn(E[8], x0))), E[11]);
+  float u = __fdiv_rn(xc, zc), v = __fdiv_rn(yc, zc);
+  u = __fadd_rn(__fmul_rn(u, P.gen_focal[sb * 2 + 0]), P.gen_cxy[sb * 2 + 0]);
+  v = __fadd_rn(__fmul_rn(v, P.gen_focal[sb * 2 + 1]), P.gen_cxy[sb * 2 + 1]);
+  u = __fsub_rn(__fmul_rn(__fdiv_rn(u, P.gen_img_w), 2.0f), 1.0f);
+  v = __fsub_rn(__fmul_rn(__fdiv_rn(v, P.gen_img_h), 2.0f), 1.0f);
+  const float ul = __fmul_rn(u, P.gen_sx), vl = __fmul_rn(v, P.gen_sy);
+  float fx = fmaf(__fadd_rn(ul, 1.0f), (float)P.Wg, -1.0f) * 0.5f;
+  float fy = fmaf(__fadd_rn(vl, 1.0f), (float)P.Hg, -1.0f) * 0.5f;
+  fx = fminf(fmaxf(fx, 0.0f), (float)(P.Wg - 1));
+  fy = fminf(fmaxf(fy, 0.0f), (float)(P.Hg - 1));
+  const float flx = floorf(fx), fly = floorf(fy);
+  const int gx0 = (int)flx, gy0 = (int)fly;
+  const int gx1 = min(gx0 + 1, P.Wg - 1), gy1 = min(gy0 + 1, P.Hg - 1);
+  const float wx = fx - flx, wy = fy - fly;
+  t.p00 = (uint32_t)(((size_t)gy0 * P.Wg + gx0) * 512); t.p01 = (uint32_t)(((size_t)gy0 * P.Wg + gx1) * 512);
+  t.p10 = (uint32_t)(((size_t)gy1 * P.Wg + gx0) * 512); t.p11 = (uint32_t)(((size_t)gy1 * P.Wg + gx1) * 512);
+  t.w00 = (1.f - wx) * (1.f - wy); t.w01 = wx * (1.f - wy); t.w10 = (1.f - wx) * wy; t.w11 = wx * wy;
 }
 
 // packed fp32 pairs (Blackwell FMUL2 / FFMA2): the two channels of a bf16x2 word travel together
@@ -134,8 +179,10 @@ __device__ __forceinline__ float blend4_lo(uint32_t a, uint32_t b, uint32_t c, u
 // order as before (mul, fma, fma, fma in tap order): bit-identical outputs.
 // SPLIT (verification mode): the latent is a bf16 hi + lo pair, the blended feature and the geometric code leave as
 // hi + lo pairs of operand images (v_hi = bf16(v), v_lo = bf16(v - v_hi)).
-template <bool SPLIT>
-__global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams P, const __nv_bfloat16* latent_lo,
+// NOVEL (src/models/novel/novel_pixelnerf.py:143-196): the sample points are given (deformed), and the feature row is
+// gen_latent[gen_uv] + latent[uv] -- a second bilinear gather from the learned map, with its own footprint cache.
+template <bool SPLIT, bool NOVEL>
+__global__ void __launch_bounds__(kEncWarps * 32, (SPLIT || NOVEL) ? 1 : 5) encode_fwd_kernel(EncodeParams P, const __nv_bfloat16* latent_lo,
                                                                     unsigned char* lat_pk_lo, unsigned char* in_pk_lo) {
   extern __shared__ __align__(16) unsigned char enc_smem[];
   unsigned char* sl = enc_smem;                                   // [64][kLatChunkStride]
@@ -143,21 +190,22 @@ __global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams
   RowTaps* taps_s = reinterpret_cast<RowTaps*>(si + kEncInBytes); // [32]
   unsigned char* sl_lo = reinterpret_cast<unsigned char*>(taps_s + 32);     // SPLIT only
   unsigned char* si_lo = sl_lo + kEncLatBytes;
+  GenTaps* gen_s = reinterpret_cast<GenTaps*>(taps_s + 32);                 // NOVEL only (never together with SPLIT)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const RowMap rm = RowMap::make(P.NV);
   const long long row_base = (long long)blockIdx.x * 32;
   const int L = 512;
 
-  // phase 1: lanes 0..7 of warp w run the projection chain of rows 8w..8w+7 (the eight chains overlap instead of running
-  // back to back on all 32 lanes)
-  if (lane < 8) {
+  // phase 1: warp 0 runs the projection chains of the slab's 32 rows, one per lane (the other warps would only repeat
+  // the same instruction stream for eight rows each)
+  if (warp == 0) {
     long long sample; int view;
     RowTaps tp;
     tp.map_plus1 = 0;
     tp.p00 = tp.p01 = tp.p10 = tp.p11 = 0u;
     tp.w00 = tp.w01 = tp.w10 = tp.w11 = 0.f;
     tp.xc = tp.yc = tp.zc = tp.dx = tp.dy = tp.dz = tp.dd = 0.f;
-    if (rm.decode(row_base + warp * 8 + lane, P.n_samples, sample, view)) {
+    if (rm.decode(row_base + lane, P.n_samples, sample, view)) {
       RowGeom g;
       row_geometry(P, sample, view, g);
       const size_t mb = g.map * (size_t)P.Hl * P.Wl;          // texels before this (scene, view) map; the whole latent holds < 2^32 elements
@@ -167,10 +215,15 @@ __global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams
       tp.w10 = (1.f - g.wx) * g.wy; tp.w11 = g.wx * g.wy;
       tp.xc = g.xc; tp.yc = g.yc; tp.zc = g.zc; tp.dx = g.dx; tp.dy = g.dy; tp.dz = g.dz; tp.dd = g.dd;
       tp.map_plus1 = (uint32_t)g.map + 1u;
+      if (NOVEL) {
+        GenTaps gt;
+        gen_geometry(P, sample, (int)(g.map / P.NV), gt);
+        gen_s[lane] = gt;
+      }
     }
-    taps_s[warp * 8 + lane] = tp;
+    taps_s[lane] = tp;
   }
-  __syncwarp();
+  __syncthreads();
 
   // phase 1b: the 55-wide geometric code of the warp's 8 rows (zero-padded to 64).  The 48 sines of a row are spread
   // over the warp as 8 x 48 = 384 = 12 full-warp evaluations, one branch-free sinf each; the 16 plain elements follow.
@@ -233,50 +286,113 @@ __global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams
   __syncthreads();
 
   // phase 2: gather.  Lane's channels: 128 warp + 4 lane .. + 3 = 8 bytes of feature chunk c = 16 warp + lane / 2.
+  // Rows are taken four at a time (same view, consecutive samples): the taps of every NEW footprint among the four are
+  // requested first -- up to four footprints (4 x 1 KB per warp) in flight -- and only then are the rows blended, each
+  // from the footprint it shares (a warp-uniform choice, so the selection is a branch, not a register copy).
   {
     const int ch = warp * 128 + lane * 4;
     unsigned char* dst0 = sl + (warp * 16 + (lane >> 1)) * kLatChunkStride + (lane & 1) * 8;
     unsigned char* dst0_lo = sl_lo + (warp * 16 + (lane >> 1)) * kLatChunkStride + (lane & 1) * 8;
     const __nv_bfloat16* lat = P.latent + ch;
     const __nv_bfloat16* lat_lo = SPLIT ? latent_lo + ch : nullptr;
-    uint2 a = make_uint2(0, 0), b = a, c = a, d = a;              // the four taps of the current footprint
-    uint2 al = a, bl = a, cl = a, dl = a;
-    uint32_t cur00 = 0xffffffffu, cur11 = 0xffffffffu;
+    struct Foot { uint2 a, b, c, d, al, bl, cl, dl; };            // (the lo taps exist in the SPLIT instantiation only)
+    uint32_t prev00 = 0xffffffffu, prev11 = 0xffffffffu;
+    uint2 ga = make_uint2(0, 0), gb = ga, gc = ga, gd = ga;       // NOVEL: the four taps of the current gen_latent footprint
+    uint32_t gcur00 = 0xffffffffu, gcur11 = 0xffffffffu;
+    const __nv_bfloat16* glat = NOVEL ? P.gen_latent + ch : nullptr;
     const int n_live = rm.SPW * rm.NV;
-    for (int v = 0; v < rm.NV; ++v) {
-#pragma unroll 2
-      for (int s = 0; s < rm.SPW; ++s) {
-        const int l = s * rm.NV + v;
-        const uint4 pp = *reinterpret_cast<const uint4*>(&taps_s[l].p00);
-        const float4 ww = *reinterpret_cast<const float4*>(&taps_s[l].w00);
-        const uint32_t live = taps_s[l].map_plus1;
-        uint2 o = make_uint2(0, 0), o_lo = o;
-        if (live) {                                                // (warp-uniform)
-          if (pp.x != cur00 || pp.w != cur11) {                    // a new footprint: p00 fixes (map, x0, y0), p11 the clamps
-            a = __ldg(reinterpret_cast<const uint2*>(lat + pp.x)); b = __ldg(reinterpret_cast<const uint2*>(lat + pp.y));
-            c = __ldg(reinterpret_cast<const uint2*>(lat + pp.z)); d = __ldg(reinterpret_cast<const uint2*>(lat + pp.w));
-            if (SPLIT) {
-              al = __ldg(reinterpret_cast<const uint2*>(lat_lo + pp.x)); bl = __ldg(reinterpret_cast<const uint2*>(lat_lo + pp.y));
-              cl = __ldg(reinterpret_cast<const uint2*>(lat_lo + pp.z)); dl = __ldg(reinterpret_cast<const uint2*>(lat_lo + pp.w));
-            }
-            cur00 = pp.x; cur11 = pp.w;
-          }
-          const uint64_t W00 = splat_f32x2(ww.x), W01 = splat_f32x2(ww.y), W10 = splat_f32x2(ww.z), W11 = splat_f32x2(ww.w);
-          float v0, v1, v2, v3;
-          v0 = blend4_lo(a.x, b.x, c.x, d.x, W00, W01, W10, W11, v1);
-          v2 = blend4_lo(a.y, b.y, c.y, d.y, W00, W01, W10, W11, v3);
-          if (SPLIT) {
-            float u0, u1, u2, u3;
-            u0 = blend4_lo(al.x, bl.x, cl.x, dl.x, W00, W01, W10, W11, u1);
-            u2 = blend4_lo(al.y, bl.y, cl.y, dl.y, W00, W01, W10, W11, u3);
-            v0 += u0; v1 += u1; v2 += u2; v3 += u3;
-          }
-          o = make_uint2(pack_bf16x2(v0, v1), pack_bf16x2(v2, v3));
-          if (SPLIT)
-            o_lo = make_uint2(pack_bf16x2(v0 - bf16lo(o.x), v1 - bf16hi(o.x)), pack_bf16x2(v2 - bf16lo(o.y), v3 - bf16hi(o.y)));
+    auto fetch = [&](Foot& f, const uint4& pp) {
+      f.a = __ldg(reinterpret_cast<const uint2*>(lat + pp.x)); f.b = __ldg(reinterpret_cast<const uint2*>(lat + pp.y));
+      f.c = __ldg(reinterpret_cast<const uint2*>(lat + pp.z)); f.d = __ldg(reinterpret_cast<const uint2*>(lat + pp.w));
+      if (SPLIT) {
+        f.al = __ldg(reinterpret_cast<const uint2*>(lat_lo + pp.x)); f.bl = __ldg(reinterpret_cast<const uint2*>(lat_lo + pp.y));
+        f.cl = __ldg(reinterpret_cast<const uint2*>(lat_lo + pp.z)); f.dl = __ldg(reinterpret_cast<const uint2*>(lat_lo + pp.w));
+      }
+    };
+    // the current footprint, unpacked ONCE to fp32 pairs: rows that share it only redo the four weighted sums
+    uint64_t ua0 = 0, ub0 = 0, uc0 = 0, ud0 = 0, ua1 = 0, ub1 = 0, uc1 = 0, ud1 = 0;
+    uint64_t la0 = 0, lb0 = 0, lc0 = 0, ld0 = 0, la1 = 0, lb1 = 0, lc1 = 0, ld1 = 0;          // SPLIT: the lo taps
+    auto unpack = [&](const Foot& f) {
+      ua0 = bf16x2_to_f32x2(f.a.x); ub0 = bf16x2_to_f32x2(f.b.x); uc0 = bf16x2_to_f32x2(f.c.x); ud0 = bf16x2_to_f32x2(f.d.x);
+      ua1 = bf16x2_to_f32x2(f.a.y); ub1 = bf16x2_to_f32x2(f.b.y); uc1 = bf16x2_to_f32x2(f.c.y); ud1 = bf16x2_to_f32x2(f.d.y);
+      if (SPLIT) {
+        la0 = bf16x2_to_f32x2(f.al.x); lb0 = bf16x2_to_f32x2(f.bl.x); lc0 = bf16x2_to_f32x2(f.cl.x); ld0 = bf16x2_to_f32x2(f.dl.x);
+        la1 = bf16x2_to_f32x2(f.al.y); lb1 = bf16x2_to_f32x2(f.bl.y); lc1 = bf16x2_to_f32x2(f.cl.y); ld1 = bf16x2_to_f32x2(f.dl.y);
+      }
+    };
+    auto wsum = [&](uint64_t a, uint64_t b, uint64_t c, uint64_t d, uint64_t W00, uint64_t W01, uint64_t W10, uint64_t W11,
+                    float& lo, float& hi) {
+      // a*w00, then fma by fma in tap order -- the same roundings as the scalar chain (and as blend4_lo)
+      uint64_t acc = mul_f32x2(a, W00);
+      acc = fma_f32x2(b, W01, acc);
+      acc = fma_f32x2(c, W10, acc);
+      acc = fma_f32x2(d, W11, acc);
+      asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(acc));
+    };
+    auto blend_store = [&](const float4& ww, int l) {
+      const uint64_t W00 = splat_f32x2(ww.x), W01 = splat_f32x2(ww.y), W10 = splat_f32x2(ww.z), W11 = splat_f32x2(ww.w);
+      float v0, v1, v2, v3;
+      wsum(ua0, ub0, uc0, ud0, W00, W01, W10, W11, v0, v1);
+      wsum(ua1, ub1, uc1, ud1, W00, W01, W10, W11, v2, v3);
+      if (SPLIT) {
+        float u0, u1, u2, u3;
+        wsum(la0, lb0, lc0, ld0, W00, W01, W10, W11, u0, u1);
+        wsum(la1, lb1, lc1, ld1, W00, W01, W10, W11, u2, u3);
+        v0 += u0; v1 += u1; v2 += u2; v3 += u3;
+      }
+      if (NOVEL) {                                                 // final_latent = gen_latent + latent (novel_pixelnerf.py:196)
+        const uint4 gp = *reinterpret_cast<const uint4*>(&gen_s[l].p00);
+        const float4 gw = *reinterpret_cast<const float4*>(&gen_s[l].w00);
+        if (gp.x != gcur00 || gp.w != gcur11) {
+          ga = __ldg(reinterpret_cast<const uint2*>(glat + gp.x)); gb = __ldg(reinterpret_cast<const uint2*>(glat + gp.y));
+          gc = __ldg(reinterpret_cast<const uint2*>(glat + gp.z)); gd = __ldg(reinterpret_cast<const uint2*>(glat + gp.w));
+          gcur00 = gp.x; gcur11 = gp.w;
         }
-        *reinterpret_cast<uint2*>(dst0 + l * 16) = o;
-        if (SPLIT) *reinterpret_cast<uint2*>(dst0_lo + l * 16) = o_lo;
+        const uint64_t G00 = splat_f32x2(gw.x), G01 = splat_f32x2(gw.y), G10 = splat_f32x2(gw.z), G11 = splat_f32x2(gw.w);
+        float u0, u1, u2, u3;
+        u0 = blend4_lo(ga.x, gb.x, gc.x, gd.x, G00, G01, G10, G11, u1);
+        u2 = blend4_lo(ga.y, gb.y, gc.y, gd.y, G00, G01, G10, G11, u3);
+        v0 = u0 + v0; v1 = u1 + v1; v2 = u2 + v2; v3 = u3 + v3;
+      }
+      const uint2 o = make_uint2(pack_bf16x2(v0, v1), pack_bf16x2(v2, v3));
+      *reinterpret_cast<uint2*>(dst0 + l * 16) = o;
+      if (SPLIT)
+        *reinterpret_cast<uint2*>(dst0_lo + l * 16) =
+            make_uint2(pack_bf16x2(v0 - bf16lo(o.x), v1 - bf16hi(o.x)), pack_bf16x2(v2 - bf16lo(o.y), v3 - bf16hi(o.y)));
+    };
+    for (int v = 0; v < rm.NV; ++v) {
+      for (int s0 = 0; s0 < rm.SPW; s0 += 4) {
+        uint4 pp[4]; float4 ww[4]; bool in[4], live[4], need[4];
+        Foot f[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          in[j] = s0 + j < rm.SPW;
+          const int l = in[j] ? (s0 + j) * rm.NV + v : 0;
+          pp[j] = *reinterpret_cast<const uint4*>(&taps_s[l].p00);
+          ww[j] = *reinterpret_cast<const float4*>(&taps_s[l].w00);
+          live[j] = in[j] && taps_s[l].map_plus1 != 0u;
+          need[j] = live[j] && (pp[j].x != prev00 || pp[j].w != prev11);      // p00 fixes (map, x0, y0), p11 the clamps
+          if (live[j]) { prev00 = pp[j].x; prev11 = pp[j].w; }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (need[j]) fetch(f[j], pp[j]);                                    // (warp-uniform)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (!in[j]) continue;
+          const int l = (s0 + j) * rm.NV + v;
+          if (!live[j]) {
+            *reinterpret_cast<uint2*>(dst0 + l * 16) = make_uint2(0, 0);
+            if (SPLIT) *reinterpret_cast<uint2*>(dst0_lo + l * 16) = make_uint2(0, 0);
+            continue;
+          }
+          // a row that opens a new footprint unpacks it (its taps were requested with the batch); the others reuse it
+          if (j == 0 && need[0]) unpack(f[0]);
+          if (j == 1 && need[1]) unpack(f[1]);
+          if (j == 2 && need[2]) unpack(f[2]);
+          if (j == 3 && need[3]) unpack(f[3]);
+          blend_store(ww[j], l);
+        }
       }
     }
     for (int l = n_live; l < 32; ++l) {                            // padding rows of the slab (NV = 3: rows 30, 31)
@@ -315,6 +431,167 @@ __global__ void __launch_bounds__(kEncWarps * 32) encode_fwd_kernel(EncodeParams
     }
   }
 }
+
+// ---- production gather (no SPLIT / NOVEL): one warp per 8 rows, 16 channels per lane, every row loads its four taps.
+// Round 2 measured three footprint-reusing variants of the slab kernel above against it on the same B200
+// (profiles/r2_encode.md): they cut the L2 -> SM tap traffic by a third (2.7 instead of 4.1 KB per row) but none was
+// faster -- the gather is bound by ALU issue (bf16 -> fp32 unpacking, address and footprint bookkeeping), not by tap
+// bytes: 2.20 ms per FaceScape frame here, 2.30 / 2.79 ms for the 2- / 4-warp slab kernels.  The slab kernel stays for
+// the SPLIT and NOVEL instantiations, where clarity matters more than the last 20 %.
+constexpr int kEnc8Warps = 4;
+constexpr int kRows8LatStride = 144;   // 8 rows * 16 B + 16 B pad -> conflict-free staging
+
+// per-row tap description, produced by one lane per row and read back by the whole warp (broadcast LDS)
+struct __align__(16) RowTaps8 {
+  uint32_t p00, p01, p10, p11;      // element offsets of the four taps inside the whole latent (all maps)
+  float w00, w01, w10, w11;
+  float xc, yc, zc, dx, dy, dz, dd;
+  uint32_t map_plus1;               // (sb*NV + view) + 1, 0 = padding row
+};
+
+__global__ void __launch_bounds__(kEnc8Warps * 32) encode_fwd_rows8_kernel(EncodeParams P) {
+  __shared__ __align__(16) unsigned char stage_lat[kEnc8Warps][64 * kRows8LatStride];
+  __shared__ __align__(16) unsigned char stage_in[kEnc8Warps][8 * 128];
+  __shared__ RowTaps8 taps_s[kEnc8Warps][8];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const RowMap rm = RowMap::make(P.NV);
+  const long long group = (long long)blockIdx.x * kEnc8Warps + warp;   // 8-row group index
+  const long long row_base = group * 8;
+  unsigned char* sl = stage_lat[warp];
+  unsigned char* si = stage_in[warp];
+  const int L = 512;
+
+  // phase 1: lanes 0..7 run the projection chain of one row each (the eight chains overlap instead of running
+  // back to back on all 32 lanes)
+  if (lane < 8) {
+    long long sample; int view;
+    RowTaps8 tp;
+    tp.map_plus1 = 0;
+    if (rm.decode(row_base + lane, P.n_samples, sample, view)) {
+      RowGeom g;
+      row_geometry(P, sample, view, g);
+      const size_t mb = g.map * (size_t)P.Hl * P.Wl;          // texels before this (scene, view) map; the whole latent holds < 2^32 elements
+      tp.p00 = (uint32_t)((mb + (size_t)g.y0 * P.Wl + g.x0) * L); tp.p01 = (uint32_t)((mb + (size_t)g.y0 * P.Wl + g.x1) * L);
+      tp.p10 = (uint32_t)((mb + (size_t)g.y1 * P.Wl + g.x0) * L); tp.p11 = (uint32_t)((mb + (size_t)g.y1 * P.Wl + g.x1) * L);
+      tp.w00 = (1.f - g.wx) * (1.f - g.wy); tp.w01 = g.wx * (1.f - g.wy);
+      tp.w10 = (1.f - g.wx) * g.wy; tp.w11 = g.wx * g.wy;
+      tp.xc = g.xc; tp.yc = g.yc; tp.zc = g.zc; tp.dx = g.dx; tp.dy = g.dy; tp.dz = g.dz; tp.dd = g.dd;
+      tp.map_plus1 = (uint32_t)g.map + 1u;
+    }
+    taps_s[warp][lane] = tp;
+  }
+  __syncwarp();
+
+  // phase 1b: the 55-wide geometric code of the 8 rows (zero-padded to 64).  The 48 sines of a row are spread over the
+  // warp as 8 x 48 = 384 = 12 full-warp evaluations, one branch-free sinf each; the 16 plain elements follow.
+  {
+    constexpr int NF = 6;                    // required by fill_encode_params (55-wide code)
+    constexpr int npos = 3 + 6 * NF;         // 39
+    constexpr int nsin_pos = 6 * NF, nsin = 8 * NF;      // 36, 48
+    // 3 x 32 lanes cover the 2 x 48 sines of a row pair, so a lane meets only three (element, frequency, coordinate)
+    // combinations: q = lane (row 2m), lane + 32 or lane - 16 (row 2m or 2m + 1), lane + 16 (row 2m + 1).  Everything
+    // that depends on q alone is hoisted out of the loop over the four row pairs.
+    int q3[3] = {lane, lane < 16 ? lane + 32 : lane - 16, lane + 16};
+    const int r3[3] = {0, lane < 16 ? 0 : 1, 1};                    // row of the pair
+    int foff[3], sto[3]; float fr[3], ph[3];
+#pragma unroll
+    for (int u = 0; u < 3; ++u) {
+      const int q = q3[u];
+      int e, fs;
+      if (q < nsin_pos) { fs = q / 3; e = 3 + q; foff[u] = q % 3; }            // xc, yc, zc
+      else { fs = q - nsin_pos; e = npos + 4 + fs; foff[u] = 6; }              // dd
+      fr[u] = P.freqs[fs]; ph[u] = P.phases[fs];
+      sto[u] = (e >> 3) * 128 + (e & 7) * 2;                                    // byte offset inside the staged code tile
+    }
+#pragma unroll
+    for (int m = 0; m < 4; ++m) {
+#pragma unroll
+      for (int u = 0; u < 3; ++u) {
+        const int i = 2 * m + r3[u];
+        const RowTaps8& tp = taps_s[warp][i];
+        const float x = (&tp.xc)[foff[u]];
+        float val = sinf(__fadd_rn(ph[u], __fmul_rn(x, fr[u])));
+        if (!tp.map_plus1) val = 0.f;
+        *reinterpret_cast<__nv_bfloat16*>(si + sto[u] + i * 16) = __float2bfloat16_rn(val);
+      }
+    }
+    // the 16 plain elements of a row (x_cam 3 | dir_cam 3 | depth distance 1 | 9 zeros): lane & 15 fixes the element, two
+    // rows per iteration
+    {
+      const int r = lane & 15;
+      int e, fo = -1;                                              // fo: field offset from RowTaps::xc, -1 = zero padding
+      if (r < 3) { e = r; fo = r; }                                // xc, yc, zc
+      else if (r < 6) { e = npos + (r - 3); fo = r; }              // dx, dy, dz
+      else if (r == 6) { e = npos + 3; fo = 6; }                   // dd
+      else e = npos + 4 + 2 * NF + (r - 7);
+      const int so = (e >> 3) * 128 + (e & 7) * 2;
+#pragma unroll
+      for (int m = 0; m < 4; ++m) {
+        const int i = 2 * m + (lane >> 4);
+        const RowTaps8& tp = taps_s[warp][i];
+        float val = fo >= 0 ? (&tp.xc)[fo] : 0.f;
+        if (!tp.map_plus1) val = 0.f;
+        *reinterpret_cast<__nv_bfloat16*>(si + so + i * 16) = __float2bfloat16_rn(val);
+      }
+    }
+  }
+
+  // phase 2: the warp gathers row after row, two rows' loads in flight
+#pragma unroll 2
+  for (int i = 0; i < 8; ++i) {
+    const RowTaps8 tp = taps_s[warp][i];
+    uint4 o0 = make_uint4(0, 0, 0, 0), o1 = o0;
+    if (tp.map_plus1) {
+      const __nv_bfloat16* lat = P.latent;
+      const uint64_t W00 = splat_f32x2(tp.w00), W01 = splat_f32x2(tp.w01), W10 = splat_f32x2(tp.w10), W11 = splat_f32x2(tp.w11);
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const int ch = half * 256 + lane * 8;
+        const uint4 a = __ldg(reinterpret_cast<const uint4*>(lat + tp.p00 + ch));
+        const uint4 b = __ldg(reinterpret_cast<const uint4*>(lat + tp.p01 + ch));
+        const uint4 c = __ldg(reinterpret_cast<const uint4*>(lat + tp.p10 + ch));
+        const uint4 d = __ldg(reinterpret_cast<const uint4*>(lat + tp.p11 + ch));
+        const uint32_t av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+        const uint32_t cv[4] = {c.x, c.y, c.z, c.w}, dv[4] = {d.x, d.y, d.z, d.w};
+        uint32_t r[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          // both channels of a bf16x2 word in one packed fp32 operation (FMUL2 / FFMA2): a*w00, then fma by fma in
+          // tap order -- the same roundings as the scalar chain
+          uint64_t acc = mul_f32x2(bf16x2_to_f32x2(av[q]), W00);
+          acc = fma_f32x2(bf16x2_to_f32x2(bv[q]), W01, acc);
+          acc = fma_f32x2(bf16x2_to_f32x2(cv[q]), W10, acc);
+          acc = fma_f32x2(bf16x2_to_f32x2(dv[q]), W11, acc);
+          float lo, hi;
+          asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(acc));
+          r[q] = pack_bf16x2(lo, hi);
+        }
+        if (half == 0) o0 = make_uint4(r[0], r[1], r[2], r[3]); else o1 = make_uint4(r[0], r[1], r[2], r[3]);
+      }
+    }
+    *reinterpret_cast<uint4*>(sl + lane * kRows8LatStride + i * 16) = o0;
+    *reinterpret_cast<uint4*>(sl + (32 + lane) * kRows8LatStride + i * 16) = o1;
+  }
+  __syncwarp();
+  // write-out: every 8 lanes move one 128-byte line (8 rows x 16 B of one feature chunk)
+  const long long tile = row_base / 128;
+  const int rr = (int)(row_base % 128);
+  unsigned char* lat_tile = P.lat_pk + (size_t)tile * (512 / 8) * 2048;
+  unsigned char* in_tile = P.in_pk + (size_t)tile * (64 / 8) * 2048;
+#pragma unroll 4
+  for (int it = 0; it < 16; ++it) {
+    const int c = it * 4 + (lane >> 3), i = lane & 7;
+    const uint4 v = *reinterpret_cast<const uint4*>(sl + c * kRows8LatStride + i * 16);
+    *reinterpret_cast<uint4*>(lat_tile + (size_t)c * 2048 + (size_t)(rr + i) * 16) = v;
+  }
+#pragma unroll
+  for (int it = 0; it < 2; ++it) {
+    const int c = it * 4 + (lane >> 3), i = lane & 7;
+    const uint4 v = *reinterpret_cast<const uint4*>(si + c * 128 + i * 16);
+    *reinterpret_cast<uint4*>(in_tile + (size_t)c * 2048 + (size_t)(rr + i) * 16) = v;
+  }
+}
+
 
 __device__ __forceinline__ void red_add_v4(float* addr, float4 v) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
@@ -447,6 +724,8 @@ static int fill_encode_params(dnr::EncodeParams& P, const float* rays, const flo
   P.n_samples = n_rays * K; P.ray_offset = ray_offset; P.n_rays = n_rays;
   DNR_REQUIRE(ray_offset >= 0 && ray_offset + n_rays <= (long long)SB * NR, "encode: ray chunk out of range");
   P.lat_pk = nullptr; P.in_pk = nullptr; P.d_latent = nullptr; P.d_lat_xr = nullptr;
+  P.pts_in = nullptr; P.pts_gen = nullptr; P.gen_poses = nullptr; P.gen_focal = nullptr; P.gen_cxy = nullptr;
+  P.gen_latent = nullptr; P.Hg = P.Wg = 0; P.gen_img_w = P.gen_img_h = P.gen_sx = P.gen_sy = 0.f;
   return 0;
 }
 
@@ -459,17 +738,20 @@ DNR_EXPORT int dnr_view_row_tiles(long long n_samples, int NV) {
 static int launch_encode_fwd(dnr::EncodeParams& P, int NV, const void* latent_lo, void* lat_pk_lo, void* in_pk_lo,
                              cudaStream_t stream) {
   if (P.n_samples <= 0) return 0;
-  const bool split = latent_lo != nullptr;
+  const bool split = latent_lo != nullptr, novel = P.gen_latent != nullptr;
   const int tiles = dnr::RowMap::make(NV).tiles_for(P.n_samples);
   const int slabs = tiles * 4;
-  const int smem = (dnr::kEncLatBytes + dnr::kEncInBytes) * (split ? 2 : 1) + 32 * (int)sizeof(dnr::RowTaps);
+  const int smem = (dnr::kEncLatBytes + dnr::kEncInBytes) * (split ? 2 : 1) + 32 * (int)sizeof(dnr::RowTaps) +
+                   (novel ? 32 * (int)sizeof(dnr::GenTaps) : 0);
   if (split) {
-    DNR_CHECK(cudaFuncSetAttribute(dnr::encode_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
+    DNR_CHECK(cudaFuncSetAttribute(dnr::encode_fwd_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
               "dnr_encode_fwd_split/attr");
-    dnr::encode_fwd_kernel<true><<<slabs, dnr::kEncWarps * 32, smem, stream>>>(
+    dnr::encode_fwd_kernel<true, false><<<slabs, dnr::kEncWarps * 32, smem, stream>>>(
         P, (const __nv_bfloat16*)latent_lo, (unsigned char*)lat_pk_lo, (unsigned char*)in_pk_lo);
+  } else if (novel) {
+    dnr::encode_fwd_kernel<false, true><<<slabs, dnr::kEncWarps * 32, smem, stream>>>(P, nullptr, nullptr, nullptr);
   } else {
-    dnr::encode_fwd_kernel<false><<<slabs, dnr::kEncWarps * 32, smem, stream>>>(P, nullptr, nullptr, nullptr);
+    dnr::encode_fwd_rows8_kernel<<<tiles * 16 / dnr::kEnc8Warps, dnr::kEnc8Warps * 32, 0, stream>>>(P);
   }
   return 0;
 }
@@ -513,6 +795,37 @@ DNR_EXPORT int dnr_encode_fwd_split(const float* rays, const float* z, const flo
   rc = launch_encode_fwd(P, NV, latent_lo, lat_pk_lo, in_pk_lo, stream);
   if (rc) return rc;
   DNR_CHECK_LAUNCH("dnr_encode_fwd_split");
+  return 0;
+}
+
+// NOVEL variant of dnr_encode_fwd (src/models/novel/novel_pixelnerf.py:143-241): pts_in / pts_gen [n_rays*K, 3] are the
+// chunk's sample points deformed with tgt_in_offsets / tgt_gen_offsets (dnr_novel_deform); pts_in replaces o + z d in the
+// projection chain, pts_gen is projected by the generic camera (gen_poses [SB,1,4,4], gen_focal / gen_cxy [SB,1,2],
+// gen_img_w/h) into gen_latent_nhwc [Hg,Wg,512] bf16 (feature-padding rescale gen_sx / gen_sy), and the feature row is
+// gen_latent[gen_uv] + latent[uv].  Forward only (the variant is built for evaluation).
+DNR_EXPORT int dnr_encode_novel_fwd(const float* rays, const float* z, const float* pts_in, const float* pts_gen,
+                                    const float* poses, const float* focal, const float* cxy, const float* depth,
+                                    const void* latent_nhwc_bf16, const float* gen_poses, const float* gen_focal,
+                                    const float* gen_cxy, const void* gen_latent_nhwc_bf16, int Hg, int Wg,
+                                    float gen_img_w, float gen_img_h, float gen_sx, float gen_sy, const float* freqs,
+                                    const float* phases, int SB, int NV, int NR, int K, int H, int W, int Hl, int Wl, int L,
+                                    int NF, long long ray_offset, long long n_rays, float img_w, float img_h, float lat_sx,
+                                    float lat_sy, void* lat_pk, void* in_pk, cudaStream_t stream) {
+  dnr::EncodeParams P;
+  int rc = fill_encode_params(P, rays, z, poses, focal, cxy, depth, latent_nhwc_bf16, freqs, phases, SB, NV, NR, K, H,
+                              W, Hl, Wl, L, NF, ray_offset, n_rays, img_w, img_h, lat_sx, lat_sy);
+  if (rc) return rc;
+  DNR_REQUIRE((unsigned long long)SB * NV * Hl * Wl * L < (1ull << 32), "dnr_encode_novel_fwd: latent too large");
+  DNR_REQUIRE(latent_nhwc_bf16 && lat_pk && in_pk && pts_in && pts_gen && gen_poses && gen_focal && gen_cxy &&
+              gen_latent_nhwc_bf16, "dnr_encode_novel_fwd: null argument");
+  DNR_REQUIRE(Hg >= 1 && Wg >= 1 && (unsigned long long)Hg * Wg * L < (1ull << 32), "dnr_encode_novel_fwd: bad gen_latent size");
+  P.lat_pk = (unsigned char*)lat_pk; P.in_pk = (unsigned char*)in_pk;
+  P.pts_in = pts_in; P.pts_gen = pts_gen; P.gen_poses = gen_poses; P.gen_focal = gen_focal; P.gen_cxy = gen_cxy;
+  P.gen_latent = (const __nv_bfloat16*)gen_latent_nhwc_bf16; P.Hg = Hg; P.Wg = Wg;
+  P.gen_img_w = gen_img_w; P.gen_img_h = gen_img_h; P.gen_sx = gen_sx; P.gen_sy = gen_sy;
+  rc = launch_encode_fwd(P, NV, nullptr, nullptr, nullptr, stream);
+  if (rc) return rc;
+  DNR_CHECK_LAUNCH("dnr_encode_novel_fwd");
   return 0;
 }
 

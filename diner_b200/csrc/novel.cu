@@ -1,0 +1,141 @@
+// NOVEL renderer variant (reference src/models/novel/nerf_novel_renderer.py, src/models/novel/novel_pixelnerf.py):
+// nearest-vertex deformation of every sampler CANDIDATE (nerf_novel_renderer.py:104-107) and of every SAMPLE point
+// (twice: tgt_in_offsets / tgt_gen_offsets, :441-442) -- K = 1 nearest neighbour against the target mesh
+// (pytorch3d.ops.knn_points: squared L2, first minimum), offset gather, add.
+//
+// A frame has SB*NR*C = 65.5 M candidates against ~5 000 vertices: brute force (csrc/deform.cu, 3e12 pairs/s) would cost
+// 110 ms per FaceScape frame, three times the whole DINER render.  Here the vertices arrive sorted along a Morton curve
+// in groups of 32 with a bounding sphere per group (diner_b200/novel.py builds them per mesh, ~0.1 ms): a query first
+// takes the smallest upper bound min_g(|x - c_g| + r_g) over the spheres, then scans only the groups whose lower bound
+// |x - c_g| - r_g does not exceed it.  The pruning is conservative (every vertex that can be the minimum or tie with it
+// is scanned) and the scanned distances use the brute-force kernel's arithmetic (x, y, z accumulated with fused
+// multiply-adds) with ties going to the lowest ORIGINAL index, so the result equals the brute force bit for bit.
+//
+// The candidate positions are recomputed exactly as csrc/sampler.cu computes them (same jitter, same op order; this file
+// is compiled with --fmad=false like the sampler), so the offsets land on the very candidates the sampler scores.
+#include "common.cuh"
+
+namespace dnr {
+
+struct NovelParams {
+  const float* rays;        // [SB*NR, 8]
+  const float* z;           // samples mode: [SB*NR, K]
+  const float* lin_tab;     // candidates mode: [C]
+  const float* u_coarse;    // candidates mode: [SB*NR, C] or null (Philox)
+  unsigned long long seed;
+  const float4* verts;      // [SB][G*32] Morton-sorted (x, y, z, original index as int bits); padding: +huge, INT_MAX
+  const float4* spheres;    // [SB][G] (cx, cy, cz, r)
+  const float* off_a;       // [SB][V][3] offsets indexed by ORIGINAL vertex index (tgt_in_offsets)
+  const float* off_b;       // samples mode: tgt_gen_offsets, or null
+  int SB, NR, per_ray, V, G;
+  float inv_c_step;
+  float* out_a;             // candidates: offsets [SB*NR, C, 3]; samples: deformed points [SB*NR*K, 3] (in)
+  float* out_b;             // samples: deformed points (gen), or null
+  int* idx_out;             // optional nearest-vertex index per query
+};
+
+constexpr int kNovelThreads = 256;
+
+template <bool CANDIDATES>
+__global__ void __launch_bounds__(kNovelThreads) novel_deform_kernel(const NovelParams P) {
+  extern __shared__ float4 sph[];
+  const int sb = blockIdx.y;
+  const float4* sp = P.spheres + (size_t)sb * P.G;
+  for (int g = threadIdx.x; g < P.G; g += blockDim.x) sph[g] = sp[g];
+  __syncthreads();
+  const long long per_scene = (long long)P.NR * P.per_ray;
+  const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;     // query inside the scene
+  if (q >= per_scene) return;
+  const long long ray = (long long)sb * P.NR + q / P.per_ray;
+  const int i = (int)(q % P.per_ray);
+  const float* rp = P.rays + ray * 8;
+  const float o0 = rp[0], o1 = rp[1], o2 = rp[2], d0 = rp[3], d1 = rp[4], d2 = rp[5];
+  float zc;
+  if (CANDIDATES) {
+    // sampler.cu, stage 1: u from the recorded draws or from Philox counter (ray, i >> 2), component i & 3
+    float u;
+    if (P.u_coarse) u = P.u_coarse[ray * P.per_ray + i];
+    else {
+      Philox rng(P.seed);
+      const uint4 r = rng((uint32_t)ray, (uint32_t)(ray >> 32), (uint32_t)(i >> 2), 0u);
+      const int c = i & 3;
+      u = u01(c == 0 ? r.x : c == 1 ? r.y : c == 2 ? r.z : r.w);
+    }
+    const float near = rp[6], far = rp[7];
+    const float s = P.lin_tab[i] + u * P.inv_c_step;       // nerf_novel_renderer.py:70-73
+    zc = near * (1.0f - s) + far * s;                      // :76
+  } else {
+    zc = P.z[ray * P.per_ray + i];
+  }
+  const float x0 = o0 + zc * d0, x1 = o1 + zc * d1, x2 = o2 + zc * d2;      // :93 / :416
+  // pass 1: the smallest upper bound on the nearest-vertex distance
+  float ub = 3.0e38f;
+  for (int g = 0; g < P.G; ++g) {
+    const float4 s = sph[g];
+    const float a = x0 - s.x, b = x1 - s.y, c = x2 - s.z;
+    ub = fminf(ub, sqrtf(a * a + b * b + c * c) + s.w);
+  }
+  const float thr = ub * 1.00001f + 1e-7f;                 // slack for the roundings of the two bounds
+  // pass 2: scan the groups that can hold the minimum
+  float best = 3.0e38f;
+  int best_i = 0x7fffffff;
+  const float4* vs = P.verts + (size_t)sb * P.G * 32;
+  for (int g = 0; g < P.G; ++g) {
+    const float4 s = sph[g];
+    const float a = x0 - s.x, b = x1 - s.y, c = x2 - s.z;
+    if (sqrtf(a * a + b * b + c * c) - s.w > thr) continue;
+    const float4* vg = vs + (size_t)g * 32;
+#pragma unroll 8
+    for (int j = 0; j < 32; ++j) {
+      const float4 v = __ldg(vg + j);
+      const float e0 = x0 - v.x, e1 = x1 - v.y, e2 = x2 - v.z;
+      const float dd = fmaf(e2, e2, fmaf(e1, e1, e0 * e0));          // the brute-force kernel's arithmetic (deform.cu)
+      const int vi = __float_as_int(v.w);
+      if (dd < best || (dd == best && vi < best_i)) { best = dd; best_i = vi; }
+    }
+  }
+  const size_t qq = (size_t)sb * per_scene + q;
+  if (P.idx_out) P.idx_out[qq] = best_i;
+  const float* oa = P.off_a + ((size_t)sb * P.V + best_i) * 3;
+  if (CANDIDATES) {
+    P.out_a[qq * 3 + 0] = oa[0]; P.out_a[qq * 3 + 1] = oa[1]; P.out_a[qq * 3 + 2] = oa[2];
+  } else {
+    P.out_a[qq * 3 + 0] = x0 + oa[0]; P.out_a[qq * 3 + 1] = x1 + oa[1]; P.out_a[qq * 3 + 2] = x2 + oa[2];     // :48-49
+    if (P.out_b) {
+      const float* ob = P.off_b + ((size_t)sb * P.V + best_i) * 3;
+      P.out_b[qq * 3 + 0] = x0 + ob[0]; P.out_b[qq * 3 + 1] = x1 + ob[1]; P.out_b[qq * 3 + 2] = x2 + ob[2];
+    }
+  }
+}
+
+}  // namespace dnr
+
+// Offsets of the sampler's candidates (mode = candidates: per_ray = C, z from lin_tab + jitter exactly as dnr_sampler_fwd
+// draws it; out_a = offsets [SB*NR, C, 3] for dnr_sampler_fwd's cand_offset) or deformed sample points (mode = samples:
+// per_ray = K, z given; out_a / out_b = points + in / gen offsets, [SB*NR*K, 3]) of the NOVEL renderer variant
+// (nerf_novel_renderer.py:40-50,104-107,441-442).  verts_sorted [SB][G*32] float4 (x, y, z, original index bits) and
+// spheres [SB][G] float4 (centre, radius) come from diner_b200.novel.build_vertex_groups; offsets are indexed by original
+// vertex index [SB][V][3].
+DNR_EXPORT int dnr_novel_deform(const float* rays, const float* z, const float* lin_tab, const float* u_coarse,
+                                unsigned long long seed, const void* verts_sorted, const void* spheres,
+                                const float* offsets_a, const float* offsets_b, int SB, int NR, int per_ray, int V, int G,
+                                int candidates, float* out_a, float* out_b, int* idx_out, cudaStream_t stream) {
+  DNR_REQUIRE(rays && verts_sorted && spheres && offsets_a && out_a, "dnr_novel_deform: null argument");
+  DNR_REQUIRE(SB >= 1 && NR >= 0 && per_ray >= 1 && V >= 1 && G >= 1 && G <= 2048, "dnr_novel_deform: bad sizes (G <= 2048)");
+  DNR_REQUIRE(candidates ? (lin_tab != nullptr) : (z != nullptr), "dnr_novel_deform: candidates need lin_tab, samples need z");
+  DNR_REQUIRE(SB <= 65535, "dnr_novel_deform: at most 65535 scenes per call");
+  if (NR == 0) return 0;
+  dnr::NovelParams P;
+  P.rays = rays; P.z = z; P.lin_tab = lin_tab; P.u_coarse = u_coarse; P.seed = seed;
+  P.verts = (const float4*)verts_sorted; P.spheres = (const float4*)spheres; P.off_a = offsets_a; P.off_b = offsets_b;
+  P.SB = SB; P.NR = NR; P.per_ray = per_ray; P.V = V; P.G = G;
+  P.inv_c_step = (float)(1.0 / (double)per_ray);
+  P.out_a = out_a; P.out_b = out_b; P.idx_out = idx_out;
+  const long long per_scene = (long long)NR * per_ray;
+  dim3 grid((unsigned)((per_scene + dnr::kNovelThreads - 1) / dnr::kNovelThreads), SB);
+  const size_t smem = (size_t)G * sizeof(float4);
+  if (candidates) dnr::novel_deform_kernel<true><<<grid, dnr::kNovelThreads, smem, stream>>>(P);
+  else dnr::novel_deform_kernel<false><<<grid, dnr::kNovelThreads, smem, stream>>>(P);
+  DNR_CHECK_LAUNCH("dnr_novel_deform");
+  return 0;
+}

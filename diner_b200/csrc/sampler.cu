@@ -29,6 +29,7 @@ struct SamplerParams {
   const float* u_fill;    // packed [n_missing] or null
   const int* gauss_off;   // [SB*NR] exclusive prefix of ray_mask (with n_gauss)
   const int* fill_off;    // [SB*NR] exclusive prefix of n_missing (with u_fill)
+  const float* cand_off;  // [SB*NR, C, 3] or null: NOVEL variant, per-candidate deformation (dnr_novel_deform)
   unsigned long long seed;
   int SB, NV, NR, H, W, C, K, G, P;
   float depth_diff_max, img_w, img_h, std_sx, std_sy, inv_c_step;
@@ -125,6 +126,10 @@ __global__ void __launch_bounds__(kSamplerWarps * 32) sampler_kernel(SamplerPara
         const float zc = near * (1.0f - s) + far * s;     // :60
         zq[q] = zc;
         x0[q] = o0 + zc * d0; x1[q] = o1 + zc * d1; x2[q] = o2 + zc * d2;   // :96
+        if (P.cand_off) {                                 // novel/nerf_novel_renderer.py:104-107 (deform_points)
+          const float* co = P.cand_off + ((size_t)ray * C + i) * 3;
+          x0[q] += co[0]; x1[q] += co[1]; x2[q] += co[2];
+        }
       }
     }
     for (int v = 0; v < NV; ++v) {
@@ -345,7 +350,8 @@ DNR_EXPORT int dnr_pad_depth_std(const float* depth_std, const float* gain_tab, 
 DNR_EXPORT int dnr_sampler_fwd(const float* rays, const float* poses, const float* focal, const float* cxy,
                                const float* depth, const float* depth_std_padded, const float* normal,
                                const float* lin_tab, const float* u_coarse, const float* n_gauss, const float* u_fill,
-                               const int* gauss_off, const int* fill_off, unsigned long long seed, int SB, int NV,
+                               const int* gauss_off, const int* fill_off, const float* cand_offset,
+                               unsigned long long seed, int SB, int NV,
                                int NR, int H, int W, int C, int K, int G, int pad, float depth_diff_max, float img_w,
                                float img_h, float std_sx, float std_sy, int count_only, int unpacked_noise,
                                float* z_out,
@@ -361,7 +367,7 @@ DNR_EXPORT int dnr_sampler_fwd(const float* rays, const float* poses, const floa
   dnr::SamplerParams P;
   P.rays = rays; P.poses = poses; P.focal = focal; P.cxy = cxy; P.depth = depth; P.stdpad = depth_std_padded;
   P.normal = normal; P.lin_tab = lin_tab; P.u_coarse = u_coarse; P.n_gauss = n_gauss; P.u_fill = u_fill;
-  P.gauss_off = gauss_off; P.fill_off = fill_off; P.seed = seed;
+  P.gauss_off = gauss_off; P.fill_off = fill_off; P.cand_off = cand_offset; P.seed = seed;
   P.SB = SB; P.NV = NV; P.NR = NR; P.H = H; P.W = W; P.C = C; P.K = K; P.G = G; P.P = pad;
   P.depth_diff_max = depth_diff_max; P.img_w = img_w; P.img_h = img_h; P.std_sx = std_sx; P.std_sy = std_sy;
   {

@@ -208,12 +208,13 @@ def _encode_args(sc: SceneBuffers, NR: int, K: int, ray0: int, n_rays: int):
 
 
 def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.Tensor, NR: int, ray0: int,
-                  save: bool, out: torch.Tensor = None, precision: str = "bf16"):
+                  save: bool, out: torch.Tensor = None, precision: str = "bf16", novel: dict = None):
     """Evaluate the field on one chunk of rays.
 
     rays (n,8) / z (n,K) are the chunk's rows of the flattened (SB*NR) batch, `ray0` the index of its first
     ray in that batch (the scene of a ray is ray // NR).  Returns (rgbsigma (n*K,4) fp32, FieldSaved | None);
-    `out` (contiguous (n*K,4) fp32) receives the result in place when given.
+    `out` (contiguous (n*K,4) fp32) receives the result in place when given.  `novel` (diner_b200.novel, inference only):
+    the chunk's deformed sample points and the generic camera / learned map of the NOVEL variant.
     """
     p, st = _lib.ptr, _lib.stream_ptr()
     dev = rays.device
@@ -232,8 +233,16 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
 
     lat = torch.empty(mv * 128 * HID, **bf)
     code = torch.empty(mv * 128 * IN_PAD, **bf)
-    _lib.call("dnr_encode_fwd", p(rays), p(z), p(sc.poses), p(sc.focal), p(sc.cxy), p(sc.depth), p(sc.latent_nhwc),
-              p(sc.freqs), p(sc.phases), *_encode_args(sc, NR, K, ray0, n), p(lat), p(code), st)
+    if novel is not None:
+        assert not save, "the NOVEL variant is forward-only"
+        g = novel
+        _lib.call("dnr_encode_novel_fwd", p(rays), p(z), p(g["pts_in"]), p(g["pts_gen"]), p(sc.poses), p(sc.focal),
+                  p(sc.cxy), p(sc.depth), p(sc.latent_nhwc), p(g["poses"]), p(g["focal"]), p(g["cxy"]), p(g["latent"]),
+                  g["Hg"], g["Wg"], g["img_w"], g["img_h"], g["sx"], g["sy"], p(sc.freqs), p(sc.phases),
+                  *_encode_args(sc, NR, K, ray0, n), p(lat), p(code), st)
+    else:
+        _lib.call("dnr_encode_fwd", p(rays), p(z), p(sc.poses), p(sc.focal), p(sc.cxy), p(sc.depth), p(sc.latent_nhwc),
+                  p(sc.freqs), p(sc.phases), *_encode_args(sc, NR, K, ray0, n), p(lat), p(code), st)
 
     if not save and FORWARD_KERNEL in ("quad", "pair") and NV <= 4:
         # inference: CTA-cluster kernels, residual stream in TMEM, lin_out fused (csrc/mlp_pair.cu)

@@ -34,7 +34,7 @@ class RenderResult(dict):
 
 
 def sample_rays(sc: SceneBuffers, rays: torch.Tensor, K: int, C: int, G: int, noise: dict | None = None,
-                seed: int | None = None, want_debug: bool = False):
+                seed: int | None = None, want_debug: bool = False, cand_offset=None):
     """Depth-guided sampling + fill-up + sort for rays (SB,NR,8) -> z (SB*NR, K).
 
     noise=None: in-kernel Philox jitter (no host sync).  noise=dict(u_coarse (SB*NR,C), n_gauss (n_masked,G)
@@ -59,7 +59,8 @@ def sample_rays(sc: SceneBuffers, rays: torch.Tensor, K: int, C: int, G: int, no
 
     def launch(u_coarse, n_gauss, u_fill, goff, foff, count_only, rm, nm, sl, pc=None, unpacked=False):
         _lib.call("dnr_sampler_fwd", p(rays), p(sc.poses), p(sc.focal), p(sc.cxy), p(sc.depth), p(sc.std_padded),
-                  p(sc.normal), p(lin), p(u_coarse), p(n_gauss), p(u_fill), p(goff), p(foff), seed & (2 ** 64 - 1),
+                  p(sc.normal), p(lin), p(u_coarse), p(n_gauss), p(u_fill), p(goff), p(foff), p(cand_offset),
+                  seed & (2 ** 64 - 1),
                   SB, sc.NV, NR, sc.H, sc.W, C, K, G, STD_PAD, DEPTH_DIFF_MAX, sc.img_w, sc.img_h, sc.std_sx, sc.std_sy,
                   1 if count_only else 0, 1 if unpacked else 0, p(z), p(rm), p(nm), p(sl), p(pc), st)
 

@@ -92,11 +92,20 @@ def lin_table(C: int, device) -> torch.Tensor:
     return _lin_tabs[k]
 
 
-def gain_table(device, pad=STD_PAD, double_width=STD_DOUBLE_WIDTH) -> torch.Tensor:
-    """exp(e / double_width * ln 2) for e = 0..pad-1, evaluated like torch_helpers.py:121 (fp32, CPU)."""
-    k = (pad, double_width, str(device))
+# Where exp(e / 12 * ln 2) of the padded ring is evaluated.  "device": with torch ops on the scene's CUDA device, i.e. the
+# bits the reference produces where it is deployed (torch's CUDA exp) -- the sampler then agrees bit for bit with the
+# reference algorithm on torch CUDA ops even when the foreground reaches the image border.  "cpu": torch's CPU exp, the
+# bits of the reference on the CPU (what tests/golden/exp_padding.npz holds).  The two differ in the last bit of a few
+# of the 100 gains; everything else of the padding is exact either way.
+GAIN_TABLE_BACKEND = "device"
+
+
+def gain_table(device, pad=STD_PAD, double_width=STD_DOUBLE_WIDTH, backend=None) -> torch.Tensor:
+    """exp(e / double_width * ln 2) for e = 0..pad-1, evaluated like torch_helpers.py:121 (fp32)."""
+    backend = backend or GAIN_TABLE_BACKEND
+    k = (pad, double_width, str(device), backend)
     if k not in _gain_tabs:
-        e = torch.arange(pad, dtype=torch.float32)
+        e = torch.arange(pad, dtype=torch.float32, device=device if backend == "device" else "cpu")
         _gain_tabs[k] = torch.exp(e / double_width * np.log(2)).to(device)
     return _gain_tabs[k]
 
@@ -136,9 +145,10 @@ def invalidate() -> None:
     the source tensors; writers that do not bump the version counter -- `t.data.copy_`, c10d broadcasts into existing
     storage, external kernels, optimizers that step on `.data` -- leave stale repacks behind, so they must call this
     (`diner_b200.sharding.broadcast_scene` does)."""
-    from . import field
+    from . import field, novel
     _cache.clear()
     field.invalidate_caches()
+    novel._gen_cache.clear()
 
 
 def get_scene(model) -> SceneBuffers:

@@ -53,11 +53,13 @@ int dnr_pad_depth_std(const float* depth_std, const float* gain_tab, int n_maps,
  *   either packed in the reference's order (gauss_off/fill_off [SB*NR] = exclusive prefix sums of ray_mask /
  *   n_missing, obtained from a count_only=1 pass) or, with unpacked_noise=1, [SB*NR,G] / [SB*NR,K].
  *   z_out [SB*NR,K] ascending.  Debug outputs (nullable): ray_mask_out, n_missing_out [SB*NR],
- *   sel_idx_out [SB*NR,K-G] (candidate index per shortlist rank, -1 = empty), p_out [SB*NR,C] likelihood. */
+ *   sel_idx_out [SB*NR,K-G] (candidate index per shortlist rank, -1 = empty), p_out [SB*NR,C] likelihood.
+ *   cand_offset [SB*NR,C,3] | NULL: NOVEL variant (src/models/novel/nerf_novel_renderer.py:104-107) -- every candidate
+ *   position is moved by the offset of its nearest target-mesh vertex (from dnr_novel_deform) before it is projected. */
 int dnr_sampler_fwd(const float* rays, const float* poses, const float* focal, const float* cxy, const float* depth,
                     const float* depth_std_padded, const float* normal, const float* lin_tab, const float* u_coarse,
                     const float* n_gauss, const float* u_fill, const int* gauss_off, const int* fill_off,
-                    unsigned long long seed, int SB, int NV, int NR, int H, int W, int C, int K, int G, int pad,
+                    const float* cand_offset, unsigned long long seed, int SB, int NV, int NR, int H, int W, int C, int K, int G, int pad,
                     float depth_diff_max, float img_w, float img_h, float std_sx, float std_sy, int count_only,
                     int unpacked_noise, float* z_out, int* ray_mask_out, int* n_missing_out, int* sel_idx_out,
                     float* p_out, dnr_stream_t stream);
@@ -90,6 +92,30 @@ int dnr_encode_fwd_split(const float* rays, const float* z, const float* poses, 
                          const float* phases, int SB, int NV, int NR, int K, int H, int W, int Hl, int Wl, int L, int NF,
                          long long ray_offset, long long n_rays, float img_w, float img_h, float lat_sx, float lat_sy,
                          void* lat_pk_hi, void* in_pk_hi, void* lat_pk_lo, void* in_pk_lo, dnr_stream_t stream);
+/* NOVEL variant of dnr_encode_fwd (src/models/novel/novel_pixelnerf.py:143-241): pts_in / pts_gen [n_rays*K,3] are the
+ * chunk's sample points deformed with tgt_in_offsets / tgt_gen_offsets (dnr_novel_deform, mode samples); pts_in replaces
+ * o + z d in the projection chain, pts_gen is projected by the ONE generic camera (gen_poses [SB,1,4,4], gen_focal /
+ * gen_cxy [SB,1,2], gen_img_w/h; :73-80) into the learned map gen_latent [Hg,Wg,512] bf16 channels-last (:46,108-141) and the
+ * feature row is gen_latent[gen_uv] + latent[uv] (:196).  Forward only. */
+int dnr_encode_novel_fwd(const float* rays, const float* z, const float* pts_in, const float* pts_gen, const float* poses,
+                         const float* focal, const float* cxy, const float* depth, const void* latent_nhwc_bf16,
+                         const float* gen_poses, const float* gen_focal, const float* gen_cxy,
+                         const void* gen_latent_nhwc_bf16, int Hg, int Wg, float gen_img_w, float gen_img_h, float gen_sx,
+                         float gen_sy, const float* freqs, const float* phases, int SB, int NV, int NR, int K, int H, int W,
+                         int Hl, int Wl, int L, int NF, long long ray_offset, long long n_rays, float img_w, float img_h,
+                         float lat_sx, float lat_sy, void* lat_pk, void* in_pk, dnr_stream_t stream);
+/* Nearest-vertex deformation of the NOVEL variant at frame scale (src/models/novel/nerf_novel_renderer.py:40-50 applied at
+ * :104-107 to every sampler candidate and at :441-442 to every sample point): K = 1 nearest neighbour (squared L2, first
+ * minimum) against a target mesh given Morton-sorted in groups of 32 with one bounding sphere per group
+ * (verts_sorted [SB][G*32] float4 = x, y, z, original index bits; spheres [SB][G] float4 = centre, radius) -- the search is
+ * pruned by the spheres and equals the brute force (dnr_deform_points) bit for bit.  candidates = 1: per_ray = C, the
+ * candidate depths are recomputed exactly as dnr_sampler_fwd draws them (lin_tab, u_coarse | Philox(seed)) and out_a
+ * receives the OFFSETS [SB*NR,C,3] for dnr_sampler_fwd's cand_offset.  candidates = 0: per_ray = K, z given, out_a / out_b
+ * (nullable) receive the points o + z d moved by offsets_a / offsets_b ([SB][V][3], indexed by original vertex). */
+int dnr_novel_deform(const float* rays, const float* z, const float* lin_tab, const float* u_coarse,
+                     unsigned long long seed, const void* verts_sorted, const void* spheres, const float* offsets_a,
+                     const float* offsets_b, int SB, int NR, int per_ray, int V, int G, int candidates, float* out_a,
+                     float* out_b, int* idx_out, dnr_stream_t stream);
 /* Backward of SpatialEncoder.index w.r.t. the latent map (grid_sample bilinear backward,
  * image_encoder.py:117-123): d_latent_nhwc [SB,NV,Hl,Wl,512] fp32 += scatter(d_lat_xr XR[rows x 512]). */
 int dnr_encode_bwd(const float* rays, const float* z, const float* poses, const float* focal, const float* cxy,

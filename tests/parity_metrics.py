@@ -81,7 +81,15 @@ def error_metrics(got: torch.Tensor, want: torch.Tensor) -> dict:
 
 
 def strided_subset(scene, n: int = 256, offset: int = 37):
-    rays = scene.rays
+    """~n rays spread over the target frame: a regular grid over the whole image (object and background),
+    or a plain stride when the ray batch is not a full frame."""
+    rays, wl = scene.rays, scene.workload
+    if rays.shape[1] == wl.tgt_H * wl.tgt_W and wl.tgt_H * wl.tgt_W > 4 * n:
+        side = int(round(n ** 0.5))
+        ys = torch.linspace(0.02 * wl.tgt_H, 0.98 * wl.tgt_H - 1, side).long()
+        xs = torch.linspace(0.02 * wl.tgt_W, 0.98 * wl.tgt_W - 1, side).long()
+        idx = (ys[:, None] * wl.tgt_W + xs[None, :]).reshape(-1)
+        return rays[:, idx].contiguous()
     stride = max(1, rays.shape[1] // n)
     return rays[:, offset::stride][:, :n].contiguous()
 
@@ -164,6 +172,8 @@ def config_shape_parity(workload: str, dev, n_rays: int = 256) -> dict:
         res["z_vs_cuda_oracle"] = error_metrics(z, og["z"])
         res["frac_fg"] = float(og["rm"].float().mean())
         res["rays_equal_cpu_oracle"] = float(torch.isclose(z.cpu(), oc["z"], rtol=1e-5, atol=1e-6).all(-1).float().mean())
+        # how far torch itself is from bit-stability across its two backends on these rays (DESIGN.md "Parity")
+        res["cuda_oracle_equal_cpu_oracle"] = float(torch.isclose(og["z"].cpu(), oc["z"], rtol=1e-5, atol=1e-6).all(-1).float().mean())
         res["sorted"] = bool((z[:, 1:] >= z[:, :-1]).all())
         r = NeRFRendererDGS(K, wl.n_candidates, wl.n_gaussian, white_bkgd=wl.white_bkgd)
         with torch.no_grad():

@@ -1,0 +1,226 @@
+"""GPU tests of the NOVEL renderer variant, run with `-m gpu` on a B200, through the C ABI.
+
+Checkers: oracle/novel_oracle.py (bit-pinned on the CPU to the reference's NOVEL renderer run unmodified except for
+pytorch3d's knn_points, tests/test_oracle.py) and the golden vectors of that run (tests/golden/novel_*.npz).
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _cuda():
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    from diner_b200 import _lib
+    _lib.load()
+    return torch.device("cuda", 0)
+
+
+def _load(name):
+    from tools.synthetic import add_novel_inputs, make_scene
+    g = dict(np.load(os.path.join(os.path.dirname(__file__), "golden", f"{name}.npz"), allow_pickle=False))
+    scene = add_novel_inputs(make_scene(str(g["workload"]), seed=int(g["seed"])), n_vertices=int(g["n_vertices"]),
+                             seed=int(g["seed"]))
+    noise = dict(u_coarse=torch.from_numpy(g["u_coarse"]), n_gauss=torch.from_numpy(g["n_gauss"]),
+                 u_fill=torch.from_numpy(g["u_fill"]))
+    return g, scene, noise
+
+
+@pytest.mark.parametrize("V,kind", [(5023, "surface"), (777, "cloud"), (33, "surface"), (1, "cloud"), (640, "ties")])
+def test_pruned_nearest_vertex_equals_brute_force(V, kind):
+    """dnr_novel_deform (Morton-sorted groups of 32 + bounding spheres) against dnr_deform_points (brute force) on the
+    same points: identical vertex indices -- including duplicated vertices (ties go to the lowest original index) -- and
+    identical deformed points, for points near the mesh and far from it."""
+    dev = _cuda()
+    from diner_b200.deform import nearest_vertex
+    from diner_b200.novel import _deform, build_vertex_groups
+    gen = torch.Generator().manual_seed(V)
+    SB, NR, K = 2, 300, 40
+    if kind == "surface":
+        u = torch.randn(SB, V, 3, generator=gen)
+        verts = u / u.norm(dim=-1, keepdim=True) * torch.tensor([0.11, 0.15, 0.12])
+    else:
+        verts = torch.randn(SB, V, 3, generator=gen) * 0.1
+    if kind == "ties":
+        verts[:, V // 2:] = verts[:, : V - V // 2]                       # every vertex twice
+    off_a, off_b = torch.randn(SB, V, 3, generator=gen) * 0.01, torch.randn(SB, V, 3, generator=gen) * 0.01
+    rays = torch.zeros(SB, NR, 8)
+    rays[..., :3] = torch.randn(SB, NR, 3, generator=gen) * 0.05 + torch.tensor([0.0, 0.0, -1.7])
+    d = torch.randn(SB, NR, 3, generator=gen) * 0.08 + torch.tensor([0.0, 0.0, 1.0])
+    rays[..., 3:6] = d / d.norm(dim=-1, keepdim=True)
+    rays[..., 6], rays[..., 7] = 1.0, 2.5
+    z = (1.0 + 1.5 * torch.rand(SB, NR, K, generator=gen)).sort(-1).values
+    rays, z, verts, off_a, off_b = (t.to(dev).contiguous() for t in (rays, z, verts, off_a, off_b))
+    pts = (rays[..., None, :3] + z.unsqueeze(-1) * rays[..., None, 3:6]).reshape(SB, NR * K, 3)
+    want_a, want_idx, _ = nearest_vertex(pts, verts, off_a)
+    want_b, _, _ = nearest_vertex(pts, verts, off_b)
+    groups = build_vertex_groups(verts)
+    got_a, got_b, idx = _deform(rays.view(-1, 8), z.view(-1, K), None, None, 0, groups, off_a, off_b, SB, NR, K, V, False,
+                                want_idx=True)
+    torch.cuda.synchronize()
+    assert torch.equal(idx.view(SB, -1), want_idx)
+    assert torch.equal(got_a.view(SB, -1, 3), want_a) and torch.equal(got_b.view(SB, -1, 3), want_b)
+
+
+@pytest.mark.parametrize("name", ["novel_tiny", "novel_tiny3"])
+def test_novel_sampler_bit_exact_vs_cuda_oracle(name):
+    """Candidates deformed by dnr_novel_deform + dnr_sampler_fwd(cand_offset) against the NOVEL oracle's sampler executed
+    with torch CUDA ops: per-candidate likelihoods, shortlist indices in rank order, masks -- bit for bit."""
+    dev = _cuda()
+    import parity_metrics as PM
+    from diner_b200 import sample_rays
+    from diner_b200.novel import _deform, build_vertex_groups
+    from diner_b200.scene import get_scene, lin_table
+    from oracle import dgs_oracle as O, novel_oracle as N
+    from tools.synthetic import novel_to_device
+    g, scene, _ = _load(name)
+    wl = scene.workload
+    rays = scene.rays
+    SB, NR = rays.shape[:2]
+    noise = PM.unpacked_noise(SB * NR, wl, seed=31)
+    novel_to_device(scene, dev)
+    m = scene.model
+    try:
+        nd = {k: v.to(dev) for k, v in noise.items()}
+        rd = rays.to(dev)
+        V = scene.target_vertices.shape[1]
+        deform = lambda x: N.deform_points(x, scene.target_vertices, scene.tgt_in_offsets)
+        with torch.no_grad():
+            z0, _, dbg = O.sample_depthguided(m, rd, wl.n_samples, wl.n_candidates, wl.n_gaussian, noise=dict(nd), deform=deform)
+            z_ref, _ = O.fill_up_uniform(z0.clone(), rd, None, nd["u_fill_full"])
+        K, M = wl.n_samples, wl.n_samples - wl.n_gaussian
+        order = dbg.order.view(-1, K)[:, :M]
+        p_ref = dbg.p.view(-1, wl.n_candidates)
+        idx_ref = torch.where(torch.gather(p_ref, 1, order) > 0, order, torch.full_like(order, -1))
+        groups = build_vertex_groups(scene.target_vertices)
+        cand_off, _, _ = _deform(rd.view(-1, 8), None, lin_table(wl.n_candidates, dev), nd["u_coarse"], 0, groups,
+                                 scene.tgt_in_offsets.contiguous(), None, SB, NR, wl.n_candidates, V, True)
+        z, d = sample_rays(get_scene(m), rd, K, wl.n_candidates, wl.n_gaussian, noise=nd, want_debug=True, cand_offset=cand_off)
+        assert int((p_ref != 0).sum()) > 1000
+        assert torch.equal(d["p"], p_ref)
+        assert torch.equal(d["sel_idx"].long(), idx_ref)
+        assert torch.equal(d["ray_mask"], dbg.ray_mask.view(-1).int())
+        torch.testing.assert_close(z, z_ref.view(-1, K), rtol=1e-5, atol=1e-6)
+        # and the deformation matters: the DINER sampler on the same rays picks other samples
+        z_plain = sample_rays(get_scene(m), rd, K, wl.n_candidates, wl.n_gaussian, noise=nd)
+        assert float((z_plain != z).any(-1).float().mean()) > 0.3
+    finally:
+        novel_to_device(scene, "cpu")
+
+
+@pytest.mark.parametrize("name", ["novel_tiny", "novel_tiny3"])
+def test_novel_render_against_reference_golden(name):
+    """diner_b200.novel.NeRFRendererDGS.forward (the reference's signature) against the golden outputs of the reference's
+    NOVEL renderer: sampler with the reference's recorded draws (most rays agree; the rest is torch's CPU-vs-CUDA
+    rounding, as for the DINER sampler), field with the second latent + compositing on the reference's own samples."""
+    dev = _cuda()
+    import parity_metrics as PM
+    from diner_b200.novel import NeRFRendererDGS
+    from tools.synthetic import novel_to_device
+    from oracle import dgs_oracle as O, novel_oracle as N
+    g, scene, noise = _load(name)
+    wl = scene.workload
+    # the reference packs its gaussian / fill draws by its OWN ray masks: locate every ray's slice with the CPU oracle's
+    # masks (as tests/test_gpu_stages.py does for the DINER sampler), so that one ray on which torch-CPU and CUDA
+    # disagree does not shift the draws of all rays behind it
+    with torch.no_grad():
+        z0, _, dbg = O.sample_depthguided(scene.model, scene.rays, wl.n_samples, wl.n_candidates, wl.n_gaussian,
+                                          noise=dict(noise), deform=lambda x: N.deform_points(
+                                              x, scene.target_vertices, scene.tgt_in_offsets))
+    rm = dbg.ray_mask.view(-1).int()
+    nm = (z0.view(-1, wl.n_samples) == 0).sum(-1).int()
+    noise = dict(noise, gauss_off=torch.cumsum(rm, 0) - rm, fill_off=torch.cumsum(nm, 0) - nm)
+    novel_to_device(scene, dev)
+    try:
+        r = NeRFRendererDGS(wl.n_samples, wl.n_candidates, wl.n_gaussian, white_bkgd=wl.white_bkgd)
+        args = (scene.model, scene.rays.to(dev), scene.target_vertices, scene.tgt_in_offsets, scene.tgt_gen_offsets)
+        with torch.no_grad():
+            out = r(*args, want_weights=True, noise={k: v.to(dev) for k, v in noise.items()}, return_samples=True)
+            out_z = r(*args, want_weights=True, noise=dict(z=torch.from_numpy(g["z"])))
+        K = wl.n_samples
+        same = torch.isclose(out.fine.z.cpu().view(-1, K), torch.from_numpy(g["z"]).view(-1, K), rtol=1e-5, atol=1e-6).all(-1)
+        assert same.float().mean().item() >= 0.85
+        for key in ("rgb", "depth", "weights"):
+            e = PM.error_metrics(out_z.fine[key], torch.from_numpy(g[key]))
+            # bf16 MLP tolerance: the mean is the meaningful figure; the second feature map roughly doubles
+            # the magnitude of the latent operand, so the tail is a little wider than on the DINER goldens
+            assert e["mean"] < 4e-3 and e["q99"] < 6e-2, (key, e)
+        assert out.fine.rgb.shape == g["rgb"].shape and torch.isfinite(out.fine.rgb).all()
+        # evaluation only: asking for gradients fails loudly instead of returning detached results
+        scene.tgt_in_offsets.requires_grad_(True)
+        with pytest.raises(NotImplementedError):
+            r(*args)
+        scene.tgt_in_offsets.requires_grad_(False)
+        # in-kernel jitter (no recorded draws): deterministic for a fixed seed, sorted samples
+        with torch.no_grad():
+            a = r(*args, noise=dict(seed=5), return_samples=True)
+            b = r(*args, noise=dict(seed=5), return_samples=True)
+        assert torch.equal(a.fine.rgb, b.fine.rgb) and bool((a.fine.z[..., 1:] >= a.fine.z[..., :-1]).all())
+    finally:
+        novel_to_device(scene, "cpu")
+
+
+def test_novel_encode_rows_vs_oracle():
+    """dnr_encode_novel_fwd: the gathered feature row equals gen_latent[gen_uv] + latent[uv] and the geometric code is
+    built from the `in`-deformed point (oracle/novel_oracle.field_inputs), to bf16 operand accuracy."""
+    dev = _cuda()
+    from diner_b200 import _lib, field as F_
+    from diner_b200.novel import NeRFRendererDGS, _deform, _gen_latent_nhwc, build_vertex_groups
+    from diner_b200.scene import get_scene
+    from oracle import novel_oracle as N
+    from tools.synthetic import novel_to_device
+    g, scene, _ = _load("novel_tiny3")
+    wl = scene.workload
+    K = wl.n_samples
+    rays = scene.rays[:, :50].contiguous()
+    SB, NR = rays.shape[:2]
+    z = torch.from_numpy(g["z"])[:, :50].contiguous()
+    pts = (rays[..., None, :3] + z.unsqueeze(-1) * rays[..., None, 3:6]).reshape(SB, NR * K, 3)
+    dirs = rays[..., None, 3:6].expand(-1, -1, K, -1).reshape(SB, NR * K, 3)
+    with torch.no_grad():
+        zx = N.field_inputs(scene.model, N.deform_points(pts, scene.target_vertices, scene.tgt_in_offsets),
+                            N.deform_points(pts, scene.target_vertices, scene.tgt_gen_offsets), dirs)      # SB,NV,B,567
+    novel_to_device(scene, dev)
+    m = scene.model
+    try:
+        sc = get_scene(m)
+        NV = sc.NV
+        rd, zd = rays.to(dev).view(-1, 8), z.to(dev).view(-1, K)
+        V = scene.target_vertices.shape[1]
+        groups = build_vertex_groups(scene.target_vertices)
+        pin, pgen, _ = _deform(rd, zd, None, None, 0, groups, scene.tgt_in_offsets.contiguous(),
+                               scene.tgt_gen_offsets.contiguous(), SB, NR, K, V, False)
+        gen_nhwc = _gen_latent_nhwc(m)
+        Hg, Wg = gen_nhwc.shape[:2]
+        gsize = torch.tensor([Wg, Hg])
+        gscale = ((gsize - float(m.encoder.feature_padding) * 2) / gsize).float()
+        f = lambda t: t.detach().float().contiguous()
+        p, st = _lib.ptr, _lib.stream_ptr()
+        n = SB * NR
+        mv = _lib.load().dnr_view_row_tiles(n * K, NV)
+        lat = torch.empty(mv * 128 * 512, device=dev, dtype=torch.bfloat16)
+        code = torch.empty(mv * 128 * 64, device=dev, dtype=torch.bfloat16)
+        gshape = m.gen_image_shape.cpu()
+        _lib.call("dnr_encode_novel_fwd", p(rd), p(zd), p(pin), p(pgen), p(sc.poses), p(sc.focal), p(sc.cxy), p(sc.depth),
+                  p(sc.latent_nhwc), p(f(m.gen_poses)), p(f(m.gen_focal)), p(f(m.gen_c)), p(gen_nhwc), Hg, Wg,
+                  float(gshape[0]), float(gshape[1]), float(gscale[0]), float(gscale[1]), p(sc.freqs), p(sc.phases),
+                  *F_._encode_args(sc, NR, K, 0, n), p(lat), p(code), st)
+        lat_rows = torch.empty(mv * 128, 512, device=dev)
+        code_rows = torch.empty(mv * 128, 64, device=dev)
+        _lib.call("dnr_unpack_rows", p(lat), mv * 128, 512, p(lat_rows), st)
+        _lib.call("dnr_unpack_rows", p(code), mv * 128, 64, p(code_rows), st)
+        torch.cuda.synchronize()
+        spw = 32 // NV
+        s_ = torch.arange(n * K)
+        for v in range(NV):
+            row = ((s_ // spw) * 32 + (s_ % spw) * NV + v).to(dev)
+            want = torch.cat([zx[sb, v] for sb in range(SB)], 0)            # rows follow the flattened (scene, ray, sample) order
+            got_l, got_c = lat_rows[row].cpu(), code_rows[row].cpu()
+            assert (got_l - want[:, :512]).abs().max() <= 2.0 ** -6 * want[:, :512].abs().max() + 1e-6
+            assert torch.allclose(got_c[:, :55], want[:, 512:], rtol=2.0 ** -8, atol=2e-3)
+    finally:
+        novel_to_device(scene, "cpu")
