@@ -55,6 +55,8 @@ _SIGNATURES = {
     "dnr_mlp_quad_max_clusters": (c_i, [c_i]),
     "dnr_mlp_quad_scratch_bytes": (c_ll, []),
     "dnr_mlp_quad_fwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_p, c_p, c_p, c_p]),
+    "dnr_mlp_quad_static_max_tiles": (c_i, []),
+    "dnr_mlp_quad_fwd_static": (c_i, [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_p, c_p]),
     "dnr_head_finalize": (c_i, [c_p, c_p, c_i, c_ll, c_i, c_p, c_p]),
     "dnr_mlp_fused_fwd": (c_i, [c_p, c_p, c_p, c_p, c_i, c_i, c_ll, c_p, c_p, c_i, c_p]),
     "dnr_head_bwd": (c_i, [c_p, c_p, c_p, c_p, c_ll, c_p, c_p, c_p, c_p]),

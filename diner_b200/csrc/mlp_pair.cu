@@ -990,3 +990,67 @@ DNR_EXPORT int dnr_head_finalize(const float* head_partial, const float* bout, i
   DNR_CHECK_LAUNCH("dnr_head_finalize");
   return 0;
 }
+
+// =====================================================================================================================
+// Allocation-free variant of dnr_mlp_quad_fwd.  NO COUNTERPART IN THE REFERENCE: added
+// for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that
+// forbid it).  The parking scratch of the MERGE path lives in a file-scope device array instead of a caller-allocated
+// buffer: kStaticQuadClusters clusters x 4 CTAs x 128 KB = 4 MiB, held by every GPU that loads the library until exit.
+// Fewer clusters than dnr_mlp_quad_fwd keeps resident (8 instead of 33), so it is a small-batch / latency entry point.
+namespace dnr {
+constexpr int kStaticQuadClusters = 8;                 // 32 CTAs
+constexpr int kStaticQuadMaxTiles = 4096;              // 524 288 view rows per call (stated maximum of this entry point)
+constexpr size_t kStaticQuadFloats = (size_t)4 * kStaticQuadClusters * 128 * 256;
+static __device__ __align__(256) float g_quad_static_scratch[kStaticQuadFloats];
+// In host code the array's name is only a host-side stand-in; the device address comes from cudaGetSymbolAddress, once
+// per device, with that device current.
+static float* g_quad_static_ptr[64] = {};
+}  // namespace dnr
+
+// dnr_mlp_quad_fwd with the merge scratch inside the library.  Allocates nothing (no cudaMalloc / cudaFree / library
+// allocator); inputs and outputs are the caller's.  mv_tiles <= dnr_mlp_quad_static_max_tiles() (4096), else
+// cudaErrorInvalidValue with a message.  The scratch is shared by every call on a device and keeps the last call's
+// contents: nothing in it has to start at zero (a merge group reads only the rows it parked itself, missing rows are
+// zero-filled in registers), but two calls that OVERLAP on the GPU (different streams, or graph branches) race on it --
+// serialise them.
+DNR_EXPORT int dnr_mlp_quad_static_max_tiles(void) { return dnr::kStaticQuadMaxTiles; }
+DNR_EXPORT int dnr_mlp_quad_fwd_static(const void* lat_pk, const void* code_pk, const void* const* weights_pk128,
+                                       const float* const* biases, const float* w_out, int NV, int mv_tiles,
+                                       float* head_partial, cudaStream_t stream) {
+  DNR_REQUIRE(NV >= 1 && NV <= 4, "dnr_mlp_quad_fwd_static: NV must be in [1,4]");
+  DNR_REQUIRE(lat_pk && code_pk && weights_pk128 && biases && w_out && head_partial, "dnr_mlp_quad_fwd_static: null argument");
+  DNR_REQUIRE(mv_tiles <= dnr::kStaticQuadMaxTiles,
+              "dnr_mlp_quad_fwd_static: mv_tiles exceeds the maximum of 4096 tiles (524288 view rows) of the allocation-free "
+              "entry point; split the batch or use dnr_mlp_quad_fwd");
+  if (mv_tiles <= 0) return 0;
+  int dev = -1;
+  DNR_CHECK(cudaGetDevice(&dev), "dnr_mlp_quad_fwd_static/device");
+  DNR_REQUIRE(dev >= 0 && dev < 64, "dnr_mlp_quad_fwd_static: device index out of range");
+  if (!dnr::g_quad_static_ptr[dev]) {          // set-up, once per device, that device current
+    float* ptr = nullptr;
+    DNR_CHECK(cudaGetSymbolAddress((void**)&ptr, dnr::g_quad_static_scratch), "dnr_mlp_quad_fwd_static/symbol");
+    DNR_REQUIRE(ptr != nullptr, "dnr_mlp_quad_fwd_static: cudaGetSymbolAddress returned null");
+    dnr::g_quad_static_ptr[dev] = ptr;
+  }
+  dnr::PairParams P;
+  P.lat_pk = (const unsigned char*)lat_pk; P.code_pk = (const unsigned char*)code_pk;
+  P.w_in = (const unsigned char*)weights_pk128[0];
+  for (int i = 0; i < 3; ++i) P.w_z[i] = (const unsigned char*)weights_pk128[1 + i];
+  for (int i = 0; i < 5; ++i) {
+    P.w_0[i] = (const unsigned char*)weights_pk128[4 + i]; P.w_1[i] = (const unsigned char*)weights_pk128[9 + i];
+  }
+  for (int i = 0; i < 6; ++i) P.cb[i] = biases[i];
+  for (int i = 0; i < 5; ++i) P.b_0[i] = biases[6 + i];
+  P.w_out = w_out; P.head_partial = (float4*)head_partial;
+  P.NV = NV; P.SPW = 32 / NV; P.mv_tiles = mv_tiles; P.prof = nullptr;
+  P.merge_scratch = dnr::g_quad_static_ptr[dev];
+  dnr::QuadKernel kern = dnr::quad_kernel(NV, NV > 1);
+  const int max_cl = dnr::quad_max_clusters(NV);      // also sets the kernels' shared-memory attribute on this device
+  DNR_REQUIRE(max_cl >= 1, "dnr_mlp_quad_fwd_static: the device cannot hold a cluster of 4 CTAs with 225 KB of shared memory each");
+  const int n_pairs = (mv_tiles + 1) / 2;
+  int clusters = n_pairs < dnr::kStaticQuadClusters ? n_pairs : dnr::kStaticQuadClusters;
+  if (clusters > max_cl) clusters = max_cl;
+  kern<<<4 * clusters, dnr::kPThreads, dnr::kQSmem, stream>>>(P);
+  DNR_CHECK_LAUNCH("dnr_mlp_quad_fwd_static");
+  return 0;
+}

@@ -177,6 +177,18 @@ long long dnr_mlp_quad_scratch_bytes(void);
 int dnr_mlp_quad_fwd(const void* lat_pk, const void* code_pk, const void* const* weights_pk128,
                      const float* const* biases, const float* w_out, int NV, int mv_tiles, void* merge_scratch,
                      float* head_partial, long long* prof /* nullable */, dnr_stream_t stream);
+/* Allocation-free variant of dnr_mlp_quad_fwd.  It has NO COUNTERPART IN THE REFERENCE: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid it).  The merge scratch lives in a file-scope device array of the library (4 MiB = 8 clusters x
+ * 4 CTAs x 128 KB, held by every GPU that loads the library until exit); the call allocates nothing and the caller still
+ * passes inputs and outputs.  mv_tiles must not exceed dnr_mlp_quad_static_max_tiles() (4096 tiles = 524 288 view rows),
+ * else cudaErrorInvalidValue with a message in dnr_last_error().  All calls on a device share the array, which keeps the
+ * last call's contents (nothing in it needs to start at zero): calls that overlap on the GPU race -- serialise them.
+ * Results are bit-identical to dnr_mlp_quad_fwd with a merge scratch. */
+int dnr_mlp_quad_static_max_tiles(void);
+int dnr_mlp_quad_fwd_static(const void* lat_pk, const void* code_pk, const void* const* weights_pk128,
+                            const float* const* biases, const float* w_out, int NV, int mv_tiles, float* head_partial,
+                            dnr_stream_t stream);
 /* Number of 4-CTA clusters the quad kernel keeps resident; SMs beyond 4x that stay idle and can run
  * dnr_mlp_pair_fwd clusters (max_clusters) on another stream at the same time. */
 int dnr_mlp_quad_max_clusters(int NV);
