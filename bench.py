@@ -400,13 +400,19 @@ class Harness:
             rec = json.load(f).get(f"{workload}_{mode}")
         if not isinstance(rec, dict):
             return
-        if rec.get("tiles") == split.get("tiles_main"):
+        # the capture must be of the launch geometry that was timed: same tiles per chunk, and the quad kernel's share of
+        # them (the split with the pair kernel adapts at run time) within 2 %
+        same = (rec.get("tiles_chunk") == split.get("tiles") and split.get("tiles_main") and
+                abs(rec.get("tiles", 0) - split["tiles_main"]) <= 0.02 * split["tiles_main"])
+        if same:
             roofline["traffic"] = rec["dram_bytes"]
             roofline["traffic_over_algorithmic"] = rec["dram_bytes"] / rec["algorithmic_bytes"]
+            roofline["traffic_tiles"] = rec["tiles"]
             roofline["traffic_source"] = rec.get("source")
         else:
-            roofline["traffic_note"] = (f"profiles/roofline_traffic.json holds a capture at {rec.get('tiles')} tiles per "
-                                        f"launch, this run launches {split.get('tiles_main')}: not reported")
+            roofline["traffic_note"] = (f"profiles/roofline_traffic.json holds a capture at {rec.get('tiles')} of "
+                                        f"{rec.get('tiles_chunk')} tiles per launch, this run launches "
+                                        f"{split.get('tiles_main')} of {split.get('tiles')}: not reported")
 
     def torch_cuda_reference(self, workload, n_chunks=4):
         """The reference ALGORITHM (oracle/dgs_oracle.py) in stock torch CUDA ops on this GPU, chunked like the reference

@@ -17,6 +17,7 @@ from __future__ import annotations
 from dataclasses import dataclass, field as dc_field
 
 import contextlib
+import os
 
 import torch
 
@@ -40,7 +41,7 @@ PAIR_SHARE = None
 # The split adapts itself: both kernels of a chunk are bracketed by CUDA events, and once a pair of timings has
 # completed (polled without synchronising) the rate of that (device, NV) moves towards the measured one.  The split
 # never changes the result (both kernels produce the same bits, tests/test_gpu_field.py), only the balance.
-ADAPT_SPLIT = True
+ADAPT_SPLIT = os.environ.get("DNR_ADAPT_SPLIT", "1") != "0"     # 0: fixed split from PAIR_RATE (reproducible captures)
 _split_state = {}            # (device, NV) -> dict(rate=float, pending=[(e_q0, e_q1, e_p0, e_p1, tiles_q, tiles_p)])
 MERGE_POOLED = True          # quad kernel: run blocks 3-4 + head once per NV tiles on merged pooled rows (NV > 1)
 _side_stream = {}
