@@ -190,7 +190,7 @@ def run_reference(args, rank, world):
                                          "the full-frame figure; torch-CPU oracle, bit-pinned to the unmodified "
                                          "reference's outputs (tests/test_oracle.py)"),
                 e2e=dict(value=value, unit="rays/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ---------------------------------------------------------------------------------------------------------------
@@ -461,6 +461,27 @@ class Harness:
                     note="once per scene, outside the per-frame timed region; rank 0 -> all, one flat fp32 bucket, NCCL")
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """stdout must carry ONE JSON line and nothing else, but libraries write there at C level (NCCL prints its version
+    banner on communicator creation): point fd 1 at stderr for the whole run and keep the real stdout for emit()."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -480,6 +501,7 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    quiet_stdout()
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
@@ -535,7 +557,7 @@ def main():
             line["cpu_baseline"] = dict(value=rate, unit="rays/s", cores=cpu.threads, kind="port",
                                         sample=f"{n} rays (one reference chunk) of the same frame, torch-CPU oracle "
                                                f"(bit-pinned to the unmodified reference), {dt:.1f} s")
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
