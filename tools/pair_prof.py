@@ -21,5 +21,9 @@ p = F_.PAIR_PROF.view(148, 16).double().cpu()
 p = p[p[:, 4] > 0]            # CTAs that ran (the quad kernel may leave SMs idle)
 print('CTAs reporting:', p.shape[0]); lead = p[p[:, 0] > 0]
 names = ["mma_total", "mma_wait_ring", "mma_wait_own", "mma_wait_peer", "epi_total", "epi_wait_accf", "-", "-", "loop_EPI_X(4/tile)", "loop_EPI_T(5/tile)", "loop_EPI_PARK(1)", "loop_EPI_HEAD(1)", "epi_merge", "wait_peer_full", "ring_lat", "pfull_lat"]
+MMA_SIDE = {0, 1, 2, 3, 13, 14, 15}           # counters of the MMA-issuing thread (even CTA of each pair only)
 for i, n in enumerate(names):
-    print(f"{n:16s} mean {p[:, i].mean():14.0f} cyc  ({100 * p[:, i].mean() / max(lead[:, 0].mean(), 1):5.1f}% of mma_total)  min {p[:, i].min():.0f} max {p[:, i].max():.0f}")
+    rows = lead if i in MMA_SIDE else p
+    ref = lead[:, 0].mean() if i in MMA_SIDE else p[:, 4].mean()
+    print(f"{n:16s} mean {rows[:, i].mean():14.0f} cyc  ({100 * rows[:, i].mean() / max(ref, 1):5.1f}% of "
+          f"{'mma_total' if i in MMA_SIDE else 'epi_total'})  min {rows[:, i].min():.0f} max {rows[:, i].max():.0f}")
