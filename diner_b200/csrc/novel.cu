@@ -5,10 +5,11 @@
 //
 // A frame has SB*NR*C = 65.5 M candidates against ~5 000 vertices: brute force (csrc/deform.cu, 3e12 pairs/s) would cost
 // 110 ms per FaceScape frame, three times the whole DINER render.  Here the vertices arrive sorted along a Morton curve
-// in groups of 32 with a bounding sphere per group (diner_b200/novel.py builds them per mesh, ~0.1 ms): a query first
-// takes the smallest upper bound min_g(|x - c_g| + r_g) over the spheres, then scans only the groups whose lower bound
-// |x - c_g| - r_g does not exceed it.  The pruning is conservative (every vertex that can be the minimum or tie with it
-// is scanned) and the scanned distances use the brute-force kernel's arithmetic (x, y, z accumulated with fused
+// in groups of 32 with a bounding sphere per group, and 8 consecutive groups form a super-group with an axis-aligned box
+// (diner_b200/novel.py builds both per mesh, ~0.1 ms).  A query scans the super-group whose box is nearest first, which
+// gives a real distance to prune with, then visits only the super-groups / groups whose lower bound (box distance,
+// |x - c_g| - r_g) does not exceed the best distance so far.  The pruning is conservative (every vertex that can be the
+// minimum or tie with it is scanned) and the scanned distances use the brute-force kernel's arithmetic (x, y, z accumulated with fused
 // multiply-adds) with ties going to the lowest ORIGINAL index, so the result equals the brute force bit for bit.
 //
 // The candidate positions are recomputed exactly as csrc/sampler.cu computes them (same jitter, same op order; this file
@@ -25,9 +26,10 @@ struct NovelParams {
   unsigned long long seed;
   const float4* verts;      // [SB][G*32] Morton-sorted (x, y, z, original index as int bits); padding: +huge, INT_MAX
   const float4* spheres;    // [SB][G] (cx, cy, cz, r)
+  const float4* supers;     // [SB][S][2] (lo.xyz, -), (hi.xyz, -): boxes of 8 consecutive groups, S = ceil(G / 8)
   const float* off_a;       // [SB][V][3] offsets indexed by ORIGINAL vertex index (tgt_in_offsets)
   const float* off_b;       // samples mode: tgt_gen_offsets, or null
-  int SB, NR, per_ray, V, G;
+  int SB, NR, per_ray, V, G, S;
   float inv_c_step;
   float* out_a;             // candidates: offsets [SB*NR, C, 3]; samples: deformed points [SB*NR*K, 3] (in)
   float* out_b;             // samples: deformed points (gen), or null
@@ -38,10 +40,13 @@ constexpr int kNovelThreads = 256;
 
 template <bool CANDIDATES>
 __global__ void __launch_bounds__(kNovelThreads) novel_deform_kernel(const NovelParams P) {
-  extern __shared__ float4 sph[];
+  extern __shared__ float4 sph[];                      // [G] spheres, then [S][2] boxes
+  float4* box = sph + P.G;
   const int sb = blockIdx.y;
   const float4* sp = P.spheres + (size_t)sb * P.G;
+  const float4* bx = P.supers + (size_t)sb * P.S * 2;
   for (int g = threadIdx.x; g < P.G; g += blockDim.x) sph[g] = sp[g];
+  for (int g = threadIdx.x; g < 2 * P.S; g += blockDim.x) box[g] = bx[g];
   __syncthreads();
   const long long per_scene = (long long)P.NR * P.per_ray;
   const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;     // query inside the scene
@@ -68,31 +73,47 @@ __global__ void __launch_bounds__(kNovelThreads) novel_deform_kernel(const Novel
     zc = P.z[ray * P.per_ray + i];
   }
   const float x0 = o0 + zc * d0, x1 = o1 + zc * d1, x2 = o2 + zc * d2;      // :93 / :416
-  // pass 1: the smallest upper bound on the nearest-vertex distance
-  float ub = 3.0e38f;
-  for (int g = 0; g < P.G; ++g) {
-    const float4 s = sph[g];
-    const float a = x0 - s.x, b = x1 - s.y, c = x2 - s.z;
-    ub = fminf(ub, sqrtf(a * a + b * b + c * c) + s.w);
-  }
-  const float thr = ub * 1.00001f + 1e-7f;                 // slack for the roundings of the two bounds
-  // pass 2: scan the groups that can hold the minimum
-  float best = 3.0e38f;
+  float best = 3.0e38f;                                    // squared distance, the brute-force kernel's arithmetic
   int best_i = 0x7fffffff;
   const float4* vs = P.verts + (size_t)sb * P.G * 32;
-  for (int g = 0; g < P.G; ++g) {
-    const float4 s = sph[g];
-    const float a = x0 - s.x, b = x1 - s.y, c = x2 - s.z;
-    if (sqrtf(a * a + b * b + c * c) - s.w > thr) continue;
-    const float4* vg = vs + (size_t)g * 32;
+  // a lower bound may be a rounding above the true distance: prune only beyond a relative + absolute slack, and never on
+  // equality (ties go to the lowest original index, so every equal-distance vertex must be seen)
+  auto beyond = [&](float lb2) { return lb2 > best * 1.00002f + 1e-12f; };
+  auto box_lb2 = [&](int sidx) {
+    const float4 lo = box[2 * sidx], hi = box[2 * sidx + 1];
+    const float a = fmaxf(fmaxf(lo.x - x0, x0 - hi.x), 0.f), b = fmaxf(fmaxf(lo.y - x1, x1 - hi.y), 0.f);
+    const float c = fmaxf(fmaxf(lo.z - x2, x2 - hi.z), 0.f);
+    return a * a + b * b + c * c;
+  };
+  auto scan_super = [&](int sidx) {
+    const int g1 = min(P.G, sidx * 8 + 8);
+    for (int g = sidx * 8; g < g1; ++g) {
+      const float4 sg = sph[g];
+      const float a = x0 - sg.x, b = x1 - sg.y, c = x2 - sg.z;
+      const float d = sqrtf(a * a + b * b + c * c) - sg.w;
+      if (d > 0.f && beyond(d * d)) continue;
+      const float4* vg = vs + (size_t)g * 32;
 #pragma unroll 8
-    for (int j = 0; j < 32; ++j) {
-      const float4 v = __ldg(vg + j);
-      const float e0 = x0 - v.x, e1 = x1 - v.y, e2 = x2 - v.z;
-      const float dd = fmaf(e2, e2, fmaf(e1, e1, e0 * e0));          // the brute-force kernel's arithmetic (deform.cu)
-      const int vi = __float_as_int(v.w);
-      if (dd < best || (dd == best && vi < best_i)) { best = dd; best_i = vi; }
+      for (int j = 0; j < 32; ++j) {
+        const float4 v = __ldg(vg + j);
+        const float e0 = x0 - v.x, e1 = x1 - v.y, e2 = x2 - v.z;
+        const float dd = fmaf(e2, e2, fmaf(e1, e1, e0 * e0));          // the brute-force kernel's arithmetic (deform.cu)
+        const int vi = __float_as_int(v.w);
+        if (dd < best || (dd == best && vi < best_i)) { best = dd; best_i = vi; }
+      }
     }
+  };
+  // seed: the super-group whose box is nearest
+  int s0 = 0;
+  float lb0 = 3.0e38f;
+  for (int sidx = 0; sidx < P.S; ++sidx) {
+    const float lb = box_lb2(sidx);
+    if (lb < lb0) { lb0 = lb; s0 = sidx; }
+  }
+  scan_super(s0);
+  for (int sidx = 0; sidx < P.S; ++sidx) {
+    if (sidx == s0 || beyond(box_lb2(sidx))) continue;
+    scan_super(sidx);
   }
   const size_t qq = (size_t)sb * per_scene + q;
   if (P.idx_out) P.idx_out[qq] = best_i;
@@ -114,26 +135,28 @@ __global__ void __launch_bounds__(kNovelThreads) novel_deform_kernel(const Novel
 // draws it; out_a = offsets [SB*NR, C, 3] for dnr_sampler_fwd's cand_offset) or deformed sample points (mode = samples:
 // per_ray = K, z given; out_a / out_b = points + in / gen offsets, [SB*NR*K, 3]) of the NOVEL renderer variant
 // (nerf_novel_renderer.py:40-50,104-107,441-442).  verts_sorted [SB][G*32] float4 (x, y, z, original index bits) and
-// spheres [SB][G] float4 (centre, radius) come from diner_b200.novel.build_vertex_groups; offsets are indexed by original
+// spheres [SB][G] float4 (centre, radius) and supers [SB][ceil(G/8)][2] float4 (box lo, hi of 8 consecutive groups) come
+// from diner_b200.novel.build_vertex_groups; offsets are indexed by original
 // vertex index [SB][V][3].
 DNR_EXPORT int dnr_novel_deform(const float* rays, const float* z, const float* lin_tab, const float* u_coarse,
                                 unsigned long long seed, const void* verts_sorted, const void* spheres,
-                                const float* offsets_a, const float* offsets_b, int SB, int NR, int per_ray, int V, int G,
+                                const void* supers, const float* offsets_a, const float* offsets_b, int SB, int NR,
+                                int per_ray, int V, int G,
                                 int candidates, float* out_a, float* out_b, int* idx_out, cudaStream_t stream) {
-  DNR_REQUIRE(rays && verts_sorted && spheres && offsets_a && out_a, "dnr_novel_deform: null argument");
+  DNR_REQUIRE(rays && verts_sorted && spheres && supers && offsets_a && out_a, "dnr_novel_deform: null argument");
   DNR_REQUIRE(SB >= 1 && NR >= 0 && per_ray >= 1 && V >= 1 && G >= 1 && G <= 2048, "dnr_novel_deform: bad sizes (G <= 2048)");
   DNR_REQUIRE(candidates ? (lin_tab != nullptr) : (z != nullptr), "dnr_novel_deform: candidates need lin_tab, samples need z");
   DNR_REQUIRE(SB <= 65535, "dnr_novel_deform: at most 65535 scenes per call");
   if (NR == 0) return 0;
   dnr::NovelParams P;
   P.rays = rays; P.z = z; P.lin_tab = lin_tab; P.u_coarse = u_coarse; P.seed = seed;
-  P.verts = (const float4*)verts_sorted; P.spheres = (const float4*)spheres; P.off_a = offsets_a; P.off_b = offsets_b;
-  P.SB = SB; P.NR = NR; P.per_ray = per_ray; P.V = V; P.G = G;
+  P.verts = (const float4*)verts_sorted; P.spheres = (const float4*)spheres; P.supers = (const float4*)supers; P.off_a = offsets_a; P.off_b = offsets_b;
+  P.SB = SB; P.NR = NR; P.per_ray = per_ray; P.V = V; P.G = G; P.S = (G + 7) / 8;
   P.inv_c_step = (float)(1.0 / (double)per_ray);
   P.out_a = out_a; P.out_b = out_b; P.idx_out = idx_out;
   const long long per_scene = (long long)NR * per_ray;
   dim3 grid((unsigned)((per_scene + dnr::kNovelThreads - 1) / dnr::kNovelThreads), SB);
-  const size_t smem = (size_t)G * sizeof(float4);
+  const size_t smem = ((size_t)G + 2 * (size_t)((G + 7) / 8)) * sizeof(float4);
   if (candidates) dnr::novel_deform_kernel<true><<<grid, dnr::kNovelThreads, smem, stream>>>(P);
   else dnr::novel_deform_kernel<false><<<grid, dnr::kNovelThreads, smem, stream>>>(P);
   DNR_CHECK_LAUNCH("dnr_novel_deform");

@@ -49,7 +49,7 @@ def _morton3(q: torch.Tensor) -> torch.Tensor:
 
 def build_vertex_groups(vertices: torch.Tensor):
     """vertices (SB,V,3) -> (verts_sorted (SB, G*32, 4) fp32 [x, y, z, original index as int32 bits],
-    spheres (SB, G, 4) fp32 [centre, radius]).  Padding slots sit at 1e18 with index INT_MAX (never the minimum)."""
+    spheres (SB, G, 4) fp32 [centre, radius], supers (SB, ceil(G/8), 2, 4) fp32 [box lo | box hi of 8 consecutive groups]).  Padding slots sit at 1e18 with index INT_MAX (never the minimum)."""
     SB, V, _ = vertices.shape
     dev = vertices.device
     v = vertices.detach().to(torch.float32)
@@ -72,11 +72,22 @@ def build_vertex_groups(vertices: torch.Tensor):
     rad = torch.where(valid[..., 0], (grp - centre.unsqueeze(2)).norm(dim=-1), torch.zeros((), device=dev)).amax(2)
     spheres = torch.cat([centre, (rad * (1 + 1e-5) + 1e-9).unsqueeze(-1)], -1).contiguous()
     verts_sorted = torch.cat([sv, idx_bits.view(torch.float32).unsqueeze(-1)], -1).contiguous()
-    return verts_sorted, spheres
+    # super-groups: the axis-aligned box of 8 consecutive groups (a little larger than tight, so that rounding cannot prune)
+    S = (G + 7) // 8
+    padg = S * 8 - G
+    gmin_p = torch.cat([gmin, torch.full((SB, padg, 3), big, device=dev)], 1) if padg else gmin
+    gmax_p = torch.cat([gmax, torch.full((SB, padg, 3), -big, device=dev)], 1) if padg else gmax
+    smin = gmin_p.view(SB, S, 8, 3).amin(2)
+    smax = gmax_p.view(SB, S, 8, 3).amax(2)
+    ext = (smax - smin).abs().amax(-1, keepdim=True)
+    smin, smax = smin - (1e-6 * ext + 1e-9), smax + (1e-6 * ext + 1e-9)
+    zero = torch.zeros(SB, S, 1, device=dev)
+    supers = torch.stack([torch.cat([smin, zero], -1), torch.cat([smax, zero], -1)], 2).contiguous()      # SB,S,2,4
+    return verts_sorted, spheres, supers
 
 
 def _deform(rays, z, lin, u_coarse, seed, groups, off_a, off_b, SB, NR, per_ray, V, candidates, want_idx=False):
-    verts_sorted, spheres = groups
+    verts_sorted, spheres, supers = groups
     dev = rays.device
     n = SB * NR * per_ray
     out_a = torch.empty(n, 3, device=dev, dtype=torch.float32)
@@ -84,7 +95,7 @@ def _deform(rays, z, lin, u_coarse, seed, groups, off_a, off_b, SB, NR, per_ray,
     idx = torch.empty(n, device=dev, dtype=torch.int32) if want_idx else None
     p = _lib.ptr
     _lib.call("dnr_novel_deform", p(rays), p(z), p(lin), p(u_coarse), seed & (2 ** 64 - 1), p(verts_sorted), p(spheres),
-              p(off_a), p(off_b), SB, NR, per_ray, V, spheres.shape[1], 1 if candidates else 0, p(out_a), p(out_b), p(idx),
+              p(supers), p(off_a), p(off_b), SB, NR, per_ray, V, spheres.shape[1], 1 if candidates else 0, p(out_a), p(out_b), p(idx),
               _lib.stream_ptr())
     return out_a, out_b, idx
 

@@ -1,0 +1,59 @@
+"""Time the NOVEL renderer variant (diner_b200.novel.NeRFRendererDGS) on a full FaceScape-shape frame against a
+FLAME-sized target mesh (5 023 vertices): frame time, per-C-ABI-call breakdown, and the DINER renderer on the same frame.
+
+    python tools/novel_bench.py [n_vertices] [steps]
+"""
+import json, os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from diner_b200 import NeRFRendererDGS as DinerRenderer, _lib
+from diner_b200.novel import NeRFRendererDGS
+from tools.synthetic import add_novel_inputs, make_scene, novel_to_device
+
+V = int(sys.argv[1]) if len(sys.argv) > 1 else 5023
+steps = int(sys.argv[2]) if len(sys.argv) > 2 else 5
+dev = torch.device("cuda", 0)
+scene = add_novel_inputs(make_scene("facescape", seed=0), n_vertices=V, seed=0, gen_hw=(192, 192))
+novel_to_device(scene, dev)
+wl = scene.workload
+rays = scene.rays.to(dev)
+args = (scene.model, rays, scene.target_vertices, scene.tgt_in_offsets, scene.tgt_gen_offsets)
+r = NeRFRendererDGS(wl.n_samples, wl.n_candidates, wl.n_gaussian, white_bkgd=wl.white_bkgd)
+rd = DinerRenderer(wl.n_samples, wl.n_candidates, wl.n_gaussian, white_bkgd=wl.white_bkgd)
+flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+
+def timed(fn):
+    for _ in range(2):
+        fn()
+    ts = []
+    for _ in range(steps):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    return min(ts), sum(ts) / len(ts)
+
+
+with torch.no_grad():
+    t_novel = timed(lambda: r(*args))
+    t_diner = timed(lambda: rd(scene.model, rays))
+    _lib.profile = []
+    r(*args)
+    torch.cuda.synchronize()
+    per = {}
+    for name, e0, e1, tag in _lib.profile:
+        d = per.setdefault(name + (" (overlapped)" if tag == "overlapped" else ""), [0.0, 0])
+        d[0] += e0.elapsed_time(e1); d[1] += 1
+    _lib.profile = None
+    out = r(*args)
+n = rays.shape[0] * rays.shape[1]
+deform_ms = per.get("dnr_novel_deform", [0, 0])[0]
+queries = n * (wl.n_candidates + wl.n_samples)
+print(json.dumps(dict(workload="facescape_eval NOVEL variant", rays=n, n_vertices=V, ms_best=t_novel[0], ms_mean=t_novel[1],
+                      rays_per_s=n / (t_novel[1] * 1e-3), diner_ms_mean=t_diner[1],
+                      breakdown_ms={k: dict(ms=v[0], launches=v[1]) for k, v in per.items()},
+                      deform_queries=queries, deform_queries_per_s=queries / (deform_ms * 1e-3) if deform_ms else None,
+                      brute_force_pairs_equivalent_per_s=queries * V / (deform_ms * 1e-3) if deform_ms else None,
+                      finite=bool(torch.isfinite(out.fine.rgb).all()))))
