@@ -20,6 +20,9 @@
 //                 complete one 64-column K-block per piece so the next layer's MMAs start after a quarter epilogue)
 #include "common.cuh"
 #include "tc05.cuh"
+#include <cuda.h>
+#include <stdlib.h>
+#include <string.h>
 
 namespace dnr {
 
@@ -45,6 +48,14 @@ struct PairParams {
   float* merge_scratch;           // quad kernel, MERGE: [gridDim][128 rows][256] fp32 parked pooled rows
   int NV, SPW, mv_tiles;
   long long* prof;                // optional [gridDim][8] cycle counters (debug)
+  int tma2;                       // quad kernel: operands through tensor-map TMA with cta_group::2 completion (QuadMaps)
+};
+
+// Tensor maps of the quad kernel's streamed operands (tma2 mode): every packed buffer is viewed as a 2-D bf16 tensor of
+// 256-element rows (512 B); a 16 KB K-block is the box of 32 consecutive rows starting at byte offset / 512.
+struct QuadMaps {
+  CUtensorMap w[14];              // lin_in, lin_z x3, fc_0 x5, fc_1 x5 (PK128 images)
+  CUtensorMap lat, code;
 };
 
 enum { EPI_X = 0, EPI_T = 1, EPI_MEAN = 2, EPI_HEAD = 3 };
@@ -439,7 +450,7 @@ __device__ __forceinline__ bool quad_last(int it, int q, int n_clusters, int n_p
 }
 
 template <int NV, bool MERGE>
-__global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_quad_fwd_kernel(const PairParams P) {
+__global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_quad_fwd_kernel(const PairParams P, const __grid_constant__ QuadMaps M) {
   extern __shared__ __align__(128) unsigned char smem[];
   unsigned char* abuf = smem;                                   // 128 KB resident A operand
   unsigned char* ring = smem + kPAbuf;                          // 6 x 16 KB
@@ -453,6 +464,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
   uint64_t* a_own2 = bars + 32;           // [4]  (even CTA) K-block p written in BOTH CTAs of the MMA pair (16 arrivals)
   uint64_t* pushed = bars + 26;           // [1]  partner received my whole half
   uint64_t* peer_free = bars + 27;        // [1]  partner's A buffer may receive my next operand
+  uint64_t* odd_peer = bars + 28;         // [2]  (even CTA, tma2) the partner's K-blocks {0,1} / {2,3} landed in the ODD CTA
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 40);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -471,6 +483,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
     for (int i = 0; i < 4; ++i) { tc::mbar_init(a_own + i, 8); tc::mbar_init(a_own2 + i, 16); }
     tc::mbar_init(a_peer + 0, 1); tc::mbar_init(a_peer + 1, 1);
     tc::mbar_init(pushed, 1); tc::mbar_init(peer_free, 1);
+    tc::mbar_init(odd_peer + 0, 1); tc::mbar_init(odd_peer + 1, 1);
     tc::fence_barrier_init();
   }
   __syncthreads();
@@ -488,11 +501,27 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
       const uint64_t pol_keep = tc::policy_evict_last(), pol_stream = tc::policy_evict_first();
       const uint64_t pol_norm = tc::policy_evict_normal();
       int slot = 0; uint32_t phase = 0;
-      auto fill = [&](const unsigned char* src, uint64_t pol) {
+      // fill(): one 16 KB K-block into the next ring slot.  Plain mode: cp.async.bulk completing on MY full barrier (the
+      // odd CTA then forwards "in place" to the even CTA).  tma2 mode: tensor-map TMA whose bytes are counted on the EVEN
+      // CTA's full barrier, which its producer arms for both CTAs' 2 x 16 KB.
+      const uint32_t even_rank = cr & ~1u;
+      auto fill = [&](const unsigned char* src, uint64_t pol, const CUtensorMap* map, int row0) {
         tc::mbar_wait(empty + slot, phase ^ 1);
-        tc::mbar_arrive_expect_tx(full + slot, kQSlot);
-        tc::bulk_g2s_hint(ring + (size_t)slot * kQSlot, src, kQSlot, full + slot, pol);
+        if (P.tma2) {
+          if (t == 0) tc::mbar_arrive_expect_tx(full + slot, 2 * kQSlot);
+          tc::tma_load_2d_2cta(ring + (size_t)slot * kQSlot, map, 0, row0, tc::cluster_addr(full + slot, even_rank), pol);
+        } else {
+          tc::mbar_arrive_expect_tx(full + slot, kQSlot);
+          tc::bulk_g2s_hint(ring + (size_t)slot * kQSlot, src, kQSlot, full + slot, pol);
+        }
         if (++slot == kQRing) { slot = 0; phase ^= 1; }
+      };
+      auto w_map = [&](const unsigned char* w) -> const CUtensorMap* {      // the tensor map of a weight image
+        if (w == P.w_in) return &M.w[0];
+        for (int i = 0; i < 3; ++i) if (w == P.w_z[i]) return &M.w[1 + i];
+        for (int i = 0; i < 5; ++i) if (w == P.w_0[i]) return &M.w[4 + i];
+        for (int i = 0; i < 5; ++i) if (w == P.w_1[i]) return &M.w[9 + i];
+        return &M.w[0];
       };
       POp d;
       for (int q = cluster, it = 0; q < n_pairs; q += n_clusters, ++it) {
@@ -507,19 +536,21 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
         for (int o = 0; o < n_ops; ++o) {
           pair_get_op(P, o, d);
           if (d.code) {
-            fill(P.code_pk + (size_t)tile * 16384, pol_stream);
-            fill(P.w_in + (size_t)cr * 16384, pol_keep);
+            fill(P.code_pk + (size_t)tile * 16384, pol_stream, &M.code, tile * 32);
+            fill(P.w_in + (size_t)cr * 16384, pol_keep, &M.w[0], (int)cr * 32);
           }
           if (d.lat_w) {
+            const CUtensorMap* wm = P.tma2 ? w_map(d.lat_w) : nullptr;
             for (int kb = 0; kb < 8; ++kb) {
-              fill(lat + (size_t)kb * 16384, o == 4 ? pol_stream : pol_norm);       // last use: evict first
-              fill(d.lat_w + (size_t)cr * 131072 + (size_t)kb * 16384, pol_keep);
+              fill(lat + (size_t)kb * 16384, o == 4 ? pol_stream : pol_norm, &M.lat, tile * 256 + kb * 32);   // last use: evict first
+              fill(d.lat_w + (size_t)cr * 131072 + (size_t)kb * 16384, pol_keep, wm, (int)cr * 256 + kb * 32);
             }
           }
           if (d.abuf_w) {
+            const CUtensorMap* wm = P.tma2 ? w_map(d.abuf_w) : nullptr;
             for (int i = 0; i < 8; ++i) {
               const int kb = pair_kb_order(h, i);
-              fill(d.abuf_w + (size_t)cr * 131072 + (size_t)kb * 16384, pol_keep);
+              fill(d.abuf_w + (size_t)cr * 131072 + (size_t)kb * 16384, pol_keep, wm, (int)cr * 256 + kb * 32);
             }
           }
         }
@@ -544,11 +575,11 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
           auto step_ring_ab = [&]() {        // A and B both come from consecutive ring slots
             const int sa = slot;
             TIMED(w_ring_lat, tc::mbar_wait(full + sa, phase));
-            TIMED(w_pfull_lat, tc::mbar_wait(peer_full + sa, phase));
+            if (!P.tma2) TIMED(w_pfull_lat, tc::mbar_wait(peer_full + sa, phase));
             if (++slot == kQRing) { slot = 0; phase ^= 1; }
             const int sb = slot;
             TIMED(w_ring_lat, tc::mbar_wait(full + sb, phase));
-            TIMED(w_pfull_lat, tc::mbar_wait(peer_full + sb, phase));
+            if (!P.tma2) TIMED(w_pfull_lat, tc::mbar_wait(peer_full + sb, phase));
             if (++slot == kQRing) { slot = 0; phase ^= 1; }
             tc::fence_after_sync();
             const uint32_t a0 = tc::smem_u32(ring + (size_t)sa * kQSlot), b0 = tc::smem_u32(ring + (size_t)sb * kQSlot);
@@ -571,8 +602,10 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
               if (i < 4) TIMED(w_own, tc::mbar_wait(a_own2 + i, par));
               if (i == 4) TIMED(w_peer, tc::mbar_wait(a_peer + 0, par));
               if (i == 6) TIMED(w_peer, tc::mbar_wait(a_peer + 1, par));
+              if (P.tma2 && i == 4) TIMED(w_peer, tc::mbar_wait(odd_peer + 0, par));     // ... and in the odd CTA
+              if (P.tma2 && i == 6) TIMED(w_peer, tc::mbar_wait(odd_peer + 1, par));
               TIMED(w_ring, tc::mbar_wait(full + slot, phase));
-              TIMED(w_pfull, tc::mbar_wait(peer_full + slot, phase));
+              if (!P.tma2) TIMED(w_pfull, tc::mbar_wait(peer_full + slot, phase));
               tc::fence_after_sync();
               const uint32_t a0 = abuf0 + (uint32_t)kb * 16384u, b0 = tc::smem_u32(ring + (size_t)slot * kQSlot);
 #pragma unroll
@@ -608,6 +641,19 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
         const int n_ops = quad_last<NV, MERGE>(it, q, n_clusters, n_pairs) ? kPOps : 7;
         for (int o = 0; o < n_ops; ++o) {
           pair_get_op(P, o, d);
+          if (P.tma2) {
+            // the ring needs no forwarding (my loads complete on the even CTA's barrier); what the even CTA still has to
+            // learn from me is that the partner's half of the A operand has landed in MY buffer
+            if (d.abuf_w) {
+              const uint32_t par = (uint32_t)(aops & 1);
+              tc::mbar_wait(a_peer + 0, par);
+              tc::mbar_arrive_remote_relaxed(odd_peer + 0, mma_peer);
+              tc::mbar_wait(a_peer + 1, par);
+              tc::mbar_arrive_remote_relaxed(odd_peer + 1, mma_peer);
+              ++aops;
+            }
+            continue;
+          }
           if (d.code) { forward(); forward(); }
           if (d.lat_w)
             for (int kb = 0; kb < 8; ++kb) { forward(); forward(); }
@@ -882,7 +928,7 @@ DNR_EXPORT int dnr_mlp_pair_fwd(const void* lat_pk, const void* code_pk, const v
   for (int i = 0; i < 6; ++i) P.cb[i] = biases[i];
   for (int i = 0; i < 5; ++i) P.b_0[i] = biases[6 + i];
   P.w_out = w_out; P.head_partial = (float4*)head_partial;
-  P.NV = NV; P.SPW = 32 / NV; P.mv_tiles = mv_tiles; P.prof = prof;
+  P.NV = NV; P.SPW = 32 / NV; P.mv_tiles = mv_tiles; P.prof = prof; P.tma2 = 0;
   void (*kern)(const dnr::PairParams) = NV == 1 ? dnr::mlp_pair_fwd_kernel<1>
                                          : NV == 2 ? dnr::mlp_pair_fwd_kernel<2>
                                          : NV == 3 ? dnr::mlp_pair_fwd_kernel<3> : dnr::mlp_pair_fwd_kernel<4>;
@@ -902,8 +948,35 @@ DNR_EXPORT int dnr_mlp_pair_fwd(const void* lat_pk, const void* code_pk, const v
 }
 
 namespace dnr {
+// cuTensorMapEncodeTiled through the runtime (no -lcuda): a 2-D bf16 view [bytes / 512][256] of a packed buffer with a box
+// of 32 rows = one 16 KB K-block, no swizzle / interleave (the buffer already is the shared-memory image).
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+static bool encode_kblock_map(CUtensorMap* m, const void* base, size_t bytes) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn || bytes % 16384 != 0 || ((uintptr_t)base & 15)) return false;
+  const cuuint64_t dims[2] = {256, (cuuint64_t)(bytes / 512)};
+  const cuuint64_t strides[1] = {512};
+  const cuuint32_t box[2] = {256, 32};
+  const cuuint32_t estr[2] = {1, 1};
+  return fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
 // how many 4-CTA clusters the device holds at once (GPCs whose SM count is not a multiple of 4 leave SMs idle); -1 on error
-typedef void (*QuadKernel)(const PairParams);
+typedef void (*QuadKernel)(const PairParams, const QuadMaps);
 static QuadKernel quad_kernel(int NV, bool merge) {
   if (merge) return NV == 2 ? mlp_quad_fwd_kernel<2, true> : NV == 3 ? mlp_quad_fwd_kernel<3, true> : mlp_quad_fwd_kernel<4, true>;
   return NV == 1 ? mlp_quad_fwd_kernel<1, false> : NV == 2 ? mlp_quad_fwd_kernel<2, false>
@@ -962,14 +1035,28 @@ DNR_EXPORT int dnr_mlp_quad_fwd(const void* lat_pk, const void* code_pk, const v
   for (int i = 0; i < 6; ++i) P.cb[i] = biases[i];
   for (int i = 0; i < 5; ++i) P.b_0[i] = biases[6 + i];
   P.w_out = w_out; P.head_partial = (float4*)head_partial;
-  P.NV = NV; P.SPW = 32 / NV; P.mv_tiles = mv_tiles; P.prof = prof;
+  P.NV = NV; P.SPW = 32 / NV; P.mv_tiles = mv_tiles; P.prof = prof; P.tma2 = 0;
   P.merge_scratch = (float*)merge_scratch;
+  dnr::QuadMaps M;
+  memset(&M, 0, sizeof(M));
+  {
+    // operand delivery: tensor-map TMA completing on the even CTA's barrier (tma2) unless DNR_QUAD_TMA2=0
+    static const char* e = getenv("DNR_QUAD_TMA2");
+    P.tma2 = (e && e[0] == '0') ? 0 : 1;
+    if (P.tma2) {
+      bool ok = dnr::encode_kblock_map(&M.w[0], weights_pk128[0], (size_t)512 * 64 * 2);
+      for (int i = 1; i < 14 && ok; ++i) ok = dnr::encode_kblock_map(&M.w[i], weights_pk128[i], (size_t)512 * 512 * 2);
+      ok = ok && dnr::encode_kblock_map(&M.lat, lat_pk, (size_t)mv_tiles * 131072);
+      ok = ok && dnr::encode_kblock_map(&M.code, code_pk, (size_t)mv_tiles * 16384);
+      DNR_REQUIRE(ok, "dnr_mlp_quad_fwd: cuTensorMapEncodeTiled failed (driver entry point missing or misaligned operand)");
+    }
+  }
   dnr::QuadKernel kern = dnr::quad_kernel(NV, merge_scratch != nullptr && NV > 1);
   const int max_cl = dnr::quad_max_clusters(NV);
   DNR_REQUIRE(max_cl >= 1, "dnr_mlp_quad_fwd: the device cannot hold a cluster of 4 CTAs with 225 KB of shared memory each");
   const int n_pairs = (mv_tiles + 1) / 2;
   const int clusters = n_pairs < max_cl ? n_pairs : max_cl;
-  kern<<<4 * clusters, dnr::kPThreads, dnr::kQSmem, stream>>>(P);
+  kern<<<4 * clusters, dnr::kPThreads, dnr::kQSmem, stream>>>(P, M);
   DNR_CHECK_LAUNCH("dnr_mlp_quad_fwd");
   return 0;
 }
@@ -1042,7 +1129,7 @@ DNR_EXPORT int dnr_mlp_quad_fwd_static(const void* lat_pk, const void* code_pk, 
   for (int i = 0; i < 6; ++i) P.cb[i] = biases[i];
   for (int i = 0; i < 5; ++i) P.b_0[i] = biases[6 + i];
   P.w_out = w_out; P.head_partial = (float4*)head_partial;
-  P.NV = NV; P.SPW = 32 / NV; P.mv_tiles = mv_tiles; P.prof = nullptr;
+  P.NV = NV; P.SPW = 32 / NV; P.mv_tiles = mv_tiles; P.prof = nullptr; P.tma2 = 0;
   P.merge_scratch = dnr::g_quad_static_ptr[dev];
   dnr::QuadKernel kern = dnr::quad_kernel(NV, NV > 1);
   const int max_cl = dnr::quad_max_clusters(NV);      // also sets the kernels' shared-memory attribute on this device
@@ -1050,7 +1137,9 @@ DNR_EXPORT int dnr_mlp_quad_fwd_static(const void* lat_pk, const void* code_pk, 
   const int n_pairs = (mv_tiles + 1) / 2;
   int clusters = n_pairs < dnr::kStaticQuadClusters ? n_pairs : dnr::kStaticQuadClusters;
   if (clusters > max_cl) clusters = max_cl;
-  kern<<<4 * clusters, dnr::kPThreads, dnr::kQSmem, stream>>>(P);
+  dnr::QuadMaps M;                                     // (plain bulk copies: this entry point keeps the first-version path)
+  memset(&M, 0, sizeof(M));
+  kern<<<4 * clusters, dnr::kPThreads, dnr::kQSmem, stream>>>(P, M);
   DNR_CHECK_LAUNCH("dnr_mlp_quad_fwd_static");
   return 0;
 }

@@ -45,6 +45,24 @@ __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, u
                : "memory");
 }
 
+// shared::cluster address of `p` (a pointer into my shared memory) as seen in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t cluster_addr(const void* p, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_u32(p)), "r"(rank));
+  return r;
+}
+// Tensor-map TMA load (SASS UTMALDG) of a 2-D box into MY shared memory whose completion (complete_tx) is counted on an
+// mbarrier given by its shared::cluster address -- with .cta_group::2 that barrier may live in the other CTA of my CTA
+// pair, which is how the odd CTA's operands become visible to the even CTA's MMA thread without a forwarding hop.
+__device__ __forceinline__ void tma_load_2d_2cta(void* smem_dst, const void* tensor_map, int c0, int c1,
+                                                 uint32_t mbar_cluster_addr, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(smem_dst)), "l"(tensor_map), "r"(mbar_cluster_addr), "r"(c0),
+      "r"(c1), "l"(policy)
+      : "memory");
+}
+
 // L2 eviction policies (createpolicy) and hinted variants of the bulk copy / vector store / vector load
 __device__ __forceinline__ uint64_t policy_evict_first() {
   uint64_t p; asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p)); return p;

@@ -4,7 +4,7 @@ MLP kernels are genuine tcgen05 / TMEM / bulk-copy-engine code:
     python tools/sass_summary.py > profiles/r2_sass_summary.md
 
 UTCHMMA = tcgen05.mma (.2CTA = cta_group::2), LDTM / STTM = tcgen05.ld / st (TMEM), UTCBAR = tcgen05.commit,
-UBLKCP = cp.async.bulk (TMA engine, non-tensor), SYNCS = mbarrier ops, FFMA2 / FMUL2 = packed f32x2 math,
+UTMALDG = cp.async.bulk.tensor (tensor-map TMA), UBLKCP = cp.async.bulk (TMA engine, non-tensor), SYNCS = mbarrier ops, FFMA2 / FMUL2 = packed f32x2 math,
 REDG / ATOMG = global reductions / atomics, CCTL.IVALL = L1 invalidate (cluster-scope acquire).
 """
 import collections
@@ -48,7 +48,7 @@ def main():
     print("# SASS summary of `diner_b200/libdiner_b200.so` (sm_100a), `python tools/sass_summary.py`\n")
     print("Per kernel: SASS instructions, registers, static shared memory, and the counts of the mnemonics that identify the "
           "Blackwell units in use.\n")
-    cols = ["UTCHMMA", "UTCHMMA.2CTA", "LDTM", "STTM", "UTCBAR", "UBLKCP", "UBLKPF", "SYNCS", "FFMA2", "FMUL2", "REDG", "ATOMG",
+    cols = ["UTCHMMA", "UTCHMMA.2CTA", "LDTM", "STTM", "UTCBAR", "UTMALDG", "UBLKCP", "UBLKPF", "SYNCS", "FFMA2", "FMUL2", "REDG", "ATOMG",
             "CCTL.IVALL", "MUFU", "SHFL"]
     print("| kernel | instr | regs | " + " | ".join(cols) + " |")
     print("|---|---:|---:|" + "---:|" * len(cols))
@@ -59,9 +59,9 @@ def main():
         print(f"| `{short}` | {total[f]} | {regs.get(f, ('', ''))[0]} | " + " | ".join(str(c[k]) if c[k] else "" for k in cols) + " |")
         tot.update(c)
     print("| **all kernels** | %d | | " % sum(total.values()) + " | ".join(str(tot[k]) if tot[k] else "" for k in cols) + " |")
-    print("\nNo `UTMALDG` (tensor-map TMA loads): operands are pre-packed into the tcgen05 canonical shared-memory image, so "
-          "plain bulk copies (`UBLKCP`) move them.  No `HMMA` / `HGMMA` (mma.sync / wgmma) anywhere: %d." %
-          len(re.findall(r"\bHG?MMA\b", sass)))
+    print("\n`UTMALDG` (tensor-map TMA loads, %d): the quad kernel's operand ring in its default mode (cta_group::2 completion on "
+          "the even CTA's barrier); everything else moves pre-packed operands with plain bulk copies (`UBLKCP`).  No `HMMA` / "
+          "`HGMMA` (mma.sync / wgmma) anywhere: %d." % (tot["UTMALDG"], len(re.findall(r"\bHG?MMA\b", sass))))
 
 
 if __name__ == "__main__":
