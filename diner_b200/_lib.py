@@ -11,7 +11,7 @@ import os
 from . import _build
 
 _lib = None
-ABI_VERSION = 12
+ABI_VERSION = 13
 
 # instrumentation used by bench.py: number of kernel launches issued through the ABI, and (when `profile` is a
 # list) one (name, start_event, end_event, tag) record per call for per-kernel CUDA-event timing
@@ -45,7 +45,7 @@ _SIGNATURES = {
     "dnr_encode_bwd": (c_i, [c_p] * 8 + [c_i] * 10 + [c_ll, c_ll] + [c_f] * 4 + [c_p, c_p, c_p]),
     "dnr_pack_latent_nhwc": (c_i, [c_p, c_i, c_i, c_i, c_i, c_p, c_p]),
     "dnr_unpack_dlatent_nchw": (c_i, [c_p, c_i, c_i, c_i, c_i, c_p, c_p]),
-    "dnr_mlp_gemm": (c_i, [c_p, c_p, c_i, c_p, c_p, c_i, c_p, c_p, c_i, c_i, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i,
+    "dnr_mlp_gemm": (c_i, [c_p, c_p, c_i, c_p, c_p, c_i, c_p, c_p, c_i, c_i, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i,
                            c_ll, c_i, c_p]),
     "dnr_mlp_wgrad": (c_i, [c_p, c_i, c_p, c_i, c_i, c_p, c_i, c_i, c_i, c_p, c_p]),
     "dnr_pack_weight": (c_i, [c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_p, c_p]),
@@ -61,6 +61,7 @@ _SIGNATURES = {
     "dnr_mlp_fused_fwd": (c_i, [c_p, c_p, c_p, c_p, c_i, c_i, c_ll, c_p, c_p, c_i, c_p]),
     "dnr_head_bwd": (c_i, [c_p, c_p, c_p, c_p, c_ll, c_p, c_p, c_p, c_p]),
     "dnr_mean_bwd": (c_i, [c_p, c_i, c_ll, c_i, c_p, c_p, c_p]),
+    "dnr_mean_bwd_pk": (c_i, [c_p, c_i, c_ll, c_i, c_p, c_p]),
     "dnr_pack_rows": (c_i, [c_p, c_ll, c_i, c_ll, c_p, c_p]),
     "dnr_unpack_rows": (c_i, [c_p, c_ll, c_i, c_p, c_p]),
     "dnr_xr_to_rows": (c_i, [c_p, c_ll, c_i, c_p, c_p]),

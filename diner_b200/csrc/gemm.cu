@@ -34,6 +34,7 @@ struct GemmParams {
   const float* bias;        // [N] or null
   const unsigned char* mask_pk;  // PK<128> [rows x N] bf16: keep acc where mask > 0 (ReLU backward) or null
   const float* res_in;      // XR [rows x N] fp32 added to the result, or null
+  const unsigned char* res_in_pk;  // PK<128> [rows x N] bf16 added to the result instead of res_in (bf16 gradient stream), or null
   float* res_out;           // XR [rows x N] fp32, or null
   unsigned char* act_out;   // PK<128> [rows x N] bf16, or null
   unsigned char* act_lo_out;  // verification mode: PK<128> bf16 image of (v - bf16(v)) beside act_out, or null
@@ -49,6 +50,7 @@ struct GemmParams {
 struct EpiOperands {
   float4 r[8];
   uint4 m[4];
+  uint4 rp[4];      // res_in_pk
 };
 __device__ __forceinline__ void epilogue_prefetch(const GemmParams& P, int m_tile, int n0, int row_in_tile,
                                                   EpiOperands& e) {
@@ -57,6 +59,11 @@ __device__ __forceinline__ void epilogue_prefetch(const GemmParams& P, int m_til
     const unsigned char* mp = P.mask_pk + ((size_t)((size_t)m_tile * (N / 8) + n0 / 8) * 128 + row_in_tile) * 16;
 #pragma unroll
     for (int c = 0; c < 4; ++c) e.m[c] = __ldg(reinterpret_cast<const uint4*>(mp + (size_t)c * 2048));
+  }
+  if (P.res_in_pk) {
+    const unsigned char* rq = P.res_in_pk + ((size_t)((size_t)m_tile * (N / 8) + n0 / 8) * 128 + row_in_tile) * 16;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) e.rp[c] = __ldg(reinterpret_cast<const uint4*>(rq + (size_t)c * 2048));
   }
   if (P.res_in && P.res_in_nv) {
     // d_x[(sample, view)] = d_mean[sample] / NV (resnetfc.py:9-14): the NV rows of a sample read the same pooled row
@@ -108,6 +115,15 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& P, int m_tile, 
     for (int c = 0; c < 8; ++c) {
       const float4 r = e.r[c];
       v[c * 4] += r.x; v[c * 4 + 1] += r.y; v[c * 4 + 2] += r.z; v[c * 4 + 3] += r.w;
+    }
+  }
+  if (P.res_in_pk) {
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const uint4 r = e.rp[c];
+      const uint32_t rv[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) { v[c * 8 + q * 2] += bf16lo(rv[q]); v[c * 8 + q * 2 + 1] += bf16hi(rv[q]); }
     }
   }
   // destination row: the (sample, view) row itself, or -- at the combine layer -- the sample
@@ -290,8 +306,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) mlp_gemm_kernel(const GemmPar
 // One fused linear layer of the field MLP (forward or dgrad), see GemmParams.
 DNR_EXPORT int dnr_mlp_gemm(const void* A0, const void* B0, int K0, const void* A1, const void* B1, int K1,
                             const void* A2, const void* B2, int K2, int m_tiles, int N, const float* bias,
-                            const void* mask_pk, const float* res_in, float* res_out, void* act_out, void* act_lo_out,
-                            int relu_act, int mean_nv, long long n_samples, int max_ctas, cudaStream_t stream) {
+                            const void* mask_pk, const float* res_in, const void* res_in_pk, float* res_out, void* act_out,
+                            void* act_lo_out, int relu_act, int mean_nv, long long n_samples, int max_ctas,
+                            cudaStream_t stream) {
   DNR_REQUIRE(N > 0 && N % dnr::kBN == 0, "dnr_mlp_gemm: N must be a multiple of 256");
   DNR_REQUIRE(A0 && B0 && K0 > 0 && K0 % dnr::kBK == 0, "dnr_mlp_gemm: segment 0 invalid (K multiple of 64)");
   DNR_REQUIRE(K1 % dnr::kBK == 0 && K2 % dnr::kBK == 0, "dnr_mlp_gemm: K must be a multiple of 64");
@@ -304,7 +321,9 @@ DNR_EXPORT int dnr_mlp_gemm(const void* A0, const void* B0, int K0, const void* 
   P.seg[2] = {(const unsigned char*)A2, (const unsigned char*)B2, K2};
   P.nseg = 1 + (A1 != nullptr && K1 > 0 ? 1 : 0);
   if (P.nseg == 2 && A2 != nullptr && K2 > 0) P.nseg = 3;
-  P.m_tiles = m_tiles; P.N = N; P.bias = bias; P.mask_pk = (const unsigned char*)mask_pk; P.res_in = res_in;
+  P.m_tiles = m_tiles; P.N = N; P.bias = bias; P.mask_pk = (const unsigned char*)mask_pk; P.res_in = res_in; P.res_in_pk = (const unsigned char*)res_in_pk;
+  DNR_REQUIRE(!(res_in && res_in_pk), "dnr_mlp_gemm: res_in and res_in_pk are exclusive");
+  DNR_REQUIRE(!(res_in_pk && mean_nv != 0), "dnr_mlp_gemm: res_in_pk cannot be combined with a view mean");
   P.res_out = res_out; P.act_out = (unsigned char*)act_out; P.act_lo_out = (unsigned char*)act_lo_out; P.relu_act = relu_act;
   DNR_REQUIRE(act_lo_out == nullptr || act_out != nullptr, "dnr_mlp_gemm: act_lo_out needs act_out");
   P.mean_nv = mean_nv > 0 ? mean_nv : 0; P.res_in_nv = mean_nv < 0 ? -mean_nv : 0;

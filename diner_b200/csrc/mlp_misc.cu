@@ -100,8 +100,10 @@ __global__ void __launch_bounds__(128) head_bwd_kernel(const unsigned char* __re
       const float g = g0 * sw[k] + g1 * sw[kHid + k] + g2 * sw[2 * kHid + k] + g3 * sw[3 * kHid + k];
       v[e] = xa > 0.f ? g : 0.f;
     }
-    xr[(size_t)(c * 2) * 128] = make_float4(v[0], v[1], v[2], v[3]);
-    xr[(size_t)(c * 2 + 1) * 128] = make_float4(v[4], v[5], v[6], v[7]);
+    if (dx_xr) {
+      xr[(size_t)(c * 2) * 128] = make_float4(v[0], v[1], v[2], v[3]);
+      xr[(size_t)(c * 2 + 1) * 128] = make_float4(v[4], v[5], v[6], v[7]);
+    }
     *reinterpret_cast<uint4*>(pb + (size_t)c * 2048) =
         make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
   }
@@ -127,6 +129,29 @@ __global__ void __launch_bounds__(128) mean_bwd_kernel(const float* __restrict__
     if (dx_xr) { xr[(size_t)(c * 2) * 128] = a; xr[(size_t)(c * 2 + 1) * 128] = b; }
     *reinterpret_cast<uint4*>(pb + (size_t)c * 2048) =
         make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y), pack_bf16x2(b.z, b.w));
+  }
+}
+
+// The same for the bf16 gradient stream: the pooled gradient arrives as its PK<128> bf16 image (indexed by sample).
+__global__ void __launch_bounds__(128) mean_bwd_pk_kernel(const unsigned char* __restrict__ dmean_pk, int NV,
+                                                          long long n_samples, unsigned char* __restrict__ dx_pk) {
+  const RowMap rm = RowMap::make(NV);
+  const long long row = (long long)blockIdx.x * 128 + threadIdx.x;
+  long long sample; int view;
+  const bool valid = rm.decode(row, n_samples, sample, view);
+  const float inv = 1.f / (float)NV;
+  const unsigned char* src = nullptr;
+  if (valid) src = dmean_pk + ((size_t)(sample >> 7) * (kHid / 8) * 128 + (size_t)(sample & 127)) * 16;
+  unsigned char* pb = dx_pk + (size_t)blockIdx.x * (kHid / 8) * 2048 + (size_t)threadIdx.x * 16;
+#pragma unroll 4
+  for (int c = 0; c < kHid / 8; ++c) {
+    uint4 o = make_uint4(0u, 0u, 0u, 0u);
+    if (valid) {
+      const uint4 a = __ldg(reinterpret_cast<const uint4*>(src + (size_t)c * 2048));
+      o = make_uint4(pack_bf16x2(bf16lo(a.x) * inv, bf16hi(a.x) * inv), pack_bf16x2(bf16lo(a.y) * inv, bf16hi(a.y) * inv),
+                     pack_bf16x2(bf16lo(a.z) * inv, bf16hi(a.z) * inv), pack_bf16x2(bf16lo(a.w) * inv, bf16hi(a.w) * inv));
+    }
+    *reinterpret_cast<uint4*>(pb + (size_t)c * 2048) = o;
   }
 }
 
@@ -219,6 +244,15 @@ DNR_EXPORT int dnr_mean_bwd(const float* dmean_xr, int NV, long long n_samples, 
   if (view_tiles <= 0) return 0;
   dnr::mean_bwd_kernel<<<view_tiles, 128, 0, stream>>>(dmean_xr, NV, n_samples, dx_xr, (unsigned char*)dx_pk);
   DNR_CHECK_LAUNCH("dnr_mean_bwd");
+  return 0;
+}
+
+DNR_EXPORT int dnr_mean_bwd_pk(const void* dmean_pk, int NV, long long n_samples, int view_tiles, void* dx_pk,
+                               cudaStream_t stream) {
+  DNR_REQUIRE(NV >= 1 && NV <= 8, "dnr_mean_bwd_pk: NV must be in [1,8]");
+  if (view_tiles <= 0) return 0;
+  dnr::mean_bwd_pk_kernel<<<view_tiles, 128, 0, stream>>>((const unsigned char*)dmean_pk, NV, n_samples, (unsigned char*)dx_pk);
+  DNR_CHECK_LAUNCH("dnr_mean_bwd_pk");
   return 0;
 }
 

@@ -1048,7 +1048,7 @@ DNR_EXPORT int dnr_mlp_quad_fwd(const void* lat_pk, const void* code_pk, const v
       for (int i = 1; i < 14 && ok; ++i) ok = dnr::encode_kblock_map(&M.w[i], weights_pk128[i], (size_t)512 * 512 * 2);
       ok = ok && dnr::encode_kblock_map(&M.lat, lat_pk, (size_t)mv_tiles * 131072);
       ok = ok && dnr::encode_kblock_map(&M.code, code_pk, (size_t)mv_tiles * 16384);
-      DNR_REQUIRE(ok, "dnr_mlp_quad_fwd: cuTensorMapEncodeTiled failed (driver entry point missing or misaligned operand)");
+      if (!ok) { P.tma2 = 0; memset(&M, 0, sizeof(M)); }     // driver entry point missing: the plain bulk-copy delivery
     }
   }
   dnr::QuadKernel kern = dnr::quad_kernel(NV, merge_scratch != nullptr && NV > 1);

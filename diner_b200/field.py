@@ -43,6 +43,10 @@ PAIR_SHARE = None
 # never changes the result (both kernels produce the same bits, tests/test_gpu_field.py), only the balance.
 ADAPT_SPLIT = os.environ.get("DNR_ADAPT_SPLIT", "1") != "0"     # 0: fixed split from PAIR_RATE (reproducible captures)
 _split_state = {}            # (device, NV) -> dict(rate=float, pending=[(e_q0, e_q1, e_p0, e_p1, tiles_q, tiles_p)])
+# Backward pass: precision of the residual GRADIENT stream d x_b between blocks.  "bf16": the stream is the bf16 operand
+# image the next dgrad GEMM reads anyway (each block adds its dgrad in fp32 and rounds once) -- 3 KB instead of 7 KB per
+# row in the HBM-bound fc_0 dgrad layers.  "fp32": a separate fp32 stream is read and written by every block (round 1).
+GRAD_STREAM = os.environ.get("DNR_GRAD_STREAM", "bf16")
 MERGE_POOLED = True          # quad kernel: run blocks 3-4 + head once per NV tiles on merged pooled rows (NV > 1)
 _side_stream = {}
 LAST_SPLIT = {}              # bench instrumentation: tiles of the most recent inference MLP launch (main / side kernel)
@@ -177,10 +181,11 @@ def _fused_scratch(dev) -> torch.Tensor:
 
 
 def _gemm(A0, B0, K0, m_tiles, N=HID, A1=None, B1=None, K1=0, A2=None, B2=None, K2=0, bias=None, mask=None,
-          res_in=None, res_out=None, act_out=None, relu=0, mean_nv=0, n_samples=0, max_ctas=0, act_lo=None):
+          res_in=None, res_out=None, act_out=None, relu=0, mean_nv=0, n_samples=0, max_ctas=0, act_lo=None, res_in_pk=None):
     p = _lib.ptr
     _lib.call("dnr_mlp_gemm", p(A0), p(B0), K0, p(A1), p(B1), K1, p(A2), p(B2), K2, m_tiles, N, p(bias), p(mask),
-              p(res_in), p(res_out), p(act_out), p(act_lo), relu, mean_nv, n_samples, max_ctas, _lib.stream_ptr())
+              p(res_in), p(res_in_pk), p(res_out), p(act_out), p(act_lo), relu, mean_nv, n_samples, max_ctas,
+              _lib.stream_ptr())
 
 
 def _gemm3(A, W, K, m_tiles, **kw):
@@ -447,7 +452,8 @@ def field_backward(sc: SceneBuffers, pk: PackedMLP, mlp, sv: FieldSaved, rays, z
     G = lambda name: grads[name]
 
     # ---- head: lin_out + activations ----
-    dx = torch.empty(ms * 128 * HID, **f32)           # d(block output), XR
+    bf16_stream = GRAD_STREAM == "bf16"
+    dx = None if bf16_stream else torch.empty(ms * 128 * HID, **f32)           # d(block output), XR (fp32 stream only)
     dx_pk = torch.empty(ms * 128 * HID, **bf)
     draw = torch.zeros(ms * 128 * 128, **bf)
     _lib.call("dnr_head_bwd", p(sv.xa[5]), p(pk.w_out), p(sv.out), p(d_out.contiguous()), n_samples, p(dx), p(dx_pk),
@@ -457,13 +463,16 @@ def field_backward(sc: SceneBuffers, pk: PackedMLP, mlp, sv: FieldSaved, rays, z
     def block_bwd(b, tiles, dx, dx_pk, pooled_dx=None):
         """dx = d x_{b+1} -> returns d x_b' (gradient at the block's input, after its lin_z was added).  With
         `pooled_dx` the fp32 stream entering the block is the POOLED gradient of the view mean: the dgrad epilogue
-        reads row (sample, view) as pooled_dx[sample] / NV and writes the per-view stream for the first time."""
+        reads row (sample, view) as pooled_dx[sample] / NV and writes the per-view stream for the first time.
+        With the bf16 gradient stream `dx` is unused: the stream IS dx_pk."""
         _wgrad(dx_pk, HID, sv.net[b], HID, tiles, G(f"blocks.{b}.fc_1.weight"), HID, HID, G(f"blocks.{b}.fc_1.bias"))
         dnet = torch.empty(tiles * 128 * HID, **bf)
         _gemm(dx_pk, pk.wt_1[b], HID, tiles, mask=sv.net[b], act_out=dnet)
         _wgrad(dnet, HID, sv.xa[b], HID, tiles, G(f"blocks.{b}.fc_0.weight"), HID, HID, G(f"blocks.{b}.fc_0.bias"))
         dx_pk2 = torch.empty(tiles * 128 * HID, **bf)
-        if pooled_dx is not None:
+        if bf16_stream:
+            _gemm(dnet, pk.wt_0[b], HID, tiles, mask=sv.xa[b], res_in_pk=dx_pk, act_out=dx_pk2)
+        elif pooled_dx is not None:
             dx = torch.empty(tiles * 128 * HID, **f32)
             _gemm(dnet, pk.wt_0[b], HID, tiles, mask=sv.xa[b], res_in=pooled_dx, res_out=dx, act_out=dx_pk2,
                   mean_nv=-NV, n_samples=n_samples)
@@ -474,10 +483,13 @@ def field_backward(sc: SceneBuffers, pk: PackedMLP, mlp, sv: FieldSaved, rays, z
     for b in (4, 3):
         dx, dx_pk = block_bwd(b, ms, dx, dx_pk)
     # ---- view mean ----
-    # only the bf16 operand image of d x / NV is materialised per view row; the fp32 stream is read from the pooled
-    # gradient by block 2's dgrad epilogue (2 KB per view row less to write and to read back)
+    # only the bf16 operand image of d x / NV is materialised per view row; with the fp32 stream the per-view fp32 values
+    # are read from the pooled gradient by block 2's dgrad epilogue (2 KB per view row less to write and to read back)
     dxv_pk = torch.empty(mv * 128 * HID, **bf)
-    _lib.call("dnr_mean_bwd", p(dx), NV, n_samples, mv, None, p(dxv_pk), st)
+    if bf16_stream:
+        _lib.call("dnr_mean_bwd_pk", p(dx_pk), NV, n_samples, mv, p(dxv_pk), st)
+    else:
+        _lib.call("dnr_mean_bwd", p(dx), NV, n_samples, mv, None, p(dxv_pk), st)
     pooled, dxv = dx, None
     del dx_pk
     dz_pk = [None, None, None]

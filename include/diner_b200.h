@@ -132,7 +132,8 @@ int dnr_pack_weight(const float* W, int rows_w, int cols_w, int ld, int transpos
 
 /* One fused linear layer of ResnetFC (src/models/resnetfc.py:61-69,129-159), forward or dgrad:
  *   D[rows x N] = sum_{seg<3} A_seg[rows x K_seg] * B_seg[N x K_seg]^T   (bf16 in, fp32 accumulate in TMEM)
- * epilogue: + bias[N]; * [mask_pk > 0] (ReLU backward); + res_in (XR); optional mean over the NV view rows of
+ * epilogue: + bias[N]; * [mask_pk > 0] (ReLU backward); + res_in (XR fp32) or + res_in_pk (PK128 bf16: the residual
+ * GRADIENT stream of the backward pass carried in bf16); optional mean over the NV view rows of
  * each sample (combine(), resnetfc.py:9-14; outputs then indexed by sample); outputs res_out (XR fp32) and/or
  * act_out (PK128 bf16, relu_act=1 applies ReLU; act_lo_out, nullable, receives the bf16 image of the rounding residue
  * v - bf16(v) for the verification mode).  A: PK128, B: PK256, K multiple of 64, N multiple of 256.
@@ -140,8 +141,8 @@ int dnr_pack_weight(const float* W, int rows_w, int cols_w, int ld, int transpos
  * sample, and row (sample, view) receives res_in[sample] / |mean_nv| (n_samples bounds the valid rows). */
 int dnr_mlp_gemm(const void* A0, const void* B0, int K0, const void* A1, const void* B1, int K1, const void* A2,
                  const void* B2, int K2, int m_tiles, int N, const float* bias, const void* mask_pk,
-                 const float* res_in, float* res_out, void* act_out, void* act_lo_out, int relu_act, int mean_nv,
-                 long long n_samples, int max_ctas, dnr_stream_t stream);
+                 const float* res_in, const void* res_in_pk, float* res_out, void* act_out, void* act_lo_out, int relu_act,
+                 int mean_nv, long long n_samples, int max_ctas, dnr_stream_t stream);
 
 /* Whole ResnetFC forward in ONE persistent kernel (inference): all 13 linear layers of resnetfc.py:129-159 with
  * the view mean (combine(), :9-14) fused, activations kept in an L2-resident per-CTA scratch instead of HBM.
@@ -208,7 +209,7 @@ int dnr_mlp_wgrad(const void* dY_pk, int Fy, const void* X_pk, int Fx, int row_t
  * the residue image of the verification mode, xa = hi + lo. */
 int dnr_head_fwd(const void* xa_pk, const void* xa_lo_pk, const float* Wout, const float* bout, long long n_samples,
                  int samples_per_tile, float* rgbsigma, dnr_stream_t stream);
-/* Backward of the head: dx (XR fp32 + PK128 bf16) and d_raw as PK128[rows x 128] (columns 0..3) for wgrad. */
+/* Backward of the head: dx (XR fp32, nullable + PK128 bf16) and d_raw as PK128[rows x 128] (columns 0..3) for wgrad. */
 int dnr_head_bwd(const void* xa_pk, const float* Wout, const float* rgbsigma, const float* d_rgbsigma,
                  long long n_samples, float* dx_xr, void* dx_pk, void* draw_pk, dnr_stream_t stream);
 /* Backward of the view mean (resnetfc.py:9-14): d_x[(sample,view)] = d_mean[sample] / NV. */
@@ -216,6 +217,9 @@ int dnr_head_bwd(const void* xa_pk, const float* Wout, const float* rgbsigma, co
  * through dnr_mlp_gemm's mean_nv < 0). */
 int dnr_mean_bwd(const float* dmean_xr, int NV, long long n_samples, int view_tiles, float* dx_xr, void* dx_pk,
                  dnr_stream_t stream);
+/* The same for the bf16 gradient stream (diner_b200.field.GRAD_STREAM = "bf16"): the pooled gradient is its PK128 bf16 image
+ * indexed by sample; d_x[(sample,view)] = bf16(d_mean[sample] / NV) as the PK128 image of the view rows. */
+int dnr_mean_bwd_pk(const void* dmean_pk, int NV, long long n_samples, int view_tiles, void* dx_pk, dnr_stream_t stream);
 
 /* Layout converters (tests, small tensors). */
 int dnr_pack_rows(const float* src, long long rows, int F, long long rows_pad, void* out_pk128, dnr_stream_t stream);

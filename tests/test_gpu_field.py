@@ -50,6 +50,25 @@ def test_gemm_layer_matches_torch(rows, K):
     torch.testing.assert_close(_unpack_rows(act, rows, 512), torch.relu(ref), rtol=1e-2, atol=1e-2)
 
 
+def test_gemm_bf16_residual_operand():
+    """Backward epilogue with the residual GRADIENT stream given as its bf16 PK128 image (res_in_pk) and a ReLU mask:
+    D = (A W^T) * [mask > 0] + res, against torch on the bf16-rounded operands."""
+    dev = _cuda()
+    from diner_b200.field import _gemm
+    from tools.gpu_diag import _pack_rows, _pack_w, _unpack_rows
+    torch.manual_seed(7)
+    bfr = lambda t: t.bfloat16().float()
+    rows, K = 700, 512
+    rp = (rows + 127) // 128 * 128
+    A = torch.randn(rows, K, device=dev); W = torch.randn(512, K, device=dev) / K ** 0.5
+    mask = torch.randn(rows, 512, device=dev); res = torch.randn(rows, 512, device=dev)
+    want = (bfr(A) @ bfr(W).T) * (bfr(mask) > 0) + bfr(res)
+    act = torch.empty(rp * 512, device=dev, dtype=torch.bfloat16)
+    _gemm(_pack_rows(A, rp), _pack_w(W), K, rp // 128, mask=_pack_rows(mask, rp), res_in_pk=_pack_rows(res, rp), act_out=act)
+    got = _unpack_rows(act, rows, 512)
+    torch.testing.assert_close(got, bfr(want), rtol=2.0 ** -7, atol=1e-3)          # one bf16 rounding of the result
+
+
 @pytest.mark.parametrize("NV", [2, 3, 4])
 def test_gemm_view_mean_epilogue(NV):
     dev = _cuda()

@@ -50,8 +50,8 @@ def test_argument_validation_needs_no_gpu():
     assert lib.dnr_view_row_tiles(10, 9) == -1
     rc = lib.dnr_composite_fwd(None, None, None, 10, 0, 1, None, None, None, None)
     assert rc == 1 and b"K must be" in lib.dnr_last_error()
-    rc = lib.dnr_mlp_gemm(None, None, 64, None, None, 0, None, None, 0, 1, 100, None, None, None, None, None, None, 0, 0,
-                          0, 0, None)
+    rc = lib.dnr_mlp_gemm(None, None, 64, None, None, 0, None, None, 0, 1, 100, None, None, None, None, None, None, None, 0,
+                          0, 0, 0, None)
     assert rc == 1 and b"multiple of 256" in lib.dnr_last_error()
     with pytest.raises(RuntimeError, match="dnr_mlp_wgrad failed"):
         _lib.call("dnr_mlp_wgrad", None, 100, None, 64, 1, None, 64, 1, 1, None, None)
