@@ -975,6 +975,21 @@ static bool encode_kblock_map(CUtensorMap* m, const void* base, size_t bytes) {
             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
+// Weight images rarely change between launches: keep their tensor maps (per thread; keyed by base pointer and size -- a
+// tensor map describes addresses, not contents, so a refilled buffer at the same address needs no new map).
+static bool cached_kblock_map(CUtensorMap* out, const void* base, size_t bytes) {
+  struct Entry { const void* base; size_t bytes; CUtensorMap m; };
+  static thread_local Entry cache[32];
+  static thread_local int used = 0, next = 0;
+  for (int i = 0; i < used; ++i)
+    if (cache[i].base == base && cache[i].bytes == bytes) { *out = cache[i].m; return true; }
+  if (!encode_kblock_map(out, base, bytes)) return false;
+  Entry& e = cache[next];
+  e.base = base; e.bytes = bytes; e.m = *out;
+  next = (next + 1) % 32;
+  if (used < 32) ++used;
+  return true;
+}
 // how many 4-CTA clusters the device holds at once (GPCs whose SM count is not a multiple of 4 leave SMs idle); -1 on error
 typedef void (*QuadKernel)(const PairParams, const QuadMaps);
 static QuadKernel quad_kernel(int NV, bool merge) {
@@ -1044,8 +1059,8 @@ DNR_EXPORT int dnr_mlp_quad_fwd(const void* lat_pk, const void* code_pk, const v
     static const char* e = getenv("DNR_QUAD_TMA2");
     P.tma2 = (e && e[0] == '0') ? 0 : 1;
     if (P.tma2) {
-      bool ok = dnr::encode_kblock_map(&M.w[0], weights_pk128[0], (size_t)512 * 64 * 2);
-      for (int i = 1; i < 14 && ok; ++i) ok = dnr::encode_kblock_map(&M.w[i], weights_pk128[i], (size_t)512 * 512 * 2);
+      bool ok = dnr::cached_kblock_map(&M.w[0], weights_pk128[0], (size_t)512 * 64 * 2);
+      for (int i = 1; i < 14 && ok; ++i) ok = dnr::cached_kblock_map(&M.w[i], weights_pk128[i], (size_t)512 * 512 * 2);
       ok = ok && dnr::encode_kblock_map(&M.lat, lat_pk, (size_t)mv_tiles * 131072);
       ok = ok && dnr::encode_kblock_map(&M.code, code_pk, (size_t)mv_tiles * 16384);
       if (!ok) { P.tma2 = 0; memset(&M, 0, sizeof(M)); }     // driver entry point missing: the plain bulk-copy delivery
