@@ -42,6 +42,7 @@ struct EncodeParams {
   const __nv_bfloat16* gen_latent;  // [Hg,Wg,L] channels-last, shared by all scenes and views
   int Hg, Wg;
   float gen_img_w, gen_img_h, gen_sx, gen_sy;
+  float* d_gen_latent;   // bwd, NOVEL: [Hg,Wg,L] fp32 (accumulated into; one map for all scenes and views)
 };
 
 struct RowGeom {
@@ -607,6 +608,10 @@ __device__ __forceinline__ void red_add_v4(float* addr, float4 v) {
 constexpr int kBwdRowStride = 33;      // float4 per staged row: 32 + 1 pad -> conflict-free 128-bit stores
 constexpr int kBwdSmemBytes = 4 * 32 * kBwdRowStride * 16;
 
+// NOVEL (novel_pixelnerf.py:196, final_latent = gen_latent + latent): the same gradient row also belongs to the learned
+// map, at the footprint of the `gen`-deformed point, which is the same for the NV views of a sample -- the views' rows
+// are summed first, then runs of samples inside one footprint, and leave as vector reductions into d_gen_latent.
+template <bool NOVEL>
 __global__ void __launch_bounds__(128) encode_bwd_kernel(EncodeParams P) {
   extern __shared__ float4 bwd_stage[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -651,7 +656,7 @@ __global__ void __launch_bounds__(128) encode_bwd_kernel(EncodeParams P) {
       if (x1 != x0) red_add_v4(dl + (y1 * P.Wl + x1) * L, a11);
     }
   };
-  for (int v = 0; v < rm.NV; ++v) {
+  for (int v = 0; v < (P.d_latent ? rm.NV : 0); ++v) {
     for (int s = 0; s < rm.SPW; ++s) {
       const int l = s * rm.NV + v;
       const uint32_t m = __shfl_sync(0xffffffffu, km, l);
@@ -672,6 +677,51 @@ __global__ void __launch_bounds__(128) encode_bwd_kernel(EncodeParams P) {
     }
   }
   flush();
+  if (NOVEL && P.d_gen_latent) {
+    GenTaps gt;
+    gt.p00 = gt.p01 = gt.p10 = gt.p11 = 0u; gt.w00 = gt.w01 = gt.w10 = gt.w11 = 0.f;
+    uint32_t gok = 0;
+    const long long smp = slab * rm.SPW + lane;
+    if (lane < rm.SPW && smp < P.n_samples) {
+      gen_geometry(P, smp, (int)((smp / P.K + P.ray_offset) / P.NR), gt);
+      gok = 1;
+    }
+    uint32_t c00 = 0, c01 = 0, c10 = 0, c11 = 0;
+    bool open = false;
+    a00 = make_float4(0.f, 0.f, 0.f, 0.f); a01 = a00; a10 = a00; a11 = a00;
+    auto gflush = [&]() {
+      if (!open) return;
+      float* dg = P.d_gen_latent + ch;
+      red_add_v4(dg + c00, a00);
+      if (c01 != c00) red_add_v4(dg + c01, a01);
+      if (c10 != c00) {
+        red_add_v4(dg + c10, a10);
+        if (c11 != c10) red_add_v4(dg + c11, a11);
+      }
+    };
+    for (int s = 0; s < rm.SPW; ++s) {
+      if (__shfl_sync(0xffffffffu, gok, s) == 0) continue;           // past the last sample (warp-uniform)
+      const uint32_t q00 = __shfl_sync(0xffffffffu, gt.p00, s), q01 = __shfl_sync(0xffffffffu, gt.p01, s);
+      const uint32_t q10 = __shfl_sync(0xffffffffu, gt.p10, s), q11 = __shfl_sync(0xffffffffu, gt.p11, s);
+      const float w00 = __shfl_sync(0xffffffffu, gt.w00, s), w01 = __shfl_sync(0xffffffffu, gt.w01, s);
+      const float w10 = __shfl_sync(0xffffffffu, gt.w10, s), w11 = __shfl_sync(0xffffffffu, gt.w11, s);
+      if (!open || q00 != c00 || q01 != c01 || q10 != c10 || q11 != c11) {
+        gflush();
+        a00 = make_float4(0.f, 0.f, 0.f, 0.f); a01 = a00; a10 = a00; a11 = a00;
+        c00 = q00; c01 = q01; c10 = q10; c11 = q11; open = true;
+      }
+      float4 d = st[(s * rm.NV) * kBwdRowStride + lane];              // sum over the sample's views
+      for (int v = 1; v < rm.NV; ++v) {
+        const float4 e = st[(s * rm.NV + v) * kBwdRowStride + lane];
+        d.x += e.x; d.y += e.y; d.z += e.z; d.w += e.w;
+      }
+      a00.x = fmaf(d.x, w00, a00.x); a00.y = fmaf(d.y, w00, a00.y); a00.z = fmaf(d.z, w00, a00.z); a00.w = fmaf(d.w, w00, a00.w);
+      a01.x = fmaf(d.x, w01, a01.x); a01.y = fmaf(d.y, w01, a01.y); a01.z = fmaf(d.z, w01, a01.z); a01.w = fmaf(d.w, w01, a01.w);
+      a10.x = fmaf(d.x, w10, a10.x); a10.y = fmaf(d.y, w10, a10.y); a10.z = fmaf(d.z, w10, a10.z); a10.w = fmaf(d.w, w10, a10.w);
+      a11.x = fmaf(d.x, w11, a11.x); a11.y = fmaf(d.y, w11, a11.y); a11.z = fmaf(d.z, w11, a11.z); a11.w = fmaf(d.w, w11, a11.w);
+    }
+    gflush();
+  }
 }
 
 // latent (N,C,H,W) fp32 -> (N,H,W,C) bf16, tiled transpose through shared memory
@@ -726,6 +776,7 @@ static int fill_encode_params(dnr::EncodeParams& P, const float* rays, const flo
   P.lat_pk = nullptr; P.in_pk = nullptr; P.d_latent = nullptr; P.d_lat_xr = nullptr;
   P.pts_in = nullptr; P.pts_gen = nullptr; P.gen_poses = nullptr; P.gen_focal = nullptr; P.gen_cxy = nullptr;
   P.gen_latent = nullptr; P.Hg = P.Wg = 0; P.gen_img_w = P.gen_img_h = P.gen_sx = P.gen_sy = 0.f;
+  P.d_gen_latent = nullptr;
   return 0;
 }
 
@@ -802,7 +853,7 @@ DNR_EXPORT int dnr_encode_fwd_split(const float* rays, const float* z, const flo
 // chunk's sample points deformed with tgt_in_offsets / tgt_gen_offsets (dnr_novel_deform); pts_in replaces o + z d in the
 // projection chain, pts_gen is projected by the generic camera (gen_poses [SB,1,4,4], gen_focal / gen_cxy [SB,1,2],
 // gen_img_w/h) into gen_latent_nhwc [Hg,Wg,512] bf16 (feature-padding rescale gen_sx / gen_sy), and the feature row is
-// gen_latent[gen_uv] + latent[uv].  Forward only (the variant is built for evaluation).
+// gen_latent[gen_uv] + latent[uv].  Backward: dnr_encode_novel_bwd.
 DNR_EXPORT int dnr_encode_novel_fwd(const float* rays, const float* z, const float* pts_in, const float* pts_gen,
                                     const float* poses, const float* focal, const float* cxy, const float* depth,
                                     const void* latent_nhwc_bf16, const float* gen_poses, const float* gen_focal,
@@ -843,12 +894,43 @@ DNR_EXPORT int dnr_encode_bwd(const float* rays, const float* z, const float* po
   P.d_lat_xr = d_lat_xr; P.d_latent = d_latent_nhwc;
   if (P.n_samples <= 0) return 0;
   const int tiles = dnr::RowMap::make(NV).tiles_for(P.n_samples);
-  DNR_CHECK(cudaFuncSetAttribute(dnr::encode_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  DNR_CHECK(cudaFuncSetAttribute(dnr::encode_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  dnr::kBwdSmemBytes), "dnr_encode_bwd");
   const long long slabs = (P.n_samples + dnr::RowMap::make(NV).SPW - 1) / dnr::RowMap::make(NV).SPW;
   (void)tiles;
-  dnr::encode_bwd_kernel<<<(unsigned)slabs, 128, dnr::kBwdSmemBytes, stream>>>(P);
+  dnr::encode_bwd_kernel<false><<<(unsigned)slabs, 128, dnr::kBwdSmemBytes, stream>>>(P);
   DNR_CHECK_LAUNCH("dnr_encode_bwd");
+  return 0;
+}
+
+// Backward of dnr_encode_novel_fwd w.r.t. the two feature maps (novel_pixelnerf.py:196: the gradient of final_latent goes
+// to encoder.latent at the footprint of the `in`-deformed point in each source view, and to gen_latent at the footprint
+// of the `gen`-deformed point under the generic camera, summed over scenes and views -- the reference repeats the one
+// learned map, :110).  Either output may be null.  d_gen_latent_nhwc [Hg,Wg,512] fp32, accumulated into.  The deformed
+// points carry no gradient (the offsets are inputs of the training step, novel.py:280-285,361-363).
+DNR_EXPORT int dnr_encode_novel_bwd(const float* rays, const float* z, const float* pts_in, const float* pts_gen,
+                                    const float* poses, const float* focal, const float* cxy, const float* depth,
+                                    const float* gen_poses, const float* gen_focal, const float* gen_cxy, int Hg, int Wg,
+                                    float gen_img_w, float gen_img_h, float gen_sx, float gen_sy, const float* freqs,
+                                    const float* phases, int SB, int NV, int NR, int K, int H, int W, int Hl, int Wl, int L,
+                                    int NF, long long ray_offset, long long n_rays, float img_w, float img_h, float lat_sx,
+                                    float lat_sy, const float* d_lat_xr, float* d_latent_nhwc, float* d_gen_latent_nhwc,
+                                    cudaStream_t stream) {
+  dnr::EncodeParams P;
+  int rc = fill_encode_params(P, rays, z, poses, focal, cxy, depth, nullptr, freqs, phases, SB, NV, NR, K, H, W, Hl,
+                              Wl, L, NF, ray_offset, n_rays, img_w, img_h, lat_sx, lat_sy);
+  if (rc) return rc;
+  DNR_REQUIRE(pts_in && pts_gen && gen_poses && gen_focal && gen_cxy && d_lat_xr, "dnr_encode_novel_bwd: null argument");
+  DNR_REQUIRE(Hg >= 1 && Wg >= 1 && (unsigned long long)Hg * Wg * L < (1ull << 32), "dnr_encode_novel_bwd: bad gen_latent size");
+  P.pts_in = pts_in; P.pts_gen = pts_gen; P.gen_poses = gen_poses; P.gen_focal = gen_focal; P.gen_cxy = gen_cxy;
+  P.Hg = Hg; P.Wg = Wg; P.gen_img_w = gen_img_w; P.gen_img_h = gen_img_h; P.gen_sx = gen_sx; P.gen_sy = gen_sy;
+  P.d_lat_xr = d_lat_xr; P.d_latent = d_latent_nhwc; P.d_gen_latent = d_gen_latent_nhwc;
+  if (P.n_samples <= 0 || (!d_latent_nhwc && !d_gen_latent_nhwc)) return 0;
+  DNR_CHECK(cudaFuncSetAttribute(dnr::encode_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 dnr::kBwdSmemBytes), "dnr_encode_novel_bwd");
+  const long long slabs = (P.n_samples + dnr::RowMap::make(NV).SPW - 1) / dnr::RowMap::make(NV).SPW;
+  dnr::encode_bwd_kernel<true><<<(unsigned)slabs, 128, dnr::kBwdSmemBytes, stream>>>(P);
+  DNR_CHECK_LAUNCH("dnr_encode_novel_bwd");
   return 0;
 }
 

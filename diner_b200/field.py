@@ -219,7 +219,7 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
 
     rays (n,8) / z (n,K) are the chunk's rows of the flattened (SB*NR) batch, `ray0` the index of its first
     ray in that batch (the scene of a ray is ray // NR).  Returns (rgbsigma (n*K,4) fp32, FieldSaved | None);
-    `out` (contiguous (n*K,4) fp32) receives the result in place when given.  `novel` (diner_b200.novel, inference only):
+    `out` (contiguous (n*K,4) fp32) receives the result in place when given.  `novel` (diner_b200.novel):
     the chunk's deformed sample points and the generic camera / learned map of the NOVEL variant.
     """
     p, st = _lib.ptr, _lib.stream_ptr()
@@ -240,7 +240,6 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
     lat = torch.empty(mv * 128 * HID, **bf)
     code = torch.empty(mv * 128 * IN_PAD, **bf)
     if novel is not None:
-        assert not save, "the NOVEL variant is forward-only"
         g = novel
         _lib.call("dnr_encode_novel_fwd", p(rays), p(z), p(g["pts_in"]), p(g["pts_gen"]), p(sc.poses), p(sc.focal),
                   p(sc.cxy), p(sc.depth), p(sc.latent_nhwc), p(g["poses"]), p(g["focal"]), p(g["cxy"]), p(g["latent"]),
@@ -439,10 +438,11 @@ def _wgrad(dY, Fy, X, Fx, tiles, dW, n_valid, k_valid, db):
 
 
 def field_backward(sc: SceneBuffers, pk: PackedMLP, mlp, sv: FieldSaved, rays, z, NR: int, ray0: int,
-                   d_out: torch.Tensor, grads: dict, d_latent_nhwc):
+                   d_out: torch.Tensor, grads: dict, d_latent_nhwc, novel=None, d_gen_nhwc=None):
     """Backward of field_forward.  Accumulates parameter gradients into `grads` (name -> fp32 tensor shaped like
     the parameter, zero-initialised by the caller) and, if not None, the feature gradient into
-    d_latent_nhwc (SB,NV,Hl,Wl,512) fp32."""
+    d_latent_nhwc (SB,NV,Hl,Wl,512) fp32.  NOVEL variant (`novel` = the dict field_forward was given): the same feature
+    gradient also goes to the learned map, d_gen_nhwc (Hg,Wg,512) fp32, if not None."""
     p, st = _lib.ptr, _lib.stream_ptr()
     dev = d_out.device
     n, K = z.shape
@@ -499,9 +499,16 @@ def field_backward(sc: SceneBuffers, pk: PackedMLP, mlp, sv: FieldSaved, rays, z
         _wgrad(dxv_pk, HID, sv.lat, HID, mv, G(f"lin_z.{b}.weight"), HID, HID, G(f"lin_z.{b}.bias"))
     _wgrad(dz_pk[0], HID, sv.code, IN_PAD, mv, G("lin_in.weight"), HID, mlp.d_in, G("lin_in.bias"))
     # ---- feature map ----
-    if d_latent_nhwc is not None:
+    if d_latent_nhwc is not None or d_gen_nhwc is not None:
         dlat = torch.empty(mv * 128 * HID, **f32)
         _gemm(dz_pk[0], pk.wt_z[0], HID, mv, A1=dz_pk[1], B1=pk.wt_z[1], K1=HID, A2=dz_pk[2], B2=pk.wt_z[2], K2=HID,
               res_out=dlat)
+        if novel is not None:
+            g = novel
+            _lib.call("dnr_encode_novel_bwd", p(rays), p(z), p(g["pts_in"]), p(g["pts_gen"]), p(sc.poses), p(sc.focal),
+                      p(sc.cxy), p(sc.depth), p(g["poses"]), p(g["focal"]), p(g["cxy"]), g["Hg"], g["Wg"], g["img_w"],
+                      g["img_h"], g["sx"], g["sy"], p(sc.freqs), p(sc.phases), *_encode_args(sc, NR, K, ray0, n), p(dlat),
+                      p(d_latent_nhwc), p(d_gen_nhwc), st)
+            return
         _lib.call("dnr_encode_bwd", p(rays), p(z), p(sc.poses), p(sc.focal), p(sc.cxy), p(sc.depth), p(sc.freqs),
                   p(sc.phases), *_encode_args(sc, NR, K, ray0, n), p(dlat), p(d_latent_nhwc), st)

@@ -1,4 +1,4 @@
-"""NOVEL renderer variant -- evaluation path.
+"""NOVEL renderer variant -- evaluation and training step.
 
 Drop-in for the reference's `src.models.novel.nerf_novel_renderer.NeRFRendererDGS` (selected by the NOVEL YAMLs'
 `renderer.module`), same constructor and the same
@@ -18,9 +18,12 @@ What the variant changes against the DINER path (reference file:line), and where
 `diner_b200.scene` reads, plus `gen_poses (SB,1,4,4)`, `gen_focal / gen_c (SB,1,2)`, `gen_image_shape (2,)`,
 `gen_latent (512,Hg,Wg)`.
 
-Scope: forward / evaluation only.  The reference trains the offset regressors through this renderer, which needs
-gradients through the projection (d uv / d point) -- a second hot path that is not built; calling this class with autograd
-enabled on tensors that require grad raises NotImplementedError rather than silently returning detached results.
+Training: the NOVEL training step renders with offsets taken from the batch and optimises `self.nerf.parameters()`
+(src/models/novel/novel.py:280-285,361-363) -- the MLP, the encoder behind `encoder.latent`, and `gen_latent`.  With
+autograd enabled the call is differentiable w.r.t. exactly those: the DINER backward (csrc/gemm.cu, wgrad.cu,
+mlp_misc.cu) plus `dnr_encode_novel_bwd`, which scatters the feature gradient into both maps.  The deformed points carry
+no gradient (nearest-vertex selection has none, and the reference's own offsets are data): offsets that require grad
+raise NotImplementedError rather than silently returning detached results.
 
 The nearest-vertex search is exact (equal to the brute force `diner_b200.deform.nearest_vertex` bit for bit) but pruned:
 the mesh is sorted along a Morton curve into groups of 32 vertices with a bounding sphere each (`build_vertex_groups`).
@@ -121,12 +124,74 @@ def _gen_latent_nhwc(model) -> torch.Tensor:
     return out
 
 
+class _NovelFieldFn(torch.autograd.Function):
+    """rgbsigma = field(deformed sample points) over all ray chunks of one forward call (NOVEL variant); differentiable
+    w.r.t. encoder.latent, gen_latent and the MLP parameter tensors.  Same structure as renderer._FieldFn."""
+
+    @staticmethod
+    def forward(ctx, sc, mlp, names, rays, z, NR, chunks, gen, pts_in, pts_gen, latent, gen_latent, *params):
+        pk = F_.get_packed(mlp, need_transposed=True)
+        K = z.shape[1]
+        out = torch.empty(z.shape[0] * K, 4, device=z.device, dtype=torch.float32)
+        saved = []
+        for r0, r1 in chunks:
+            novel = dict(gen, pts_in=pts_in[r0 * K:r1 * K], pts_gen=pts_gen[r0 * K:r1 * K])
+            _, sv = F_.field_forward(sc, pk, rays[r0:r1], z[r0:r1], NR, r0, save=True, out=out[r0 * K:r1 * K], novel=novel)
+            saved.append(sv)
+        ctx.sc, ctx.mlp, ctx.names, ctx.pk, ctx.saved = sc, mlp, names, pk, saved
+        ctx.rays, ctx.z, ctx.NR, ctx.chunks, ctx.gen, ctx.pts = rays, z, NR, chunks, gen, (pts_in, pts_gen)
+        ctx.latent_shape, ctx.gen_shape = latent.shape, gen_latent.shape
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        sc, mlp, gen = ctx.sc, ctx.mlp, ctx.gen
+        dev = d_out.device
+        p = _lib.ptr
+        with torch.cuda.device(dev):
+            params = dict(mlp.named_parameters())
+            offs, total = {}, 0
+            for n in ctx.names:
+                offs[n] = total
+                total += (params[n].numel() + 3) // 4 * 4
+            flat = torch.zeros(total, device=dev, dtype=torch.float32)
+            grads = {n: flat[offs[n]:offs[n] + params[n].numel()].view(params[n].shape) for n in ctx.names}
+            d_lat_nhwc = d_gen_nhwc = None
+            if ctx.needs_input_grad[10]:
+                d_lat_nhwc = torch.zeros(sc.SB, sc.NV, sc.Hl, sc.Wl, sc.L, device=dev, dtype=torch.float32)
+            if ctx.needs_input_grad[11]:
+                d_gen_nhwc = torch.zeros(gen["Hg"], gen["Wg"], sc.L, device=dev, dtype=torch.float32)
+            d_out = d_out.contiguous()
+            K = ctx.z.shape[1]
+            pts_in, pts_gen = ctx.pts
+            for (r0, r1), sv in zip(ctx.chunks, ctx.saved):
+                novel = dict(gen, pts_in=pts_in[r0 * K:r1 * K], pts_gen=pts_gen[r0 * K:r1 * K])
+                F_.field_backward(sc, ctx.pk, mlp, sv, ctx.rays[r0:r1], ctx.z[r0:r1], ctx.NR, r0, d_out[r0 * K:r1 * K],
+                                  grads, d_lat_nhwc, novel=novel, d_gen_nhwc=d_gen_nhwc)
+            d_latent = d_gen = None
+            if d_lat_nhwc is not None:
+                d_latent = torch.empty(ctx.latent_shape, device=dev, dtype=torch.float32)
+                _lib.call("dnr_unpack_dlatent_nchw", p(d_lat_nhwc), sc.SB * sc.NV, sc.L, sc.Hl, sc.Wl, p(d_latent),
+                          _lib.stream_ptr())
+            if d_gen_nhwc is not None:
+                d_gen = torch.empty(ctx.gen_shape, device=dev, dtype=torch.float32)
+                _lib.call("dnr_unpack_dlatent_nchw", p(d_gen_nhwc), 1, sc.L, gen["Hg"], gen["Wg"], p(d_gen),
+                          _lib.stream_ptr())
+            ctx.saved = None
+            pg = tuple(grads[n].to(params[n].dtype) if ctx.needs_input_grad[12 + i] else None
+                       for i, n in enumerate(ctx.names))
+        return (None,) * 10 + (d_latent, d_gen, *pg)
+
+
 class NeRFRendererDGS(torch.nn.Module):
     """NOVEL variant of the depth-guided renderer (reference src/models/novel/nerf_novel_renderer.py:12-556); see the
     module docstring.  Same constructor as the DINER renderer."""
 
+    ROWS_INFERENCE = 1 << 22
+    ROWS_TRAINING = 1 << 20
+
     def __init__(self, n_samples=40, n_depth_candidates=1000, n_gaussian=15, eval_batch_size=100000, white_bkgd=True,
-                 rows_per_chunk=1 << 22):
+                 rows_per_chunk=None):
         super().__init__()
         self.n_samples = n_samples
         self.n_depth_candidates = n_depth_candidates
@@ -146,11 +211,10 @@ class NeRFRendererDGS(torch.nn.Module):
         assert self.n_samples >= self.n_gaussian
         if not rays.is_cuda:
             raise RuntimeError("diner_b200.novel.NeRFRendererDGS needs CUDA tensors (no CPU path)")
-        if torch.is_grad_enabled() and any(t.requires_grad for t in (tgt_in_offsets, tgt_gen_offsets, model.gen_latent,
-                                                                     model.encoder.latent, *model.mlp_fine.parameters())):
-            raise NotImplementedError("diner_b200.novel: the NOVEL variant is built for evaluation only -- call it under "
-                                      "torch.no_grad() (training needs gradients through the projection, DESIGN.md)")
-        with torch.cuda.device(rays.device), torch.no_grad():
+        if torch.is_grad_enabled() and any(t.requires_grad for t in (tgt_in_offsets, tgt_gen_offsets, target_vertices)):
+            raise NotImplementedError("diner_b200.novel: no gradient flows to the offsets / vertices (the reference's "
+                                      "training step takes them from the batch, novel.py:280-285) -- detach them")
+        with torch.cuda.device(rays.device):
             return self._forward(model, rays, target_vertices, tgt_in_offsets, tgt_gen_offsets, want_weights, noise,
                                  return_samples)
 
@@ -200,11 +264,24 @@ class NeRFRendererDGS(torch.nn.Module):
                    img_w=float(gshape[0]), img_h=float(gshape[1]), sx=float(gscale[0]), sy=float(gscale[1]))
         if gen["poses"].shape != (SB, 1, 4, 4):
             raise ValueError(f"model.gen_poses must be (SB,1,4,4), got {tuple(gen['poses'].shape)}")
-        pk = F_.get_packed(model.mlp_fine, need_transposed=False)
-        rgbsigma = torch.empty(n_rays * K, 4, device=dev, dtype=torch.float32)
-        for r0, r1 in balanced_chunks(n_rays, max(1, self.rows_per_chunk // (K * sc.NV))):
-            novel = dict(gen, pts_in=pts_in[r0 * K:r1 * K], pts_gen=pts_gen[r0 * K:r1 * K])
-            F_.field_forward(sc, pk, flat[r0:r1], z[r0:r1], NR, r0, save=False, out=rgbsigma[r0 * K:r1 * K], novel=novel)
+        mlp = model.mlp_fine
+        names = [n for n, _ in mlp.named_parameters()]
+        params = [q for _, q in mlp.named_parameters()]
+        latent, gen_latent = model.encoder.latent, model.gen_latent
+        track = torch.is_grad_enabled() and (latent.requires_grad or gen_latent.requires_grad or
+                                             any(q.requires_grad for q in params))
+        rows = self.rows_per_chunk or (self.ROWS_TRAINING if track else self.ROWS_INFERENCE)
+        chunks = balanced_chunks(n_rays, max(1, rows // (K * sc.NV)))
+        if track:
+            rgbsigma = _NovelFieldFn.apply(sc, mlp, names, flat, z, NR, chunks, gen, pts_in, pts_gen, latent, gen_latent,
+                                           *params)
+        else:
+            pk = F_.get_packed(mlp, need_transposed=False)
+            rgbsigma = torch.empty(n_rays * K, 4, device=dev, dtype=torch.float32)
+            for r0, r1 in chunks:
+                novel = dict(gen, pts_in=pts_in[r0 * K:r1 * K], pts_gen=pts_gen[r0 * K:r1 * K])
+                F_.field_forward(sc, pk, flat[r0:r1], z[r0:r1], NR, r0, save=False, out=rgbsigma[r0 * K:r1 * K],
+                                 novel=novel)
         rgb, depth, w = _CompositeFn.apply(rgbsigma, z, flat, self.white_bkgd)
         out = RenderResult(rgb=rgb.view(SB, NR, 3), depth=depth.view(SB, NR))
         if want_weights:

@@ -96,7 +96,7 @@ int dnr_encode_fwd_split(const float* rays, const float* z, const float* poses, 
  * chunk's sample points deformed with tgt_in_offsets / tgt_gen_offsets (dnr_novel_deform, mode samples); pts_in replaces
  * o + z d in the projection chain, pts_gen is projected by the ONE generic camera (gen_poses [SB,1,4,4], gen_focal /
  * gen_cxy [SB,1,2], gen_img_w/h; :73-80) into the learned map gen_latent [Hg,Wg,512] bf16 channels-last (:46,108-141) and the
- * feature row is gen_latent[gen_uv] + latent[uv] (:196).  Forward only. */
+ * feature row is gen_latent[gen_uv] + latent[uv] (:196).  Backward: dnr_encode_novel_bwd. */
 int dnr_encode_novel_fwd(const float* rays, const float* z, const float* pts_in, const float* pts_gen, const float* poses,
                          const float* focal, const float* cxy, const float* depth, const void* latent_nhwc_bf16,
                          const float* gen_poses, const float* gen_focal, const float* gen_cxy,
@@ -104,6 +104,18 @@ int dnr_encode_novel_fwd(const float* rays, const float* z, const float* pts_in,
                          float gen_sy, const float* freqs, const float* phases, int SB, int NV, int NR, int K, int H, int W,
                          int Hl, int Wl, int L, int NF, long long ray_offset, long long n_rays, float img_w, float img_h,
                          float lat_sx, float lat_sy, void* lat_pk, void* in_pk, dnr_stream_t stream);
+/* Backward of dnr_encode_novel_fwd w.r.t. the two feature maps (novel_pixelnerf.py:196 under autograd; the NOVEL training
+ * step optimises the field's parameters only, novel.py:280-285,361-363, so the deformed points carry no gradient):
+ * d_lat_xr [rows_pad x 512] fp32 XR is scattered into d_latent_nhwc [SB,NV,Hl,Wl,512] fp32 at the footprint of pts_in in
+ * each source view and into d_gen_latent_nhwc [Hg,Wg,512] fp32 at the footprint of pts_gen under the generic camera (one
+ * learned map for all scenes and views, :110).  Both are accumulated into; either may be null. */
+int dnr_encode_novel_bwd(const float* rays, const float* z, const float* pts_in, const float* pts_gen, const float* poses,
+                         const float* focal, const float* cxy, const float* depth, const float* gen_poses,
+                         const float* gen_focal, const float* gen_cxy, int Hg, int Wg, float gen_img_w, float gen_img_h,
+                         float gen_sx, float gen_sy, const float* freqs, const float* phases, int SB, int NV, int NR, int K,
+                         int H, int W, int Hl, int Wl, int L, int NF, long long ray_offset, long long n_rays, float img_w,
+                         float img_h, float lat_sx, float lat_sy, const float* d_lat_xr, float* d_latent_nhwc,
+                         float* d_gen_latent_nhwc, dnr_stream_t stream);
 /* Nearest-vertex deformation of the NOVEL variant at frame scale (src/models/novel/nerf_novel_renderer.py:40-50 applied at
  * :104-107 to every sampler candidate and at :441-442 to every sample point): K = 1 nearest neighbour (squared L2, first
  * minimum) against a target mesh given Morton-sorted in groups of 32 with one bounding sphere per group

@@ -1,4 +1,4 @@
-"""Generate tests/golden/novel_tiny.npz by running the reference's NOVEL renderer variant (build container only).
+"""Generate tests/golden/novel_tiny{,3}.npz (forward) and novel_tiny{,3}_grad.npz (gradients) by running the reference's NOVEL renderer variant (build container only).
 
     python -m oracle.make_golden_novel
 
@@ -69,6 +69,8 @@ def run_case(ref, name):
         torch.manual_seed(noise_seed)
         z_plain = dref.NeRFRendererDGS(wl.n_samples, wl.n_candidates, wl.n_gaussian).sample_depthguided(
             rays, nerf, n_samples=wl.n_samples, n_candidates=wl.n_candidates, n_gaussian=wl.n_gaussian)
+    grad_data = reference_gradients(ref, nerf, renderer, rays, V, oi, og, noise_seed)
+    assert np.array_equal(grad_data.pop("rgb"), out.fine.rgb.numpy())          # same draws, same frame
     moved = float((z_plain != z_unf).any(-1).float().mean())
     data = dict(workload=wl_name, seed=seed, noise_seed=noise_seed, n_vertices=n_vert,
                 u_coarse=noise["u_coarse"].numpy(),
@@ -78,6 +80,41 @@ def run_case(ref, name):
                 weights=out.fine.weights.numpy())
     print(f"[{name}] rays={tuple(rays.shape)} vertices={n_vert} rays whose samples the deformation moved: {moved:.3f} "
           f"sum_w in [{out.fine.weights.sum(-1).min():.4f},{out.fine.weights.sum(-1).max():.4f}]")
+    return data, grad_data
+
+
+def reference_gradients(ref, nerf, renderer, rays, V, oi, og, noise_seed):
+    """Gradients of a fixed scalar loss through the UNMODIFIED reference NOVEL renderer w.r.t. what its training step
+    optimises (novel.py:361-363, `self.nerf.parameters()`): the MLP, gen_latent, and encoder.latent (the encoder's
+    output: the encoder trunk itself is outside the path)."""
+    nerf.encoder.latent.requires_grad_(True)
+    torch.manual_seed(noise_seed)
+    with ref_shim.record_noise({}):
+        out = renderer.forward(nerf, rays, V, oi, og, want_weights=True)
+    rgb, depth = out.fine.rgb, out.fine.depth
+    g = torch.Generator().manual_seed(11)
+    w_rgb = torch.randn(rgb.shape, generator=g)
+    w_dep = torch.randn(depth.shape, generator=g)
+    loss = (rgb * w_rgb).sum() + (depth * w_dep).sum()
+    loss.backward()
+
+    def picked(t, prefix):
+        nz = t.flatten().nonzero().flatten()
+        pick = nz[torch.linspace(0, len(nz) - 1, 4096).long()]
+        return {f"{prefix}_idx": pick.numpy(), f"{prefix}_val": t.flatten()[pick].numpy(),
+                f"{prefix}_norm": np.float64(t.double().norm().item()), f"{prefix}_sum": np.float64(t.double().sum().item()),
+                f"{prefix}_nnz": np.int64(len(nz))}
+
+    data = dict(loss=np.float64(loss.item()), rgb=rgb.detach().numpy())
+    data.update(picked(nerf.encoder.latent.grad, "glat"))
+    data.update(picked(nerf.gen_latent.grad, "ggen"))
+    for k, v in nerf.mlp_fine.named_parameters():
+        if k in ("lin_out.weight", "lin_out.bias", "lin_in.bias", "blocks.4.fc_0.bias", "blocks.1.fc_1.bias", "lin_z.1.bias"):
+            data[f"grad.{k}"] = v.grad.numpy()
+        data[f"gradnorm.{k}"] = np.float64(v.grad.double().norm().item())
+    nerf.encoder.latent.requires_grad_(False)
+    print(f"  reference gradients: loss={loss.item():.5f} |d latent|={data['glat_norm']:.4e} ({data['glat_nnz']} entries) "
+          f"|d gen_latent|={data['ggen_norm']:.4e} ({data['ggen_nnz']} entries)")
     return data
 
 
@@ -85,10 +122,11 @@ def main():
     ref = ref_shim.load_novel()
     torch.set_num_threads(os.cpu_count() or 1)
     for name in (sys.argv[1:] or list(CASES)):
-        data = run_case(ref, name)
-        path = os.path.join(GOLDEN, f"{name}.npz")
-        np.savez_compressed(path, **data)
-        print("wrote", path, f"{os.path.getsize(path) / 1e6:.2f} MB")
+        data, grad_data = run_case(ref, name)
+        for suffix, d in (("", data), ("_grad", grad_data)):
+            path = os.path.join(GOLDEN, f"{name}{suffix}.npz")
+            np.savez_compressed(path, **d)
+            print("wrote", path, f"{os.path.getsize(path) / 1e6:.2f} MB")
 
 
 if __name__ == "__main__":

@@ -150,7 +150,7 @@ def test_novel_render_against_reference_golden(name):
             # the magnitude of the latent operand, so the tail is a little wider than on the DINER goldens
             assert e["mean"] < 4e-3 and e["q99"] < 6e-2, (key, e)
         assert out.fine.rgb.shape == g["rgb"].shape and torch.isfinite(out.fine.rgb).all()
-        # evaluation only: asking for gradients fails loudly instead of returning detached results
+        # no gradient flows to the offsets (data in the reference's training step): asking for one fails loudly
         scene.tgt_in_offsets.requires_grad_(True)
         with pytest.raises(NotImplementedError):
             r(*args)
@@ -224,3 +224,166 @@ def test_novel_encode_rows_vs_oracle():
             assert torch.allclose(got_c[:, :55], want[:, 512:], rtol=2.0 ** -8, atol=2e-3)
     finally:
         novel_to_device(scene, "cpu")
+
+
+@pytest.mark.parametrize("n_rays,name", [(50, "novel_tiny3"), (97, "novel_tiny")])
+def test_novel_encode_bwd_vs_oracle_autograd(n_rays, name):
+    """dnr_encode_novel_bwd: a random upstream gradient of the feature rows, scattered into encoder.latent (footprint of
+    the `in`-deformed point per view) and into gen_latent (footprint of the `gen`-deformed point, summed over views and
+    scenes) -- against torch autograd through oracle/novel_oracle.field_inputs (fp32, CPU).  Also each output alone
+    (the other pointer null)."""
+    dev = _cuda()
+    from diner_b200 import _lib, field as F_
+    from diner_b200.novel import _deform, build_vertex_groups
+    from diner_b200.scene import get_scene
+    from oracle import novel_oracle as N
+    from tools.synthetic import novel_to_device
+    g, scene, _ = _load(name)
+    wl = scene.workload
+    K = wl.n_samples
+    rays = scene.rays[:, :n_rays].contiguous()
+    SB, NR = rays.shape[:2]
+    z = torch.from_numpy(g["z"])[:, :n_rays].contiguous()
+    pts = (rays[..., None, :3] + z.unsqueeze(-1) * rays[..., None, 3:6]).reshape(SB, NR * K, 3)
+    dirs = rays[..., None, 3:6].expand(-1, -1, K, -1).reshape(SB, NR * K, 3)
+    m = scene.model
+    lat_leaf = m.encoder.latent.detach().clone().requires_grad_(True)
+    gen_leaf = m.gen_latent.detach().clone().requires_grad_(True)
+    m.encoder.latent, m.gen_latent = lat_leaf, gen_leaf
+    zx = N.field_inputs(m, N.deform_points(pts, scene.target_vertices, scene.tgt_in_offsets),
+                        N.deform_points(pts, scene.target_vertices, scene.tgt_gen_offsets), dirs)      # SB,NV,B,567
+    NV = zx.shape[1]
+    gen = torch.Generator().manual_seed(n_rays)
+    G = torch.randn(SB, NV, NR * K, 512, generator=gen)
+    (zx[..., :512] * G).sum().backward()
+    want_dlat, want_dgen = lat_leaf.grad.clone(), gen_leaf.grad.clone()
+    m.encoder.latent, m.gen_latent = lat_leaf.detach(), gen_leaf.detach()
+    novel_to_device(scene, dev)
+    try:
+        sc = get_scene(m)
+        rd, zd = rays.to(dev).view(-1, 8), z.to(dev).view(-1, K)
+        V = scene.target_vertices.shape[1]
+        pin, pgen, _ = _deform(rd, zd, None, None, 0, build_vertex_groups(scene.target_vertices),
+                               scene.tgt_in_offsets.contiguous(), scene.tgt_gen_offsets.contiguous(), SB, NR, K, V, False)
+        Hg, Wg = m.gen_latent.shape[1:]
+        gsize = torch.tensor([Wg, Hg])
+        gscale = ((gsize - float(m.encoder.feature_padding) * 2) / gsize).float()
+        gshape = m.gen_image_shape.cpu()
+        f = lambda t: t.detach().float().contiguous()
+        p, st = _lib.ptr, _lib.stream_ptr()
+        n = SB * NR
+        mv = _lib.load().dnr_view_row_tiles(n * K, NV)
+        spw = 32 // NV
+        s_ = torch.arange(n * K)
+        g_rows = torch.randn(mv * 128, 512, generator=gen)               # padding rows hold junk on purpose
+        for v in range(NV):
+            row = (s_ // spw) * 32 + (s_ % spw) * NV + v
+            g_rows[row] = torch.cat([G[sb, v] for sb in range(SB)], 0)
+        g_xr = torch.empty(mv * 128 * 512, device=dev)
+        _lib.call("dnr_rows_to_xr", p(g_rows.to(dev).contiguous()), mv * 128, 512, mv * 128, p(g_xr), st)
+        gp, gf, gc = f(m.gen_poses), f(m.gen_focal), f(m.gen_c)
+
+        def run(want_lat, want_gen):
+            d_lat = torch.zeros(sc.SB, sc.NV, sc.Hl, sc.Wl, 512, device=dev) if want_lat else None
+            d_gen = torch.zeros(Hg, Wg, 512, device=dev) if want_gen else None
+            _lib.call("dnr_encode_novel_bwd", p(rd), p(zd), p(pin), p(pgen), p(sc.poses), p(sc.focal), p(sc.cxy),
+                      p(sc.depth), p(gp), p(gf), p(gc), Hg, Wg, float(gshape[0]), float(gshape[1]), float(gscale[0]),
+                      float(gscale[1]), p(sc.freqs), p(sc.phases), *F_._encode_args(sc, NR, K, 0, n), p(g_xr), p(d_lat),
+                      p(d_gen), st)
+            torch.cuda.synchronize()
+            return d_lat, d_gen
+
+        d_lat, d_gen = run(True, True)
+        got_lat, got_gen = d_lat.permute(0, 1, 4, 2, 3).cpu(), d_gen.permute(2, 0, 1).cpu()
+        assert got_lat.shape == want_dlat.shape and got_gen.shape == want_dgen.shape
+        for got, want in ((got_lat, want_dlat), (got_gen, want_dgen)):
+            err = (got - want).abs().max().item()
+            assert err <= 1e-4 * max(want.abs().max().item(), 1.0), err      # fp32 sums in a different order
+            assert (want != 0).sum() > 10000 and ((got != 0) == (want != 0)).float().mean() > 0.999
+        only_lat, none_gen = run(True, False)
+        none_lat, only_gen = run(False, True)
+        assert none_gen is None and none_lat is None
+        # same rows, same reductions: equal up to the order of the atomic additions
+        assert torch.allclose(only_lat, d_lat, rtol=1e-5, atol=1e-5) and torch.allclose(only_gen, d_gen, rtol=1e-5, atol=1e-5)
+    finally:
+        novel_to_device(scene, "cpu")
+
+
+@pytest.mark.parametrize("name", ["novel_tiny", "novel_tiny3"])
+def test_novel_training_step_against_reference_golden_gradients(name):
+    """The NOVEL training step (novel.py:280-296,361-363: render with offsets from the batch, optimise nerf.parameters())
+    on the reference's own samples: gradients of loss = sum(rgb * w_rgb) + sum(depth * w_dep) w.r.t. the MLP, gen_latent
+    and encoder.latent against those of the UNMODIFIED reference (tests/golden/novel_*_grad.npz, oracle/make_golden_novel.py).
+
+    The forward state is bf16 here (the variant has no split mode), and the synthetic density head is calibrated to logits
+    of +-150, so -- exactly as for the DINER goldens (test_gpu_parity_r2.py::test_backward_against_reference_golden_gradients,
+    bf16 case) -- the deviation is the loss's sensitivity to the forward value; the scatter itself is held to 1e-4 by
+    test_novel_encode_bwd_vs_oracle_autograd and the MLP backward kernels by the DINER split-mode test.  Asserted here:
+    direction and scale of every gradient, and that the gradients land on the right ENTRIES of both maps."""
+    dev = _cuda()
+    import parity_metrics as PM
+    from diner_b200.novel import NeRFRendererDGS
+    from tools.synthetic import novel_to_device
+    g, scene, _ = _load(name)
+    gg = dict(np.load(os.path.join(os.path.dirname(__file__), "golden", f"{name}_grad.npz"), allow_pickle=False))
+    wl = scene.workload
+    novel_to_device(scene, dev)
+    m = scene.model
+    try:
+        m.encoder.latent = m.encoder.latent.detach().requires_grad_(True)
+        m.gen_latent = m.gen_latent.detach().requires_grad_(True)
+        for q in m.mlp_fine.parameters():
+            q.requires_grad_(True)
+            q.grad = None
+        r = NeRFRendererDGS(wl.n_samples, wl.n_candidates, wl.n_gaussian, white_bkgd=wl.white_bkgd)
+        out = r(m, scene.rays.to(dev), scene.target_vertices, scene.tgt_in_offsets, scene.tgt_gen_offsets,
+                noise=dict(z=torch.from_numpy(g["z"])))
+        loss = PM.golden_loss(out.fine.rgb, out.fine.depth)
+        loss.backward()
+        torch.cuda.synchronize()
+        # the training-mode forward (per-layer kernels, operands saved) to the tolerance of the evaluation path's test
+        for key in ("rgb", "depth"):
+            e = PM.error_metrics(out.fine[key], torch.from_numpy(g[key]))
+            assert e["mean"] < 4e-3 and e["q99"] < 6e-2, (key, e)
+        for k, v in m.mlp_fine.named_parameters():
+            ratio = v.grad.double().norm().item() / max(float(gg[f"gradnorm.{k}"]), 1e-300)
+            assert 0.4 < ratio < 1.8, (k, ratio)
+            if f"grad.{k}" in gg:
+                e = PM.grad_metrics(v.grad, torch.from_numpy(gg[f"grad.{k}"]))
+                assert e["cos"] > 0.6, (k, e)
+        for key, t in (("glat", m.encoder.latent.grad), ("ggen", m.gen_latent.grad)):
+            assert t is not None and torch.isfinite(t).all()
+            pick = t.flatten()[torch.from_numpy(gg[f"{key}_idx"]).to(dev)]
+            e = PM.grad_metrics(pick, torch.from_numpy(gg[f"{key}_val"]))
+            assert e["cos"] > 0.8, (key, e)
+            assert 0.4 < t.double().norm().item() / float(gg[f"{key}_norm"]) < 1.8
+            # footprints: the entries the reference's gradient touches (ours may underflow to 0 on a few, not more)
+            nnz = int((t != 0).sum())
+            assert 0.9 * int(gg[f"{key}_nnz"]) <= nnz <= 1.001 * int(gg[f"{key}_nnz"]), (key, nnz, int(gg[f"{key}_nnz"]))
+            want = torch.from_numpy(gg[f"{key}_val"]).to(dev)
+            big = want.abs() > 1e-9 * want.abs().max()                # (entries of 1e-30 underflow in the bf16 stream)
+            assert int(big.sum()) > 1000 and float((pick[big] != 0).float().mean()) > 0.99
+        # chunking of the training step is invisible (two balanced chunks instead of one)
+        first = {k: v.grad.clone() for k, v in m.mlp_fine.named_parameters()}
+        ggen_first = m.gen_latent.grad.clone()
+        for q in (*m.mlp_fine.parameters(), m.gen_latent, m.encoder.latent):
+            q.grad = None
+        r2 = NeRFRendererDGS(wl.n_samples, wl.n_candidates, wl.n_gaussian, white_bkgd=wl.white_bkgd,
+                             rows_per_chunk=(scene.rays.shape[0] * scene.rays.shape[1] * wl.n_samples * get_nv(m)) // 2 + 1)
+        out2 = r2(m, scene.rays.to(dev), scene.target_vertices, scene.tgt_in_offsets, scene.tgt_gen_offsets,
+                  noise=dict(z=torch.from_numpy(g["z"])))
+        assert torch.equal(out2.fine.rgb, out.fine.rgb)
+        PM.golden_loss(out2.fine.rgb, out2.fine.depth).backward()
+        for k, v in m.mlp_fine.named_parameters():
+            assert PM.grad_metrics(v.grad, first[k])["rel_l2"] < 1e-3, k
+        assert PM.grad_metrics(m.gen_latent.grad, ggen_first)["rel_l2"] < 1e-4
+    finally:
+        m.encoder.latent = m.encoder.latent.detach()
+        m.gen_latent = m.gen_latent.detach()
+        for q in m.mlp_fine.parameters():
+            q.grad = None
+        novel_to_device(scene, "cpu")
+
+
+def get_nv(model):
+    return int(model.poses.shape[1])
