@@ -43,10 +43,23 @@ struct EncodeParams {
   int Hg, Wg;
   float gen_img_w, gen_img_h, gen_sx, gen_sy;
   float* d_gen_latent;   // bwd, NOVEL: [Hg,Wg,L] fp32 (accumulated into; one map for all scenes and views)
+  const float* d_gen_xr; // bwd, NOVEL: XR gradient rows scattered into d_gen_latent (null: d_lat_xr)
+  // NOVEL_PE variant (src/models/novel_pe/pe_novel_pixelnerf.py:200-275), all null / 0 otherwise
+  const float* pe_src;   // [SB,NV,3,Hp,Wp] fp32 positional maps of the source views, tapped at the source uv (:133-166,260)
+  const float* pe_tgt;   // [SB,1,3,Ht,Wt] fp32 positional map of the target view, tapped at the target-camera uv of the
+                         // UNDEFORMED point (:168-198,223-226,248-251,262)
+  const float* tgt_poses;   // [SB,1,4,4]
+  const float* tgt_focal;   // [SB,1,2]
+  const float* tgt_cxy;     // [SB,1,2]
+  int Hp, Wp, Ht, Wt;
+  float pe_sx, pe_sy, tgt_img_w, tgt_img_h, tgt_sx, tgt_sy;
+  unsigned char* gen_pk;  // PK<128> [rows_pad x 512] bf16: the gen_latent taps, kept apart from lat_pk (the deformation
+                          // layer sits between the encoder feature and the sum, :265-268)
 };
 
 struct RowGeom {
   float xc, yc, zc, dx, dy, dz, dd;
+  float u, v;   // normalised image coordinates in the source view, before the feature-padding rescale
   int x0, y0, x1, y1;
   float wx, wy;
   size_t map;   // (sb*NV+v)
@@ -79,6 +92,7 @@ __device__ __forceinline__ void row_geometry(const EncodeParams& P, long long sa
   v = __fadd_rn(__fmul_rn(v, P.focal[g.map * 2 + 1]), P.cxy[g.map * 2 + 1]);
   u = __fsub_rn(__fmul_rn(__fdiv_rn(u, P.img_w), 2.0f), 1.0f);
   v = __fsub_rn(__fmul_rn(__fdiv_rn(v, P.img_h), 2.0f), 1.0f);
+  g.u = u; g.v = v;
   // nearest depth tap, border padding
   float px = __fdiv_rn(__fsub_rn(__fmul_rn(__fadd_rn(u, 1.0f), (float)P.W), 1.0f), 2.0f);
   float py = __fdiv_rn(__fsub_rn(__fmul_rn(__fadd_rn(v, 1.0f), (float)P.H), 1.0f), 2.0f);
@@ -128,6 +142,47 @@ __device__ __forceinline__ void gen_geometry(const EncodeParams& P, long long sa
   t.p00 = (uint32_t)(((size_t)gy0 * P.Wg + gx0) * 512); t.p01 = (uint32_t)(((size_t)gy0 * P.Wg + gx1) * 512);
   t.p10 = (uint32_t)(((size_t)gy1 * P.Wg + gx0) * 512); t.p11 = (uint32_t)(((size_t)gy1 * P.Wg + gx1) * 512);
   t.w00 = (1.f - wx) * (1.f - wy); t.w01 = wx * (1.f - wy); t.w10 = (1.f - wx) * wy; t.w11 = wx * wy;
+}
+
+// NOVEL_PE: bilinear tap (border padding, align_corners = False) of a 3-channel fp32 map [3][H][W] at normalised (u, v)
+// after the feature-padding rescale (pe_novel_pixelnerf.py:150-163); one lane per row
+__device__ __forceinline__ void tap3_bilinear(const float* map, int H, int W, float u, float v, float* out) {
+  float fx = fmaf(__fadd_rn(u, 1.0f), (float)W, -1.0f) * 0.5f;
+  float fy = fmaf(__fadd_rn(v, 1.0f), (float)H, -1.0f) * 0.5f;
+  fx = fminf(fmaxf(fx, 0.0f), (float)(W - 1));
+  fy = fminf(fmaxf(fy, 0.0f), (float)(H - 1));
+  const float flx = floorf(fx), fly = floorf(fy);
+  const int x0 = (int)flx, y0 = (int)fly;
+  const int x1 = min(x0 + 1, W - 1), y1 = min(y0 + 1, H - 1);
+  const float wx = fx - flx, wy = fy - fly;
+  const float w00 = (1.f - wx) * (1.f - wy), w01 = wx * (1.f - wy), w10 = (1.f - wx) * wy, w11 = wx * wy;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    const float* m = map + (size_t)c * H * W;
+    out[c] = fmaf(__ldg(m + (size_t)y1 * W + x1), w11, fmaf(__ldg(m + (size_t)y1 * W + x0), w10,
+             fmaf(__ldg(m + (size_t)y0 * W + x1), w01, __ldg(m + (size_t)y0 * W + x0) * w00)));
+  }
+}
+// NOVEL_PE: the six positional values of a row -- the source view's map at the row's own uv, the target view's map at
+// the projection of the undeformed sample point o + z d by the target camera (pe_novel_pixelnerf.py:223-226,248-262)
+__device__ __forceinline__ void pe_values(const EncodeParams& P, long long sample, const RowGeom& g, float* out) {
+  tap3_bilinear(P.pe_src + g.map * 3 * (size_t)P.Hp * P.Wp, P.Hp, P.Wp, __fmul_rn(g.u, P.pe_sx), __fmul_rn(g.v, P.pe_sy), out);
+  const long long ray = sample / P.K;
+  const int sb = (int)(g.map / P.NV);
+  const float* rp = P.rays + ray * 8;
+  const float zs = P.z[sample];
+  const float x0 = __fadd_rn(rp[0], __fmul_rn(zs, rp[3])), x1 = __fadd_rn(rp[1], __fmul_rn(zs, rp[4]));
+  const float x2 = __fadd_rn(rp[2], __fmul_rn(zs, rp[5]));
+  const float* E = P.tgt_poses + (size_t)sb * 16;
+  const float xc = __fadd_rn(fmaf(E[2], x2, fmaf(E[1], x1, __fmul_rn(E[0], x0))), E[3]);
+  const float yc = __fadd_rn(fmaf(E[6], x2, fmaf(E[5], x1, __fmul_rn(E[4], x0))), E[7]);
+  const float zc = __fadd_rn(fmaf(E[10], x2, fmaf(E[9], x1, __fmul_rn(E[8], x0))), E[11]);
+  float u = __fdiv_rn(xc, zc), v = __fdiv_rn(yc, zc);
+  u = __fadd_rn(__fmul_rn(u, P.tgt_focal[sb * 2 + 0]), P.tgt_cxy[sb * 2 + 0]);
+  v = __fadd_rn(__fmul_rn(v, P.tgt_focal[sb * 2 + 1]), P.tgt_cxy[sb * 2 + 1]);
+  u = __fsub_rn(__fmul_rn(__fdiv_rn(u, P.tgt_img_w), 2.0f), 1.0f);
+  v = __fsub_rn(__fmul_rn(__fdiv_rn(v, P.tgt_img_h), 2.0f), 1.0f);
+  tap3_bilinear(P.pe_tgt + (size_t)sb * 3 * P.Ht * P.Wt, P.Ht, P.Wt, __fmul_rn(u, P.tgt_sx), __fmul_rn(v, P.tgt_sy), out + 3);
 }
 
 // packed fp32 pairs (Blackwell FMUL2 / FFMA2): the two channels of a bf16x2 word travel together
@@ -182,7 +237,10 @@ __device__ __forceinline__ float blend4_lo(uint32_t a, uint32_t b, uint32_t c, u
 // hi + lo pairs of operand images (v_hi = bf16(v), v_lo = bf16(v - v_hi)).
 // NOVEL (src/models/novel/novel_pixelnerf.py:143-196): the sample points are given (deformed), and the feature row is
 // gen_latent[gen_uv] + latent[uv] -- a second bilinear gather from the learned map, with its own footprint cache.
-template <bool SPLIT, bool NOVEL>
+// PE (NOVEL_PE, src/models/novel_pe/pe_novel_pixelnerf.py:260-275; with NOVEL): the encoder feature and the gen_latent
+// taps leave as two operand images (a linear layer sits between them), and the six positional values of the row take the
+// first six padding columns (55..60) of the geometric code.
+template <bool SPLIT, bool NOVEL, bool PE = false>
 __global__ void __launch_bounds__(kEncWarps * 32, (SPLIT || NOVEL) ? 1 : 5) encode_fwd_kernel(EncodeParams P, const __nv_bfloat16* latent_lo,
                                                                     unsigned char* lat_pk_lo, unsigned char* in_pk_lo) {
   extern __shared__ __align__(16) unsigned char enc_smem[];
@@ -192,6 +250,8 @@ __global__ void __launch_bounds__(kEncWarps * 32, (SPLIT || NOVEL) ? 1 : 5) enco
   unsigned char* sl_lo = reinterpret_cast<unsigned char*>(taps_s + 32);     // SPLIT only
   unsigned char* si_lo = sl_lo + kEncLatBytes;
   GenTaps* gen_s = reinterpret_cast<GenTaps*>(taps_s + 32);                 // NOVEL only (never together with SPLIT)
+  unsigned char* sg = reinterpret_cast<unsigned char*>(gen_s + 32);         // PE only: [64][kLatChunkStride] gen taps
+  float* pe_s = reinterpret_cast<float*>(sg + kEncLatBytes);                // PE only: [32][8]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const RowMap rm = RowMap::make(P.NV);
   const long long row_base = (long long)blockIdx.x * 32;
@@ -221,6 +281,10 @@ __global__ void __launch_bounds__(kEncWarps * 32, (SPLIT || NOVEL) ? 1 : 5) enco
         gen_geometry(P, sample, (int)(g.map / P.NV), gt);
         gen_s[lane] = gt;
       }
+      if (PE) pe_values(P, sample, g, pe_s + lane * 8);
+    } else if (PE) {
+#pragma unroll
+      for (int j = 0; j < 6; ++j) pe_s[lane * 8 + j] = 0.f;
     }
     taps_s[lane] = tp;
   }
@@ -279,6 +343,7 @@ __global__ void __launch_bounds__(kEncWarps * 32, (SPLIT || NOVEL) ? 1 : 5) enco
         const int i = warp * 8 + 2 * m + (lane >> 4);
         const RowTaps& tp = taps_s[i];
         float val = fo >= 0 ? (&tp.xc)[fo] : 0.f;
+        if (PE && r >= 7 && r < 13) val = pe_s[i * 8 + (r - 7)];    // columns 55..60: src_pos_encodings | tgt_pos_encodings
         if (!tp.map_plus1) val = 0.f;
         put(so + i * 16, val);
       }
@@ -294,6 +359,7 @@ __global__ void __launch_bounds__(kEncWarps * 32, (SPLIT || NOVEL) ? 1 : 5) enco
     const int ch = warp * 128 + lane * 4;
     unsigned char* dst0 = sl + (warp * 16 + (lane >> 1)) * kLatChunkStride + (lane & 1) * 8;
     unsigned char* dst0_lo = sl_lo + (warp * 16 + (lane >> 1)) * kLatChunkStride + (lane & 1) * 8;
+    unsigned char* dstg = sg + (warp * 16 + (lane >> 1)) * kLatChunkStride + (lane & 1) * 8;
     const __nv_bfloat16* lat = P.latent + ch;
     const __nv_bfloat16* lat_lo = SPLIT ? latent_lo + ch : nullptr;
     struct Foot { uint2 a, b, c, d, al, bl, cl, dl; };            // (the lo taps exist in the SPLIT instantiation only)
@@ -353,7 +419,8 @@ __global__ void __launch_bounds__(kEncWarps * 32, (SPLIT || NOVEL) ? 1 : 5) enco
         float u0, u1, u2, u3;
         u0 = blend4_lo(ga.x, gb.x, gc.x, gd.x, G00, G01, G10, G11, u1);
         u2 = blend4_lo(ga.y, gb.y, gc.y, gd.y, G00, G01, G10, G11, u3);
-        v0 = u0 + v0; v1 = u1 + v1; v2 = u2 + v2; v3 = u3 + v3;
+        if (PE) *reinterpret_cast<uint2*>(dstg + l * 16) = make_uint2(pack_bf16x2(u0, u1), pack_bf16x2(u2, u3));
+        else { v0 = u0 + v0; v1 = u1 + v1; v2 = u2 + v2; v3 = u3 + v3; }
       }
       const uint2 o = make_uint2(pack_bf16x2(v0, v1), pack_bf16x2(v2, v3));
       *reinterpret_cast<uint2*>(dst0 + l * 16) = o;
@@ -385,6 +452,7 @@ __global__ void __launch_bounds__(kEncWarps * 32, (SPLIT || NOVEL) ? 1 : 5) enco
           if (!live[j]) {
             *reinterpret_cast<uint2*>(dst0 + l * 16) = make_uint2(0, 0);
             if (SPLIT) *reinterpret_cast<uint2*>(dst0_lo + l * 16) = make_uint2(0, 0);
+            if (PE) *reinterpret_cast<uint2*>(dstg + l * 16) = make_uint2(0, 0);
             continue;
           }
           // a row that opens a new footprint unpacks it (its taps were requested with the batch); the others reuse it
@@ -399,6 +467,7 @@ __global__ void __launch_bounds__(kEncWarps * 32, (SPLIT || NOVEL) ? 1 : 5) enco
     for (int l = n_live; l < 32; ++l) {                            // padding rows of the slab (NV = 3: rows 30, 31)
       *reinterpret_cast<uint2*>(dst0 + l * 16) = make_uint2(0, 0);
       if (SPLIT) *reinterpret_cast<uint2*>(dst0_lo + l * 16) = make_uint2(0, 0);
+      if (PE) *reinterpret_cast<uint2*>(dstg + l * 16) = make_uint2(0, 0);
     }
   }
   __syncthreads();
@@ -417,6 +486,14 @@ __global__ void __launch_bounds__(kEncWarps * 32, (SPLIT || NOVEL) ? 1 : 5) enco
     for (int it = 0; it < 2; ++it) {
       const int c = it * 4 + warp;
       *reinterpret_cast<uint4*>(in_tile + (size_t)c * 2048) = *reinterpret_cast<const uint4*>(si + c * kLatChunkStride + lane * 16);
+    }
+  }
+  if (PE) {
+    unsigned char* gen_tile = P.gen_pk + (size_t)tile * (512 / 8) * 2048 + (size_t)(rr + lane) * 16;
+#pragma unroll 4
+    for (int it = 0; it < 16; ++it) {
+      const int c = it * 4 + warp;
+      *reinterpret_cast<uint4*>(gen_tile + (size_t)c * 2048) = *reinterpret_cast<const uint4*>(sg + c * kLatChunkStride + lane * 16);
     }
   }
   if (SPLIT) {
@@ -488,7 +565,7 @@ __global__ void __launch_bounds__(kEnc8Warps * 32) encode_fwd_rows8_kernel(Encod
   {
     constexpr int NF = 6;                    // required by fill_encode_params (55-wide code)
     constexpr int npos = 3 + 6 * NF;         // 39
-    constexpr int nsin_pos = 6 * NF, nsin = 8 * NF;      // 36, 48
+    constexpr int nsin_pos = 6 * NF;      // 36, 48
     // 3 x 32 lanes cover the 2 x 48 sines of a row pair, so a lane meets only three (element, frequency, coordinate)
     // combinations: q = lane (row 2m), lane + 32 or lane - 16 (row 2m or 2m + 1), lane + 16 (row 2m + 1).  Everything
     // that depends on q alone is hoisted out of the loop over the four row pairs.
@@ -634,13 +711,16 @@ __global__ void __launch_bounds__(128) encode_bwd_kernel(EncodeParams P) {
   }
   // stage this warp's 128 channels of the 32 rows: st[row][n4]
   float4* st = bwd_stage + warp * 32 * kBwdRowStride;
-  {
+  auto stage = [&](const float* xr) {
     const long long tile = row / 128;
     const int rr = (int)(row % 128);
-    const float4* src = reinterpret_cast<const float4*>(P.d_lat_xr) + ((size_t)tile * (L / 4) + warp * 32) * 128 + rr;
+    const float4* src = reinterpret_cast<const float4*>(xr) + ((size_t)tile * (L / 4) + warp * 32) * 128 + rr;
 #pragma unroll 8
     for (int n4 = 0; n4 < 32; ++n4) st[lane * kBwdRowStride + n4] = src[(size_t)n4 * 128];
-  }
+  };
+  const float* gen_xr = (NOVEL && P.d_gen_xr) ? P.d_gen_xr : P.d_lat_xr;
+  const float* first_xr = P.d_latent ? P.d_lat_xr : gen_xr;
+  stage(first_xr);
   __syncwarp();
   float4 a00 = make_float4(0.f, 0.f, 0.f, 0.f), a01 = a00, a10 = a00, a11 = a00;
   uint32_t cx = 0, cy = 0, cm = 0;
@@ -678,6 +758,11 @@ __global__ void __launch_bounds__(128) encode_bwd_kernel(EncodeParams P) {
   }
   flush();
   if (NOVEL && P.d_gen_latent) {
+    if (gen_xr != first_xr) {            // NOVEL_PE: the learned map has its own gradient rows
+      __syncwarp();
+      stage(gen_xr);
+      __syncwarp();
+    }
     GenTaps gt;
     gt.p00 = gt.p01 = gt.p10 = gt.p11 = 0u; gt.w00 = gt.w01 = gt.w10 = gt.w11 = 0.f;
     uint32_t gok = 0;
@@ -776,7 +861,9 @@ static int fill_encode_params(dnr::EncodeParams& P, const float* rays, const flo
   P.lat_pk = nullptr; P.in_pk = nullptr; P.d_latent = nullptr; P.d_lat_xr = nullptr;
   P.pts_in = nullptr; P.pts_gen = nullptr; P.gen_poses = nullptr; P.gen_focal = nullptr; P.gen_cxy = nullptr;
   P.gen_latent = nullptr; P.Hg = P.Wg = 0; P.gen_img_w = P.gen_img_h = P.gen_sx = P.gen_sy = 0.f;
-  P.d_gen_latent = nullptr;
+  P.d_gen_latent = nullptr; P.d_gen_xr = nullptr;
+  P.pe_src = P.pe_tgt = P.tgt_poses = P.tgt_focal = P.tgt_cxy = nullptr; P.Hp = P.Wp = P.Ht = P.Wt = 0;
+  P.pe_sx = P.pe_sy = P.tgt_img_w = P.tgt_img_h = P.tgt_sx = P.tgt_sy = 0.f; P.gen_pk = nullptr;
   return 0;
 }
 
@@ -789,16 +876,20 @@ DNR_EXPORT int dnr_view_row_tiles(long long n_samples, int NV) {
 static int launch_encode_fwd(dnr::EncodeParams& P, int NV, const void* latent_lo, void* lat_pk_lo, void* in_pk_lo,
                              cudaStream_t stream) {
   if (P.n_samples <= 0) return 0;
-  const bool split = latent_lo != nullptr, novel = P.gen_latent != nullptr;
+  const bool split = latent_lo != nullptr, novel = P.gen_latent != nullptr, pe = P.pe_src != nullptr;
   const int tiles = dnr::RowMap::make(NV).tiles_for(P.n_samples);
   const int slabs = tiles * 4;
   const int smem = (dnr::kEncLatBytes + dnr::kEncInBytes) * (split ? 2 : 1) + 32 * (int)sizeof(dnr::RowTaps) +
-                   (novel ? 32 * (int)sizeof(dnr::GenTaps) : 0);
+                   (novel ? 32 * (int)sizeof(dnr::GenTaps) : 0) + (pe ? dnr::kEncLatBytes + 32 * 8 * 4 : 0);
   if (split) {
     DNR_CHECK(cudaFuncSetAttribute(dnr::encode_fwd_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
               "dnr_encode_fwd_split/attr");
     dnr::encode_fwd_kernel<true, false><<<slabs, dnr::kEncWarps * 32, smem, stream>>>(
         P, (const __nv_bfloat16*)latent_lo, (unsigned char*)lat_pk_lo, (unsigned char*)in_pk_lo);
+  } else if (pe) {
+    DNR_CHECK(cudaFuncSetAttribute(dnr::encode_fwd_kernel<false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
+              "dnr_encode_novel_pe_fwd/attr");
+    dnr::encode_fwd_kernel<false, true, true><<<slabs, dnr::kEncWarps * 32, smem, stream>>>(P, nullptr, nullptr, nullptr);
   } else if (novel) {
     dnr::encode_fwd_kernel<false, true><<<slabs, dnr::kEncWarps * 32, smem, stream>>>(P, nullptr, nullptr, nullptr);
   } else {
@@ -880,6 +971,49 @@ DNR_EXPORT int dnr_encode_novel_fwd(const float* rays, const float* z, const flo
   return 0;
 }
 
+// NOVEL_PE variant of dnr_encode_novel_fwd (src/models/novel_pe/pe_novel_pixelnerf.py:200-275).  Against the NOVEL entry:
+// lat_pk receives the encoder feature ALONE and gen_pk [rows_pad x 512] bf16 PK128 the gen_latent taps (the variant's
+// deformation layer, a 518 -> 512 nn.Linear, is applied to [feature | 6 positional values] before the two are added,
+// :265-268 -- a dnr_mlp_gemm with gen_pk as its bf16 residual operand), and columns 55..60 of in_pk carry
+// [src_pos_encodings 3 | tgt_pos_encodings 3]: pe_src [SB,NV,3,Hp,Wp] fp32 tapped bilinearly at the row's source uv
+// (rescaled by pe_sx / pe_sy, :133-166), pe_tgt [SB,1,3,Ht,Wt] fp32 at the projection of the UNDEFORMED point o + z d by
+// the target camera tgt_poses [SB,1,4,4], tgt_focal / tgt_cxy [SB,1,2], tgt_img_w/h (rescaled by tgt_sx / tgt_sy,
+// :168-198,223-226,248-251).  The MLP input of the variant, [final_latent | pe 6 | code 55] (:275), is these operands.
+DNR_EXPORT int dnr_encode_novel_pe_fwd(const float* rays, const float* z, const float* pts_in, const float* pts_gen,
+                                       const float* poses, const float* focal, const float* cxy, const float* depth,
+                                       const void* latent_nhwc_bf16, const float* gen_poses, const float* gen_focal,
+                                       const float* gen_cxy, const void* gen_latent_nhwc_bf16, int Hg, int Wg,
+                                       float gen_img_w, float gen_img_h, float gen_sx, float gen_sy, const float* pe_src,
+                                       int Hp, int Wp, float pe_sx, float pe_sy, const float* tgt_poses,
+                                       const float* tgt_focal, const float* tgt_cxy, float tgt_img_w, float tgt_img_h,
+                                       const float* pe_tgt, int Ht, int Wt, float tgt_sx, float tgt_sy,
+                                       const float* freqs, const float* phases, int SB, int NV, int NR, int K, int H,
+                                       int W, int Hl, int Wl, int L, int NF, long long ray_offset, long long n_rays,
+                                       float img_w, float img_h, float lat_sx, float lat_sy, void* lat_pk, void* gen_pk,
+                                       void* in_pk, cudaStream_t stream) {
+  dnr::EncodeParams P;
+  int rc = fill_encode_params(P, rays, z, poses, focal, cxy, depth, latent_nhwc_bf16, freqs, phases, SB, NV, NR, K, H,
+                              W, Hl, Wl, L, NF, ray_offset, n_rays, img_w, img_h, lat_sx, lat_sy);
+  if (rc) return rc;
+  DNR_REQUIRE((unsigned long long)SB * NV * Hl * Wl * L < (1ull << 32), "dnr_encode_novel_pe_fwd: latent too large");
+  DNR_REQUIRE(z && latent_nhwc_bf16 && lat_pk && gen_pk && in_pk && pts_in && pts_gen && gen_poses && gen_focal && gen_cxy &&
+              gen_latent_nhwc_bf16 && pe_src && pe_tgt && tgt_poses && tgt_focal && tgt_cxy,
+              "dnr_encode_novel_pe_fwd: null argument");
+  DNR_REQUIRE(Hg >= 1 && Wg >= 1 && (unsigned long long)Hg * Wg * L < (1ull << 32), "dnr_encode_novel_pe_fwd: bad gen_latent size");
+  DNR_REQUIRE(Hp >= 1 && Wp >= 1 && Ht >= 1 && Wt >= 1, "dnr_encode_novel_pe_fwd: bad positional map size");
+  P.lat_pk = (unsigned char*)lat_pk; P.in_pk = (unsigned char*)in_pk; P.gen_pk = (unsigned char*)gen_pk;
+  P.pts_in = pts_in; P.pts_gen = pts_gen; P.gen_poses = gen_poses; P.gen_focal = gen_focal; P.gen_cxy = gen_cxy;
+  P.gen_latent = (const __nv_bfloat16*)gen_latent_nhwc_bf16; P.Hg = Hg; P.Wg = Wg;
+  P.gen_img_w = gen_img_w; P.gen_img_h = gen_img_h; P.gen_sx = gen_sx; P.gen_sy = gen_sy;
+  P.pe_src = pe_src; P.Hp = Hp; P.Wp = Wp; P.pe_sx = pe_sx; P.pe_sy = pe_sy;
+  P.tgt_poses = tgt_poses; P.tgt_focal = tgt_focal; P.tgt_cxy = tgt_cxy; P.tgt_img_w = tgt_img_w; P.tgt_img_h = tgt_img_h;
+  P.pe_tgt = pe_tgt; P.Ht = Ht; P.Wt = Wt; P.tgt_sx = tgt_sx; P.tgt_sy = tgt_sy;
+  rc = launch_encode_fwd(P, NV, nullptr, nullptr, nullptr, stream);
+  if (rc) return rc;
+  DNR_CHECK_LAUNCH("dnr_encode_novel_pe_fwd");
+  return 0;
+}
+
 // Backward of SpatialEncoder.index (grid_sample bilinear w.r.t. the latent map, image_encoder.py:117-123).
 DNR_EXPORT int dnr_encode_bwd(const float* rays, const float* z, const float* poses, const float* focal,
                               const float* cxy, const float* depth, const float* freqs, const float* phases, int SB,
@@ -907,24 +1041,28 @@ DNR_EXPORT int dnr_encode_bwd(const float* rays, const float* z, const float* po
 // to encoder.latent at the footprint of the `in`-deformed point in each source view, and to gen_latent at the footprint
 // of the `gen`-deformed point under the generic camera, summed over scenes and views -- the reference repeats the one
 // learned map, :110).  Either output may be null.  d_gen_latent_nhwc [Hg,Wg,512] fp32, accumulated into.  The deformed
-// points carry no gradient (the offsets are inputs of the training step, novel.py:280-285,361-363).
+// points carry no gradient (the offsets are inputs of the training step, novel.py:280-285,361-363).  d_gen_xr: the
+// gradient rows of the gen_latent taps when they differ from those of the encoder feature (NOVEL_PE: a linear layer sits
+// between the encoder feature and the sum); null = d_lat_xr.
 DNR_EXPORT int dnr_encode_novel_bwd(const float* rays, const float* z, const float* pts_in, const float* pts_gen,
                                     const float* poses, const float* focal, const float* cxy, const float* depth,
                                     const float* gen_poses, const float* gen_focal, const float* gen_cxy, int Hg, int Wg,
                                     float gen_img_w, float gen_img_h, float gen_sx, float gen_sy, const float* freqs,
                                     const float* phases, int SB, int NV, int NR, int K, int H, int W, int Hl, int Wl, int L,
                                     int NF, long long ray_offset, long long n_rays, float img_w, float img_h, float lat_sx,
-                                    float lat_sy, const float* d_lat_xr, float* d_latent_nhwc, float* d_gen_latent_nhwc,
-                                    cudaStream_t stream) {
+                                    float lat_sy, const float* d_lat_xr, const float* d_gen_xr, float* d_latent_nhwc,
+                                    float* d_gen_latent_nhwc, cudaStream_t stream) {
   dnr::EncodeParams P;
   int rc = fill_encode_params(P, rays, z, poses, focal, cxy, depth, nullptr, freqs, phases, SB, NV, NR, K, H, W, Hl,
                               Wl, L, NF, ray_offset, n_rays, img_w, img_h, lat_sx, lat_sy);
   if (rc) return rc;
-  DNR_REQUIRE(pts_in && pts_gen && gen_poses && gen_focal && gen_cxy && d_lat_xr, "dnr_encode_novel_bwd: null argument");
+  DNR_REQUIRE(pts_in && pts_gen && gen_poses && gen_focal && gen_cxy, "dnr_encode_novel_bwd: null argument");
+  DNR_REQUIRE(!d_latent_nhwc || d_lat_xr, "dnr_encode_novel_bwd: d_latent_nhwc needs d_lat_xr");
+  DNR_REQUIRE(!d_gen_latent_nhwc || d_gen_xr || d_lat_xr, "dnr_encode_novel_bwd: d_gen_latent_nhwc needs d_gen_xr or d_lat_xr");
   DNR_REQUIRE(Hg >= 1 && Wg >= 1 && (unsigned long long)Hg * Wg * L < (1ull << 32), "dnr_encode_novel_bwd: bad gen_latent size");
   P.pts_in = pts_in; P.pts_gen = pts_gen; P.gen_poses = gen_poses; P.gen_focal = gen_focal; P.gen_cxy = gen_cxy;
   P.Hg = Hg; P.Wg = Wg; P.gen_img_w = gen_img_w; P.gen_img_h = gen_img_h; P.gen_sx = gen_sx; P.gen_sy = gen_sy;
-  P.d_lat_xr = d_lat_xr; P.d_latent = d_latent_nhwc; P.d_gen_latent = d_gen_latent_nhwc;
+  P.d_lat_xr = d_lat_xr; P.d_gen_xr = d_gen_xr; P.d_latent = d_latent_nhwc; P.d_gen_latent = d_gen_latent_nhwc;
   if (P.n_samples <= 0 || (!d_latent_nhwc && !d_gen_latent_nhwc)) return 0;
   DNR_CHECK(cudaFuncSetAttribute(dnr::encode_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  dnr::kBwdSmemBytes), "dnr_encode_novel_bwd");

@@ -56,25 +56,26 @@ def _mlp_signature(mlp):
     return tuple((p.data_ptr(), p._version) for p in mlp.parameters())
 
 
+def _pack_weight(w: torch.Tensor, transpose: bool = False) -> torch.Tensor:
+    """nn.Linear weight (out, in) -> bf16 tensor-core image [N/256][K/8][256][8] of W (or of W^T), zero-padded."""
+    w = w.detach().to(torch.float32).contiguous()
+    rows, cols = w.shape
+    n, k = (cols, rows) if transpose else (rows, cols)
+    n_pad, k_pad = (n + 255) // 256 * 256, (k + 63) // 64 * 64
+    out = torch.empty(n_pad * k_pad, device=w.device, dtype=torch.bfloat16)
+    _lib.call("dnr_pack_weight", _lib.ptr(w), rows, cols, cols, 1 if transpose else 0, n_pad, k_pad, _lib.ptr(out),
+              _lib.stream_ptr())
+    return out
+
+
 class PackedMLP:
     """bf16 tensor-core images of the ResnetFC weights (W for forward, W^T for dgrad) + fp32 biases."""
 
     def __init__(self, mlp, need_transposed: bool, split: bool = False):
-        dev = mlp.lin_out.weight.device
         self.sig = _mlp_signature(mlp)
         self.has_t = need_transposed
         self.has_split = split
-        st = _lib.stream_ptr()
-
-        def pack(w, transpose=False):
-            w = w.detach().to(torch.float32).contiguous()
-            rows, cols = w.shape
-            n, k = (cols, rows) if transpose else (rows, cols)
-            n_pad, k_pad = (n + 255) // 256 * 256, (k + 63) // 64 * 64
-            out = torch.empty(n_pad * k_pad, device=dev, dtype=torch.bfloat16)
-            _lib.call("dnr_pack_weight", _lib.ptr(w), rows, cols, cols, 1 if transpose else 0, n_pad, k_pad,
-                      _lib.ptr(out), st)
-            return out
+        pack = _pack_weight
 
         f = lambda t: t.detach().to(torch.float32).contiguous()
         self.w_in = pack(mlp.lin_in.weight)                      # [512 x 64]
@@ -121,7 +122,63 @@ class PackedMLP:
             self.lo_1 = [lo(b.fc_1.weight) for b in mlp.blocks]
 
 
+class _Lin:
+    def __init__(self, weight, bias):
+        self.weight, self.bias = weight, bias
+
+
+class PackedPE(PackedMLP):
+    """NOVEL_PE field (src/models/novel_pe/pe_novel_pixelnerf.py): ResnetFC with d_latent = 518 behind a 518 -> 512
+    `deformation_layer`.  The six positional values of a row travel in columns 55..60 of the 64-wide geometric-code
+    operand (dnr_encode_novel_pe_fwd), so every 518-wide nn.Linear becomes two K segments of one GEMM:
+
+        W[:, :512] on the 512-wide operand   +   [0 (55) | W[:, 512:518] | 0 (3)] on the code operand
+
+    and lin_in (55 columns of the same operand) merges with lin_z[0]'s positional columns into ONE 512 x 64 image.  With
+    that, the attributes of PackedMLP keep their meaning (w_in, w_z, ...) and the per-layer sequence needs only the extra
+    segment `w_zc[b]` in blocks 1-2 and the deformation GEMM (`wd`, `wdc`, `b_d`) in front."""
+
+    def __init__(self, model, need_transposed: bool):
+        mlp, dl = model.mlp_fine, model.deformation_layer
+        d_in = mlp.lin_in.weight.shape[1]
+        if mlp.lin_z[0].weight.shape[1] != HID + 6 or dl.weight.shape != (HID, HID + 6) or d_in + 6 > IN_PAD:
+            raise NotImplementedError("diner_b200: the NOVEL_PE field needs d_latent = 518 and a 518 -> 512 deformation layer")
+        self.d_in = d_in
+
+        def code_side(w6, w_code=None):
+            """(512, 6) positional columns [+ (512, d_in) code columns] -> dense (512, d_in + 6) over operand columns 0..60"""
+            left = w_code.detach().float() if w_code is not None else torch.zeros(HID, d_in, device=w6.device)
+            return torch.cat([left, w6.detach().float()], 1)
+
+        wz = [l.weight.detach().float() for l in mlp.lin_z]
+        shim = _Lin(None, None)
+        shim.lin_in = _Lin(code_side(wz[0][:, HID:], mlp.lin_in.weight), mlp.lin_in.bias)
+        shim.lin_z = [_Lin(w[:, :HID], l.bias) for w, l in zip(wz, mlp.lin_z)]
+        shim.blocks, shim.lin_out = mlp.blocks, mlp.lin_out
+        shim.parameters = lambda: [*mlp.parameters(), *dl.parameters()]
+        super().__init__(shim, need_transposed)
+        wd = dl.weight.detach().float()
+        self.w_zc = [None] + [_pack_weight(code_side(w[:, HID:])) for w in wz[1:]]      # blocks 1, 2
+        self.wd, self.wdc = _pack_weight(wd[:, :HID]), _pack_weight(code_side(wd[:, HID:]))
+        self.b_d = dl.bias.detach().float().contiguous()
+        if need_transposed:
+            self.wt_d = _pack_weight(wd[:, :HID], True)
+
+
 _packed_cache: dict = {}
+_packed_pe_cache: dict = {}
+
+
+def get_packed_pe(model, need_transposed: bool) -> PackedPE:
+    """PackedPE of a NOVEL_PE model, cached like get_packed (same invalidation rules)."""
+    sig = tuple((q.data_ptr(), q._version) for q in (*model.mlp_fine.parameters(), *model.deformation_layer.parameters()))
+    hit = _packed_pe_cache.get(id(model))
+    if hit is not None and hit.sig == sig and (hit.has_t or not need_transposed):
+        return hit
+    pk = PackedPE(model, need_transposed)
+    _packed_pe_cache.clear()
+    _packed_pe_cache[id(model)] = pk
+    return pk
 
 
 def get_packed(mlp, need_transposed: bool, split: bool = False) -> PackedMLP:
@@ -141,6 +198,7 @@ def get_packed(mlp, need_transposed: bool, split: bool = False) -> PackedMLP:
 def invalidate_caches() -> None:
     """Forget the packed weights (and, via scene.invalidate, the per-scene repacks)."""
     _packed_cache.clear()
+    _packed_pe_cache.clear()
 
 
 _scratch: dict = {}
@@ -206,6 +264,7 @@ class FieldSaved:
     xa: list = dc_field(default_factory=list)      # relu(x_b) entering block b (b = 0..4); xa[5] = relu(x_5)
     net: list = dc_field(default_factory=list)     # relu(fc_0(.)) of block b
     out: torch.Tensor = None
+    lat_src: torch.Tensor = None                   # NOVEL_PE: the encoder feature alone (`lat` is then final_latent)
 
 
 def _encode_args(sc: SceneBuffers, NR: int, K: int, ray0: int, n_rays: int):
@@ -239,7 +298,23 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
 
     lat = torch.empty(mv * 128 * HID, **bf)
     code = torch.empty(mv * 128 * IN_PAD, **bf)
-    if novel is not None:
+    pe = novel is not None and novel.get("pe") is not None
+    lat_src = None
+    if pe:
+        # NOVEL_PE (pe_novel_pixelnerf.py:260-275): encoder feature, gen_latent taps and [code | pe 6] leave as three
+        # operands; final_latent = gen + deformation_layer([feature | pe 6]) is one GEMM with the taps as residual operand
+        g, e = novel, novel["pe"]
+        gen_pk = torch.empty(mv * 128 * HID, **bf)
+        _lib.call("dnr_encode_novel_pe_fwd", p(rays), p(z), p(g["pts_in"]), p(g["pts_gen"]), p(sc.poses), p(sc.focal),
+                  p(sc.cxy), p(sc.depth), p(sc.latent_nhwc), p(g["poses"]), p(g["focal"]), p(g["cxy"]), p(g["latent"]),
+                  g["Hg"], g["Wg"], g["img_w"], g["img_h"], g["sx"], g["sy"], p(e["src"]), e["Hp"], e["Wp"], e["sx"],
+                  e["sy"], p(e["tgt_poses"]), p(e["tgt_focal"]), p(e["tgt_cxy"]), e["tgt_img_w"], e["tgt_img_h"],
+                  p(e["tgt"]), e["Ht"], e["Wt"], e["tgt_sx"], e["tgt_sy"], p(sc.freqs), p(sc.phases),
+                  *_encode_args(sc, NR, K, ray0, n), p(lat), p(gen_pk), p(code), st)
+        lat_src, lat = lat, torch.empty(mv * 128 * HID, **bf)
+        _gemm(lat_src, pk.wd, HID, mv, A1=code, B1=pk.wdc, K1=IN_PAD, bias=pk.b_d, res_in_pk=gen_pk, act_out=lat)
+        del gen_pk
+    elif novel is not None:
         g = novel
         _lib.call("dnr_encode_novel_fwd", p(rays), p(z), p(g["pts_in"]), p(g["pts_gen"]), p(sc.poses), p(sc.focal),
                   p(sc.cxy), p(sc.depth), p(sc.latent_nhwc), p(g["poses"]), p(g["focal"]), p(g["cxy"]), p(g["latent"]),
@@ -249,7 +324,7 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
         _lib.call("dnr_encode_fwd", p(rays), p(z), p(sc.poses), p(sc.focal), p(sc.cxy), p(sc.depth), p(sc.latent_nhwc),
                   p(sc.freqs), p(sc.phases), *_encode_args(sc, NR, K, ray0, n), p(lat), p(code), st)
 
-    if not save and FORWARD_KERNEL in ("quad", "pair") and NV <= 4:
+    if not save and FORWARD_KERNEL in ("quad", "pair") and NV <= 4 and not pe:
         # inference: CTA-cluster kernels, residual stream in TMEM, lin_out fused (csrc/mlp_pair.cu)
         per_tile = 4 * (32 // NV)                                # samples per 128-row view tile (RowMap)
         mv_q, spare = mv, 0
@@ -303,7 +378,7 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
             if side is not None:
                 cur.wait_stream(side)                            # join
         return out, None
-    if not save and FORWARD_KERNEL != "layers":
+    if not save and FORWARD_KERNEL != "layers" and not pe:
         # inference: the whole ResnetFC in one persistent kernel, activations stay in L2 (csrc/mlp_fused.cu)
         S = 4 * NV * (32 // NV)
         groups = (mv + NV - 1) // NV
@@ -312,7 +387,8 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
                   p(_fused_scratch(dev)), p(xa), 0, st)
         _lib.call("dnr_head_fwd", p(xa), None, p(pk.w_out), p(pk.b_out), n_samples, S, p(out), st)
         return out, None
-    sv = FieldSaved(n_samples=n_samples, mv=mv, ms=ms, lat=lat, code=code) if save else None
+    sv = FieldSaved(n_samples=n_samples, mv=mv, ms=ms, lat=lat, code=code, lat_src=lat_src) if save else None
+    zc = (lambda b: dict(A2=code, B2=pk.w_zc[b], K2=IN_PAD)) if pe else (lambda b: {})     # NOVEL_PE: lin_z's pe columns
     x = torch.empty(mv * 128 * HID, **f32)                      # residual stream, XR layout (updated in place)
     new_act = lambda tiles: torch.empty(tiles * 128 * HID, **bf)
     xa = new_act(mv)
@@ -331,7 +407,7 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
             xa_next = new_act(mv) if save else xa
             # x = x + fc_1(net) + lin_z[b+1](lat)                 resnetfc.py:63-69,152-154
             _gemm(net, pk.w_1[b], HID, mv, A1=lat, B1=pk.w_z[b + 1], K1=HID, bias=pk.b_1[b], res_in=x, res_out=x,
-                  act_out=xa_next, relu=1)
+                  act_out=xa_next, relu=1, **zc(b + 1))
             xa = xa_next
             if save:
                 net = new_act(mv)
@@ -492,11 +568,16 @@ def field_backward(sc: SceneBuffers, pk: PackedMLP, mlp, sv: FieldSaved, rays, z
         _lib.call("dnr_mean_bwd", p(dx), NV, n_samples, mv, None, p(dxv_pk), st)
     pooled, dxv = dx, None
     del dx_pk
+    pe = sv.lat_src is not None
     dz_pk = [None, None, None]
     for b in (2, 1, 0):
         dxv, dxv_pk = block_bwd(b, mv, dxv, dxv_pk, pooled_dx=pooled if b == 2 else None)
         dz_pk[b] = dxv_pk
+        # (NOVEL_PE: the weight is (512, 518); its first 512 columns are written here, leading dimension 518)
         _wgrad(dxv_pk, HID, sv.lat, HID, mv, G(f"lin_z.{b}.weight"), HID, HID, G(f"lin_z.{b}.bias"))
+    if pe:
+        _field_backward_pe(sc, pk, sv, rays, z, NR, ray0, dz_pk, grads, d_latent_nhwc, novel, d_gen_nhwc)
+        return
     _wgrad(dz_pk[0], HID, sv.code, IN_PAD, mv, G("lin_in.weight"), HID, mlp.d_in, G("lin_in.bias"))
     # ---- feature map ----
     if d_latent_nhwc is not None or d_gen_nhwc is not None:
@@ -508,7 +589,46 @@ def field_backward(sc: SceneBuffers, pk: PackedMLP, mlp, sv: FieldSaved, rays, z
             _lib.call("dnr_encode_novel_bwd", p(rays), p(z), p(g["pts_in"]), p(g["pts_gen"]), p(sc.poses), p(sc.focal),
                       p(sc.cxy), p(sc.depth), p(g["poses"]), p(g["focal"]), p(g["cxy"]), g["Hg"], g["Wg"], g["img_w"],
                       g["img_h"], g["sx"], g["sy"], p(sc.freqs), p(sc.phases), *_encode_args(sc, NR, K, ray0, n), p(dlat),
-                      p(d_latent_nhwc), p(d_gen_nhwc), st)
+                      None, p(d_latent_nhwc), p(d_gen_nhwc), st)
             return
         _lib.call("dnr_encode_bwd", p(rays), p(z), p(sc.poses), p(sc.focal), p(sc.cxy), p(sc.depth), p(sc.freqs),
                   p(sc.phases), *_encode_args(sc, NR, K, ray0, n), p(dlat), p(d_latent_nhwc), st)
+
+
+def _field_backward_pe(sc, pk, sv, rays, z, NR, ray0, dz_pk, grads, d_latent_nhwc, novel, d_gen_nhwc):
+    """Tail of field_backward for the NOVEL_PE field (pe_novel_pixelnerf.py:260-275 under autograd): the code-side columns
+    of lin_in / lin_z / deformation_layer, the deformation layer itself, and the two feature-map gradients."""
+    p, st = _lib.ptr, _lib.stream_ptr()
+    dev = dz_pk[0].device
+    n, K = z.shape
+    mv, d_in = sv.mv, pk.d_in
+    f32 = dict(device=dev, dtype=torch.float32)
+    bf = dict(device=dev, dtype=torch.bfloat16)
+    G = lambda name: grads[name]
+    # code operand columns: [code d_in | pe 6 | 0]; one 512 x 64 weight gradient per consumer
+    tmp = torch.zeros(4, HID, IN_PAD, **f32)
+    for b in range(3):
+        _wgrad(dz_pk[b], HID, sv.code, IN_PAD, mv, tmp[b], HID, d_in + 6, G("lin_in.bias") if b == 0 else None)
+    # d final_latent = sum_b lin_z[b][:, :512]^T dz_b: fp32 rows for the gen_latent scatter, bf16 operand for what follows
+    dfin = torch.empty(mv * 128 * HID, **f32) if d_gen_nhwc is not None else None
+    dfin_pk = torch.empty(mv * 128 * HID, **bf)
+    _gemm(dz_pk[0], pk.wt_z[0], HID, mv, A1=dz_pk[1], B1=pk.wt_z[1], K1=HID, A2=dz_pk[2], B2=pk.wt_z[2], K2=HID,
+          res_out=dfin, act_out=dfin_pk)
+    # deformation_layer: conditioned = W_d [feature | pe 6] + b_d, final_latent = gen + conditioned   (:265-268)
+    _wgrad(dfin_pk, HID, sv.lat_src, HID, mv, G("deformation_layer.weight"), HID, HID, G("deformation_layer.bias"))
+    _wgrad(dfin_pk, HID, sv.code, IN_PAD, mv, tmp[3], HID, d_in + 6, None)
+    G("lin_in.weight").add_(tmp[0, :, :d_in])
+    for b in range(3):
+        G(f"lin_z.{b}.weight")[:, HID:].add_(tmp[b, :, d_in:d_in + 6])
+    G("deformation_layer.weight")[:, HID:].add_(tmp[3, :, d_in:d_in + 6])
+    if d_latent_nhwc is None and d_gen_nhwc is None:
+        return
+    dlat = None
+    if d_latent_nhwc is not None:
+        dlat = torch.empty(mv * 128 * HID, **f32)
+        _gemm(dfin_pk, pk.wt_d, HID, mv, res_out=dlat)
+    g = novel
+    _lib.call("dnr_encode_novel_bwd", p(rays), p(z), p(g["pts_in"]), p(g["pts_gen"]), p(sc.poses), p(sc.focal), p(sc.cxy),
+              p(sc.depth), p(g["poses"]), p(g["focal"]), p(g["cxy"]), g["Hg"], g["Wg"], g["img_w"], g["img_h"], g["sx"],
+              g["sy"], p(sc.freqs), p(sc.phases), *_encode_args(sc, NR, K, ray0, n), p(dlat), p(dfin), p(d_latent_nhwc),
+              p(d_gen_nhwc), st)

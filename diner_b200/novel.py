@@ -14,6 +14,9 @@ What the variant changes against the DINER path (reference file:line), and where
     encoder feature (novel_pixelnerf.py:46,73-80,108-141,163-196)                             -> `dnr_encode_novel_fwd`
   * MLP and compositing are the DINER kernels.
 
+NOVEL_PE (src/models/novel_pe/): the same renderer (pe_nerf_novel_renderer.py differs in one line, :444) over another
+field -- recognised by `model.deformation_layer`; see `diner_b200.novel_pe`, `field.PackedPE`, `dnr_encode_novel_pe_fwd`.
+
 `model` is the reference's novel `PixelNeRF` after `encode()` and `encode_gen()` (duck-typed): everything
 `diner_b200.scene` reads, plus `gen_poses (SB,1,4,4)`, `gen_focal / gen_c (SB,1,2)`, `gen_image_shape (2,)`,
 `gen_latent (512,Hg,Wg)`.
@@ -124,13 +127,32 @@ def _gen_latent_nhwc(model) -> torch.Tensor:
     return out
 
 
+def _is_pe(model) -> bool:
+    """NOVEL_PE field (src/models/novel_pe/pe_novel_pixelnerf.py): a `deformation_layer` in front of a 518-latent MLP."""
+    return getattr(model, "deformation_layer", None) is not None
+
+
+def _named_params(model) -> dict:
+    """Everything the renderer's output depends on among `nerf.parameters()`, apart from the two feature maps."""
+    named = dict(model.mlp_fine.named_parameters())
+    if _is_pe(model):
+        named.update({f"deformation_layer.{n}": q for n, q in model.deformation_layer.named_parameters()})
+    return named
+
+
+def _packed(model, need_transposed: bool):
+    if _is_pe(model):
+        return F_.get_packed_pe(model, need_transposed)
+    return F_.get_packed(model.mlp_fine, need_transposed=need_transposed)
+
+
 class _NovelFieldFn(torch.autograd.Function):
     """rgbsigma = field(deformed sample points) over all ray chunks of one forward call (NOVEL variant); differentiable
     w.r.t. encoder.latent, gen_latent and the MLP parameter tensors.  Same structure as renderer._FieldFn."""
 
     @staticmethod
-    def forward(ctx, sc, mlp, names, rays, z, NR, chunks, gen, pts_in, pts_gen, latent, gen_latent, *params):
-        pk = F_.get_packed(mlp, need_transposed=True)
+    def forward(ctx, sc, model, names, rays, z, NR, chunks, gen, pts_in, pts_gen, latent, gen_latent, *params):
+        pk = _packed(model, True)
         K = z.shape[1]
         out = torch.empty(z.shape[0] * K, 4, device=z.device, dtype=torch.float32)
         saved = []
@@ -138,18 +160,18 @@ class _NovelFieldFn(torch.autograd.Function):
             novel = dict(gen, pts_in=pts_in[r0 * K:r1 * K], pts_gen=pts_gen[r0 * K:r1 * K])
             _, sv = F_.field_forward(sc, pk, rays[r0:r1], z[r0:r1], NR, r0, save=True, out=out[r0 * K:r1 * K], novel=novel)
             saved.append(sv)
-        ctx.sc, ctx.mlp, ctx.names, ctx.pk, ctx.saved = sc, mlp, names, pk, saved
+        ctx.sc, ctx.model, ctx.names, ctx.pk, ctx.saved = sc, model, names, pk, saved
         ctx.rays, ctx.z, ctx.NR, ctx.chunks, ctx.gen, ctx.pts = rays, z, NR, chunks, gen, (pts_in, pts_gen)
         ctx.latent_shape, ctx.gen_shape = latent.shape, gen_latent.shape
         return out
 
     @staticmethod
     def backward(ctx, d_out):
-        sc, mlp, gen = ctx.sc, ctx.mlp, ctx.gen
+        sc, mlp, gen = ctx.sc, ctx.model.mlp_fine, ctx.gen
         dev = d_out.device
         p = _lib.ptr
         with torch.cuda.device(dev):
-            params = dict(mlp.named_parameters())
+            params = _named_params(ctx.model)
             offs, total = {}, 0
             for n in ctx.names:
                 offs[n] = total
@@ -218,6 +240,29 @@ class NeRFRendererDGS(torch.nn.Module):
             return self._forward(model, rays, target_vertices, tgt_in_offsets, tgt_gen_offsets, want_weights, noise,
                                  return_samples)
 
+    @staticmethod
+    def _pe_inputs(model, SB, NV, f):
+        """NOVEL_PE: the positional maps and the target camera (pe_novel_pixelnerf.py:75,90-99,133-198)."""
+        src, tgt = model.pos_encodings, model.tgt_pos_encoding
+        if src.dim() != 5 or tuple(src.shape[:3]) != (SB, NV, 3):
+            raise ValueError(f"model.pos_encodings must be (SB,NV,3,H,W), got {tuple(src.shape)}")
+        if tgt.dim() != 5 or tuple(tgt.shape[:3]) != (SB, 1, 3):
+            raise ValueError(f"model.tgt_pos_encoding must be (SB,1,3,H,W), got {tuple(tgt.shape)}")
+        if tuple(model.tgt_poses.shape) != (SB, 1, 4, 4):
+            raise ValueError(f"model.tgt_poses must be (SB,1,4,4), got {tuple(model.tgt_poses.shape)}")
+        fp = float(model.encoder.feature_padding)
+
+        def rescale(t):                                           # :150-152, :185-187 (W then H)
+            size = torch.tensor([t.shape[-1], t.shape[-2]])
+            sc_ = ((size - fp * 2) / size).float()
+            return float(sc_[0]), float(sc_[1])
+
+        (sx, sy), (tx, ty) = rescale(src), rescale(tgt)
+        tshape = model.tgt_image_shape.detach().float().cpu()
+        return dict(src=f(src), Hp=src.shape[-2], Wp=src.shape[-1], sx=sx, sy=sy, tgt=f(tgt), Ht=tgt.shape[-2],
+                    Wt=tgt.shape[-1], tgt_sx=tx, tgt_sy=ty, tgt_poses=f(model.tgt_poses), tgt_focal=f(model.tgt_focal),
+                    tgt_cxy=f(model.tgt_c), tgt_img_w=float(tshape[0]), tgt_img_h=float(tshape[1]))
+
     def _forward(self, model, rays, verts, off_in, off_gen, want_weights, noise, return_samples):
         SB, NR, _ = rays.shape
         dev = rays.device
@@ -264,19 +309,20 @@ class NeRFRendererDGS(torch.nn.Module):
                    img_w=float(gshape[0]), img_h=float(gshape[1]), sx=float(gscale[0]), sy=float(gscale[1]))
         if gen["poses"].shape != (SB, 1, 4, 4):
             raise ValueError(f"model.gen_poses must be (SB,1,4,4), got {tuple(gen['poses'].shape)}")
-        mlp = model.mlp_fine
-        names = [n for n, _ in mlp.named_parameters()]
-        params = [q for _, q in mlp.named_parameters()]
+        if _is_pe(model):
+            gen["pe"] = self._pe_inputs(model, SB, sc.NV, f)
+        named = _named_params(model)
+        names, params = list(named), list(named.values())
         latent, gen_latent = model.encoder.latent, model.gen_latent
         track = torch.is_grad_enabled() and (latent.requires_grad or gen_latent.requires_grad or
                                              any(q.requires_grad for q in params))
         rows = self.rows_per_chunk or (self.ROWS_TRAINING if track else self.ROWS_INFERENCE)
         chunks = balanced_chunks(n_rays, max(1, rows // (K * sc.NV)))
         if track:
-            rgbsigma = _NovelFieldFn.apply(sc, mlp, names, flat, z, NR, chunks, gen, pts_in, pts_gen, latent, gen_latent,
+            rgbsigma = _NovelFieldFn.apply(sc, model, names, flat, z, NR, chunks, gen, pts_in, pts_gen, latent, gen_latent,
                                            *params)
         else:
-            pk = F_.get_packed(mlp, need_transposed=False)
+            pk = _packed(model, False)
             rgbsigma = torch.empty(n_rays * K, 4, device=dev, dtype=torch.float32)
             for r0, r1 in chunks:
                 novel = dict(gen, pts_in=pts_in[r0 * K:r1 * K], pts_gen=pts_gen[r0 * K:r1 * K])

@@ -243,6 +243,8 @@ class NeRFRendererDGS(torch.nn.Module):
 
     def _forward(self, model, rays, want_weights, noise, return_samples):
         SB, NR, _ = rays.shape
+        if getattr(model, "deformation_layer", None) is not None:
+            raise NotImplementedError("diner_b200.NeRFRendererDGS: this is a NOVEL_PE field -- use diner_b200.novel_pe")
         sc = get_scene(model)
         if SB != sc.SB:
             raise ValueError(f"rays batch {SB} does not match the encoded scenes {sc.SB}")

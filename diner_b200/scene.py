@@ -115,8 +115,11 @@ def validate_model(model) -> None:
     enc, mlp = model.encoder, model.mlp_fine
     if getattr(enc, "index_interp", "bilinear") != "bilinear" or getattr(enc, "index_padding", "border") != "border":
         raise NotImplementedError("diner_b200: encoder.index must be bilinear / border")
-    if mlp.d_hidden != 512 or mlp.d_latent != 512 or mlp.n_blocks != 5 or mlp.combine_layer != 3:
-        raise NotImplementedError("diner_b200: ResnetFC must be 5 blocks x 512 with combine_layer 3 and d_latent 512")
+    # NOVEL_PE (pe_novel_pixelnerf.py:21,27): d_latent = 518 behind a 518 -> 512 deformation layer (diner_b200.novel only)
+    d_latent = 518 if getattr(model, "deformation_layer", None) is not None else 512
+    if mlp.d_hidden != 512 or mlp.d_latent != d_latent or mlp.n_blocks != 5 or mlp.combine_layer != 3:
+        raise NotImplementedError("diner_b200: ResnetFC must be 5 blocks x 512 with combine_layer 3 and d_latent 512 "
+                                  "(518 with the NOVEL_PE deformation layer)")
     if getattr(mlp, "combine_type", "average") != "average":
         raise NotImplementedError("diner_b200: combine_type must be 'average'")
     if not isinstance(mlp.activation, torch.nn.ReLU):

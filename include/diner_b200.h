@@ -108,14 +108,33 @@ int dnr_encode_novel_fwd(const float* rays, const float* z, const float* pts_in,
  * step optimises the field's parameters only, novel.py:280-285,361-363, so the deformed points carry no gradient):
  * d_lat_xr [rows_pad x 512] fp32 XR is scattered into d_latent_nhwc [SB,NV,Hl,Wl,512] fp32 at the footprint of pts_in in
  * each source view and into d_gen_latent_nhwc [Hg,Wg,512] fp32 at the footprint of pts_gen under the generic camera (one
- * learned map for all scenes and views, :110).  Both are accumulated into; either may be null. */
+ * learned map for all scenes and views, :110).  Both are accumulated into; either may be null.  d_gen_xr: gradient rows
+ * of the gen_latent taps when they are not those of the encoder feature (NOVEL_PE), null = d_lat_xr. */
 int dnr_encode_novel_bwd(const float* rays, const float* z, const float* pts_in, const float* pts_gen, const float* poses,
                          const float* focal, const float* cxy, const float* depth, const float* gen_poses,
                          const float* gen_focal, const float* gen_cxy, int Hg, int Wg, float gen_img_w, float gen_img_h,
                          float gen_sx, float gen_sy, const float* freqs, const float* phases, int SB, int NV, int NR, int K,
                          int H, int W, int Hl, int Wl, int L, int NF, long long ray_offset, long long n_rays, float img_w,
-                         float img_h, float lat_sx, float lat_sy, const float* d_lat_xr, float* d_latent_nhwc,
-                         float* d_gen_latent_nhwc, dnr_stream_t stream);
+                         float img_h, float lat_sx, float lat_sy, const float* d_lat_xr, const float* d_gen_xr,
+                         float* d_latent_nhwc, float* d_gen_latent_nhwc, dnr_stream_t stream);
+/* NOVEL_PE variant of dnr_encode_novel_fwd (src/models/novel_pe/pe_novel_pixelnerf.py:200-275): lat_pk receives the
+ * encoder feature alone and gen_pk [rows_pad x 512] bf16 PK128 the gen_latent taps (the variant's deformation layer, a
+ * 518 -> 512 nn.Linear on [feature | 6 positional values], is applied before the two are added, :265-268: one
+ * dnr_mlp_gemm with gen_pk as res_in_pk); columns 55..60 of in_pk carry [src_pos_encodings 3 | tgt_pos_encodings 3]:
+ * pe_src [SB,NV,3,Hp,Wp] fp32 tapped bilinearly (border) at the row's source uv rescaled by pe_sx / pe_sy (:133-166),
+ * pe_tgt [SB,1,3,Ht,Wt] fp32 at the projection of the UNDEFORMED point o + z d by the target camera (tgt_poses [SB,1,4,4],
+ * tgt_focal / tgt_cxy [SB,1,2], tgt_img_w/h) rescaled by tgt_sx / tgt_sy (:168-198,223-226,248-251). */
+int dnr_encode_novel_pe_fwd(const float* rays, const float* z, const float* pts_in, const float* pts_gen,
+                            const float* poses, const float* focal, const float* cxy, const float* depth,
+                            const void* latent_nhwc_bf16, const float* gen_poses, const float* gen_focal,
+                            const float* gen_cxy, const void* gen_latent_nhwc_bf16, int Hg, int Wg, float gen_img_w,
+                            float gen_img_h, float gen_sx, float gen_sy, const float* pe_src, int Hp, int Wp, float pe_sx,
+                            float pe_sy, const float* tgt_poses, const float* tgt_focal, const float* tgt_cxy,
+                            float tgt_img_w, float tgt_img_h, const float* pe_tgt, int Ht, int Wt, float tgt_sx,
+                            float tgt_sy, const float* freqs, const float* phases, int SB, int NV, int NR, int K, int H,
+                            int W, int Hl, int Wl, int L, int NF, long long ray_offset, long long n_rays, float img_w,
+                            float img_h, float lat_sx, float lat_sy, void* lat_pk, void* gen_pk, void* in_pk,
+                            dnr_stream_t stream);
 /* Nearest-vertex deformation of the NOVEL variant at frame scale (src/models/novel/nerf_novel_renderer.py:40-50 applied at
  * :104-107 to every sampler candidate and at :441-442 to every sample point): K = 1 nearest neighbour (squared L2, first
  * minimum) against a target mesh given Morton-sorted in groups of 32 with one bounding sphere per group

@@ -1,9 +1,10 @@
-"""Generate tests/golden/novel_tiny{,3}.npz (forward) and novel_tiny{,3}_grad.npz (gradients) by running the reference's NOVEL renderer variant (build container only).
+"""Generate tests/golden/novel{,_pe}_tiny{,3}.npz (forward) and novel{,_pe}_tiny{,3}_grad.npz (gradients) by running the reference's NOVEL renderer variant (build container only).
 
     python -m oracle.make_golden_novel
 
 The reference classes `src.models.novel.nerf_novel_renderer.NeRFRendererDGS` and `src.models.novel.novel_pixelnerf.PixelNeRF`
-run UNMODIFIED on a seeded synthetic scene with the three random draws recorded; the only substitution is
+(and, for the `novel_pe_*` cases, `src.models.novel_pe.pe_nerf_novel_renderer.NeRFRendererDGS` and
+`src.models.novel_pe.pe_novel_pixelnerf.PixelNeRF`) run UNMODIFIED on a seeded synthetic scene with the three random draws recorded; the only substitution is
 `pytorch3d.ops.knn.knn_points` -> oracle.novel_oracle.nearest_vertex (pytorch3d is not in the build image; published K = 1
 semantics).  Test infrastructure.
 """
@@ -18,10 +19,12 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 from oracle import ref_shim  # noqa: E402
-from tools.synthetic import add_novel_inputs, make_scene  # noqa: E402
+from tools.synthetic import add_novel_inputs, add_novel_pe_inputs, make_scene  # noqa: E402
 
 GOLDEN = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
-CASES = {"novel_tiny": ("tiny", 0, 6, 400), "novel_tiny3": ("tiny3", 1, 7, 300)}
+CASES = {"novel_tiny": ("tiny", 0, 6, 400), "novel_tiny3": ("tiny3", 1, 7, 300),
+         # NOVEL_PE (src/models/novel_pe/): same scenes + positional maps, target camera, deformation layer, 518-latent MLP
+         "novel_pe_tiny": ("tiny", 0, 8, 400), "novel_pe_tiny3": ("tiny3", 1, 9, 300)}
 
 
 def build_reference_model(ref, scene):
@@ -43,12 +46,19 @@ def build_reference_model(ref, scene):
     nerf.gen_poses, nerf.gen_focal, nerf.gen_c = m.gen_poses, m.gen_focal, m.gen_c
     nerf.gen_image_shape = m.gen_image_shape.clone()
     nerf.gen_latent = torch.nn.Parameter(m.gen_latent.clone())
+    if getattr(m, "deformation_layer", None) is not None:            # NOVEL_PE
+        nerf.deformation_layer.load_state_dict(m.deformation_layer.state_dict())
+        nerf.pos_encodings, nerf.tgt_pos_encoding = m.pos_encodings, m.tgt_pos_encoding
+        nerf.tgt_poses, nerf.tgt_focal, nerf.tgt_c = m.tgt_poses, m.tgt_focal, m.tgt_c
+        nerf.tgt_image_shape = m.tgt_image_shape.clone()
     return nerf
 
 
 def run_case(ref, name):
     wl_name, seed, noise_seed, n_vert = CASES[name]
     scene = add_novel_inputs(make_scene(wl_name, seed=seed), n_vertices=n_vert, seed=seed)
+    if name.startswith("novel_pe"):
+        scene = add_novel_pe_inputs(scene, seed=seed)
     wl = scene.workload
     nerf = build_reference_model(ref, scene)
     rays = scene.rays
@@ -112,6 +122,17 @@ def reference_gradients(ref, nerf, renderer, rays, V, oi, og, noise_seed):
         if k in ("lin_out.weight", "lin_out.bias", "lin_in.bias", "blocks.4.fc_0.bias", "blocks.1.fc_1.bias", "lin_z.1.bias"):
             data[f"grad.{k}"] = v.grad.numpy()
         data[f"gradnorm.{k}"] = np.float64(v.grad.double().norm().item())
+    if getattr(nerf, "deformation_layer", None) is not None:         # NOVEL_PE: the layers with positional columns, in full
+        # (the 518-column weights: the six positional columns in full + every 61st entry of the rest -- small fixtures)
+        for k, v in (("deformation_layer.weight", nerf.deformation_layer.weight),
+                     ("lin_z.0.weight", nerf.mlp_fine.lin_z[0].weight), ("lin_z.1.weight", nerf.mlp_fine.lin_z[1].weight),
+                     ("lin_z.2.weight", nerf.mlp_fine.lin_z[2].weight)):
+            data[f"gradpe.{k}"] = v.grad[:, 512:].numpy().copy()
+            data[f"gradsub.{k}"] = v.grad[:, :512].flatten()[::61].numpy().copy()
+            data[f"gradnorm.{k}"] = np.float64(v.grad.double().norm().item())
+        for k, v in (("deformation_layer.bias", nerf.deformation_layer.bias), ("lin_in.weight", nerf.mlp_fine.lin_in.weight)):
+            data[f"grad.{k}"] = v.grad.numpy()
+            data[f"gradnorm.{k}"] = np.float64(v.grad.double().norm().item())
     nerf.encoder.latent.requires_grad_(False)
     print(f"  reference gradients: loss={loss.item():.5f} |d latent|={data['glat_norm']:.4e} ({data['glat_nnz']} entries) "
           f"|d gen_latent|={data['ggen_norm']:.4e} ({data['ggen_nnz']} entries)")
@@ -119,10 +140,10 @@ def reference_gradients(ref, nerf, renderer, rays, V, oi, og, noise_seed):
 
 
 def main():
-    ref = ref_shim.load_novel()
+    ref, ref_pe = ref_shim.load_novel(), ref_shim.load_novel_pe()
     torch.set_num_threads(os.cpu_count() or 1)
     for name in (sys.argv[1:] or list(CASES)):
-        data, grad_data = run_case(ref, name)
+        data, grad_data = run_case(ref_pe if name.startswith("novel_pe") else ref, name)
         for suffix, d in (("", data), ("_grad", grad_data)):
             path = os.path.join(GOLDEN, f"{name}{suffix}.npz")
             np.savez_compressed(path, **d)

@@ -11,6 +11,15 @@ Restates, on top of oracle/dgs_oracle.py, what the reference's NOVEL variant cha
                                               gen_focal, gen_c, gen_image_shape :73-80) into the learned `gen_latent` map
                                               (:46, index :108-141) and `final_latent = gen_latent + latent` (:196)
 
+    src/models/novel_pe/                      NOVEL_PE: the same renderer (pe_nerf_novel_renderer.py differs in ONE line,
+                                              :444: the undeformed points are passed to the field as well); the field
+                                              (pe_novel_pixelnerf.py:200-275) taps two 3-channel positional maps -- the
+                                              source views' at the source uv (:133-166), the target view's at the
+                                              projection of the UNDEFORMED point by the target camera (:168-198,223-226,
+                                              248-251) -- runs [latent | 6 values] through a 518 -> 512 `deformation_layer`
+                                              before gen_latent is added (:265-268), and feeds the six values to the MLP
+                                              after final_latent (d_latent = 518, :21,275)        -> *_pe functions below
+
 Pinning: `oracle/make_golden_novel.py` runs the UNMODIFIED reference classes above with a single substitution --
 `pytorch3d.ops.knn.knn_points`, which cannot be imported here, is replaced by `nearest_vertex` below (published semantics of
 K = 1: squared L2, first minimum) -- and `tests/test_oracle.py` requires this file to reproduce those outputs bit for bit.
@@ -89,6 +98,52 @@ def field_inputs(model, xyz, gen_xyz, viewdirs):
     return torch.cat((final_latent, feat, dfeat), dim=-1)
 
 
+def _tap_scaled(model, maps, uv):
+    """pe_novel_pixelnerf.py:133-166 / 168-198: a map (SB,NV,C,H,W) sampled like SpatialEncoder.index, the feature-padding
+    rescale computed from the map's OWN size."""
+    size = torch.tensor([maps.shape[-1], maps.shape[-2]], device=uv.device)
+    uv = uv * ((size - model.encoder.feature_padding * 2) / size).view(1, 1, 1, 2)
+    return O._tap(maps, uv, model.encoder.index_interp, model.encoder.index_padding)
+
+
+def project_tgt(model, tgt_xyz, NV):
+    """pe_novel_pixelnerf.py:223-226,248-251: the target camera, broadcast over the NV source views."""
+    x = tgt_xyz.unsqueeze(1).expand(-1, NV, -1, -1)
+    x = torch.matmul(model.tgt_poses[:, :, :3, :3], x.transpose(-2, -1)).transpose(-2, -1) + model.tgt_poses[:, :, :3, -1].unsqueeze(-2)
+    uv = x[..., :2] / x[..., 2:]
+    uv *= model.tgt_focal.unsqueeze(-2)
+    uv += model.tgt_c.unsqueeze(-2)
+    uv = uv / model.tgt_image_shape * 2 - 1
+    return uv
+
+
+def field_inputs_pe(model, xyz, gen_xyz, tgt_xyz, viewdirs):
+    """(SB,B,3) x4 -> MLP input (SB,NV,B,573) = [gen_latent + deformation_layer([latent | src pe 3 | tgt pe 3]) 512 |
+    src pe 3 | tgt pe 3 | poscode(x_cam) 39 | dir_cam 3 | depthcode 13]        pe_novel_pixelnerf.py:200-275."""
+    x_cam, uv = O.project_to_views(model, xyz)
+    NV = x_cam.shape[1]
+    feat = O.posenc(model.poscode, x_cam)
+    feat = torch.cat((feat, O.rotate_to_views(model, viewdirs)), dim=-1)
+    gen_uv = project_gen(model, gen_xyz, NV)
+    tgt_uv = project_tgt(model, tgt_xyz, NV)
+    latent = O.tap_latent(model, uv).transpose(-1, -2)
+    gen_latent = tap_gen_latent(model, gen_uv).transpose(-1, -2)
+    src_pe = _tap_scaled(model, model.pos_encodings, uv).transpose(-1, -2)
+    tgt_pe = _tap_scaled(model, model.tgt_pos_encoding.repeat(1, NV, 1, 1, 1), tgt_uv).transpose(-1, -2)
+    conditioned = model.deformation_layer(torch.cat((latent, src_pe, tgt_pe), dim=-1))
+    final_latent = gen_latent + conditioned
+    d_ref = O.tap_depth(model, uv)
+    dd = d_ref.squeeze(-2) - x_cam[..., -1]
+    dfeat = O.posenc(model.depthcode, dd.unsqueeze(-1))
+    return torch.cat((final_latent, src_pe, tgt_pe, feat, dfeat), dim=-1)
+
+
+def field_pe(model, xyz, gen_xyz, tgt_xyz, viewdirs):
+    SB, B, _ = xyz.shape
+    out = O.resnetfc(model.mlp_fine, field_inputs_pe(model, xyz, gen_xyz, tgt_xyz, viewdirs)).reshape(SB, B, 4)
+    return torch.cat([torch.sigmoid(out[..., :3]), torch.relu(out[..., 3:4])], dim=-1)
+
+
 def field(model, xyz, gen_xyz, viewdirs):
     SB, B, _ = xyz.shape
     out = O.resnetfc(model.mlp_fine, field_inputs(model, xyz, gen_xyz, viewdirs)).reshape(SB, B, 4)
@@ -102,8 +157,10 @@ def composite(model, rays, z, vertices, in_offsets, gen_offsets, white_bkgd=True
     dirs = rays[..., None, 3:6].expand(-1, -1, K, -1).reshape(SB, B * K, 3)
     chunk = (eval_batch_size - 1) // SB + 1
     outs = []
+    pe = getattr(model, "deformation_layer", None) is not None          # NOVEL_PE (pe_nerf_novel_renderer.py:444)
     for p, d in zip(torch.split(pts, chunk, dim=1), torch.split(dirs, chunk, dim=1)):
-        outs.append(field(model, deform_points(p, vertices, in_offsets), deform_points(p, vertices, gen_offsets), d))
+        p_in, p_gen = deform_points(p, vertices, in_offsets), deform_points(p, vertices, gen_offsets)
+        outs.append(field_pe(model, p_in, p_gen, p, d) if pe else field(model, p_in, p_gen, d))
     rgbsigma = torch.cat(outs, dim=1).reshape(SB, B, K, -1)
     w, rgb, depth = O.alpha_composite(rgbsigma, z, rays, white_bkgd)
     return w, rgb, depth, rgbsigma

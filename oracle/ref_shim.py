@@ -86,6 +86,15 @@ def load_novel():
     return types.SimpleNamespace(NeRFRendererDGS=NeRFRendererDGS, PixelNeRF=PixelNeRF, DotMap=_AttrDict)
 
 
+def load_novel_pe():
+    """The reference's NOVEL_PE renderer and PixelNeRF (src/models/novel_pe/), UNMODIFIED, knn_points replaced as in
+    load_novel()."""
+    load_novel()
+    from src.models.novel_pe.pe_nerf_novel_renderer import NeRFRendererDGS
+    from src.models.novel_pe.pe_novel_pixelnerf import PixelNeRF
+    return types.SimpleNamespace(NeRFRendererDGS=NeRFRendererDGS, PixelNeRF=PixelNeRF, DotMap=_AttrDict)
+
+
 @contextmanager
 def record_noise(store: dict):
     """Record the three random tensors the reference draws, in order:

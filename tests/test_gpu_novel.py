@@ -20,11 +20,16 @@ def _cuda():
     return torch.device("cuda", 0)
 
 
+ALL = ["novel_tiny", "novel_tiny3", "novel_pe_tiny", "novel_pe_tiny3"]      # novel_pe_*: the NOVEL_PE field
+
+
 def _load(name):
-    from tools.synthetic import add_novel_inputs, make_scene
+    from tools.synthetic import add_novel_inputs, add_novel_pe_inputs, make_scene
     g = dict(np.load(os.path.join(os.path.dirname(__file__), "golden", f"{name}.npz"), allow_pickle=False))
     scene = add_novel_inputs(make_scene(str(g["workload"]), seed=int(g["seed"])), n_vertices=int(g["n_vertices"]),
                              seed=int(g["seed"]))
+    if name.startswith("novel_pe"):
+        scene = add_novel_pe_inputs(scene, seed=int(g["seed"]))
     noise = dict(u_coarse=torch.from_numpy(g["u_coarse"]), n_gauss=torch.from_numpy(g["n_gauss"]),
                  u_fill=torch.from_numpy(g["u_fill"]))
     return g, scene, noise
@@ -112,7 +117,7 @@ def test_novel_sampler_bit_exact_vs_cuda_oracle(name):
         novel_to_device(scene, "cpu")
 
 
-@pytest.mark.parametrize("name", ["novel_tiny", "novel_tiny3"])
+@pytest.mark.parametrize("name", ALL)
 def test_novel_render_against_reference_golden(name):
     """diner_b200.novel.NeRFRendererDGS.forward (the reference's signature) against the golden outputs of the reference's
     NOVEL renderer: sampler with the reference's recorded draws (most rays agree; the rest is torch's CPU-vs-CUDA
@@ -288,7 +293,7 @@ def test_novel_encode_bwd_vs_oracle_autograd(n_rays, name):
             d_gen = torch.zeros(Hg, Wg, 512, device=dev) if want_gen else None
             _lib.call("dnr_encode_novel_bwd", p(rd), p(zd), p(pin), p(pgen), p(sc.poses), p(sc.focal), p(sc.cxy),
                       p(sc.depth), p(gp), p(gf), p(gc), Hg, Wg, float(gshape[0]), float(gshape[1]), float(gscale[0]),
-                      float(gscale[1]), p(sc.freqs), p(sc.phases), *F_._encode_args(sc, NR, K, 0, n), p(g_xr), p(d_lat),
+                      float(gscale[1]), p(sc.freqs), p(sc.phases), *F_._encode_args(sc, NR, K, 0, n), p(g_xr), None, p(d_lat),
                       p(d_gen), st)
             torch.cuda.synchronize()
             return d_lat, d_gen
@@ -309,7 +314,7 @@ def test_novel_encode_bwd_vs_oracle_autograd(n_rays, name):
         novel_to_device(scene, "cpu")
 
 
-@pytest.mark.parametrize("name", ["novel_tiny", "novel_tiny3"])
+@pytest.mark.parametrize("name", ALL)
 def test_novel_training_step_against_reference_golden_gradients(name):
     """The NOVEL training step (novel.py:280-296,361-363: render with offsets from the batch, optimise nerf.parameters())
     on the reference's own samples: gradients of loss = sum(rgb * w_rgb) + sum(depth * w_dep) w.r.t. the MLP, gen_latent
@@ -332,7 +337,10 @@ def test_novel_training_step_against_reference_golden_gradients(name):
     try:
         m.encoder.latent = m.encoder.latent.detach().requires_grad_(True)
         m.gen_latent = m.gen_latent.detach().requires_grad_(True)
-        for q in m.mlp_fine.parameters():
+        named = dict(m.mlp_fine.named_parameters())
+        if name.startswith("novel_pe"):
+            named.update({f"deformation_layer.{k}": v for k, v in m.deformation_layer.named_parameters()})
+        for q in named.values():
             q.requires_grad_(True)
             q.grad = None
         r = NeRFRendererDGS(wl.n_samples, wl.n_candidates, wl.n_gaussian, white_bkgd=wl.white_bkgd)
@@ -345,12 +353,17 @@ def test_novel_training_step_against_reference_golden_gradients(name):
         for key in ("rgb", "depth"):
             e = PM.error_metrics(out.fine[key], torch.from_numpy(g[key]))
             assert e["mean"] < 4e-3 and e["q99"] < 6e-2, (key, e)
-        for k, v in m.mlp_fine.named_parameters():
+        for k, v in named.items():
             ratio = v.grad.double().norm().item() / max(float(gg[f"gradnorm.{k}"]), 1e-300)
             assert 0.4 < ratio < 1.8, (k, ratio)
             if f"grad.{k}" in gg:
                 e = PM.grad_metrics(v.grad, torch.from_numpy(gg[f"grad.{k}"]))
                 assert e["cos"] > 0.6, (k, e)
+            if f"gradpe.{k}" in gg:       # NOVEL_PE, 518-column weights: the six positional columns and a sub-sample of the rest
+                e = PM.grad_metrics(v.grad[:, 512:], torch.from_numpy(gg[f"gradpe.{k}"]))
+                assert e["cos"] > 0.6 and 0.4 < e["ratio"] < 1.8, (k, "positional columns", e)
+                e = PM.grad_metrics(v.grad[:, :512].flatten()[::61], torch.from_numpy(gg[f"gradsub.{k}"]))
+                assert e["cos"] > 0.6 and 0.4 < e["ratio"] < 1.8, (k, "feature columns", e)
         for key, t in (("glat", m.encoder.latent.grad), ("ggen", m.gen_latent.grad)):
             assert t is not None and torch.isfinite(t).all()
             pick = t.flatten()[torch.from_numpy(gg[f"{key}_idx"]).to(dev)]
@@ -364,9 +377,9 @@ def test_novel_training_step_against_reference_golden_gradients(name):
             big = want.abs() > 1e-9 * want.abs().max()                # (entries of 1e-30 underflow in the bf16 stream)
             assert int(big.sum()) > 1000 and float((pick[big] != 0).float().mean()) > 0.99
         # chunking of the training step is invisible (two balanced chunks instead of one)
-        first = {k: v.grad.clone() for k, v in m.mlp_fine.named_parameters()}
+        first = {k: v.grad.clone() for k, v in named.items()}
         ggen_first = m.gen_latent.grad.clone()
-        for q in (*m.mlp_fine.parameters(), m.gen_latent, m.encoder.latent):
+        for q in (*named.values(), m.gen_latent, m.encoder.latent):
             q.grad = None
         r2 = NeRFRendererDGS(wl.n_samples, wl.n_candidates, wl.n_gaussian, white_bkgd=wl.white_bkgd,
                              rows_per_chunk=(scene.rays.shape[0] * scene.rays.shape[1] * wl.n_samples * get_nv(m)) // 2 + 1)
@@ -374,16 +387,103 @@ def test_novel_training_step_against_reference_golden_gradients(name):
                   noise=dict(z=torch.from_numpy(g["z"])))
         assert torch.equal(out2.fine.rgb, out.fine.rgb)
         PM.golden_loss(out2.fine.rgb, out2.fine.depth).backward()
-        for k, v in m.mlp_fine.named_parameters():
+        for k, v in named.items():
             assert PM.grad_metrics(v.grad, first[k])["rel_l2"] < 1e-3, k
         assert PM.grad_metrics(m.gen_latent.grad, ggen_first)["rel_l2"] < 1e-4
     finally:
         m.encoder.latent = m.encoder.latent.detach()
         m.gen_latent = m.gen_latent.detach()
-        for q in m.mlp_fine.parameters():
+        for q in named.values():
             q.grad = None
         novel_to_device(scene, "cpu")
 
 
 def get_nv(model):
     return int(model.poses.shape[1])
+
+
+def test_novel_pe_operands_vs_oracle():
+    """dnr_encode_novel_pe_fwd (NOVEL_PE, pe_novel_pixelnerf.py:200-275): the three operand images against the oracle's
+    pieces -- encoder feature alone in lat_pk, gen_latent taps in gen_pk, and [code 55 | src pe 3 | tgt pe 3 | 0 3] in
+    in_pk -- then the deformation GEMM: final_latent = gen + deformation_layer([feature | pe 6]) to bf16 operand accuracy."""
+    dev = _cuda()
+    from diner_b200 import _lib, field as F_
+    from diner_b200.novel import NeRFRendererDGS, _deform, _gen_latent_nhwc, build_vertex_groups
+    from diner_b200.scene import get_scene
+    from oracle import dgs_oracle as O, novel_oracle as N
+    from tools.synthetic import novel_to_device
+    g, scene, _ = _load("novel_pe_tiny3")
+    wl = scene.workload
+    K = wl.n_samples
+    rays = scene.rays[:, :50].contiguous()
+    SB, NR = rays.shape[:2]
+    z = torch.from_numpy(g["z"])[:, :50].contiguous()
+    pts = (rays[..., None, :3] + z.unsqueeze(-1) * rays[..., None, 3:6]).reshape(SB, NR * K, 3)
+    dirs = rays[..., None, 3:6].expand(-1, -1, K, -1).reshape(SB, NR * K, 3)
+    m = scene.model
+    with torch.no_grad():
+        p_in = N.deform_points(pts, scene.target_vertices, scene.tgt_in_offsets)
+        p_gen = N.deform_points(pts, scene.target_vertices, scene.tgt_gen_offsets)
+        zx = N.field_inputs_pe(m, p_in, p_gen, pts, dirs)                                   # SB,NV,B,573
+        _, uv = O.project_to_views(m, p_in)
+        NV = uv.shape[1]
+        want_lat = O.tap_latent(m, uv).transpose(-1, -2)
+        want_gen = N.tap_gen_latent(m, N.project_gen(m, p_gen, NV)).transpose(-1, -2)
+    novel_to_device(scene, dev)
+    try:
+        sc = get_scene(m)
+        rd, zd = rays.to(dev).view(-1, 8), z.to(dev).view(-1, K)
+        V = scene.target_vertices.shape[1]
+        pin, pgen, _ = _deform(rd, zd, None, None, 0, build_vertex_groups(scene.target_vertices),
+                               scene.tgt_in_offsets.contiguous(), scene.tgt_gen_offsets.contiguous(), SB, NR, K, V, False)
+        gen_nhwc = _gen_latent_nhwc(m)
+        Hg, Wg = gen_nhwc.shape[:2]
+        gsize = torch.tensor([Wg, Hg])
+        gscale = ((gsize - float(m.encoder.feature_padding) * 2) / gsize).float()
+        f = lambda t: t.detach().float().contiguous()
+        gshape = m.gen_image_shape.cpu()
+        gen = dict(poses=f(m.gen_poses), focal=f(m.gen_focal), cxy=f(m.gen_c), latent=gen_nhwc, Hg=Hg, Wg=Wg,
+                   img_w=float(gshape[0]), img_h=float(gshape[1]), sx=float(gscale[0]), sy=float(gscale[1]),
+                   pts_in=pin, pts_gen=pgen, pe=NeRFRendererDGS._pe_inputs(m, SB, NV, f))
+        e = gen["pe"]
+        p, st = _lib.ptr, _lib.stream_ptr()
+        n = SB * NR
+        mv = _lib.load().dnr_view_row_tiles(n * K, NV)
+        bf = dict(device=dev, dtype=torch.bfloat16)
+        lat, gpk, code = torch.empty(mv * 128 * 512, **bf), torch.empty(mv * 128 * 512, **bf), torch.empty(mv * 128 * 64, **bf)
+        _lib.call("dnr_encode_novel_pe_fwd", p(rd), p(zd), p(pin), p(pgen), p(sc.poses), p(sc.focal), p(sc.cxy), p(sc.depth),
+                  p(sc.latent_nhwc), p(gen["poses"]), p(gen["focal"]), p(gen["cxy"]), p(gen_nhwc), Hg, Wg, gen["img_w"],
+                  gen["img_h"], gen["sx"], gen["sy"], p(e["src"]), e["Hp"], e["Wp"], e["sx"], e["sy"], p(e["tgt_poses"]),
+                  p(e["tgt_focal"]), p(e["tgt_cxy"]), e["tgt_img_w"], e["tgt_img_h"], p(e["tgt"]), e["Ht"], e["Wt"],
+                  e["tgt_sx"], e["tgt_sy"], p(sc.freqs), p(sc.phases), *F_._encode_args(sc, NR, K, 0, n), p(lat), p(gpk),
+                  p(code), st)
+        pk = F_.get_packed_pe(m, need_transposed=False)
+        final = torch.empty(mv * 128 * 512, **bf)
+        F_._gemm(lat, pk.wd, 512, mv, A1=code, B1=pk.wdc, K1=64, bias=pk.b_d, res_in_pk=gpk, act_out=final)
+
+        def rows_of(buf, width):
+            out = torch.empty(mv * 128, width, device=dev)
+            _lib.call("dnr_unpack_rows", p(buf), mv * 128, width, p(out), st)
+            return out
+
+        lat_rows, gen_rows, code_rows, fin_rows = rows_of(lat, 512), rows_of(gpk, 512), rows_of(code, 64), rows_of(final, 512)
+        torch.cuda.synchronize()
+        spw = 32 // NV
+        s_ = torch.arange(n * K)
+        cat = lambda t, v: torch.cat([t[sb, v] for sb in range(SB)], 0)
+        for v in range(NV):
+            row = ((s_ // spw) * 32 + (s_ % spw) * NV + v).to(dev)
+            w = cat(zx, v)                                       # [final 512 | src pe 3 | tgt pe 3 | code 55]
+            wl_, wg_ = cat(want_lat, v), cat(want_gen, v)
+            assert (lat_rows[row].cpu() - wl_).abs().max() <= 2.0 ** -7 * wl_.abs().max() + 1e-6
+            assert (gen_rows[row].cpu() - wg_).abs().max() <= 2.0 ** -7 * wg_.abs().max() + 1e-6
+            got_c = code_rows[row].cpu()
+            assert torch.allclose(got_c[:, :55], w[:, 518:], rtol=2.0 ** -8, atol=2e-3)
+            assert torch.allclose(got_c[:, 55:61], w[:, 512:518], rtol=2.0 ** -7, atol=2e-3)      # bilinear taps, bf16
+            assert float(w[:, 512:518].abs().mean()) > 0.05 and (got_c[:, 61:] == 0).all()
+            # bf16 operands into a 518-term fp32 sum, bf16 result
+            got_f, want_f = fin_rows[row].cpu(), w[:, :512]
+            assert (got_f - want_f).abs().max() <= 2.0 ** -5 * want_f.abs().max(), float((got_f - want_f).abs().max())
+            assert (got_f - want_f).abs().mean() <= 2.0 ** -8 * want_f.abs().mean() * 4
+    finally:
+        novel_to_device(scene, "cpu")

@@ -428,9 +428,48 @@ def add_novel_inputs(scene, n_vertices: int = 400, seed: int = 0, offset_std: fl
     return scene
 
 
+def add_novel_pe_inputs(scene, seed: int = 0):
+    """NOVEL_PE inputs on top of add_novel_inputs (src/models/novel_pe/pe_novel_pixelnerf.py:21,27,35,45-49,57-99):
+    model.pos_encodings (SB,NV,3,Hp,Wp), model.tgt_pos_encoding (SB,1,3,Ht,Wt), the target camera model.tgt_poses
+    (SB,1,4,4) / tgt_focal / tgt_c (SB,1,2) / tgt_image_shape (2,), model.deformation_layer = nn.Linear(518, 512), and an
+    MLP with d_latent = 518 (the scene's MLP with six more lin_z columns, so the calibrated density head stays alive)."""
+    wl, m = scene.workload, scene.model
+    g = torch.Generator().manual_seed(9100 + seed)
+    m.pos_encodings = (torch.randn(wl.SB, wl.NV, 3, wl.H, wl.W, generator=g) * 0.5).contiguous()
+    m.tgt_pos_encoding = (torch.randn(wl.SB, 1, 3, wl.H + 16, wl.W + 24, generator=g) * 0.5).contiguous()   # its own size
+    dist = 0.5 * (wl.near + wl.far)
+    E = torch.stack([look_at_extrinsics(_cam_center(20.0, 5.0, dist)).float() for _ in range(wl.SB)])
+    K = _intrinsics(wl.H, wl.W, dist, wl.scale).float()
+    m.tgt_poses = E.unsqueeze(1).contiguous()
+    m.tgt_focal = torch.stack((K[0, 0], K[1, 1])).view(1, 1, 2).expand(wl.SB, 1, 2).contiguous()
+    m.tgt_c = K[:2, 2].view(1, 1, 2).expand(wl.SB, 1, 2).contiguous()
+    m.tgt_image_shape = torch.tensor([float(wl.W), float(wl.H)])
+    old = m.mlp_fine
+    new = FieldMLP(d_in=old.d_in, d_latent=old.d_latent + 6)
+    with torch.no_grad():
+        sd = old.state_dict()
+        for k, v in new.state_dict().items():
+            if k.startswith("lin_z.") and k.endswith(".weight"):
+                v[:, :old.d_latent] = sd[k]
+                v[:, old.d_latent:] = torch.randn(v.shape[0], 6, generator=g) * 0.5
+            else:
+                v.copy_(sd[k])
+    m.mlp_fine = new
+    dl = nn.Linear(old.d_latent + 6, old.d_latent)
+    with torch.no_grad():
+        dl.weight[:, :old.d_latent] = 0.8 * torch.eye(old.d_latent) + 0.02 * torch.randn(old.d_latent, old.d_latent, generator=g)
+        dl.weight[:, old.d_latent:] = 0.3 * torch.randn(old.d_latent, 6, generator=g)
+        dl.bias.copy_(0.05 * torch.randn(old.d_latent, generator=g))
+    m.deformation_layer = dl
+    return scene
+
+
 def novel_to_device(scene, device):
     m = scene.model
-    for k in ("gen_poses", "gen_focal", "gen_c", "gen_image_shape", "gen_latent"):
+    for k in ("gen_poses", "gen_focal", "gen_c", "gen_image_shape", "gen_latent", "pos_encodings", "tgt_pos_encoding",
+              "tgt_poses", "tgt_focal", "tgt_c", "tgt_image_shape"):
+        if getattr(m, k, None) is None:
+            continue
         setattr(m, k, getattr(m, k).to(device))
     for k in ("target_vertices", "tgt_in_offsets", "tgt_gen_offsets"):
         setattr(scene, k, getattr(scene, k).to(device))
