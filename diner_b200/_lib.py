@@ -11,7 +11,7 @@ import os
 from . import _build
 
 _lib = None
-ABI_VERSION = 15
+ABI_VERSION = 16
 
 # instrumentation used by bench.py: number of kernel launches issued through the ABI, and (when `profile` is a
 # list) one (name, start_event, end_event, tag) record per call for per-kernel CUDA-event timing
@@ -46,7 +46,7 @@ _SIGNATURES = {
     "dnr_encode_novel_pe_fwd": (c_i, [c_p] * 13 + [c_i, c_i] + [c_f] * 4 + [c_p, c_i, c_i, c_f, c_f] + [c_p] * 3
                                 + [c_f, c_f] + [c_p, c_i, c_i, c_f, c_f] + [c_p, c_p] + [c_i] * 10 + [c_ll, c_ll]
                                 + [c_f] * 4 + [c_p] * 4),
-    "dnr_novel_deform": (c_i, [c_p] * 4 + [c_ull] + [c_p] * 5 + [c_i] * 6 + [c_p] * 4),
+    "dnr_novel_deform": (c_i, [c_p] * 4 + [c_ull] + [c_p] * 6 + [c_i] * 6 + [c_p] * 4),
     "dnr_encode_bwd": (c_i, [c_p] * 8 + [c_i] * 10 + [c_ll, c_ll] + [c_f] * 4 + [c_p, c_p, c_p]),
     "dnr_pack_latent_nhwc": (c_i, [c_p, c_i, c_i, c_i, c_i, c_p, c_p]),
     "dnr_unpack_dlatent_nchw": (c_i, [c_p, c_i, c_i, c_i, c_i, c_p, c_p]),

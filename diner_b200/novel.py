@@ -40,6 +40,7 @@ from .renderer import RenderResult, _CompositeFn, balanced_chunks, sample_rays
 from .scene import SceneBuffers, get_scene, lin_table
 
 GROUP = 32
+SUB_SPHERES = True       # third pruning level of the nearest-vertex search (A/B switch; the result is the same bits)
 
 
 def _morton3(q: torch.Tensor) -> torch.Tensor:
@@ -55,7 +56,9 @@ def _morton3(q: torch.Tensor) -> torch.Tensor:
 
 def build_vertex_groups(vertices: torch.Tensor):
     """vertices (SB,V,3) -> (verts_sorted (SB, G*32, 4) fp32 [x, y, z, original index as int32 bits],
-    spheres (SB, G, 4) fp32 [centre, radius], supers (SB, ceil(G/8), 2, 4) fp32 [box lo | box hi of 8 consecutive groups]).  Padding slots sit at 1e18 with index INT_MAX (never the minimum)."""
+    spheres (SB, G, 4) fp32 [centre, radius], supers (SB, ceil(G/8), 2, 4) fp32 [box lo | box hi of 8 consecutive groups],
+    subs (SB, G, 4, 4) fp32 [centre, radius of each run of 8 vertices]).  Padding slots sit at 1e18 with index INT_MAX
+    (never the minimum)."""
     SB, V, _ = vertices.shape
     dev = vertices.device
     v = vertices.detach().to(torch.float32)
@@ -89,11 +92,20 @@ def build_vertex_groups(vertices: torch.Tensor):
     smin, smax = smin - (1e-6 * ext + 1e-9), smax + (1e-6 * ext + 1e-9)
     zero = torch.zeros(SB, S, 1, device=dev)
     supers = torch.stack([torch.cat([smin, zero], -1), torch.cat([smax, zero], -1)], 2).contiguous()      # SB,S,2,4
-    return verts_sorted, spheres, supers
+    # third level: the four runs of 8 consecutive (Morton-sorted) vertices of a group, a sphere each
+    if not SUB_SPHERES:
+        return verts_sorted, spheres, supers, None
+    run, rvalid = sv.view(SB, G, 4, 8, 3), valid.view(1, G, 4, 8, 1)
+    rmin = torch.where(rvalid, run, torch.full_like(run, big)).amin(3)
+    rmax = torch.where(rvalid, run, torch.full_like(run, -big)).amax(3)
+    rc = 0.5 * (rmin + rmax)                                                           # (empty runs: centre 0, radius 0)
+    rr = torch.where(rvalid[..., 0], (run - rc.unsqueeze(3)).norm(dim=-1), torch.zeros((), device=dev)).amax(3)
+    subs = torch.cat([rc, (rr * (1 + 1e-5) + 1e-9).unsqueeze(-1)], -1).contiguous()   # SB,G,4,4
+    return verts_sorted, spheres, supers, subs
 
 
 def _deform(rays, z, lin, u_coarse, seed, groups, off_a, off_b, SB, NR, per_ray, V, candidates, want_idx=False):
-    verts_sorted, spheres, supers = groups
+    verts_sorted, spheres, supers, subs = groups
     dev = rays.device
     n = SB * NR * per_ray
     out_a = torch.empty(n, 3, device=dev, dtype=torch.float32)
@@ -101,7 +113,7 @@ def _deform(rays, z, lin, u_coarse, seed, groups, off_a, off_b, SB, NR, per_ray,
     idx = torch.empty(n, device=dev, dtype=torch.int32) if want_idx else None
     p = _lib.ptr
     _lib.call("dnr_novel_deform", p(rays), p(z), p(lin), p(u_coarse), seed & (2 ** 64 - 1), p(verts_sorted), p(spheres),
-              p(supers), p(off_a), p(off_b), SB, NR, per_ray, V, spheres.shape[1], 1 if candidates else 0, p(out_a), p(out_b), p(idx),
+              p(supers), p(subs), p(off_a), p(off_b), SB, NR, per_ray, V, spheres.shape[1], 1 if candidates else 0, p(out_a), p(out_b), p(idx),
               _lib.stream_ptr())
     return out_a, out_b, idx
 

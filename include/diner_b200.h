@@ -138,15 +138,17 @@ int dnr_encode_novel_pe_fwd(const float* rays, const float* z, const float* pts_
 /* Nearest-vertex deformation of the NOVEL variant at frame scale (src/models/novel/nerf_novel_renderer.py:40-50 applied at
  * :104-107 to every sampler candidate and at :441-442 to every sample point): K = 1 nearest neighbour (squared L2, first
  * minimum) against a target mesh given Morton-sorted in groups of 32 with one bounding sphere per group
- * (verts_sorted [SB][G*32] float4 = x, y, z, original index bits; spheres [SB][G] float4 = centre, radius; supers [SB][ceil(G/8)][2] float4 = box lo / hi of 8 consecutive groups) -- the search is
- * pruned by the spheres and equals the brute force (dnr_deform_points) bit for bit.  candidates = 1: per_ray = C, the
+ * (verts_sorted [SB][G*32] float4 = x, y, z, original index bits; spheres [SB][G] float4 = centre, radius; supers
+ * [SB][ceil(G/8)][2] float4 = box lo / hi of 8 consecutive groups; subs [SB][G][4] float4 = spheres of the four runs of 8
+ * vertices inside a group, nullable) -- the search is pruned by boxes and spheres and equals the brute force
+ * (dnr_deform_points) bit for bit.  candidates = 1: per_ray = C, the
  * candidate depths are recomputed exactly as dnr_sampler_fwd draws them (lin_tab, u_coarse | Philox(seed)) and out_a
  * receives the OFFSETS [SB*NR,C,3] for dnr_sampler_fwd's cand_offset.  candidates = 0: per_ray = K, z given, out_a / out_b
  * (nullable) receive the points o + z d moved by offsets_a / offsets_b ([SB][V][3], indexed by original vertex). */
 int dnr_novel_deform(const float* rays, const float* z, const float* lin_tab, const float* u_coarse,
                      unsigned long long seed, const void* verts_sorted, const void* spheres, const void* supers,
-                     const float* offsets_a, const float* offsets_b, int SB, int NR, int per_ray, int V, int G, int candidates, float* out_a,
-                     float* out_b, int* idx_out, dnr_stream_t stream);
+                     const void* subs, const float* offsets_a, const float* offsets_b, int SB, int NR, int per_ray, int V,
+                     int G, int candidates, float* out_a, float* out_b, int* idx_out, dnr_stream_t stream);
 /* Backward of SpatialEncoder.index w.r.t. the latent map (grid_sample bilinear backward,
  * image_encoder.py:117-123): d_latent_nhwc [SB,NV,Hl,Wl,512] fp32 += scatter(d_lat_xr XR[rows x 512]). */
 int dnr_encode_bwd(const float* rays, const float* z, const float* poses, const float* focal, const float* cxy,

@@ -487,3 +487,46 @@ def test_novel_pe_operands_vs_oracle():
             assert (got_f - want_f).abs().mean() <= 2.0 ** -8 * want_f.abs().mean() * 4
     finally:
         novel_to_device(scene, "cpu")
+
+
+@pytest.mark.parametrize("NR,neighbours", [(37, True), (37, False), (256, True)])
+def test_candidate_tiling_does_not_change_the_result(NR, neighbours):
+    """dnr_novel_deform, candidates mode: warps take 8 candidates x 4 neighbouring rays where that is more compact than 32
+    candidates of one ray (decided per group of four rays).  Same offsets and vertex indices as the plain order
+    (DNR_NOVEL_TILE=0), for ray counts that are not a multiple of four, neighbouring and scattered rays."""
+    dev = _cuda()
+    from diner_b200.novel import _deform, build_vertex_groups
+    from diner_b200.scene import lin_table
+    gen = torch.Generator().manual_seed(NR)
+    SB, C, V = 2, 1000, 1500
+    u = torch.randn(SB, V, 3, generator=gen)
+    verts = u / u.norm(dim=-1, keepdim=True) * torch.tensor([0.11, 0.15, 0.12])
+    off = torch.randn(SB, V, 3, generator=gen) * 0.01
+    rays = torch.zeros(SB, NR, 8)
+    rays[..., :3] = torch.tensor([0.0, 0.0, -1.7])
+    if neighbours:          # adjacent pixels of one camera
+        px = torch.arange(NR).float().view(1, NR, 1) * 0.0007
+        d = torch.cat([px - 0.01, torch.zeros(1, NR, 1) + 0.003, torch.ones(1, NR, 1)], -1).expand(SB, -1, -1)
+    else:
+        d = torch.randn(SB, NR, 3, generator=gen) * 0.08 + torch.tensor([0.0, 0.0, 1.0])
+    rays[..., 3:6] = d / d.norm(dim=-1, keepdim=True)
+    rays[..., 6], rays[..., 7] = 1.0, 2.5
+    u_coarse = torch.rand(SB * NR, C, generator=gen)
+    rays, verts, off, u_coarse = (t.to(dev).contiguous() for t in (rays, verts, off, u_coarse))
+    groups = build_vertex_groups(verts)
+    run = lambda: _deform(rays.view(-1, 8), None, lin_table(C, dev), u_coarse, 0, groups, off, None, SB, NR, C, V, True,
+                          want_idx=True)
+    old = os.environ.get("DNR_NOVEL_TILE")
+    try:
+        os.environ["DNR_NOVEL_TILE"] = "0"
+        want_off, _, want_idx = run()
+        os.environ["DNR_NOVEL_TILE"] = "1"
+        got_off, _, got_idx = run()
+        torch.cuda.synchronize()
+    finally:
+        if old is None:
+            os.environ.pop("DNR_NOVEL_TILE", None)
+        else:
+            os.environ["DNR_NOVEL_TILE"] = old
+    assert torch.equal(got_idx, want_idx) and torch.equal(got_off, want_off)
+    assert int(got_idx.unique().numel()) > 50 and int(got_idx.max()) < V
