@@ -326,6 +326,7 @@ class Harness:
         total_ms, launches, window = self.timed(step_device, steps, warmup)
         clk = clocks.stop(*window) if clocks is not None else None
         e2e_ms = self.timed(step_e2e, steps, 2)[0] if with_e2e else None
+        F_.LAST_SPLIT.clear()                                            # (a training step never sets it: no stale record)
         breakdown = self.kernel_breakdown(step_device)
         split = dict(F_.LAST_SPLIT)
 
@@ -348,7 +349,10 @@ class Harness:
                         frac_of_burst_peak=achieved / peaks["bf16_tflops"],
                         peak_source=f"{peaks['source']} sustained bf16 (kernel timed inside a long step)",
                         launches_per_step=gemm_launches, kernel_ms_per_step=gemm_ms, algorithmic_flops_per_step=flops,
-                        tiles_per_launch=split or None)
+                        tiles_per_launch=split or None,
+                        timing="CUDA events around every C-ABI call on 3 instrumented steps right after the timed region "
+                               "(the timed region issues the same launches through ONE call, dnr_render_fwd; the "
+                               "instrumented steps issue them call by call -- same kernels, arguments and order)")
         self._attach_traffic(roofline, workload, mode, split)
 
         def _gbs(nbytes, key):

@@ -26,6 +26,7 @@ SOURCES = [
     ("deform.cu", []),
     ("novel.cu", ["--fmad=false"]),
     ("mlp_misc.cu", []),
+    ("render.cu", []),            # host sequencing of a whole evaluation render; includes include/diner_b200.h
 ]
 COMMON = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
           "-Xcompiler", "-fPIC,-fvisibility=hidden", "--expt-relaxed-constexpr"]
@@ -49,6 +50,10 @@ def source_hash() -> str:
     for name in sorted(os.listdir(CSRC)):
         with open(os.path.join(CSRC, name), "rb") as f:
             h.update(name.encode() + b"\0" + f.read())
+    header = os.path.join(os.path.dirname(HERE), "include", "diner_b200.h")      # render.cu compiles against it
+    if os.path.exists(header):
+        with open(header, "rb") as f:
+            h.update(b"diner_b200.h\0" + f.read())
     return h.hexdigest()
 
 

@@ -11,7 +11,7 @@ import os
 from . import _build
 
 _lib = None
-ABI_VERSION = 16
+ABI_VERSION = 17
 
 # instrumentation used by bench.py: number of kernel launches issued through the ABI, and (when `profile` is a
 # list) one (name, start_event, end_event, tag) record per call for per-kernel CUDA-event timing
@@ -23,6 +23,21 @@ c_i = C.c_int
 c_ll = C.c_longlong
 c_f = C.c_float
 c_ull = C.c_ulonglong
+
+
+
+class SceneDesc(C.Structure):
+    """dnr_scene_desc of include/diner_b200.h."""
+    _fields_ = ([(n, c_p) for n in ("poses", "focal", "cxy", "depth", "depth_std_padded", "normal", "latent_nhwc_bf16",
+                                   "freqs", "phases", "lin_tab")]
+                + [(n, c_i) for n in ("SB", "NV", "H", "W", "Hl", "Wl", "L", "NF", "pad")]
+                + [(n, c_f) for n in ("img_w", "img_h", "std_sx", "std_sy", "lat_sx", "lat_sy", "depth_diff_max")])
+
+
+class MlpDesc(C.Structure):
+    """dnr_mlp_desc of include/diner_b200.h."""
+    _fields_ = [(n, c_p) for n in ("w128", "w256", "pair_biases", "w_out", "b_out")]
+
 
 _SIGNATURES = {
     "dnr_abi_version": (c_i, []),
@@ -67,6 +82,9 @@ _SIGNATURES = {
     "dnr_head_bwd": (c_i, [c_p, c_p, c_p, c_p, c_ll, c_p, c_p, c_p, c_p]),
     "dnr_mean_bwd": (c_i, [c_p, c_i, c_ll, c_i, c_p, c_p, c_p]),
     "dnr_mean_bwd_pk": (c_i, [c_p, c_i, c_ll, c_i, c_p, c_p]),
+    "dnr_render_workspace_bytes": (c_ll, [c_i, c_ll, c_i, c_ll]),
+    "dnr_render_fwd": (c_i, [c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_ull, c_p, c_i, c_ll, c_p, c_ll, c_p, c_p, c_p, c_p, c_p,
+                             c_p]),
     "dnr_pack_rows": (c_i, [c_p, c_ll, c_i, c_ll, c_p, c_p]),
     "dnr_unpack_rows": (c_i, [c_p, c_ll, c_i, c_p, c_p]),
     "dnr_xr_to_rows": (c_i, [c_p, c_ll, c_i, c_p, c_p]),

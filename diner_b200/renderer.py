@@ -21,6 +21,35 @@ from . import _lib, field as F_
 from .scene import DEPTH_DIFF_MAX, STD_PAD, SceneBuffers, get_scene, lin_table
 
 
+# Evaluation renders go through ONE C-ABI call (dnr_render_fwd, csrc/render.cu: the same launches in the same order, issued
+# by the library) unless a test or the bench's per-call instrumentation asks for the call-by-call sequence below.
+USE_NATIVE_FRAME = True
+_workspaces: dict = {}
+
+
+def _native_descs(sc: SceneBuffers, pk, lin: torch.Tensor):
+    """ctypes images of dnr_scene_desc / dnr_mlp_desc, cached on the scene buffers / packed weights they point into."""
+    sd = getattr(sc, "_desc", None)
+    if sd is None:
+        p = _lib.ptr
+        sd = _lib.SceneDesc(poses=p(sc.poses), focal=p(sc.focal), cxy=p(sc.cxy), depth=p(sc.depth),
+                            depth_std_padded=p(sc.std_padded), normal=p(sc.normal), latent_nhwc_bf16=p(sc.latent_nhwc),
+                            freqs=p(sc.freqs), phases=p(sc.phases), lin_tab=None, SB=sc.SB, NV=sc.NV, H=sc.H, W=sc.W,
+                            Hl=sc.Hl, Wl=sc.Wl, L=sc.L, NF=sc.num_freqs, pad=STD_PAD, img_w=sc.img_w, img_h=sc.img_h,
+                            std_sx=sc.std_sx, std_sy=sc.std_sy, lat_sx=sc.lat_sx, lat_sy=sc.lat_sy,
+                            depth_diff_max=DEPTH_DIFF_MAX)
+        sc._desc = sd
+    sd.lin_tab = lin.data_ptr()
+    md = getattr(pk, "_desc", None)
+    if md is None:
+        import ctypes as C
+        cast = lambda a: C.cast(a, C.c_void_p)
+        md = _lib.MlpDesc(w128=cast(pk.w128_ptrs), w256=cast(pk.w_ptrs), pair_biases=cast(pk.pair_b_ptrs),
+                          w_out=pk.w_out.data_ptr(), b_out=pk.b_out.data_ptr())
+        pk._desc = md
+    return sd, md
+
+
 class RenderResult(dict):
     """Attribute-access dict (stands in for dotmap.DotMap, nerf_renderer.py:421-430)."""
 
@@ -226,7 +255,7 @@ class NeRFRendererDGS(torch.nn.Module):
         :param model: PixelNeRF-like object after encode() (see diner_b200.scene)
         :param rays: [origin(3), direction(3), near, far]  (SB, B, 8), CUDA fp32
         :param want_weights: also return compositing weights (SB, B, K)
-        :param noise: optional recorded jitter (parity mode), see sample_rays
+        :param noise: optional recorded jitter (parity mode), see sample_rays; dict(seed=int) fixes the in-kernel jitter
         :return: result with .fine.rgb (SB,B,3), .fine.depth (SB,B) [, .fine.weights (SB,B,K)]
         """
         assert len(rays.shape) == 3
@@ -257,12 +286,6 @@ class NeRFRendererDGS(torch.nn.Module):
             if return_samples:
                 empty.z = rays.new_zeros(SB, 0, K)
             return RenderResult(fine=empty)
-        if noise is not None and noise.get("z") is not None:
-            # parity hook: evaluate field + compositing on externally supplied (sorted) sample depths
-            z = noise["z"].detach().to(device=rays.device, dtype=torch.float32).reshape(SB * NR, K).contiguous()
-        else:
-            z = sample_rays(sc, rays, K, self.n_depth_candidates, self.n_gaussian, noise=noise)
-
         mlp = model.mlp_fine
         names = [n for n, _ in mlp.named_parameters()]
         params = [q for _, q in mlp.named_parameters()]
@@ -273,6 +296,22 @@ class NeRFRendererDGS(torch.nn.Module):
         n_rays = SB * NR
         track = torch.is_grad_enabled() and (latent.requires_grad or any(q.requires_grad for q in params))
         rows = self.rows_per_chunk or (self.ROWS_TRAINING if track or self.precision == "split" else self.ROWS_INFERENCE)
+        # one library call for the whole render when nothing asks for the call-by-call sequence (recorded reference draws,
+        # another MLP kernel, the verification mode, per-call timing)
+        native = (USE_NATIVE_FRAME and not track and self.precision == "bf16" and sc.NV <= 4 and _lib.profile is None
+                  and F_.FORWARD_KERNEL == "quad" and F_.MERGE_POOLED and F_.PAIR_SHARE is None and F_.PAIR_PROF is None
+                  and (noise is None or set(noise) <= {"z", "seed"}))
+        z = None
+        if noise is not None and noise.get("z") is not None:
+            # parity hook: evaluate field + compositing on externally supplied (sorted) sample depths
+            z = noise["z"].detach().to(device=rays.device, dtype=torch.float32).reshape(SB * NR, K).contiguous()
+        elif not native:
+            draws = {k: v for k, v in (noise or {}).items() if k != "seed"} or None
+            z = sample_rays(sc, rays, K, self.n_depth_candidates, self.n_gaussian, noise=draws,
+                            seed=(noise or {}).get("seed"))
+        if native:
+            return self._render_native(sc, mlp, flat, SB, NR, z, rows, (noise or {}).get("seed"), want_weights,
+                                       return_samples)
         chunks = balanced_chunks(n_rays, max(1, rows // (K * sc.NV)))
         if track:
             rgbsigma = _FieldFn.apply(sc, mlp, names, flat, z, NR, chunks, self.precision, latent, *params)
@@ -289,4 +328,38 @@ class NeRFRendererDGS(torch.nn.Module):
             out.weights = w.view(SB, NR, K)
         if return_samples:
             out.z = z.view(SB, NR, K)
+        return RenderResult(fine=out)
+
+    def _render_native(self, sc, mlp, flat, SB, NR, z_in, rows, seed, want_weights, return_samples):
+        """The evaluation render as one C-ABI call (dnr_render_fwd): same launches, same order, same bits."""
+        import ctypes as C
+        dev = flat.device
+        K, Cn, G = self.n_samples, self.n_depth_candidates, self.n_gaussian
+        n_rays = SB * NR
+        pk = F_.get_packed(mlp, need_transposed=False)
+        sd, md = _native_descs(sc, pk, lin_table(Cn, dev))
+        need = _lib.load().dnr_render_workspace_bytes(sc.NV, n_rays, K, rows)
+        key = (str(dev), torch.cuda.current_stream(dev).cuda_stream)          # one per stream: calls on two streams may overlap
+        ws = _workspaces.get(key)
+        if ws is None or ws.numel() < need:
+            _workspaces.pop(key, None)
+            ws = None                                                         # (release before growing)
+            ws = _workspaces[key] = torch.empty(need, device=dev, dtype=torch.uint8)
+        f32 = dict(device=dev, dtype=torch.float32)
+        rgb, depth = torch.empty(n_rays, 3, **f32), torch.empty(n_rays, **f32)
+        w = torch.empty(n_rays, K, **f32) if want_weights else None
+        z_out = (z_in if z_in is not None else torch.empty(n_rays, K, **f32)) if return_samples else None
+        if seed is None and z_in is None:
+            seed = int(torch.empty((), dtype=torch.int64).random_().item())
+        info = (C.c_int * 8)()
+        p = _lib.ptr
+        _lib.call("dnr_render_fwd", C.byref(sd), C.byref(md), p(flat), NR, K, Cn, G, (seed or 0) & (2 ** 64 - 1), p(z_in),
+                  int(self.white_bkgd), rows, p(ws), ws.numel(), p(rgb), p(depth), p(w), p(z_out), info, _lib.stream_ptr())
+        _lib.launch_count += info[0] - 1                                      # (call() counted one)
+        F_.LAST_SPLIT.update(tiles_main=info[2], tiles_side=info[3], tiles=info[4], kernel="quad")
+        out = RenderResult(rgb=rgb.view(SB, NR, 3), depth=depth.view(SB, NR))
+        if want_weights:
+            out.weights = w.view(SB, NR, K)
+        if return_samples:
+            out.z = z_out.view(SB, NR, K)
         return RenderResult(fine=out)

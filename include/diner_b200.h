@@ -271,6 +271,51 @@ int dnr_composite_bwd(const float* rgbsigma, const float* z, const float* rays, 
                       const float* d_depth, const float* d_weights, int n_rays, int K, int white_bkgd,
                       float* d_rgbsigma, dnr_stream_t stream);
 
+/* ---- the whole evaluation render in one call --------------------------------------------------------------------- */
+/* Device-side description of the encoded scenes (what PixelNeRF.encode() leaves behind, src/models/pixelnerf.py:34-53,
+ * after the per-scene repacks above): all pointers are device pointers that stay valid for the call. */
+typedef struct dnr_scene_desc {
+  const float* poses;            /* [SB,NV,4,4] world -> camera */
+  const float* focal;            /* [SB,NV,2] */
+  const float* cxy;              /* [SB,NV,2] */
+  const float* depth;            /* [SB,NV,H,W] */
+  const float* depth_std_padded; /* [SB,NV,H+2pad,W+2pad] (dnr_pad_depth_std) */
+  const float* normal;           /* [SB,NV,3,H,W] */
+  const void* latent_nhwc_bf16;  /* [SB,NV,Hl,Wl,L] (dnr_pack_latent_nhwc) */
+  const float* freqs;            /* [2*NF] */
+  const float* phases;           /* [2*NF] */
+  const float* lin_tab;          /* [C] = linspace(0, 1 - 1/C, C) */
+  int SB, NV, H, W, Hl, Wl, L, NF, pad;
+  float img_w, img_h, std_sx, std_sy, lat_sx, lat_sy, depth_diff_max;
+} dnr_scene_desc;
+/* The packed ResnetFC (dnr_pack_weight): the 14 matrices lin_in, lin_z x3, fc_0 x5, fc_1 x5 in both cluster-kernel layouts
+ * (HOST arrays of device pointers, as dnr_mlp_quad_fwd / dnr_mlp_pair_fwd take them), the 11 bias vectors of
+ * dnr_mlp_pair_fwd, and lin_out in fp32. */
+typedef struct dnr_mlp_desc {
+  const void* const* w128;
+  const void* const* w256;
+  const float* const* pair_biases;
+  const float* w_out;            /* [4,512] */
+  const float* b_out;            /* [4] */
+} dnr_mlp_desc;
+/* Bytes of device workspace for dnr_render_fwd: n_rays = SB*NR rays, K samples per ray, NV views, chunks of at most
+ * rows_per_chunk per-view MLP rows (<= 0: 2^22). */
+long long dnr_render_workspace_bytes(int NV, long long n_rays, int K, long long rows_per_chunk);
+/* NeRFRendererDGS.forward for evaluation (src/models/nerf_renderer.py:399-424 -> sample_depthguided :65-284,
+ * fill_up_uniform_samples :367-397, composite :286-365) as ONE host call: dnr_sampler_fwd (in-kernel Philox jitter from
+ * `seed`; or z_in [SB*NR,K], sorted sample depths supplied by the caller), then per balanced chunk of rays dnr_encode_fwd,
+ * dnr_mlp_quad_fwd with dnr_mlp_pair_fwd on the SMs the 4-CTA clusters cannot occupy (a side stream the library keeps per
+ * device; the split adapts to the two kernels' measured times unless DNR_ADAPT_SPLIT=0) and dnr_head_finalize, then one
+ * dnr_composite_fwd.  rays [SB*NR,8]; outputs rgb [SB*NR,3], depth [SB*NR], nullable weights_out / z_out [SB*NR,K].
+ * workspace: 256-byte aligned device memory of dnr_render_workspace_bytes(...) bytes, owned by the caller; the call
+ * allocates no device memory.  info (nullable, HOST int[8]): kernel launches, chunks, tiles of the last chunk on the 4-CTA
+ * / 2-CTA clusters, their sum.  Same bits as the call-by-call sequence.  One call at a time per device and process (the
+ * side stream is shared).  NV <= 4. */
+int dnr_render_fwd(const dnr_scene_desc* scene, const dnr_mlp_desc* mlp, const float* rays, long long NR, int K, int C,
+                   int G, unsigned long long seed, const float* z_in, int white_bkgd, long long rows_per_chunk,
+                   void* workspace, long long workspace_bytes, float* rgb, float* depth, float* weights_out, float* z_out,
+                   int* info, dnr_stream_t stream);
+
 /* ---- input producers next to the path ---------------------------------------------------- */
 
 /* Pixel-centre rays of B target cameras: rays [B,H,W,8] = [origin 3 | unit direction 3 | near | far] from world->cam

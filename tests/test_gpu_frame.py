@@ -214,3 +214,48 @@ def test_full_frame_properties_other_shapes(workload, max_rays):
         assert float(o.fine.depth.max()) <= wl.far + 1e-3 and float(o.fine.depth.min()) >= 0
     finally:
         m.to_device("cpu")
+
+
+@pytest.mark.parametrize("workload,n_rays,rows", [("facescape", 65536, None), ("facescape", 4096, None),
+                                                  ("facescape", 20000, 1 << 19), ("tiny3", 288, None), ("tiny", 129, 1 << 12),
+                                                  ("multiface", 6000, None), ("tiny", 1, None)])
+def test_single_call_render_equals_call_by_call_sequence(workload, n_rays, rows):
+    """dnr_render_fwd (csrc/render.cu: the evaluation render as ONE C-ABI call, sequenced by the library) against the
+    same launches issued call by call from Python (renderer.py / field.py): rgb, depth, weights and samples are the same
+    bits, for the in-kernel jitter (same seed) and for caller-supplied samples; view counts 2 / 3 / 4, one and several
+    chunks (with and without a 2-CTA-cluster share), ragged last tiles, two scenes per call."""
+    dev = _cuda()
+    import diner_b200.renderer as R
+    from diner_b200 import NeRFRendererDGS, _lib
+    from tools.synthetic import make_scene
+    scene = make_scene(workload, seed=3)
+    wl = scene.workload
+    m = scene.model.to_device(dev)
+    per_scene = max(1, n_rays // wl.SB)
+    rays = scene.rays[:, :per_scene].contiguous().to(dev)
+    r = NeRFRendererDGS(wl.n_samples, wl.n_candidates, wl.n_gaussian, white_bkgd=wl.white_bkgd, rows_per_chunk=rows)
+    old = R.USE_NATIVE_FRAME
+    try:
+        outs = {}
+        with torch.no_grad():
+            r(m, rays)                                           # (per-scene / per-weights repacks happen here)
+        for native in (True, False):
+            R.USE_NATIVE_FRAME = native
+            n0 = _lib.launch_count
+            with torch.no_grad():
+                a = r(m, rays, want_weights=True, return_samples=True, noise=dict(seed=77))
+                b = r(m, rays, noise=dict(z=a.fine.z))
+                torch.manual_seed(5)
+                c = r(m, rays)                                   # seed drawn from torch's CPU generator
+            outs[native] = (a, b, c, _lib.launch_count - n0)
+        torch.cuda.synchronize()
+    finally:
+        R.USE_NATIVE_FRAME = old
+        m.to_device("cpu")
+    (a1, b1, c1, l1), (a0, b0, c0, l0) = outs[True], outs[False]
+    for k in ("rgb", "depth", "weights", "z"):
+        assert torch.equal(a1.fine[k], a0.fine[k]), k
+    for k in ("rgb", "depth"):
+        assert torch.equal(b1.fine[k], b0.fine[k]) and torch.equal(c1.fine[k], c0.fine[k]), k
+        assert torch.equal(b1.fine[k], a1.fine[k])               # the renderer on its own samples
+    assert torch.isfinite(a1.fine.rgb).all() and l1 == l0        # and the same number of kernel launches is claimed
