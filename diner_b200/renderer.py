@@ -15,6 +15,8 @@ of include/diner_b200.h; there is no CPU or torch-op fallback.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from . import _lib, field as F_
@@ -23,7 +25,7 @@ from .scene import DEPTH_DIFF_MAX, STD_PAD, SceneBuffers, get_scene, lin_table
 
 # Evaluation renders go through ONE C-ABI call (dnr_render_fwd, csrc/render.cu: the same launches in the same order, issued
 # by the library) unless a test or the bench's per-call instrumentation asks for the call-by-call sequence below.
-USE_NATIVE_FRAME = True
+USE_NATIVE_FRAME = os.environ.get("DNR_NATIVE_FRAME", "1") != "0"
 _workspaces: dict = {}
 
 
