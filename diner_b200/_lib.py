@@ -11,7 +11,7 @@ import os
 from . import _build
 
 _lib = None
-ABI_VERSION = 17
+ABI_VERSION = 18
 
 # instrumentation used by bench.py: number of kernel launches issued through the ABI, and (when `profile` is a
 # list) one (name, start_event, end_event, tag) record per call for per-kernel CUDA-event timing
@@ -75,6 +75,8 @@ _SIGNATURES = {
     "dnr_mlp_quad_max_clusters": (c_i, [c_i]),
     "dnr_mlp_quad_scratch_bytes": (c_ll, []),
     "dnr_mlp_quad_fwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_p, c_p, c_p, c_p]),
+    "dnr_mlp_pair_fwd_pe": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_p, c_p]),
+    "dnr_mlp_quad_fwd_pe": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_p, c_p, c_p]),
     "dnr_mlp_quad_static_max_tiles": (c_i, []),
     "dnr_mlp_quad_fwd_static": (c_i, [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_p, c_p]),
     "dnr_head_finalize": (c_i, [c_p, c_p, c_i, c_ll, c_i, c_p, c_p]),

@@ -39,6 +39,8 @@ struct PairParams {
   const unsigned char* code_pk;   // PK128 [mv_tiles x 64]
   const unsigned char* w_in;      // PK256 [512 x 64]
   const unsigned char* w_z[3];
+  const unsigned char* w_zc[2];   // NOVEL_PE, else null: [512 x 64] weights of a second code K-step in fc_1 of blocks 0 / 1
+                                  // (lin_z[1], lin_z[2] applied to the six positional values in the code operand)
   const unsigned char* w_0[5];
   const unsigned char* w_1[5];
   const float* cb[6];             // cumulative residual-stream biases: after lin_in+z0, block 0, 1, 2 | block 3, 4
@@ -56,6 +58,7 @@ struct PairParams {
 struct QuadMaps {
   CUtensorMap w[14];              // lin_in, lin_z x3, fc_0 x5, fc_1 x5 (PK128 images)
   CUtensorMap lat, code;
+  CUtensorMap wc[2];              // PairParams::w_zc
 };
 
 enum { EPI_X = 0, EPI_T = 1, EPI_MEAN = 2, EPI_HEAD = 3 };
@@ -64,21 +67,25 @@ struct POp {
   const unsigned char* lat_w;     // lin_z weights (A = streamed lat) or null
   const unsigned char* abuf_w;    // weights applied to the resident A operand or null
   const float* bias;
-  int code;                       // lin_in K-step (op 0)
+  const unsigned char* code_w;    // weights of the op's code K-step (lin_in in op 0; NOVEL_PE: w_zc in ops 2, 4) or null
+  int code;                       // the op starts with a K-step on the 64-wide code operand
   int acc_x;                      // accumulator: X (1) or T (0)
   int fresh;                      // first MMA overwrites
   int epi;
 };
 
 __device__ __forceinline__ void pair_get_op(const PairParams& P, int o, POp& d) {
-  d.lat_w = nullptr; d.abuf_w = nullptr; d.code = 0; d.acc_x = 1; d.fresh = 0; d.epi = EPI_X;
-  if (o == 0) { d.code = 1; d.lat_w = P.w_z[0]; d.fresh = 1; d.bias = P.cb[0]; return; }
+  d.lat_w = nullptr; d.abuf_w = nullptr; d.code_w = nullptr; d.code = 0; d.acc_x = 1; d.fresh = 0; d.epi = EPI_X;
+  if (o == 0) { d.code = 1; d.code_w = P.w_in; d.lat_w = P.w_z[0]; d.fresh = 1; d.bias = P.cb[0]; return; }
   const int b = (o - 1) >> 1;
   if (o & 1) {                      // fc_0 of block b
     d.abuf_w = P.w_0[b]; d.acc_x = 0; d.fresh = 1; d.epi = EPI_T; d.bias = P.b_0[b];
   } else {                          // fc_1 of block b (+ lin_z[b+1])
     d.abuf_w = P.w_1[b];
-    if (b < 2) d.lat_w = P.w_z[b + 1];
+    if (b < 2) {
+      d.lat_w = P.w_z[b + 1];
+      if (P.w_zc[b]) { d.code = 1; d.code_w = P.w_zc[b]; }
+    }
     d.bias = P.cb[b + 1];
     d.epi = b == 4 ? EPI_HEAD : EPI_X;
   }
@@ -224,8 +231,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
         for (int o = 0; o < kPOps; ++o) {
           pair_get_op(P, o, d);
           if (d.code) {
-            fill(P.code_pk + (size_t)tile * 16384, 16384, pol_stream);
-            fill(P.w_in + (size_t)rank * 32768, 32768, pol_keep);
+            fill(P.code_pk + (size_t)tile * 16384, 16384, (o == 4 || !P.w_zc[0]) ? pol_stream : pol_norm);
+            fill(d.code_w + (size_t)rank * 32768, 32768, pol_keep);
           }
           if (d.lat_w) {
             for (int kb = 0; kb < 8; ++kb) {
@@ -518,6 +525,8 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
       };
       auto w_map = [&](const unsigned char* w) -> const CUtensorMap* {      // the tensor map of a weight image
         if (w == P.w_in) return &M.w[0];
+        if (w == P.w_zc[0]) return &M.wc[0];
+        if (w == P.w_zc[1]) return &M.wc[1];
         for (int i = 0; i < 3; ++i) if (w == P.w_z[i]) return &M.w[1 + i];
         for (int i = 0; i < 5; ++i) if (w == P.w_0[i]) return &M.w[4 + i];
         for (int i = 0; i < 5; ++i) if (w == P.w_1[i]) return &M.w[9 + i];
@@ -536,8 +545,8 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
         for (int o = 0; o < n_ops; ++o) {
           pair_get_op(P, o, d);
           if (d.code) {
-            fill(P.code_pk + (size_t)tile * 16384, pol_stream, &M.code, tile * 32);
-            fill(P.w_in + (size_t)cr * 16384, pol_keep, &M.w[0], (int)cr * 32);
+            fill(P.code_pk + (size_t)tile * 16384, (o == 4 || !P.w_zc[0]) ? pol_stream : pol_norm, &M.code, tile * 32);
+            fill(d.code_w + (size_t)cr * 16384, pol_keep, P.tma2 ? w_map(d.code_w) : nullptr, (int)cr * 32);
           }
           if (d.lat_w) {
             const CUtensorMap* wm = P.tma2 ? w_map(d.lat_w) : nullptr;
@@ -913,9 +922,28 @@ __global__ void head_finalize_kernel(const float4* __restrict__ part, const floa
 // [lin_in, lin_z0..2, fc_0 x5, fc_1 x5]; biases: 11 fp32[512] pointers [cb0..cb5 (cumulative residual biases),
 // fc_0 bias x5]; w_out fp32 [4 x 512]; head_partial: [mv_tiles*2*128] float4; max_clusters: 0 = all SM pairs, else
 // the number of clusters to launch (to run beside another kernel on the SMs that one leaves idle).
+static int pair_fwd_impl(const void* lat_pk, const void* code_pk, const void* const* weights,
+                         const void* const* code_weights, const float* const* biases, const float* w_out, int NV,
+                         int mv_tiles, int max_clusters, float* head_partial, long long* prof, cudaStream_t stream);
 DNR_EXPORT int dnr_mlp_pair_fwd(const void* lat_pk, const void* code_pk, const void* const* weights,
                                 const float* const* biases, const float* w_out, int NV, int mv_tiles, int max_clusters,
                                 float* head_partial, long long* prof, cudaStream_t stream) {
+  return pair_fwd_impl(lat_pk, code_pk, weights, nullptr, biases, w_out, NV, mv_tiles, max_clusters, head_partial, prof, stream);
+}
+// NOVEL_PE field (src/models/novel_pe/pe_novel_pixelnerf.py:263-275, d_latent = 518): fc_1 of blocks 0 and 1 gets a second
+// K-step on the 64-wide code operand, whose columns 55..60 carry the six positional values -- code_weights[b]: PK256
+// [512 x 64] image of [0 (55) | lin_z[b+1].weight[:, 512:518] | 0 (3)] (diner_b200.field.PackedPE); lat_pk is then the
+// variant's final_latent.  Otherwise dnr_mlp_pair_fwd.
+DNR_EXPORT int dnr_mlp_pair_fwd_pe(const void* lat_pk, const void* code_pk, const void* const* weights,
+                                   const void* const* code_weights, const float* const* biases, const float* w_out, int NV,
+                                   int mv_tiles, int max_clusters, float* head_partial, cudaStream_t stream) {
+  DNR_REQUIRE(code_weights && code_weights[0] && code_weights[1], "dnr_mlp_pair_fwd_pe: null code weights");
+  return pair_fwd_impl(lat_pk, code_pk, weights, code_weights, biases, w_out, NV, mv_tiles, max_clusters, head_partial,
+                       nullptr, stream);
+}
+static int pair_fwd_impl(const void* lat_pk, const void* code_pk, const void* const* weights,
+                         const void* const* code_weights, const float* const* biases, const float* w_out, int NV,
+                         int mv_tiles, int max_clusters, float* head_partial, long long* prof, cudaStream_t stream) {
   DNR_REQUIRE(NV >= 1 && NV <= 4, "dnr_mlp_pair_fwd: NV must be in [1,4]");
   DNR_REQUIRE(max_clusters >= 0, "dnr_mlp_pair_fwd: max_clusters must be >= 0 (0 = one cluster per SM pair)");
   DNR_REQUIRE(lat_pk && code_pk && weights && biases && w_out && head_partial, "dnr_mlp_pair_fwd: null argument");
@@ -923,6 +951,7 @@ DNR_EXPORT int dnr_mlp_pair_fwd(const void* lat_pk, const void* code_pk, const v
   dnr::PairParams P;
   P.lat_pk = (const unsigned char*)lat_pk; P.code_pk = (const unsigned char*)code_pk;
   P.w_in = (const unsigned char*)weights[0];
+  for (int i = 0; i < 2; ++i) P.w_zc[i] = code_weights ? (const unsigned char*)code_weights[i] : nullptr;
   for (int i = 0; i < 3; ++i) P.w_z[i] = (const unsigned char*)weights[1 + i];
   for (int i = 0; i < 5; ++i) { P.w_0[i] = (const unsigned char*)weights[4 + i]; P.w_1[i] = (const unsigned char*)weights[9 + i]; }
   for (int i = 0; i < 6; ++i) P.cb[i] = biases[i];
@@ -1034,15 +1063,33 @@ DNR_EXPORT long long dnr_mlp_quad_scratch_bytes(void) { return 4LL * dnr::kQuadM
 // dnr_mlp_pair_fwd but in the PK128 layout [N/128][K/8][128][8]; head_partial: [mv_tiles*4*128] float4
 // (dnr_head_finalize with n_partials = 4); merge_scratch: null, or dnr_mlp_quad_scratch_bytes() bytes -> blocks 3-4 and
 // the head run once per NV tiles on merged pooled rows (NV > 1; the partial sums land where they would otherwise).
+static int quad_fwd_impl(const void* lat_pk, const void* code_pk, const void* const* weights_pk128,
+                         const void* const* code_weights, const float* const* biases, const float* w_out, int NV,
+                         int mv_tiles, void* merge_scratch, float* head_partial, long long* prof, cudaStream_t stream);
 DNR_EXPORT int dnr_mlp_quad_fwd(const void* lat_pk, const void* code_pk, const void* const* weights_pk128,
                                 const float* const* biases, const float* w_out, int NV, int mv_tiles,
                                 void* merge_scratch, float* head_partial, long long* prof, cudaStream_t stream) {
+  return quad_fwd_impl(lat_pk, code_pk, weights_pk128, nullptr, biases, w_out, NV, mv_tiles, merge_scratch, head_partial,
+                       prof, stream);
+}
+// NOVEL_PE counterpart of dnr_mlp_quad_fwd (see dnr_mlp_pair_fwd_pe): code_weights_pk128[b] = PK128 [512 x 64] images.
+DNR_EXPORT int dnr_mlp_quad_fwd_pe(const void* lat_pk, const void* code_pk, const void* const* weights_pk128,
+                                   const void* const* code_weights_pk128, const float* const* biases, const float* w_out,
+                                   int NV, int mv_tiles, void* merge_scratch, float* head_partial, cudaStream_t stream) {
+  DNR_REQUIRE(code_weights_pk128 && code_weights_pk128[0] && code_weights_pk128[1], "dnr_mlp_quad_fwd_pe: null code weights");
+  return quad_fwd_impl(lat_pk, code_pk, weights_pk128, code_weights_pk128, biases, w_out, NV, mv_tiles, merge_scratch,
+                       head_partial, nullptr, stream);
+}
+static int quad_fwd_impl(const void* lat_pk, const void* code_pk, const void* const* weights_pk128,
+                         const void* const* code_weights, const float* const* biases, const float* w_out, int NV,
+                         int mv_tiles, void* merge_scratch, float* head_partial, long long* prof, cudaStream_t stream) {
   DNR_REQUIRE(NV >= 1 && NV <= 4, "dnr_mlp_quad_fwd: NV must be in [1,4]");
   DNR_REQUIRE(lat_pk && code_pk && weights_pk128 && biases && w_out && head_partial, "dnr_mlp_quad_fwd: null argument");
   if (mv_tiles <= 0) return 0;
   dnr::PairParams P;
   P.lat_pk = (const unsigned char*)lat_pk; P.code_pk = (const unsigned char*)code_pk;
   P.w_in = (const unsigned char*)weights_pk128[0];
+  for (int i = 0; i < 2; ++i) P.w_zc[i] = code_weights ? (const unsigned char*)code_weights[i] : nullptr;
   for (int i = 0; i < 3; ++i) P.w_z[i] = (const unsigned char*)weights_pk128[1 + i];
   for (int i = 0; i < 5; ++i) {
     P.w_0[i] = (const unsigned char*)weights_pk128[4 + i]; P.w_1[i] = (const unsigned char*)weights_pk128[9 + i];
@@ -1061,6 +1108,7 @@ DNR_EXPORT int dnr_mlp_quad_fwd(const void* lat_pk, const void* code_pk, const v
     if (P.tma2) {
       bool ok = dnr::cached_kblock_map(&M.w[0], weights_pk128[0], (size_t)512 * 64 * 2);
       for (int i = 1; i < 14 && ok; ++i) ok = dnr::cached_kblock_map(&M.w[i], weights_pk128[i], (size_t)512 * 512 * 2);
+      for (int i = 0; i < 2 && ok && code_weights; ++i) ok = dnr::cached_kblock_map(&M.wc[i], code_weights[i], (size_t)512 * 64 * 2);
       ok = ok && dnr::encode_kblock_map(&M.lat, lat_pk, (size_t)mv_tiles * 131072);
       ok = ok && dnr::encode_kblock_map(&M.code, code_pk, (size_t)mv_tiles * 16384);
       if (!ok) { P.tma2 = 0; memset(&M, 0, sizeof(M)); }     // driver entry point missing: the plain bulk-copy delivery
@@ -1145,6 +1193,7 @@ DNR_EXPORT int dnr_mlp_quad_fwd_static(const void* lat_pk, const void* code_pk, 
   for (int i = 0; i < 5; ++i) P.b_0[i] = biases[6 + i];
   P.w_out = w_out; P.head_partial = (float4*)head_partial;
   P.NV = NV; P.SPW = 32 / NV; P.mv_tiles = mv_tiles; P.prof = nullptr; P.tma2 = 0;
+  P.w_zc[0] = P.w_zc[1] = nullptr;
   P.merge_scratch = dnr::g_quad_static_ptr[dev];
   dnr::QuadKernel kern = dnr::quad_kernel(NV, NV > 1);
   const int max_cl = dnr::quad_max_clusters(NV);      // also sets the kernels' shared-memory attribute on this device

@@ -47,6 +47,7 @@ _split_state = {}            # (device, NV) -> dict(rate=float, pending=[(e_q0, 
 # image the next dgrad GEMM reads anyway (each block adds its dgrad in fp32 and rounds once) -- 3 KB instead of 7 KB per
 # row in the HBM-bound fc_0 dgrad layers.  "fp32": a separate fp32 stream is read and written by every block (round 1).
 GRAD_STREAM = os.environ.get("DNR_GRAD_STREAM", "bf16")
+PE_FORWARD_LAYERS = False     # NOVEL_PE evaluation on the per-layer kernels instead of the cluster kernels (tests, A/B)
 MERGE_POOLED = True          # quad kernel: run blocks 3-4 + head once per NV tiles on merged pooled rows (NV > 1)
 _side_stream = {}
 LAST_SPLIT = {}              # bench instrumentation: tiles of the most recent inference MLP launch (main / side kernel)
@@ -163,6 +164,11 @@ class PackedPE(PackedMLP):
         self.b_d = dl.bias.detach().float().contiguous()
         if need_transposed:
             self.wt_d = _pack_weight(wd[:, :HID], True)
+        # the cluster kernels' second code K-step (dnr_mlp_pair_fwd_pe / dnr_mlp_quad_fwd_pe): PK256 and PK128 images
+        import ctypes as C
+        self.w_zc128 = [w.view(-1, IN_PAD // 8, 2, 128, 8).permute(0, 2, 1, 3, 4).contiguous().view(-1) for w in self.w_zc[1:]]
+        self.zc_ptrs = (C.c_void_p * 2)(*[t.data_ptr() for t in self.w_zc[1:]])
+        self.zc128_ptrs = (C.c_void_p * 2)(*[t.data_ptr() for t in self.w_zc128])
 
 
 _packed_cache: dict = {}
@@ -324,7 +330,7 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
         _lib.call("dnr_encode_fwd", p(rays), p(z), p(sc.poses), p(sc.focal), p(sc.cxy), p(sc.depth), p(sc.latent_nhwc),
                   p(sc.freqs), p(sc.phases), *_encode_args(sc, NR, K, ray0, n), p(lat), p(code), st)
 
-    if not save and FORWARD_KERNEL in ("quad", "pair") and NV <= 4 and not pe:
+    if not save and FORWARD_KERNEL in ("quad", "pair") and NV <= 4 and not (pe and PE_FORWARD_LAYERS):
         # inference: CTA-cluster kernels, residual stream in TMEM, lin_out fused (csrc/mlp_pair.cu)
         per_tile = 4 * (32 // NV)                                # samples per 128-row view tile (RowMap)
         mv_q, spare = mv, 0
@@ -354,8 +360,12 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
             part_q = torch.empty(mv_q * 4 * 128, 4, **f32)
             if timing:
                 ev[0].record(cur)
-            _lib.call("dnr_mlp_quad_fwd", p(lat), p(code), pk.w128_ptrs, pk.pair_b_ptrs, p(pk.w_out), NV, mv_q,
-                      p(_quad_scratch(dev)) if MERGE_POOLED and NV > 1 else None, p(part_q), p(PAIR_PROF), st)
+            if pe:
+                _lib.call("dnr_mlp_quad_fwd_pe", p(lat), p(code), pk.w128_ptrs, pk.zc128_ptrs, pk.pair_b_ptrs, p(pk.w_out),
+                          NV, mv_q, p(_quad_scratch(dev)) if MERGE_POOLED and NV > 1 else None, p(part_q), st)
+            else:
+                _lib.call("dnr_mlp_quad_fwd", p(lat), p(code), pk.w128_ptrs, pk.pair_b_ptrs, p(pk.w_out), NV, mv_q,
+                          p(_quad_scratch(dev)) if MERGE_POOLED and NV > 1 else None, p(part_q), p(PAIR_PROF), st)
             if timing:
                 ev[1].record(cur)
             _lib.call("dnr_head_finalize", p(part_q), p(pk.b_out), NV, min(n_samples, mv_q * per_tile), 4, p(out), st)
@@ -368,9 +378,14 @@ def field_forward(sc: SceneBuffers, pk: PackedMLP, rays: torch.Tensor, z: torch.
                 st2 = _lib.stream_ptr()
                 if timing:
                     ev[2].record(side)
-                _lib.call("dnr_mlp_pair_fwd", p(lat_p), p(code_p), pk.w_ptrs, pk.pair_b_ptrs, p(pk.w_out), NV, n_p,
-                          spare if side is not None else 0, p(part_p), p(PAIR_PROF) if mv_q == 0 else None, st2,
-                          tag="overlapped" if side is not None else None)
+                if pe:
+                    _lib.call("dnr_mlp_pair_fwd_pe", p(lat_p), p(code_p), pk.w_ptrs, pk.zc_ptrs, pk.pair_b_ptrs, p(pk.w_out),
+                              NV, n_p, spare if side is not None else 0, p(part_p), st2,
+                              tag="overlapped" if side is not None else None)
+                else:
+                    _lib.call("dnr_mlp_pair_fwd", p(lat_p), p(code_p), pk.w_ptrs, pk.pair_b_ptrs, p(pk.w_out), NV, n_p,
+                              spare if side is not None else 0, p(part_p), p(PAIR_PROF) if mv_q == 0 else None, st2,
+                              tag="overlapped" if side is not None else None)
                 if timing:
                     ev[3].record(side)
                     state["pending"].append((*ev, mv_q, n_p))

@@ -211,6 +211,17 @@ long long dnr_mlp_quad_scratch_bytes(void);
 int dnr_mlp_quad_fwd(const void* lat_pk, const void* code_pk, const void* const* weights_pk128,
                      const float* const* biases, const float* w_out, int NV, int mv_tiles, void* merge_scratch,
                      float* head_partial, long long* prof /* nullable */, dnr_stream_t stream);
+/* NOVEL_PE field (src/models/novel_pe/pe_novel_pixelnerf.py:263-275: ResnetFC with d_latent = 518): the cluster kernels
+ * with a second K-step on the 64-wide code operand in fc_1 of blocks 0 and 1 -- columns 55..60 of that operand carry the six
+ * positional values (dnr_encode_novel_pe_fwd), code_weights[b] is the [512 x 64] image of [0 (55) | lin_z[b+1].weight[:,
+ * 512:518] | 0 (3)] in the kernel's weight layout (PK256 for pair, PK128 for quad), weights[0] merges lin_in with
+ * lin_z[0]'s positional columns, and lat_pk is the variant's final_latent.  Otherwise as dnr_mlp_pair_fwd / _quad_fwd. */
+int dnr_mlp_pair_fwd_pe(const void* lat_pk, const void* code_pk, const void* const* weights,
+                        const void* const* code_weights, const float* const* biases, const float* w_out, int NV,
+                        int mv_tiles, int max_clusters, float* head_partial, dnr_stream_t stream);
+int dnr_mlp_quad_fwd_pe(const void* lat_pk, const void* code_pk, const void* const* weights_pk128,
+                        const void* const* code_weights_pk128, const float* const* biases, const float* w_out, int NV,
+                        int mv_tiles, void* merge_scratch, float* head_partial, dnr_stream_t stream);
 /* Allocation-free variant of dnr_mlp_quad_fwd.  It has NO COUNTERPART IN THE REFERENCE: it was added
  * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops,
  * harnesses that forbid it).  The merge scratch lives in a file-scope device array of the library (4 MiB = 8 clusters x

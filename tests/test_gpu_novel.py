@@ -530,3 +530,68 @@ def test_candidate_tiling_does_not_change_the_result(NR, neighbours):
             os.environ["DNR_NOVEL_TILE"] = old
     assert torch.equal(got_idx, want_idx) and torch.equal(got_off, want_off)
     assert int(got_idx.unique().numel()) > 50 and int(got_idx.max()) < V
+
+
+@pytest.mark.parametrize("name", ["novel_pe_tiny", "novel_pe_tiny3"])
+def test_novel_pe_cluster_kernels_agree_with_per_layer_path(name):
+    """NOVEL_PE evaluation: the cluster kernels with the second code K-step in fc_1 of blocks 0 / 1 (dnr_mlp_quad_fwd_pe,
+    dnr_mlp_pair_fwd_pe) against the per-layer GEMMs (three K segments, field.PackedPE) on the same operands: pair == quad
+    bit for bit, both within the DINER kernels' mutual tolerance of the per-layer result
+    (test_gpu_field.py::test_inference_kernels_agree), deterministic, and the plain DINER path is not disturbed."""
+    dev = _cuda()
+    from diner_b200 import field as F_
+    from diner_b200.novel import NeRFRendererDGS, _deform, _gen_latent_nhwc, build_vertex_groups
+    from diner_b200.scene import get_scene
+    from tools.synthetic import novel_to_device
+    g, scene, _ = _load(name)
+    wl = scene.workload
+    K = wl.n_samples
+    novel_to_device(scene, dev)
+    m = scene.model
+    keep = (F_.FORWARD_KERNEL, F_.PE_FORWARD_LAYERS)
+    try:
+        sc = get_scene(m)
+        SB, NR = scene.rays.shape[:2]
+        NV = sc.NV
+        rd = scene.rays.to(dev).view(-1, 8)
+        zd = torch.from_numpy(g["z"]).view(-1, K).to(dev)
+        V = scene.target_vertices.shape[1]
+        pin, pgen, _ = _deform(rd, zd, None, None, 0, build_vertex_groups(scene.target_vertices),
+                               scene.tgt_in_offsets.contiguous(), scene.tgt_gen_offsets.contiguous(), SB, NR, K, V, False)
+        gen_nhwc = _gen_latent_nhwc(m)
+        Hg, Wg = gen_nhwc.shape[:2]
+        gsize = torch.tensor([Wg, Hg])
+        gscale = ((gsize - float(m.encoder.feature_padding) * 2) / gsize).float()
+        f = lambda t: t.detach().float().contiguous()
+        gshape = m.gen_image_shape.cpu()
+        novel = dict(poses=f(m.gen_poses), focal=f(m.gen_focal), cxy=f(m.gen_c), latent=gen_nhwc, Hg=Hg, Wg=Wg,
+                     img_w=float(gshape[0]), img_h=float(gshape[1]), sx=float(gscale[0]), sy=float(gscale[1]),
+                     pts_in=pin, pts_gen=pgen, pe=NeRFRendererDGS._pe_inputs(m, SB, NV, f))
+        pk = F_.get_packed_pe(m, need_transposed=False)
+        outs = {}
+        for kern in ("layers", "pair", "quad"):
+            F_.FORWARD_KERNEL, F_.PE_FORWARD_LAYERS = ("quad", True) if kern == "layers" else (kern, False)
+            outs[kern], _ = F_.field_forward(sc, pk, rd, zd, NR, 0, save=False, novel=novel)
+            again, _ = F_.field_forward(sc, pk, rd, zd, NR, 0, save=False, novel=novel)
+            torch.cuda.synchronize()
+            assert torch.isfinite(outs[kern]).all() and torch.equal(outs[kern], again), kern
+        assert torch.equal(outs["quad"], outs["pair"])
+        a, b = outs["pair"], outs["layers"]
+        smax = float(b[:, 3].max())
+        assert smax > 1.0
+        assert float((a[:, :3] - b[:, :3]).abs().max()) < 1.5e-2 and float((a[:, :3] - b[:, :3]).abs().mean()) < 5e-4
+        assert float((a[:, 3] - b[:, 3]).abs().max()) < 1e-2 * smax and float((a[:, 3] - b[:, 3]).abs().mean()) < 5e-4 * smax
+        # the positional columns matter: zeroing the second code K-step's weights moves the result
+        import ctypes as C
+        zero = torch.zeros_like(pk.w_zc128[0])
+        pk_zero = (C.c_void_p * 2)(zero.data_ptr(), zero.data_ptr())
+        real, pk.zc128_ptrs = pk.zc128_ptrs, pk_zero
+        try:
+            F_.FORWARD_KERNEL, F_.PE_FORWARD_LAYERS = "quad", False
+            moved, _ = F_.field_forward(sc, pk, rd, zd, NR, 0, save=False, novel=novel)
+        finally:
+            pk.zc128_ptrs = real
+        assert float((moved - outs["quad"]).abs().max()) > 1e-3
+    finally:
+        F_.FORWARD_KERNEL, F_.PE_FORWARD_LAYERS = keep
+        novel_to_device(scene, "cpu")
