@@ -241,7 +241,7 @@ __device__ __forceinline__ float blend4_lo(uint32_t a, uint32_t b, uint32_t c, u
 // taps leave as two operand images (a linear layer sits between them), and the six positional values of the row take the
 // first six padding columns (55..60) of the geometric code.
 template <bool SPLIT, bool NOVEL, bool PE = false>
-__global__ void __launch_bounds__(kEncWarps * 32, (SPLIT || NOVEL) ? 1 : 5) encode_fwd_kernel(EncodeParams P, const __nv_bfloat16* latent_lo,
+__global__ void __launch_bounds__(kEncWarps * 32, (SPLIT || PE) ? 1 : (NOVEL ? 4 : 5)) encode_fwd_kernel(EncodeParams P, const __nv_bfloat16* latent_lo,
                                                                     unsigned char* lat_pk_lo, unsigned char* in_pk_lo) {
   extern __shared__ __align__(16) unsigned char enc_smem[];
   unsigned char* sl = enc_smem;                                   // [64][kLatChunkStride]
