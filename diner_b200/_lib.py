@@ -11,7 +11,7 @@ import os
 from . import _build
 
 _lib = None
-ABI_VERSION = 18
+ABI_VERSION = 19
 
 # instrumentation used by bench.py: number of kernel launches issued through the ABI, and (when `profile` is a
 # list) one (name, start_event, end_event, tag) record per call for per-kernel CUDA-event timing
@@ -87,6 +87,7 @@ _SIGNATURES = {
     "dnr_render_workspace_bytes": (c_ll, [c_i, c_ll, c_i, c_ll]),
     "dnr_render_fwd": (c_i, [c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_ull, c_p, c_i, c_ll, c_p, c_ll, c_p, c_p, c_p, c_p, c_p,
                              c_p]),
+    "dnr_render_timings": (c_i, [c_p, c_p, c_p]),
     "dnr_pack_rows": (c_i, [c_p, c_ll, c_i, c_ll, c_p, c_p]),
     "dnr_unpack_rows": (c_i, [c_p, c_ll, c_i, c_p, c_p]),
     "dnr_xr_to_rows": (c_i, [c_p, c_ll, c_i, c_p, c_p]),

@@ -25,4 +25,4 @@ DeviceInfo* device_info() {
 }  // namespace dnr
 
 DNR_EXPORT const char* dnr_last_error() { return dnr::g_last_error; }
-DNR_EXPORT int dnr_abi_version() { return 18; }
+DNR_EXPORT int dnr_abi_version() { return 19; }

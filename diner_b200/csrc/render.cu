@@ -16,7 +16,7 @@
 namespace dnr {
 
 constexpr int kRenderDevices = 64;
-constexpr int kPending = 8;
+constexpr int kPending = 128;     // timing records in flight (a host that runs many frames ahead of the GPU fills them)
 
 // throughput of one 2-CTA cluster relative to one 4-CTA cluster by view count (measured on the BASELINE.json shapes,
 // diner_b200/field.py PAIR_RATE); the split adapts from there
@@ -34,6 +34,8 @@ struct RenderState {
   bool ready;
   float rate[5];              // per view count
   SplitTiming pending[kPending];
+  double quad_ms, pair_ms;    // cumulative device time of the timed 4-CTA / 2-CTA cluster launches (dnr_render_timings)
+  long long n_timed;
 };
 static RenderState g_render[kRenderDevices];      // zero-initialised
 
@@ -57,18 +59,21 @@ static RenderState* render_state() {
   return s;
 }
 
-// fold completed (quad, pair) timings into the pair rate (field.py::_update_split)
-static void update_split(RenderState* s, int NV, int spare, int n_quad) {
+// fold completed (quad, pair) timings into the running totals and, with `adapt`, into the pair rate
+// (field.py::_update_split)
+static void update_split(RenderState* s, int NV, int spare, int n_quad, bool adapt) {
   for (int i = 0; i < kPending; ++i) {
     SplitTiming& t = s->pending[i];
     if (!t.used) continue;
     if (cudaEventQuery(t.q1) != cudaSuccess || cudaEventQuery(t.p1) != cudaSuccess) { (void)cudaGetLastError(); continue; }
     float tq = 0.f, tp = 0.f;
-    if (cudaEventElapsedTime(&tq, t.q0, t.q1) == cudaSuccess && cudaEventElapsedTime(&tp, t.p0, t.p1) == cudaSuccess &&
-        tq > 0.05f && tp > 0.05f && spare > 0) {
-      float measured = ((float)t.tiles_p / tp / (float)spare) / ((float)t.tiles_q / tq / (float)n_quad);
-      measured = fminf(fmaxf(measured, 0.15f), 0.6f);
-      s->rate[NV] += (0.97f * measured - s->rate[NV]) / 3.0f;      // a third of the way, aim 3 % low
+    if (cudaEventElapsedTime(&tq, t.q0, t.q1) == cudaSuccess && cudaEventElapsedTime(&tp, t.p0, t.p1) == cudaSuccess) {
+      s->quad_ms += tq; s->pair_ms += tp; ++s->n_timed;
+      if (adapt && tq > 0.05f && tp > 0.05f && spare > 0 && n_quad > 0) {
+        float measured = ((float)t.tiles_p / tp / (float)spare) / ((float)t.tiles_q / tq / (float)n_quad);
+        measured = fminf(fmaxf(measured, 0.15f), 0.6f);
+        s->rate[NV] += (0.97f * measured - s->rate[NV]) / 3.0f;    // a third of the way, aim 3 % low
+      }
     }
     (void)cudaGetLastError();
     t.used = false;
@@ -173,8 +178,8 @@ DNR_EXPORT int dnr_render_fwd(const dnr_scene_desc* sc, const dnr_mlp_desc* mlp,
                         sc->img_h, sc->lat_sx, sc->lat_sy, lat, code, stream_);
     if (rc) return rc;
     ++launches;
-    if (adapt) dnr::update_split(st, NV, spare, n_quad);
-    else st->rate[NV] = dnr::kPairRate[NV];
+    dnr::update_split(st, NV, spare, n_quad, adapt);
+    if (!adapt) st->rate[NV] = dnr::kPairRate[NV];
     const float r = st->rate[NV];
     const float share = spare > 0 ? r * spare / (r * spare + n_quad) : 0.f;
     int mv_q = mv;
@@ -190,9 +195,8 @@ DNR_EXPORT int dnr_render_fwd(const dnr_scene_desc* sc, const dnr_mlp_desc* mlp,
     if (n_p > 0 && mv_q > 0) {                                // fork: the pair clusters run beside the quad clusters
       DNR_CHECK(cudaEventRecord(st->fork, stream), "dnr_render_fwd/fork");
       DNR_CHECK(cudaStreamWaitEvent(st->side, st->fork, 0), "dnr_render_fwd/fork");
-      if (adapt)
-        for (int i = 0; i < dnr::kPending; ++i)
-          if (!st->pending[i].used) { tm = &st->pending[i]; break; }
+      for (int i = 0; i < dnr::kPending; ++i)                   // (a free slot: the two kernels of this chunk are timed)
+        if (!st->pending[i].used) { tm = &st->pending[i]; break; }
     }
     if (mv_q > 0) {
       if (tm) DNR_CHECK(cudaEventRecord(tm->q0, stream), "dnr_render_fwd/timing");
@@ -234,5 +238,19 @@ DNR_EXPORT int dnr_render_fwd(const dnr_scene_desc* sc, const dnr_mlp_desc* mlp,
   if (rc) return rc;
   ++launches;
   if (info) { info[0] = launches; info[1] = (int)n_chunks; info[2] = last_q; info[3] = last_p; info[4] = last_q + last_p; }
+  return 0;
+}
+
+// Cumulative device time (ms, CUDA events on the launching streams) of the 4-CTA / 2-CTA cluster MLP launches that
+// dnr_render_fwd has issued and timed on the current device since the library was loaded, and their number (pairs of
+// launches).  Records still in flight are not included: synchronise first.  For benchmarks: the kernel's duration inside
+// a timed region without a second, instrumented pass.
+DNR_EXPORT int dnr_render_timings(double* quad_ms, double* pair_ms, long long* n_timed) {
+  dnr::RenderState* st = dnr::render_state();
+  DNR_REQUIRE(st != nullptr, "dnr_render_timings: no current CUDA device");
+  dnr::update_split(st, 0, 0, 0, false);
+  if (quad_ms) *quad_ms = st->quad_ms;
+  if (pair_ms) *pair_ms = st->pair_ms;
+  if (n_timed) *n_timed = st->n_timed;
   return 0;
 }

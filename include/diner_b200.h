@@ -327,6 +327,11 @@ int dnr_render_fwd(const dnr_scene_desc* scene, const dnr_mlp_desc* mlp, const f
                    void* workspace, long long workspace_bytes, float* rgb, float* depth, float* weights_out, float* z_out,
                    int* info, dnr_stream_t stream);
 
+/* Cumulative device time (ms) of the 4-CTA / 2-CTA cluster MLP launches dnr_render_fwd has issued and timed (CUDA events
+ * on the launching streams) on the current device since the library was loaded, and the number of timed launch pairs;
+ * launches still in flight are not included (synchronise first).  HOST pointers, nullable. */
+int dnr_render_timings(double* quad_ms, double* pair_ms, long long* n_timed);
+
 /* ---- input producers next to the path ---------------------------------------------------- */
 
 /* Pixel-centre rays of B target cameras: rays [B,H,W,8] = [origin 3 | unit direction 3 | near | far] from world->cam
