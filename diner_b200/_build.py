@@ -30,6 +30,8 @@ SOURCES = [
 ]
 COMMON = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
           "-Xcompiler", "-fPIC,-fvisibility=hidden", "--expt-relaxed-constexpr"]
+if os.environ.get("DNR_CLUSTER_PROF", "0") == "1":      # profiling build: cycle counters in the cluster MLP kernels
+    COMMON.append("-DDNR_CLUSTER_PROF=1")               # (tools/pair_prof.py; part of the source hash, so toggling rebuilds)
 
 
 def _nvcc() -> str:

@@ -24,6 +24,19 @@
 #include <stdlib.h>
 #include <string.h>
 
+// in-kernel cycle counters (tools/pair_prof.py): compiled in only with -DDNR_CLUSTER_PROF=1 (DNR_CLUSTER_PROF=1 in the
+// environment of diner_b200._build); a production build reads no clocks
+#ifndef DNR_CLUSTER_PROF
+#define DNR_CLUSTER_PROF 0
+#endif
+#if DNR_CLUSTER_PROF
+#define TIMED(acc, stmt) { long long t__ = clock64(); stmt; acc += clock64() - t__; }
+#define PROF_CLOCK() clock64()
+#else
+#define TIMED(acc, stmt) { stmt; }
+#define PROF_CLOCK() 0LL
+#endif
+
 namespace dnr {
 
 constexpr int kPThreads = 384;
@@ -259,8 +272,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
       int titer = 0;
       POp d;
       const uint32_t abuf0 = tc::smem_u32(abuf);
-      long long w_ring = 0, w_own = 0, w_peer = 0, t_start = clock64();
-#define TIMED(acc, stmt) { long long t__ = clock64(); stmt; acc += clock64() - t__; }
+      long long w_ring = 0, w_own = 0, w_peer = 0, t_start = PROF_CLOCK();
+
       for (int tile = cluster; tile < P.mv_tiles; tile += n_clusters, ++titer) {
         const uint32_t x_col = (titer & 1) ? 256u : 0u;           // X / T swap regions every tile
         for (int o = 0; o < kPOps; ++o, ++opc) {
@@ -314,7 +327,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
       }
       if (P.prof) {
         long long* pr = P.prof + (size_t)blockIdx.x * 16;
-        pr[0] = clock64() - t_start; pr[1] = w_ring; pr[2] = w_own; pr[3] = w_peer;
+        pr[0] = PROF_CLOCK() - t_start; pr[1] = w_ring; pr[2] = w_own; pr[3] = w_peer;
       }
     }
   } else if (warp == 2) {
@@ -359,7 +372,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
     const int row = quad * 32 + lane;
     const bool leader = (warp == 4 && lane == 0);
     int opc = 0, xops = 0, titer = 0;
-    long long w_acc = 0, w_fence = 0, w_sig = 0, w_push = 0, t_epi0 = clock64();
+    long long w_acc = 0, w_fence = 0, w_sig = 0, w_push = 0, t_epi0 = PROF_CLOCK();
     long long w_kind[4] = {0, 0, 0, 0};
     POp d;
     for (int tile = cluster; tile < P.mv_tiles; tile += n_clusters, ++titer) {
@@ -373,7 +386,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
         // the previous operand has left my half of the A buffer (pusher's bulk stores have read it)
         if (d.epi != EPI_HEAD && xops > 0) TIMED(w_push, tc::mbar_wait(pushed, (uint32_t)((xops - 1) & 1)));
         float hp0 = 0.f, hp1 = 0.f, hp2 = 0.f, hp3 = 0.f;
-        const long long tl0 = clock64();
+        const long long tl0 = PROF_CLOCK();
 #pragma unroll 1
         for (int st = 0; st < 4; ++st) {                       // four 32-column pieces; the two halves share K-block st
           uint32_t acc[32];
@@ -399,15 +412,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
             else pair_act_stage<NV, false>(acc, bq, bias, lane, dst_s, t0 + nl0);
             // my part of K-block (half*2 + st) is in shared memory: order it before the MMAs (async proxy) and
             // before the pusher's bulk copy, then one arrival per warp
-            const long long t__ = clock64();
+            const long long t__ = PROF_CLOCK();
             tc::fence_before_sync();
             tc::fence_proxy_async();            // generic smem writes -> async proxy (MMA reads, pusher's bulk store)
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(a_own + st);
-            w_sig += clock64() - t__;
+            w_sig += PROF_CLOCK() - t__;
           }
         }
-        w_kind[d.epi] += clock64() - tl0;
+        w_kind[d.epi] += PROF_CLOCK() - tl0;
         if (d.epi == EPI_HEAD) {
           tc::fence_before_sync();
           // combine the two column halves of the CTA, then one float4 of partial sums per row
@@ -425,7 +438,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
     }
     if (leader && P.prof) {
       long long* pr = P.prof + (size_t)blockIdx.x * 16;
-      pr[4] = clock64() - t_epi0; pr[5] = w_acc; pr[6] = w_fence; pr[7] = w_sig; pr[12] = w_push;
+      pr[4] = PROF_CLOCK() - t_epi0; pr[5] = w_acc; pr[6] = w_fence; pr[7] = w_sig; pr[12] = w_push;
       pr[8] = w_kind[0]; pr[9] = w_kind[1]; pr[10] = w_kind[2]; pr[11] = w_kind[3];
     }
   }
@@ -573,7 +586,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
       int opc = 0, aops = 0, titer = 0;
       POp d;
       const uint32_t abuf0 = tc::smem_u32(abuf);
-      long long w_ring = 0, w_own = 0, w_peer = 0, w_pfull = 0, w_ring_lat = 0, w_pfull_lat = 0, t_start = clock64();
+      long long w_ring = 0, w_own = 0, w_peer = 0, w_pfull = 0, w_ring_lat = 0, w_pfull_lat = 0, t_start = PROF_CLOCK();
       for (int q = cluster; q < n_pairs; q += n_clusters, ++titer) {
         const uint32_t x_col = (titer & 1) ? 256u : 0u;           // X / T swap regions every tile
         const int n_ops = quad_last<NV, MERGE>(titer, q, n_clusters, n_pairs) ? kPOps : 7;
@@ -633,7 +646,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
       }
       if (P.prof) {
         long long* pr = P.prof + (size_t)blockIdx.x * 16;
-        pr[0] = clock64() - t_start; pr[1] = w_ring; pr[2] = w_own; pr[3] = w_peer; pr[13] = w_pfull;
+        pr[0] = PROF_CLOCK() - t_start; pr[1] = w_ring; pr[2] = w_own; pr[3] = w_peer; pr[13] = w_pfull;
         pr[14] = w_ring_lat; pr[15] = w_pfull_lat;
       }
     } else if (lane == 0) {
@@ -728,7 +741,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
     float* park = MERGE ? P.merge_scratch + (size_t)blockIdx.x * (128 * 256) : nullptr;     // [NV*U <= 128][256] fp32
     const uint64_t pol_keep = tc::policy_evict_last();
     int opc = 0, xops = 0, titer = 0;
-    long long w_acc = 0, w_merge = 0, t_epi0 = clock64();
+    long long w_acc = 0, w_merge = 0, t_epi0 = PROF_CLOCK();
     long long w_kind[4] = {0, 0, 0, 0};
     POp d;
     auto signal_kblock = [&](int st) {               // my part of own K-block st is in shared memory
@@ -752,7 +765,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
         TIMED(w_acc, tc::mbar_wait(accf + (opc & 1), (uint32_t)((opc >> 1) & 1)));
         tc::fence_after_sync();
         const uint32_t t0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (d.acc_x ? x_col : (256u - x_col));
-        const long long tl0 = clock64();
+        const long long tl0 = PROF_CLOCK();
         if (MERGE && o == 6) {
           // ---- park: mean over the view rows (resnetfc.py:9-14,148-151); the first row of every sample stores it
           const bool first_view = (lane % NV == 0) && (lane / NV < SPWc);
@@ -785,9 +798,9 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
                 tc::st_hint_v4(dst + (size_t)g * 128, acc[4 * g], acc[4 * g + 1], acc[4 * g + 2], acc[4 * g + 3], pol_keep);
             }
           }
-          w_kind[EPI_MEAN] += clock64() - tl0;
+          w_kind[EPI_MEAN] += PROF_CLOCK() - tl0;
           if (!last) continue;
-          const long long tm0 = clock64();
+          const long long tm0 = PROF_CLOCK();
           bar_sync_epi();                  // the parked rows of the whole group are visible to all epilogue threads
           // ---- merge: thread = row m of the merged tile = pooled row (m % U) of the group's tile (m / U)
           const int i_src = row / U, j_src = row % U;
@@ -819,7 +832,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
             tc::tmem_st_wait();
             signal_kblock(st);
           }
-          w_merge += clock64() - tm0;
+          w_merge += PROF_CLOCK() - tm0;
           ++xops;
           continue;
         }
@@ -852,7 +865,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
             signal_kblock(st);
           }
         }
-        w_kind[d.epi] += clock64() - tl0;
+        w_kind[d.epi] += PROF_CLOCK() - tl0;
         if (d.epi == EPI_HEAD) {
           tc::fence_before_sync();
           // the two column groups of a row are summed by head_finalize (4 partials per row and tile)
@@ -875,7 +888,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
     }
     if (leader && P.prof) {
       long long* pr = P.prof + (size_t)blockIdx.x * 16;
-      pr[4] = clock64() - t_epi0; pr[5] = w_acc; pr[12] = w_merge;
+      pr[4] = PROF_CLOCK() - t_epi0; pr[5] = w_acc; pr[12] = w_merge;
       pr[8] = w_kind[0]; pr[9] = w_kind[1]; pr[10] = w_kind[2]; pr[11] = w_kind[3];
     }
   }

@@ -1,5 +1,14 @@
-"""Cycle-counter breakdown of the CTA-pair MLP kernel (development tool)."""
+"""Cycle-counter breakdown of the cluster MLP kernels (development tool).
+
+The counters are compiled in only in a profiling build of the library:
+
+    DNR_CLUSTER_PROF=1 python tools/pair_prof.py        # rebuilds diner_b200/libdiner_b200.so with -DDNR_CLUSTER_PROF=1
+
+(the production build reads no clocks; the next import without the variable rebuilds it).
+"""
 import os, sys
+if os.environ.get("DNR_CLUSTER_PROF", "0") != "1":
+    sys.exit("set DNR_CLUSTER_PROF=1: the cycle counters are not part of the production build")
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from diner_b200 import NeRFRendererDGS, field as F_
