@@ -579,7 +579,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && t == 0) {
+    if (t == 0) {              // the whole warp runs the loop (warp-uniform operands); one elected lane issues
       // ================= MMA issuer for the CTA pair =================
       constexpr uint32_t idesc = tc::make_idesc_bf16(256, 256, 0, 0);
       int slot = 0; uint32_t phase = 0;
@@ -605,14 +605,16 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
             if (++slot == kQRing) { slot = 0; phase ^= 1; }
             tc::fence_after_sync();
             const uint32_t a0 = tc::smem_u32(ring + (size_t)sa * kQSlot), b0 = tc::smem_u32(ring + (size_t)sb * kQSlot);
+            if (tc::elect_one()) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              tc::mma_bf16_2cta(d_tmem, tc::make_smem_desc(a0 + j * 4096, 2048, 128),
-                                tc::make_smem_desc(b0 + j * 4096, 2048, 128), idesc, accumulate);
-              accumulate = 1;
+              for (int j = 0; j < 4; ++j)
+                tc::mma_bf16_2cta(d_tmem, tc::make_smem_desc(a0 + j * 4096, 2048, 128),
+                                  tc::make_smem_desc(b0 + j * 4096, 2048, 128), idesc, j == 0 ? accumulate : 1u);
+              tc::mma_commit_2cta_mc(empty + sa, pair_mask);
+              tc::mma_commit_2cta_mc(empty + sb, pair_mask);
             }
-            tc::mma_commit_2cta_mc(empty + sa, pair_mask);
-            tc::mma_commit_2cta_mc(empty + sb, pair_mask);
+            __syncwarp();
+            accumulate = 1;
           };
           if (d.code) step_ring_ab();
           if (d.lat_w)
@@ -630,21 +632,24 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
               if (!P.tma2) TIMED(w_pfull, tc::mbar_wait(peer_full + slot, phase));
               tc::fence_after_sync();
               const uint32_t a0 = abuf0 + (uint32_t)kb * 16384u, b0 = tc::smem_u32(ring + (size_t)slot * kQSlot);
+              if (tc::elect_one()) {
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                tc::mma_bf16_2cta(d_tmem, tc::make_smem_desc(a0 + j * 4096, 2048, 128),
-                                  tc::make_smem_desc(b0 + j * 4096, 2048, 128), idesc, accumulate);
-                accumulate = 1;
+                for (int j = 0; j < 4; ++j)
+                  tc::mma_bf16_2cta(d_tmem, tc::make_smem_desc(a0 + j * 4096, 2048, 128),
+                                    tc::make_smem_desc(b0 + j * 4096, 2048, 128), idesc, j == 0 ? accumulate : 1u);
+                tc::mma_commit_2cta_mc(empty + slot, pair_mask);
               }
-              tc::mma_commit_2cta_mc(empty + slot, pair_mask);
+              __syncwarp();
+              accumulate = 1;
               if (++slot == kQRing) { slot = 0; phase ^= 1; }
             }
             ++aops;
           }
-          tc::mma_commit_2cta_mc(accf + (opc & 1), pair_mask);
+          if (tc::elect_one()) tc::mma_commit_2cta_mc(accf + (opc & 1), pair_mask);
+          __syncwarp();
         }
       }
-      if (P.prof) {
+      if (P.prof && lane == 0) {
         long long* pr = P.prof + (size_t)blockIdx.x * 16;
         pr[0] = PROF_CLOCK() - t_start; pr[1] = w_ring; pr[2] = w_own; pr[3] = w_peer; pr[13] = w_pfull;
         pr[14] = w_ring_lat; pr[15] = w_pfull_lat;

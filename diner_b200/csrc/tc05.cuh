@@ -156,6 +156,19 @@ __device__ __forceinline__ void tmem_alloc_2cta(uint32_t* smem_result, uint32_t 
 __device__ __forceinline__ void tmem_dealloc_2cta(uint32_t taddr, uint32_t ncols) {
   asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
 }
+// One lane of the (converged) warp: the issue path of tcgen05.mma / commit.  With the WHOLE warp running the surrounding
+// loop, every operand is warp-uniform and lives in uniform registers; a loop entered by lane 0 alone makes ptxas move each
+// operand into a uniform register behind an ELECT / R2UR.BROADCAST waterfall in front of every UTCHMMA (~20 instructions).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void mma_bf16_2cta(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
                                               uint32_t accumulate) {
   asm volatile(
