@@ -216,7 +216,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) mlp_gemm_kernel(const GemmPar
 
   if (warp == 0) {
     // ================= producer: bulk copies of packed operand K-blocks =================
-    if (lane == 0) {
+    {     // the whole warp runs the loop (warp-uniform operands -> uniform registers); one elected lane issues the copies
       int stage = 0; uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int m_tile = tile / n_tiles_n, n_tile = tile % n_tiles_n;
@@ -226,9 +226,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) mlp_gemm_kernel(const GemmPar
           const unsigned char* b = P.seg[sg].B + (size_t)n_tile * (K / 8) * 4096;
           for (int kb = 0; kb < K / kBK; ++kb) {
             tc::mbar_wait(empty + stage, phase ^ 1);
-            tc::mbar_arrive_expect_tx(full + stage, kAStage + kBStage);
-            tc::bulk_g2s(sA + (size_t)stage * kAStage, a + (size_t)kb * kAStage, kAStage, full + stage);
-            tc::bulk_g2s(sB + (size_t)stage * kBStage, b + (size_t)kb * kBStage, kBStage, full + stage);
+            if (tc::elect_one()) {
+              tc::mbar_arrive_expect_tx(full + stage, kAStage + kBStage);
+              tc::bulk_g2s(sA + (size_t)stage * kAStage, a + (size_t)kb * kAStage, kAStage, full + stage);
+              tc::bulk_g2s(sB + (size_t)stage * kBStage, b + (size_t)kb * kBStage, kBStage, full + stage);
+            }
+            __syncwarp();
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
         }
@@ -236,7 +239,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) mlp_gemm_kernel(const GemmPar
     }
   } else if (warp == 1) {
     // ================= MMA issuer =================
-    if (lane == 0) {
+    {     // whole warp, one elected lane issues (see tc::elect_one)
       constexpr uint32_t idesc = tc::make_idesc_bf16(kBM, kBN, 0, 0);
       int stage = 0; uint32_t phase = 0;
       int it = 0;
@@ -252,19 +255,23 @@ __global__ void __launch_bounds__(kGemmThreads, 1) mlp_gemm_kernel(const GemmPar
             tc::fence_after_sync();
             const uint32_t a0 = tc::smem_u32(sA + (size_t)stage * kAStage);
             const uint32_t b0 = tc::smem_u32(sB + (size_t)stage * kBStage);
+            if (tc::elect_one()) {
 #pragma unroll
-            for (int j = 0; j < kBK / 16; ++j) {
-              // K-major: one MMA consumes two 8-element K chunks (A: 2 KB apart, B: 4 KB apart)
-              const uint64_t ad = tc::make_smem_desc(a0 + j * 2 * 2048, 2048, 128);
-              const uint64_t bd = tc::make_smem_desc(b0 + j * 2 * 4096, 4096, 128);
-              tc::mma_bf16(d_tmem, ad, bd, idesc, accumulate);
-              accumulate = 1;
+              for (int j = 0; j < kBK / 16; ++j) {
+                // K-major: one MMA consumes two 8-element K chunks (A: 2 KB apart, B: 4 KB apart)
+                const uint64_t ad = tc::make_smem_desc(a0 + j * 2 * 2048, 2048, 128);
+                const uint64_t bd = tc::make_smem_desc(b0 + j * 2 * 4096, 4096, 128);
+                tc::mma_bf16(d_tmem, ad, bd, idesc, j == 0 ? accumulate : 1u);
+              }
+              tc::mma_commit(empty + stage);
             }
-            tc::mma_commit(empty + stage);
+            __syncwarp();
+            accumulate = 1;
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
         }
-        tc::mma_commit(tfull + buf);
+        if (tc::elect_one()) tc::mma_commit(tfull + buf);
+        __syncwarp();
       }
     }
   } else {

@@ -224,20 +224,23 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
 
   if (warp == 0) {
     // ================= ring producer =================
-    if (lane == 0) {
+    {     // whole warp (warp-uniform operands -> uniform registers), one elected lane issues the copies
       const uint64_t pol_keep = tc::policy_evict_last(), pol_stream = tc::policy_evict_first();
       const uint64_t pol_norm = tc::policy_evict_normal();
       int slot = 0; uint32_t phase = 0;
       auto fill = [&](const unsigned char* src, uint32_t bytes, uint64_t pol) {
         tc::mbar_wait(empty + slot, phase ^ 1);
-        tc::mbar_arrive_expect_tx(full + slot, bytes);
-        tc::bulk_g2s_hint(ring + (size_t)slot * kPSlot, src, bytes, full + slot, pol);
+        if (tc::elect_one()) {
+          tc::mbar_arrive_expect_tx(full + slot, bytes);
+          tc::bulk_g2s_hint(ring + (size_t)slot * kPSlot, src, bytes, full + slot, pol);
+        }
+        __syncwarp();
         if (++slot == kPRing) { slot = 0; phase ^= 1; }
       };
       POp d;
       for (int tile = cluster; tile < P.mv_tiles; tile += n_clusters) {
         const unsigned char* lat = P.lat_pk + (size_t)tile * 131072;
-        if (tile + n_clusters < P.mv_tiles) {     // pull the next tile's inputs from HBM into L2 while this one computes
+        if (tile + n_clusters < P.mv_tiles && lane == 0) {     // pull the next tile's inputs from HBM into L2 while this one computes
           tc::bulk_prefetch_l2(P.lat_pk + (size_t)(tile + n_clusters) * 131072, 131072);
           tc::bulk_prefetch_l2(P.code_pk + (size_t)(tile + n_clusters) * 16384, 16384);
         }
@@ -264,7 +267,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
     }
   } else if (warp == 1) {
     // ================= MMA issuer =================
-    if (lane == 0) {
+    {     // whole warp (warp-uniform operands -> uniform registers), one elected lane issues
       constexpr uint32_t idesc = tc::make_idesc_bf16(128, 256, 0, 0);
       int slot = 0; uint32_t phase = 0;
       int opc = 0;                           // ops issued (all kinds)
@@ -289,14 +292,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
             if (++slot == kPRing) { slot = 0; phase ^= 1; }
             tc::fence_after_sync();
             const uint32_t a0 = tc::smem_u32(ring + (size_t)sa * kPSlot), b0 = tc::smem_u32(ring + (size_t)sb * kPSlot);
+            if (tc::elect_one()) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              tc::mma_bf16(d_tmem, tc::make_smem_desc(a0 + j * 4096, 2048, 128), tc::make_smem_desc(b0 + j * 8192, 4096, 128),
-                           idesc, accumulate);
-              accumulate = 1;
+              for (int j = 0; j < 4; ++j)
+                tc::mma_bf16(d_tmem, tc::make_smem_desc(a0 + j * 4096, 2048, 128), tc::make_smem_desc(b0 + j * 8192, 4096, 128),
+                             idesc, j == 0 ? accumulate : 1u);
+              tc::mma_commit(empty + sa);
+              tc::mma_commit(empty + sb);
             }
-            tc::mma_commit(empty + sa);
-            tc::mma_commit(empty + sb);
+            __syncwarp();
+            accumulate = 1;
           };
           if (d.code) step_ring_ab();
           if (d.lat_w)
@@ -311,21 +316,24 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
               TIMED(w_ring, tc::mbar_wait(full + slot, phase));
               tc::fence_after_sync();
               const uint32_t a0 = abuf0 + (uint32_t)kb * 16384u, b0 = tc::smem_u32(ring + (size_t)slot * kPSlot);
+              if (tc::elect_one()) {
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                tc::mma_bf16(d_tmem, tc::make_smem_desc(a0 + j * 4096, 2048, 128),
-                             tc::make_smem_desc(b0 + j * 8192, 4096, 128), idesc, accumulate);
-                accumulate = 1;
+                for (int j = 0; j < 4; ++j)
+                  tc::mma_bf16(d_tmem, tc::make_smem_desc(a0 + j * 4096, 2048, 128),
+                               tc::make_smem_desc(b0 + j * 8192, 4096, 128), idesc, j == 0 ? accumulate : 1u);
+                tc::mma_commit(empty + slot);
               }
-              tc::mma_commit(empty + slot);
+              __syncwarp();
+              accumulate = 1;
               if (++slot == kPRing) { slot = 0; phase ^= 1; }
             }
             ++aops;
           }
-          tc::mma_commit(accf + (opc & 1));
+          if (tc::elect_one()) tc::mma_commit(accf + (opc & 1));
+          __syncwarp();
         }
       }
-      if (P.prof) {
+      if (P.prof && lane == 0) {
         long long* pr = P.prof + (size_t)blockIdx.x * 16;
         pr[0] = PROF_CLOCK() - t_start; pr[1] = w_ring; pr[2] = w_own; pr[3] = w_peer;
       }
@@ -517,7 +525,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
 
   if (warp == 0) {
     // ================= ring producer (every CTA: its half of the weights, its tile's streamed operands) =============
-    if (lane == 0) {
+    {     // the whole warp runs the loop (warp-uniform operands -> uniform registers); one elected lane issues the copies
       const uint64_t pol_keep = tc::policy_evict_last(), pol_stream = tc::policy_evict_first();
       const uint64_t pol_norm = tc::policy_evict_normal();
       int slot = 0; uint32_t phase = 0;
@@ -527,13 +535,16 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
       const uint32_t even_rank = cr & ~1u;
       auto fill = [&](const unsigned char* src, uint64_t pol, const CUtensorMap* map, int row0) {
         tc::mbar_wait(empty + slot, phase ^ 1);
-        if (P.tma2) {
-          if (t == 0) tc::mbar_arrive_expect_tx(full + slot, 2 * kQSlot);
-          tc::tma_load_2d_2cta(ring + (size_t)slot * kQSlot, map, 0, row0, tc::cluster_addr(full + slot, even_rank), pol);
-        } else {
-          tc::mbar_arrive_expect_tx(full + slot, kQSlot);
-          tc::bulk_g2s_hint(ring + (size_t)slot * kQSlot, src, kQSlot, full + slot, pol);
+        if (tc::elect_one()) {
+          if (P.tma2) {
+            if (t == 0) tc::mbar_arrive_expect_tx(full + slot, 2 * kQSlot);
+            tc::tma_load_2d_2cta(ring + (size_t)slot * kQSlot, map, 0, row0, tc::cluster_addr(full + slot, even_rank), pol);
+          } else {
+            tc::mbar_arrive_expect_tx(full + slot, kQSlot);
+            tc::bulk_g2s_hint(ring + (size_t)slot * kQSlot, src, kQSlot, full + slot, pol);
+          }
         }
+        __syncwarp();
         if (++slot == kQRing) { slot = 0; phase ^= 1; }
       };
       auto w_map = [&](const unsigned char* w) -> const CUtensorMap* {      // the tensor map of a weight image
@@ -550,7 +561,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
         const int n_ops = quad_last<NV, MERGE>(it, q, n_clusters, n_pairs) ? kPOps : 7;
         const int tile = tile_of(q);
         const unsigned char* lat = P.lat_pk + (size_t)tile * 131072;
-        if (q + n_clusters < n_pairs) {           // pull the next tile's inputs from HBM into L2 while this one computes
+        if (q + n_clusters < n_pairs && lane == 0) {     // pull the next tile's inputs from HBM into L2 while this one computes
           const int nt = tile_of(q + n_clusters);
           tc::bulk_prefetch_l2(P.lat_pk + (size_t)nt * 131072, 131072);
           tc::bulk_prefetch_l2(P.code_pk + (size_t)nt * 16384, 16384);

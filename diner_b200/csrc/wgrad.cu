@@ -69,25 +69,28 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const WgradPar
     return;
   }
 
+  // producer and MMA issuer: the whole warp runs the loop (warp-uniform operands -> uniform registers), one elected lane
+  // issues (tc::elect_one)
   if (warp == 0) {
-    if (lane == 0) {
+    {
       int stage = 0; uint32_t phase = 0;
       for (int rt = rt0; rt < rt1; ++rt) {
         tc::mbar_wait(empty + stage, phase ^ 1);
-        tc::mbar_arrive_expect_tx(full + stage, kWgAStage + b_stage);
-        tc::bulk_g2s(sA + (size_t)stage * kWgAStage, P.dY + ((size_t)rt * (P.Fy / 8) + (size_t)n_tile * 16) * 2048,
-                     kWgAStage, full + stage);
-        {
+        if (tc::elect_one()) {
+          tc::mbar_arrive_expect_tx(full + stage, kWgAStage + b_stage);
+          tc::bulk_g2s(sA + (size_t)stage * kWgAStage, P.dY + ((size_t)rt * (P.Fy / 8) + (size_t)n_tile * 16) * 2048,
+                       kWgAStage, full + stage);
           const unsigned char* xsrc = P.X + ((size_t)rt * (P.Fx / 8) + (size_t)k_tile * (P.NB / 8)) * 2048;
           const int piece = P.copy_piece;
           for (int off = 0; off < b_stage; off += piece)
             tc::bulk_g2s(sB + (size_t)stage * b_stage + off, xsrc + off, piece, full + stage);
         }
+        __syncwarp();
         if (++stage == kWgStages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {
       const uint32_t idesc = tc::make_idesc_bf16(128, P.NB, 1, 1);
       const uint32_t idesc_ones = tc::make_idesc_bf16(128, 16, 1, 1);
       const uint32_t ones0 = tc::smem_u32(sOnes);
@@ -98,22 +101,26 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(const WgradPar
         tc::fence_after_sync();
         const uint32_t a0 = tc::smem_u32(sA + (size_t)stage * kWgAStage);
         const uint32_t b0 = tc::smem_u32(sB + (size_t)stage * b_stage);
+        if (tc::elect_one()) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          // MN-major: 16 batch rows per MMA = two 8-row groups 128 B apart; feature groups 2 KB apart
-          const uint64_t ad = tc::make_smem_desc(a0 + j * 256, 128, 2048);
-          const uint64_t bd = tc::make_smem_desc(b0 + j * 256, 128, 2048);
-          tc::mma_bf16(tmem_base, ad, bd, idesc, accumulate);
-          if (with_bias) {
-            const uint64_t od = tc::make_smem_desc(ones0 + j * 256, 128, 2048);
-            tc::mma_bf16(tmem_base + 256, ad, od, idesc_ones, accumulate);
+          for (int j = 0; j < 8; ++j) {
+            // MN-major: 16 batch rows per MMA = two 8-row groups 128 B apart; feature groups 2 KB apart
+            const uint64_t ad = tc::make_smem_desc(a0 + j * 256, 128, 2048);
+            const uint64_t bd = tc::make_smem_desc(b0 + j * 256, 128, 2048);
+            tc::mma_bf16(tmem_base, ad, bd, idesc, j == 0 ? accumulate : 1u);
+            if (with_bias) {
+              const uint64_t od = tc::make_smem_desc(ones0 + j * 256, 128, 2048);
+              tc::mma_bf16(tmem_base + 256, ad, od, idesc_ones, j == 0 ? accumulate : 1u);
+            }
           }
-          accumulate = 1;
+          tc::mma_commit(empty + stage);
         }
-        tc::mma_commit(empty + stage);
+        __syncwarp();
+        accumulate = 1;
         if (++stage == kWgStages) { stage = 0; phase ^= 1; }
       }
-      tc::mma_commit(done);
+      if (tc::elect_one()) tc::mma_commit(done);
+      __syncwarp();
     }
   } else {
     const int quad = warp & 3;
@@ -196,20 +203,23 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kWgThreads, 1) mlp_w
 
   if (rt0 < rt1) {
     if (warp == 0) {
-      if (lane == 0) {
+      {     // whole warp, one elected lane issues the copies (tc::elect_one)
         int stage = 0; uint32_t phase = 0;
         for (int rt = rt0; rt < rt1; ++rt) {
           tc::mbar_wait(empty + stage, phase ^ 1);
-          tc::mbar_arrive_expect_tx(full + stage, 2 * kW2Op);
-          tc::bulk_g2s(sA + (size_t)stage * kW2Op, P.dY + ((size_t)rt * (P.Fy / 8) + (size_t)n_tile * 16) * 2048, kW2Op,
-                       full + stage);
-          tc::bulk_g2s(sB + (size_t)stage * kW2Op,
-                       P.X + ((size_t)rt * (P.Fx / 8) + (size_t)k_tile * 32 + (size_t)cr * 16) * 2048, kW2Op, full + stage);
+          if (tc::elect_one()) {
+            tc::mbar_arrive_expect_tx(full + stage, 2 * kW2Op);
+            tc::bulk_g2s(sA + (size_t)stage * kW2Op, P.dY + ((size_t)rt * (P.Fy / 8) + (size_t)n_tile * 16) * 2048, kW2Op,
+                         full + stage);
+            tc::bulk_g2s(sB + (size_t)stage * kW2Op,
+                         P.X + ((size_t)rt * (P.Fx / 8) + (size_t)k_tile * 32 + (size_t)cr * 16) * 2048, kW2Op, full + stage);
+          }
+          __syncwarp();
           if (++stage == kW2Stages) { stage = 0; phase ^= 1; }
         }
       }
     } else if (warp == 1) {
-      if (lane == 0 && cr == 0) {
+      if (cr == 0) {        // whole warp, one elected lane issues
         constexpr uint32_t idesc = tc::make_idesc_bf16(256, 256, 1, 1);
         constexpr uint32_t idesc_ones = tc::make_idesc_bf16(256, 32, 1, 1);
         const uint32_t ones0 = tc::smem_u32(sOnes);
@@ -221,18 +231,23 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kWgThreads, 1) mlp_w
           tc::fence_after_sync();
           const uint32_t a0 = tc::smem_u32(sA + (size_t)stage * kW2Op);
           const uint32_t b0 = tc::smem_u32(sB + (size_t)stage * kW2Op);
+          if (tc::elect_one()) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const uint64_t ad = tc::make_smem_desc(a0 + j * 256, 128, 2048);
-            tc::mma_bf16_2cta(tmem_base, ad, tc::make_smem_desc(b0 + j * 256, 128, 2048), idesc, accumulate);
-            if (with_bias)
-              tc::mma_bf16_2cta(tmem_base + 256, ad, tc::make_smem_desc(ones0 + j * 256, 128, 2048), idesc_ones, accumulate);
-            accumulate = 1;
+            for (int j = 0; j < 8; ++j) {
+              const uint64_t ad = tc::make_smem_desc(a0 + j * 256, 128, 2048);
+              tc::mma_bf16_2cta(tmem_base, ad, tc::make_smem_desc(b0 + j * 256, 128, 2048), idesc, j == 0 ? accumulate : 1u);
+              if (with_bias)
+                tc::mma_bf16_2cta(tmem_base + 256, ad, tc::make_smem_desc(ones0 + j * 256, 128, 2048), idesc_ones,
+                                  j == 0 ? accumulate : 1u);
+            }
+            tc::mma_commit_2cta_mc(empty + stage, (uint16_t)3);
           }
-          tc::mma_commit_2cta_mc(empty + stage, (uint16_t)3);
+          __syncwarp();
+          accumulate = 1;
           if (++stage == kW2Stages) { stage = 0; phase ^= 1; }
         }
-        tc::mma_commit_2cta_mc(done, (uint16_t)3);
+        if (tc::elect_one()) tc::mma_commit_2cta_mc(done, (uint16_t)3);
+        __syncwarp();
       } else if (lane == 0) {
         int stage = 0; uint32_t phase = 0;
         for (int rt = rt0; rt < rt1; ++rt) {
