@@ -596,7 +596,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
       int slot = 0; uint32_t phase = 0;
       int opc = 0, aops = 0, titer = 0;
       POp d;
-      const uint32_t abuf0 = tc::smem_u32(abuf);
+      const uint32_t abuf0 = tc::smem_u32(abuf), ring0 = tc::smem_u32(ring);
       long long w_ring = 0, w_own = 0, w_peer = 0, w_pfull = 0, w_ring_lat = 0, w_pfull_lat = 0, t_start = PROF_CLOCK();
       for (int q = cluster; q < n_pairs; q += n_clusters, ++titer) {
         const uint32_t x_col = (titer & 1) ? 256u : 0u;           // X / T swap regions every tile
@@ -607,6 +607,12 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
           uint32_t accumulate = d.fresh ? 0u : 1u;
           auto step_ring_ab = [&]() {        // A and B both come from consecutive ring slots
             const int sa = slot;
+            // (descriptors first: they depend on the slot numbers only and must not sit between "operands landed" and
+            // the first MMA -- the issuing warp's latency per K-step is on the kernel's critical path)
+            const int sb_ = sa + 1 == kQRing ? 0 : sa + 1;
+            uint64_t ad0 = tc::make_smem_desc(ring0 + (uint32_t)sa * kQSlot, 2048, 128);
+            uint64_t bd0 = tc::make_smem_desc(ring0 + (uint32_t)sb_ * kQSlot, 2048, 128);
+            asm volatile("" : "+l"(ad0), "+l"(bd0));
             TIMED(w_ring_lat, tc::mbar_wait(full + sa, phase));
             if (!P.tma2) TIMED(w_pfull_lat, tc::mbar_wait(peer_full + sa, phase));
             if (++slot == kQRing) { slot = 0; phase ^= 1; }
@@ -615,12 +621,11 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
             if (!P.tma2) TIMED(w_pfull_lat, tc::mbar_wait(peer_full + sb, phase));
             if (++slot == kQRing) { slot = 0; phase ^= 1; }
             tc::fence_after_sync();
-            const uint32_t a0 = tc::smem_u32(ring + (size_t)sa * kQSlot), b0 = tc::smem_u32(ring + (size_t)sb * kQSlot);
             if (tc::elect_one()) {
 #pragma unroll
-              for (int j = 0; j < 4; ++j)
-                tc::mma_bf16_2cta(d_tmem, tc::make_smem_desc(a0 + j * 4096, 2048, 128),
-                                  tc::make_smem_desc(b0 + j * 4096, 2048, 128), idesc, j == 0 ? accumulate : 1u);
+              for (int j = 0; j < 4; ++j)        // + 4 KB per K = 16: 256 in the descriptor's 16-byte address field
+                tc::mma_bf16_2cta(d_tmem, ad0 + (uint64_t)(j * 256), bd0 + (uint64_t)(j * 256), idesc,
+                                  j == 0 ? accumulate : 1u);
               tc::mma_commit_2cta_mc(empty + sa, pair_mask);
               tc::mma_commit_2cta_mc(empty + sb, pair_mask);
             }
@@ -634,6 +639,9 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
             const uint32_t par = (uint32_t)(aops & 1);
             for (int i = 0; i < 8; ++i) {
               const int kb = pair_kb_order(h, i);
+              uint64_t ad0 = tc::make_smem_desc(abuf0 + (uint32_t)kb * 16384u, 2048, 128);
+              uint64_t bd0 = tc::make_smem_desc(ring0 + (uint32_t)slot * kQSlot, 2048, 128);
+              asm volatile("" : "+l"(ad0), "+l"(bd0));                      // (before the waits, see step_ring_ab)
               if (i < 4) TIMED(w_own, tc::mbar_wait(a_own2 + i, par));
               if (i == 4) TIMED(w_peer, tc::mbar_wait(a_peer + 0, par));
               if (i == 6) TIMED(w_peer, tc::mbar_wait(a_peer + 1, par));
@@ -642,12 +650,11 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
               TIMED(w_ring, tc::mbar_wait(full + slot, phase));
               if (!P.tma2) TIMED(w_pfull, tc::mbar_wait(peer_full + slot, phase));
               tc::fence_after_sync();
-              const uint32_t a0 = abuf0 + (uint32_t)kb * 16384u, b0 = tc::smem_u32(ring + (size_t)slot * kQSlot);
               if (tc::elect_one()) {
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
-                  tc::mma_bf16_2cta(d_tmem, tc::make_smem_desc(a0 + j * 4096, 2048, 128),
-                                    tc::make_smem_desc(b0 + j * 4096, 2048, 128), idesc, j == 0 ? accumulate : 1u);
+                  tc::mma_bf16_2cta(d_tmem, ad0 + (uint64_t)(j * 256), bd0 + (uint64_t)(j * 256), idesc,
+                                    j == 0 ? accumulate : 1u);
                 tc::mma_commit_2cta_mc(empty + slot, pair_mask);
               }
               __syncwarp();
