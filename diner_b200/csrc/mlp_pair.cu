@@ -274,7 +274,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
       int aops = 0;                          // ops that read the resident A operand
       int titer = 0;
       POp d;
-      const uint32_t abuf0 = tc::smem_u32(abuf);
+      const uint32_t abuf0 = tc::smem_u32(abuf), ring0 = tc::smem_u32(ring);
       long long w_ring = 0, w_own = 0, w_peer = 0, t_start = PROF_CLOCK();
 
       for (int tile = cluster; tile < P.mv_tiles; tile += n_clusters, ++titer) {
@@ -284,6 +284,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
           const uint32_t d_tmem = tmem_base + (d.acc_x ? x_col : (256u - x_col));
           uint32_t accumulate = d.fresh ? 0u : 1u;
           auto step_ring_ab = [&]() {        // A and B both come from consecutive ring slots
+            uint64_t ad0 = tc::make_smem_desc(ring0 + (uint32_t)slot * kPSlot, 2048, 128);
+            uint64_t bd0 = tc::make_smem_desc(ring0 + (uint32_t)(slot + 1 == kPRing ? 0 : slot + 1) * kPSlot, 4096, 128);
+            asm volatile("" : "+l"(ad0), "+l"(bd0));     // (before the waits: off the path "operands landed" -> first MMA)
             TIMED(w_ring, tc::mbar_wait(full + slot, phase));
             const int sa = slot;
             if (++slot == kPRing) { slot = 0; phase ^= 1; }
@@ -291,12 +294,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
             const int sb = slot;
             if (++slot == kPRing) { slot = 0; phase ^= 1; }
             tc::fence_after_sync();
-            const uint32_t a0 = tc::smem_u32(ring + (size_t)sa * kPSlot), b0 = tc::smem_u32(ring + (size_t)sb * kPSlot);
             if (tc::elect_one()) {
 #pragma unroll
-              for (int j = 0; j < 4; ++j)
-                tc::mma_bf16(d_tmem, tc::make_smem_desc(a0 + j * 4096, 2048, 128), tc::make_smem_desc(b0 + j * 8192, 4096, 128),
-                             idesc, j == 0 ? accumulate : 1u);
+              for (int j = 0; j < 4; ++j)        // K = 16 further: 4 KB in A (+256), 8 KB in B (+512, 256 weight rows)
+                tc::mma_bf16(d_tmem, ad0 + (uint64_t)(j * 256), bd0 + (uint64_t)(j * 512), idesc, j == 0 ? accumulate : 1u);
               tc::mma_commit(empty + sa);
               tc::mma_commit(empty + sb);
             }
@@ -310,17 +311,18 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
             const uint32_t par = (uint32_t)((aops) & 1);
             for (int i = 0; i < 8; ++i) {
               const int kb = pair_kb_order((int)rank, i);
+              uint64_t ad0 = tc::make_smem_desc(abuf0 + (uint32_t)kb * 16384u, 2048, 128);
+              uint64_t bd0 = tc::make_smem_desc(ring0 + (uint32_t)slot * kPSlot, 4096, 128);
+              asm volatile("" : "+l"(ad0), "+l"(bd0));
               if (i < 4) TIMED(w_own, tc::mbar_wait(a_own + i, par));
               if (i == 4) TIMED(w_peer, tc::mbar_wait(a_peer + 0, par));
               if (i == 6) TIMED(w_peer, tc::mbar_wait(a_peer + 1, par));
               TIMED(w_ring, tc::mbar_wait(full + slot, phase));
               tc::fence_after_sync();
-              const uint32_t a0 = abuf0 + (uint32_t)kb * 16384u, b0 = tc::smem_u32(ring + (size_t)slot * kPSlot);
               if (tc::elect_one()) {
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
-                  tc::mma_bf16(d_tmem, tc::make_smem_desc(a0 + j * 4096, 2048, 128),
-                               tc::make_smem_desc(b0 + j * 8192, 4096, 128), idesc, j == 0 ? accumulate : 1u);
+                  tc::mma_bf16(d_tmem, ad0 + (uint64_t)(j * 256), bd0 + (uint64_t)(j * 512), idesc, j == 0 ? accumulate : 1u);
                 tc::mma_commit(empty + slot);
               }
               __syncwarp();
@@ -642,12 +644,22 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
               uint64_t ad0 = tc::make_smem_desc(abuf0 + (uint32_t)kb * 16384u, 2048, 128);
               uint64_t bd0 = tc::make_smem_desc(ring0 + (uint32_t)slot * kQSlot, 2048, 128);
               asm volatile("" : "+l"(ad0), "+l"(bd0));                      // (before the waits, see step_ring_ab)
+#if DNR_CLUSTER_PROF
               if (i < 4) TIMED(w_own, tc::mbar_wait(a_own2 + i, par));
               if (i == 4) TIMED(w_peer, tc::mbar_wait(a_peer + 0, par));
               if (i == 6) TIMED(w_peer, tc::mbar_wait(a_peer + 1, par));
               if (P.tma2 && i == 4) TIMED(w_peer, tc::mbar_wait(odd_peer + 0, par));     // ... and in the odd CTA
               if (P.tma2 && i == 6) TIMED(w_peer, tc::mbar_wait(odd_peer + 1, par));
               TIMED(w_ring, tc::mbar_wait(full + slot, phase));
+#else
+              // production build: the operand-block barrier and the ring slot are polled together
+              if (i < 4) tc::mbar_wait2(a_own2 + i, par, full + slot, phase);
+              else if (i == 4 || i == 6) {
+                const int e = (i - 4) >> 1;
+                tc::mbar_wait2(a_peer + e, par, full + slot, phase);
+                if (P.tma2) tc::mbar_wait(odd_peer + e, par);                             // ... and in the odd CTA
+              } else tc::mbar_wait(full + slot, phase);
+#endif
               if (!P.tma2) TIMED(w_pfull, tc::mbar_wait(peer_full + slot, phase));
               tc::fence_after_sync();
               if (tc::elect_one()) {
@@ -717,7 +729,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
   }
   else if (warp == 2) {
     // ================= pusher: my finished K-blocks -> the partner's resident A buffer (bulk copy over DSMEM) =========
-    if (lane == 0) {
+    {     // whole warp, one elected lane issues the copies (tc::elect_one)
       int xops = 0;
       unsigned char* mine = abuf + (size_t)h * 65536;
       for (int q = cluster, it = 0; q < n_pairs; q += n_clusters, ++it) {
@@ -728,7 +740,8 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
           for (int st = 0; st < 2; ++st) {
             tc::mbar_wait(a_own + 2 * st + 1, (uint32_t)(xops & 1));
             if (st == 0) tc::mbar_wait(peer_free, (uint32_t)(xops & 1));
-            tc::bulk_s2s_peer(mine + (size_t)st * 32768, 32768, a_peer + st, partner);
+            if (tc::elect_one()) tc::bulk_s2s_peer(mine + (size_t)st * 32768, 32768, a_peer + st, partner);
+            __syncwarp();
           }
         }
       }

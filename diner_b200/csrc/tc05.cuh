@@ -37,6 +37,22 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
 
+// both barriers, polled together: the two try_waits are in flight at the same time (an issuing warp that waits for "my
+// operand block is written" and "the weights have landed" in sequence pays two shared-memory round trips per K-step)
+__device__ __forceinline__ void mbar_wait2(uint64_t* bar_a, uint32_t parity_a, uint64_t* bar_b, uint32_t parity_b) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred pa, pb;\n\t"
+      "WAIT2_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 pa, [%0], %1;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 pb, [%2], %3;\n\t"
+      "and.pred pa, pa, pb;\n\t"
+      "@pa bra WAIT2_DONE;\n\t"
+      "bra WAIT2_LOOP;\n\t"
+      "WAIT2_DONE:\n\t"
+      "}" ::"r"(smem_u32(bar_a)), "r"(parity_a), "r"(smem_u32(bar_b)), "r"(parity_b) : "memory");
+}
+
 // ---- bulk async copy global -> shared (non-tensor TMA), completes on an mbarrier -------------------
 __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
