@@ -55,6 +55,23 @@ def test_argument_validation_needs_no_gpu():
     assert rc == 1 and b"multiple of 256" in lib.dnr_last_error()
     with pytest.raises(RuntimeError, match="dnr_mlp_wgrad failed"):
         _lib.call("dnr_mlp_wgrad", None, 100, None, 64, 1, None, 64, 1, 1, None, None)
+    # the single-call render: workspace planning is host arithmetic, argument checks come before any device call
+    ws = lib.dnr_render_workspace_bytes(2, 65536, 40, 0)
+    rows = 32768 * 40 * 2                                   # two balanced chunks of 32 768 rays (2^22-row limit)
+    assert ws >= rows * (1024 + 128) + 65536 * 40 * 16 and ws % 256 == 0
+    assert lib.dnr_render_workspace_bytes(2, 65536, 40, 1 << 20) < ws          # smaller chunks, smaller operand buffers
+    assert lib.dnr_render_workspace_bytes(5, 65536, 40, 0) == -1 and lib.dnr_render_workspace_bytes(2, -1, 40, 0) == -1
+    rc = lib.dnr_render_fwd(None, None, None, 10, 40, 1000, 15, 0, None, 1, 0, None, 0, None, None, None, None, None, None)
+    assert rc == 1 and b"null argument" in lib.dnr_last_error()
+    sd, md = _lib.SceneDesc(SB=1, NV=7), _lib.MlpDesc()
+    dummy = ctypes.c_float(0)
+    rc = lib.dnr_render_fwd(ctypes.byref(sd), ctypes.byref(md), ctypes.byref(dummy), 10, 40, 1000, 15, 0, None, 1, 0, None, 0,
+                            ctypes.byref(dummy), ctypes.byref(dummy), None, None, None, None)
+    assert rc == 1 and b"NV must be in [1,4]" in lib.dnr_last_error()
+    sd.NV = 2
+    rc = lib.dnr_render_fwd(ctypes.byref(sd), ctypes.byref(md), ctypes.byref(dummy), 10, 40, 1000, 15, 0, None, 1, 0, None, 0,
+                            ctypes.byref(dummy), ctypes.byref(dummy), None, None, None, None)
+    assert rc == 1 and b"workspace too small" in lib.dnr_last_error()
 
 
 def test_renderer_signature_and_errors():
