@@ -489,12 +489,13 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
   uint64_t* empty = bars + 6;             // [6]  ring slot consumed in BOTH CTAs of the MMA pair (multicast commit)
   uint64_t* peer_full = bars + 12;        // [6]  (even CTA) the odd CTA's operands of this ring step are in place
   uint64_t* accf = bars + 18;             // [2]  accumulator of op (parity) complete (multicast commit)
-  uint64_t* a_peer = bars + 20;           // [2]  exchange partner's K-blocks {0,1} / {2,3} landed
+  uint64_t* a_peer = bars + 36;           // [4]  exchange partner's K-block p landed (one 16 KB push each: the first remote
+                                          //      K-block is needed four K-steps after the first own one)
   uint64_t* a_own = bars + 22;            // [4]  own K-block p written (one arrival per epilogue warp; pusher waits here)
   uint64_t* a_own2 = bars + 32;           // [4]  (even CTA) K-block p written in BOTH CTAs of the MMA pair (16 arrivals)
   uint64_t* pushed = bars + 26;           // [1]  partner received my whole half
   uint64_t* peer_free = bars + 27;        // [1]  partner's A buffer may receive my next operand
-  uint64_t* odd_peer = bars + 28;         // [2]  (even CTA, tma2) the partner's K-blocks {0,1} / {2,3} landed in the ODD CTA
+  uint64_t* odd_peer = bars + 28;         // [4]  (even CTA, tma2) the partner's K-block p landed in the ODD CTA
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 40);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -511,9 +512,8 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
     for (int s = 0; s < kQRing; ++s) { tc::mbar_init(full + s, 1); tc::mbar_init(empty + s, 1); tc::mbar_init(peer_full + s, 1); }
     tc::mbar_init(accf + 0, 1); tc::mbar_init(accf + 1, 1);
     for (int i = 0; i < 4; ++i) { tc::mbar_init(a_own + i, 8); tc::mbar_init(a_own2 + i, 16); }
-    tc::mbar_init(a_peer + 0, 1); tc::mbar_init(a_peer + 1, 1);
+    for (int i = 0; i < 4; ++i) { tc::mbar_init(a_peer + i, 1); tc::mbar_init(odd_peer + i, 1); }
     tc::mbar_init(pushed, 1); tc::mbar_init(peer_free, 1);
-    tc::mbar_init(odd_peer + 0, 1); tc::mbar_init(odd_peer + 1, 1);
     tc::fence_barrier_init();
   }
   __syncthreads();
@@ -646,19 +646,16 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
               asm volatile("" : "+l"(ad0), "+l"(bd0));                      // (before the waits, see step_ring_ab)
 #if DNR_CLUSTER_PROF
               if (i < 4) TIMED(w_own, tc::mbar_wait(a_own2 + i, par));
-              if (i == 4) TIMED(w_peer, tc::mbar_wait(a_peer + 0, par));
-              if (i == 6) TIMED(w_peer, tc::mbar_wait(a_peer + 1, par));
-              if (P.tma2 && i == 4) TIMED(w_peer, tc::mbar_wait(odd_peer + 0, par));     // ... and in the odd CTA
-              if (P.tma2 && i == 6) TIMED(w_peer, tc::mbar_wait(odd_peer + 1, par));
+              if (i >= 4) TIMED(w_peer, tc::mbar_wait(a_peer + (i - 4), par));
+              if (P.tma2 && i >= 4) TIMED(w_peer, tc::mbar_wait(odd_peer + (i - 4), par));     // ... and in the odd CTA
               TIMED(w_ring, tc::mbar_wait(full + slot, phase));
 #else
               // production build: the operand-block barrier and the ring slot are polled together
               if (i < 4) tc::mbar_wait2(a_own2 + i, par, full + slot, phase);
-              else if (i == 4 || i == 6) {
-                const int e = (i - 4) >> 1;
-                tc::mbar_wait2(a_peer + e, par, full + slot, phase);
-                if (P.tma2) tc::mbar_wait(odd_peer + e, par);                             // ... and in the odd CTA
-              } else tc::mbar_wait(full + slot, phase);
+              else {
+                tc::mbar_wait2(a_peer + (i - 4), par, full + slot, phase);
+                if (P.tma2) tc::mbar_wait(odd_peer + (i - 4), par);                       // ... and in the odd CTA
+              }
 #endif
               if (!P.tma2) TIMED(w_pfull, tc::mbar_wait(peer_full + slot, phase));
               tc::fence_after_sync();
@@ -703,10 +700,10 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
             // learn from me is that the partner's half of the A operand has landed in MY buffer
             if (d.abuf_w) {
               const uint32_t par = (uint32_t)(aops & 1);
-              tc::mbar_wait(a_peer + 0, par);
-              tc::mbar_arrive_remote_relaxed(odd_peer + 0, mma_peer);
-              tc::mbar_wait(a_peer + 1, par);
-              tc::mbar_arrive_remote_relaxed(odd_peer + 1, mma_peer);
+              for (int e = 0; e < 4; ++e) {
+                tc::mbar_wait(a_peer + e, par);
+                tc::mbar_arrive_remote_relaxed(odd_peer + e, mma_peer);
+              }
               ++aops;
             }
             continue;
@@ -717,8 +714,7 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
           if (d.abuf_w) {
             const uint32_t par = (uint32_t)(aops & 1);
             for (int i = 0; i < 8; ++i) {
-              if (i == 4) tc::mbar_wait(a_peer + 0, par);     // (own K-blocks: the epilogue warps signal the even CTA directly)
-              if (i == 6) tc::mbar_wait(a_peer + 1, par);
+              if (i >= 4) tc::mbar_wait(a_peer + (i - 4), par);   // (own K-blocks: the epilogue warps signal the even CTA directly)
               forward();
             }
             ++aops;
@@ -737,10 +733,10 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
         // by the merge after op 6 and the epilogues of ops 7..9
         const int n_events = quad_last<NV, MERGE>(it, q, n_clusters, n_pairs) ? kPOps - 1 : 6;
         for (int o = 0; o < n_events; ++o, ++xops) {
-          for (int st = 0; st < 2; ++st) {
-            tc::mbar_wait(a_own + 2 * st + 1, (uint32_t)(xops & 1));
-            if (st == 0) tc::mbar_wait(peer_free, (uint32_t)(xops & 1));
-            if (tc::elect_one()) tc::bulk_s2s_peer(mine + (size_t)st * 32768, 32768, a_peer + st, partner);
+          for (int kb = 0; kb < 4; ++kb) {                    // one push per K-block, as soon as it is written
+            tc::mbar_wait(a_own + kb, (uint32_t)(xops & 1));
+            if (kb == 0) tc::mbar_wait(peer_free, (uint32_t)(xops & 1));
+            if (tc::elect_one()) tc::bulk_s2s_peer(mine + (size_t)kb * 16384, 16384, a_peer + kb, partner);
             __syncwarp();
           }
         }
@@ -756,11 +752,9 @@ __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(kPThreads, 1) mlp_qu
         for (int o = 0; o < n_ops; ++o, ++opc) {
           if (!(o < 6 || (last && o < kPOps - 1))) continue;                  // this op's output is no A operand
           tc::mbar_wait(accf + (opc & 1), (uint32_t)((opc >> 1) & 1));     // the MMAs of this op no longer read my buffer
-          tc::mbar_arrive_expect_tx(a_peer + 0, 32768);
-          tc::mbar_arrive_expect_tx(a_peer + 1, 32768);
+          for (int e = 0; e < 4; ++e) tc::mbar_arrive_expect_tx(a_peer + e, 16384);
           tc::mbar_arrive_remote_relaxed(peer_free, partner);
-          tc::mbar_wait(a_peer + 1, (uint32_t)(xops & 1));
-          tc::mbar_wait(a_peer + 0, (uint32_t)(xops & 1));
+          for (int e = 3; e >= 0; --e) tc::mbar_wait(a_peer + e, (uint32_t)(xops & 1));
           tc::mbar_arrive_remote_relaxed(pushed, partner);
           ++xops;
         }
