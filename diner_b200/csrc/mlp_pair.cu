@@ -5,7 +5,7 @@
 //   TMEM   (512 cols)  X = fp32 residual stream of its 256 columns (fc_1 / lin_z accumulate straight into it, so the
 //                      residual add costs nothing and never leaves the SM) + T = fc_0 accumulator
 //   smem   128 KB      the full-K bf16 A operand (relu(x) or relu(net)) in the tcgen05 canonical layout: its own
-//                      256 columns are written by its epilogue warps and pushed, 32 KB at a time, into the peer's
+//                      256 columns are written by its epilogue warps and pushed, one 16 KB K-block at a time, into the peer's
 //                      buffer by cp.async.bulk shared::cta -> shared::cluster (DSMEM), which completes the peer's
 //                      landing barrier; the peer does the same, so nothing of the exchange touches L2
 //          3 x 32 KB   ring for the streamed operands: weight K-blocks of its 256 output rows, and the
@@ -197,7 +197,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
   uint64_t* empty = bars + 3;             // [3]  ring slot consumed
   uint64_t* accf = bars + 6;              // [2]  accumulator of op (parity) complete
   uint64_t* a_own = bars + 12;            // [4]  own K-block p of the A operand written (one arrival per epilogue warp)
-  uint64_t* a_peer = bars + 10;           // [2]  peer K-blocks {0,1} / {2,3} landed (bulk copies over DSMEM)
+  uint64_t* a_peer = bars + 8;            // [4]  peer K-block p landed (one 16 KB bulk copy over DSMEM each)
   uint64_t* pushed = bars + 16;           // [1]  the peer has received my whole half (remote ack): my half may be rewritten
   uint64_t* peer_free = bars + 17;        // [1]  the peer's A buffer may receive my next operand (remote credit)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
@@ -211,7 +211,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
     for (int s = 0; s < kPRing; ++s) { tc::mbar_init(full + s, 1); tc::mbar_init(empty + s, 1); }
     tc::mbar_init(accf + 0, 1); tc::mbar_init(accf + 1, 1);
     for (int i = 0; i < 4; ++i) tc::mbar_init(a_own + i, 8);
-    tc::mbar_init(a_peer + 0, 1); tc::mbar_init(a_peer + 1, 1);
+    for (int i = 0; i < 4; ++i) tc::mbar_init(a_peer + i, 1);
     tc::mbar_init(pushed, 1); tc::mbar_init(peer_free, 1);
     tc::fence_barrier_init();
   }
@@ -315,8 +315,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
               uint64_t bd0 = tc::make_smem_desc(ring0 + (uint32_t)slot * kPSlot, 4096, 128);
               asm volatile("" : "+l"(ad0), "+l"(bd0));
               if (i < 4) TIMED(w_own, tc::mbar_wait(a_own + i, par));
-              if (i == 4) TIMED(w_peer, tc::mbar_wait(a_peer + 0, par));
-              if (i == 6) TIMED(w_peer, tc::mbar_wait(a_peer + 1, par));
+              if (i >= 4) TIMED(w_peer, tc::mbar_wait(a_peer + (i - 4), par));
               TIMED(w_ring, tc::mbar_wait(full + slot, phase));
               tc::fence_after_sync();
               if (tc::elect_one()) {
@@ -347,11 +346,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
       for (int tile = cluster; tile < P.mv_tiles; tile += n_clusters) {
         for (int o = 0; o < kPOps - 1; ++o, ++xops) {          // every op but the head produces an A operand
           unsigned char* mine = abuf + (size_t)rank * 65536;
-          for (int st = 0; st < 2; ++st) {
-            // all epilogue warps wrote (and proxy-fenced) K-blocks 2st, 2st+1 (a warp reaches 2st+1 after 2st)
-            tc::mbar_wait(a_own + 2 * st + 1, (uint32_t)(xops & 1));
-            if (st == 0) tc::mbar_wait(peer_free, (uint32_t)(xops & 1));   // peer's MMAs left its buffer, tx armed
-            tc::bulk_s2s_peer(mine + (size_t)st * 32768, 32768, a_peer + st, peer);
+          for (int kb = 0; kb < 4; ++kb) {
+            // all epilogue warps wrote (and proxy-fenced) K-block kb: push it now (the peer's MMAs need its first remote
+            // K-block four K-steps after their first own one)
+            tc::mbar_wait(a_own + kb, (uint32_t)(xops & 1));
+            if (kb == 0) tc::mbar_wait(peer_free, (uint32_t)(xops & 1));   // peer's MMAs left its buffer, tx armed
+            tc::bulk_s2s_peer(mine + (size_t)kb * 16384, 16384, a_peer + kb, peer);
           }
         }
       }
@@ -364,11 +364,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1) mlp_pa
         for (int o = 0; o < kPOps; ++o, ++opc) {
           if (o == kPOps - 1) continue;
           tc::mbar_wait(accf + (opc & 1), (uint32_t)((opc >> 1) & 1));     // my MMAs of this op no longer read the buffer
-          tc::mbar_arrive_expect_tx(a_peer + 0, 32768);
-          tc::mbar_arrive_expect_tx(a_peer + 1, 32768);
+          for (int e = 0; e < 4; ++e) tc::mbar_arrive_expect_tx(a_peer + e, 16384);
           tc::mbar_arrive_remote_relaxed(peer_free, peer);
-          tc::mbar_wait(a_peer + 1, (uint32_t)(xops & 1));         // everything of this operand has landed
-          tc::mbar_wait(a_peer + 0, (uint32_t)(xops & 1));
+          for (int e = 3; e >= 0; --e) tc::mbar_wait(a_peer + e, (uint32_t)(xops & 1));     // everything of this operand has landed
           tc::mbar_arrive_remote_relaxed(pushed, peer);
           ++xops;
         }
