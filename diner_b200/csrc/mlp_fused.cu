@@ -205,7 +205,7 @@ __global__ void __launch_bounds__(kFThreads, 1) mlp_fused_fwd_kernel(const Fused
 
   if (warp == 0) {
     // ================= producer =================
-    if (lane == 0) {
+    {     // the whole warp runs the loop (warp-uniform operands -> uniform registers); one elected lane issues (tc::elect_one)
       int stage = 0; uint32_t phase = 0;
       int c = 0;                                   // ops executed so far by this CTA
       const uint64_t pol_keep = tc::policy_evict_last(), pol_stream = tc::policy_evict_first();
@@ -226,10 +226,13 @@ __global__ void __launch_bounds__(kFThreads, 1) mlp_fused_fwd_kernel(const Fused
                   if ((d.K[0] >= kHidden && kb == 4) || (d.K[0] < kHidden && kb == 0)) tc::mbar_wait(done + 1, dep_parity);
                 }
                 tc::mbar_wait(empty + stage, phase ^ 1);
-                tc::mbar_arrive_expect_tx(full + stage, kFAStage + kFBStage);
-                tc::bulk_g2s_hint(sA + (size_t)stage * kFAStage, a + (size_t)kb * kFAStage, kFAStage, full + stage,
-                                  d.a_stream[sg] ? pol_stream : pol_keep);
-                tc::bulk_g2s_hint(sB + (size_t)stage * kFBStage, b + (size_t)kb * kFBStage, kFBStage, full + stage, pol_keep);
+                if (tc::elect_one()) {
+                  tc::mbar_arrive_expect_tx(full + stage, kFAStage + kFBStage);
+                  tc::bulk_g2s_hint(sA + (size_t)stage * kFAStage, a + (size_t)kb * kFAStage, kFAStage, full + stage,
+                                    d.a_stream[sg] ? pol_stream : pol_keep);
+                  tc::bulk_g2s_hint(sB + (size_t)stage * kFBStage, b + (size_t)kb * kFBStage, kFBStage, full + stage, pol_keep);
+                }
+                __syncwarp();
                 if (++stage == kFStages) { stage = 0; phase ^= 1; }
               }
             }
@@ -240,7 +243,7 @@ __global__ void __launch_bounds__(kFThreads, 1) mlp_fused_fwd_kernel(const Fused
     }
   } else if (warp == 1) {
     // ================= MMA issuer =================
-    if (lane == 0) {
+    {     // whole warp, one elected lane issues
       constexpr uint32_t idesc = tc::make_idesc_bf16(kFBM, kFBN, 0, 0);
       int stage = 0; uint32_t phase = 0;
       int it = 0;
@@ -260,18 +263,22 @@ __global__ void __launch_bounds__(kFThreads, 1) mlp_fused_fwd_kernel(const Fused
                 tc::fence_after_sync();
                 const uint32_t a0 = tc::smem_u32(sA + (size_t)stage * kFAStage);
                 const uint32_t b0 = tc::smem_u32(sB + (size_t)stage * kFBStage);
+                if (tc::elect_one()) {
 #pragma unroll
-                for (int j = 0; j < kFBK / 16; ++j) {
-                  const uint64_t ad = tc::make_smem_desc(a0 + j * 2 * 2048, 2048, 128);
-                  const uint64_t bd = tc::make_smem_desc(b0 + j * 2 * 4096, 4096, 128);
-                  tc::mma_bf16(d_tmem, ad, bd, idesc, accumulate);
-                  accumulate = 1;
+                  for (int j = 0; j < kFBK / 16; ++j) {
+                    const uint64_t ad = tc::make_smem_desc(a0 + j * 2 * 2048, 2048, 128);
+                    const uint64_t bd = tc::make_smem_desc(b0 + j * 2 * 4096, 4096, 128);
+                    tc::mma_bf16(d_tmem, ad, bd, idesc, j == 0 ? accumulate : 1u);
+                  }
+                  tc::mma_commit(empty + stage);
                 }
-                tc::mma_commit(empty + stage);
+                __syncwarp();
+                accumulate = 1;
                 if (++stage == kFStages) { stage = 0; phase ^= 1; }
               }
             }
-            tc::mma_commit(tfull + buf);
+            if (tc::elect_one()) tc::mma_commit(tfull + buf);
+            __syncwarp();
           }
         }
       }
